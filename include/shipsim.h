@@ -1,0 +1,208 @@
+/* libshipsim -- C ABI of the B200-native batched ship-in-transit simulator.
+ *
+ * This header is the drop-in boundary for the hot path of AndreasKing-Goks/sac-maritime-ast:
+ * the scalar Python ship simulator (simulators/ship_in_transit/) and the two-ship RL env step
+ * (RLEnv/MSRL_env_ex.py).  The reference has no FFI of its own (pure Python); every entry point
+ * below cites the reference interface it replaces.  Conventions:
+ *   - extern "C", plain pointers and sizes, no torch / C++ types in any signature;
+ *   - returns 0 on success or a negative SitError; never throws; sit_last_error() gives the
+ *     thread-local message of the last failure;
+ *   - a handle owns no simulation memory: the caller allocates ONE device buffer of
+ *     sit_state_bytes() bytes and passes it to every call (layout: sit_layout());
+ *   - device entry points only enqueue work on the caller's CUDA stream (a cudaStream_t passed
+ *     as void*; NULL = legacy default stream) and never synchronise;
+ *   - the *_host entry points take HOST buffers, copy in, run, copy out and synchronise;
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef SHIPSIM_H
+#define SHIPSIM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SIT_ABI_VERSION 1
+#define SIT_MAX_WP 16     /* route capacity per ship: 2 + sampling_frequency (main_ast.py:47) fits */
+#define SIT_MAX_MODES 4   /* machinery modes per ship (PTO / PTI / MEC, main_ast.py:136-158) */
+#define SIT_MAX_EDGES 128 /* polygon ring segments of the map (default map: 39, main_ast.py:200-205) */
+#define SIT_N_OBS 10      /* observation vector, MSRL_env_ex.py:424-435 */
+#define SIT_N_TRAJ 8      /* trajectory channels N, E, psi, u, v, r, omega, k */
+#define SIT_N_LOG 27      /* simulation_results channels, ship_model.py:645-684 */
+#define SIT_N_STATS 16    /* 12 status-bit counters + done, steps, decisions, reserved */
+
+typedef enum SitError {
+    SIT_OK = 0,
+    SIT_E_INVALID = -1,   /* bad argument / config */
+    SIT_E_CUDA = -2,      /* CUDA runtime error (message in sit_last_error) */
+    SIT_E_NODEVICE = -3,  /* no CUDA device: there is no CPU fallback */
+    SIT_E_KIND = -4       /* call not valid for this handle kind */
+} SitError;
+
+enum { SIT_F64 = 0, SIT_F32 = 1 };            /* arithmetic of the step kernels */
+enum { SIT_KIND_FLEET = 1, SIT_KIND_ENV = 2 };/* bare ships | two-ship AST envs */
+enum { SIT_SG_MOTOR = 0, SIT_SG_GEN = 1, SIT_SG_OFF = 2 }; /* ship_engine.py:32-44 */
+enum { SIT_ROLE_TEST = 0, SIT_ROLE_OBS = 1 };
+
+/* status bits; strings at MSRL_env_ex.py:760-899 (sit_status_string) */
+enum {
+    SIT_ST_TEST_ENDPOINT = 1 << 0, SIT_ST_TEST_HORIZON = 1 << 1, SIT_ST_TEST_TERRAIN = 1 << 2,
+    SIT_ST_TEST_MECH = 1 << 3, SIT_ST_TEST_NAV = 1 << 4, SIT_ST_TEST_BLACKOUT = 1 << 5,
+    SIT_ST_OBS_ENDPOINT = 1 << 6, SIT_ST_OBS_HORIZON = 1 << 7, SIT_ST_OBS_TERRAIN = 1 << 8,
+    SIT_ST_OBS_IW = 1 << 9, SIT_ST_OBS_NAV = 1 << 10, SIT_ST_COLLISION = 1 << 11
+};
+
+/* Uniform parameters of one ship role: the reference's config NamedTuples flattened.
+ * ShipConfiguration ship_model.py:20-35; MachinerySystemConfiguration + MachineryModeParams
+ * ship_engine.py:17-20,121-138; ThrottleControllerGains / HeadingControllerGains
+ * controllers.py:16-31; LosParameters LOS_guidance.py:15-19; SimulationConfiguration
+ * .integration_step ship_model.py:52.  Derived constants (mass, inertia, added mass, wind areas,
+ * available power per mode: ship_model.py:71-86,123-130,193-209; ship_engine.py:32-44) are
+ * computed inside sit_create. */
+typedef struct SitShipParams {
+    double dt;
+    double dead_weight_tonnage, coefficient_of_deadweight_to_displacement, bunkers, ballast;
+    double length_of_ship, width_of_ship;
+    double added_mass_coefficient_in_surge, added_mass_coefficient_in_sway, added_mass_coefficient_in_yaw;
+    double mass_over_linear_friction_coefficient_in_surge, mass_over_linear_friction_coefficient_in_sway,
+           mass_over_linear_friction_coefficient_in_yaw;
+    double nonlinear_friction_coefficient__in_surge, nonlinear_friction_coefficient__in_sway,
+           nonlinear_friction_coefficient__in_yaw;
+    int32_t n_modes, _pad0;
+    double mode_main_engine_capacity[SIT_MAX_MODES], mode_electrical_capacity[SIT_MAX_MODES];
+    int32_t mode_shaft_generator_state[SIT_MAX_MODES];
+    double hotel_load;
+    double linear_friction_main_engine, linear_friction_hybrid_shaft_generator;
+    double gear_ratio_between_main_engine_and_propeller, gear_ratio_between_hybrid_shaft_generator_and_propeller;
+    double propeller_inertia, propeller_speed_to_torque_coefficient, propeller_diameter,
+           propeller_speed_to_thrust_force_coefficient;
+    double rudder_angle_to_sway_force_coefficient, rudder_angle_to_yaw_force_coefficient, max_rudder_angle_degrees;
+    double sfc_me[3], sfc_dg[3];                       /* FuelConsumptionCoefficients a, b, c */
+    double kp_ship_speed, ki_ship_speed, kp_shaft_speed, ki_shaft_speed;
+    double kp_heading, kd_heading, ki_heading;
+    double radius_of_acceptance, lookahead_distance, los_integral_gain, los_integrator_windup_limit;
+} SitShipParams;
+
+/* PolygonObstacle (obstacle.py:92-148): ring segments in (x, y) = (east, north), one poly id per
+ * segment; segments of one polygon are contiguous. */
+typedef struct SitMap {
+    int32_t n_edges, n_poly;
+    double x1[SIT_MAX_EDGES], y1[SIT_MAX_EDGES], x2[SIT_MAX_EDGES], y2[SIT_MAX_EDGES];
+    int32_t poly[SIT_MAX_EDGES];
+} SitMap;
+
+typedef struct SitConfig {
+    int32_t abi_version;      /* SIT_ABI_VERSION */
+    int32_t kind;             /* SIT_KIND_FLEET or SIT_KIND_ENV */
+    int32_t precision;        /* SIT_F64 or SIT_F32 (positions are carried in f64 in both) */
+    int32_t max_wp;           /* route capacity actually allocated, 2..SIT_MAX_WP */
+    SitShipParams ship[2];    /* [SIT_ROLE_TEST], [SIT_ROLE_OBS]; a fleet uses ship[0] */
+    SitMap map;               /* envs only */
+    double sampling_frequency;/* args.sampling_frequency, MSRL_env_ex.py:125 */
+    double theta;             /* args.theta, MSRL_env_ex.py:130 */
+} SitConfig;
+
+typedef struct SitHandle_* SitHandle;
+
+/* one named SoA array inside the state buffer */
+enum { SIT_DT_F64 = 0, SIT_DT_F32 = 1, SIT_DT_I32 = 2 };
+typedef struct SitField {
+    char name[32];
+    int64_t offset;     /* bytes from the start of the state buffer */
+    int32_t dtype;      /* SIT_DT_* */
+    int32_t rows;       /* 1, or max_wp for route arrays: array is [rows][count] */
+    int64_t count;      /* elements per row: n_ships for ship fields, n_envs for env fields */
+} SitField;
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+/* Replaces constructing ShipModelAST / controllers / MultiShipRLEnv (ship_model.py:545-574,
+ * controllers.py:108-136,253-296, MSRL_env_ex.py:40-114) for n_envs independent copies. */
+int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out);
+int sit_destroy(SitHandle h);
+int sit_state_bytes(SitHandle h, size_t* nbytes);
+/* fields == NULL: only *n_fields is written */
+int sit_layout(SitHandle h, SitField* fields, int32_t capacity, int32_t* n_fields);
+int64_t sit_n_ships(SitHandle h);
+
+/* ---- bare ships (simulators/ship_in_transit) ------------------------------------------------- */
+typedef struct SitFleetIO {
+    /* inputs, device pointers, may be NULL */
+    const void* dist;        /* [dist_steps][4][n_ships] reals: current north, current east, wind speed,
+                                wind dir assigned before each step (ship_model.py:154-156); dist_steps is
+                                1 (held for the launch) or K */
+    int32_t dist_steps;
+    int32_t avoid;           /* 1: collision-avoidance branch MSRL_env_ex.py:240-249 on every ship */
+    int32_t store;           /* 1: store_simulation_data + next_time (normal step); 0: init_step (MSRL_env_ex.py:188-215) */
+    int32_t traj_steps;      /* traj holds K rows (0 or K: every step) or 1 row (the last step of the launch) */
+    /* outputs, device pointers, may be NULL */
+    void* traj;              /* [traj_steps][SIT_N_TRAJ][n_ships] reals, post-step */
+    void* log27;             /* [K][SIT_N_LOG][n_ships] reals, the 27 stored channels of each step */
+    void* cmd;               /* [K][2][n_ships] reals: rudder, throttle commanded in each step */
+} SitFleetIO;
+
+/* K ship-steps for every ship: guidance (LOS_guidance.py:88-121) -> heading PID
+ * (controllers.py:72-100,175-189,306-314) -> throttle cascade (controllers.py:138-143) -> store
+ * (ship_model.py:645-684, ship_engine.py:239-292) -> update_differentials / integrate
+ * (ship_model.py:576-643, ship_engine.py:355-395) -> next_time (utils.py:42-48). */
+int sit_fleet_step_k(SitHandle h, void* state, int32_t K, const SitFleetIO* io, void* stream);
+/* Host-buffer form of sit_fleet_step_k for callers that keep their arrays on the host (the reference's
+ * callers do): dist_h [4][n_ships] reals (may be NULL) is copied in and held for the K steps, the post-step
+ * (N, E, psi, u, v, r, omega, k) of the LAST step is copied out to pose_h [SIT_N_TRAJ][n_ships]; synchronises. */
+int sit_fleet_step_host(SitHandle h, void* state, int32_t K, const void* dist_h, int32_t avoid, void* pose_h,
+                        void* stream);
+/* snapshot pose / environment / route as the values reset() restores (the deepcopy at
+ * MSRL_env_ex.py:55-56 and the init_* attributes set in ship_model.py:132-157) */
+int sit_capture_init(SitHandle h, void* state, void* stream);
+/* ShipModelAST.reset + controller resets (ship_model.py:340-400,708-712; controllers.py:145-151,
+ * 333-350; LOS_guidance.py:123-136).  mask: NULL = all, else uint8[n_envs].  hard != 0 also
+ * restores what the reference leaves alone (omega, integrators, fuel): a fresh construction. */
+int sit_reset(SitHandle h, void* state, const uint8_t* mask, int32_t hard, void* stream);
+
+/* ---- two-ship AST env (RLEnv/MSRL_env_ex.py MultiShipRLEnv) ---------------------------------- */
+typedef struct SitEnvIO {
+    /* inputs (device) */
+    const void* action;      /* [act_steps][2][n_envs] reals: converted_action (north, east) */
+    const uint8_t* sac_update;/* [act_steps][n_envs]: insert the waypoint at that step (MSRL_env_ex.py:324-338) */
+    int32_t act_steps;       /* 1: action held for the launch, sac_update applies to its first step; or K */
+    int32_t init;            /* `init` argument of step(): 1/0 for the first step of the launch, -1 = per-env
+                                "first step since reset" flag */
+    int32_t auto_reset;      /* 1: reset() + init_step() inside the kernel right after a done step */
+    int32_t rec_steps;       /* outputs hold rec_steps = K (every step) or 1 (last step of the launch) */
+    /* outputs (device), may be NULL */
+    void* obs;               /* [rec_steps][SIT_N_OBS][n_envs] reals */
+    void* reward;            /* [rec_steps][n_envs] reals */
+    uint8_t* done;           /* [rec_steps][n_envs] */
+    int32_t* status;         /* [rec_steps][n_envs] bitmask SIT_ST_* */
+    void* reward_sum;        /* [n_envs] reals: sum of the K step rewards of this launch */
+    uint8_t* done_any;       /* [n_envs]: any step of this launch was done */
+    unsigned long long* stats; /* [SIT_N_STATS] accumulated with warp-reduced atomics: counts of each status
+                                bit (0..11), done steps (12), env-steps (13) */
+} SitEnvIO;
+
+/* MultiShipRLEnv.reset (MSRL_env_ex.py:145-186): same as sit_reset on an env handle */
+/* MultiShipRLEnv.init_step (MSRL_env_ex.py:188-215) */
+int sit_env_init_step(SitHandle h, void* state, const uint8_t* mask, void* stream);
+/* K x MultiShipRLEnv.step (MSRL_env_ex.py:402-440): test_step :217-283, obs_step :285-400,
+ * observation :424-435, reward_function :906-980 with the failure predicates :453-603 */
+int sit_env_step_k(SitHandle h, void* state, int32_t K, const SitEnvIO* io, void* stream);
+
+/* Host-buffer drop-in for one MultiShipRLEnv.step over all envs: action [2][n_envs] and
+ * sac_update [n_envs] are HOST arrays, obs [10][n_envs], reward, done, status are HOST outputs
+ * (reals in the handle's precision).  Copies, runs K steps (outputs of the last), synchronises. */
+int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h, const uint8_t* sac_update_h,
+                      int32_t init, void* obs_h, void* reward_h, uint8_t* done_h, int32_t* status_h, void* stream);
+
+/* ---- misc ------------------------------------------------------------------------------------ */
+const char* sit_last_error(void);
+const char* sit_status_string(int32_t bit_index);  /* exact reference strings, MSRL_env_ex.py:760-899 */
+int sit_abi_version(void);
+/* CUDA-core FMA peak of this device measured with a register-resident FMA chain (roofline
+ * denominator for the compute-bound step kernels).  precision SIT_F32 / SIT_F64; returns TFLOP/s. */
+int sit_measure_fma_peak(int device, int32_t precision, double* tflops, double* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SHIPSIM_H */

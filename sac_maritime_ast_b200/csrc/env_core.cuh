@@ -1,0 +1,98 @@
+// Device-side polygon map queries and two-ship env constants (RLEnv/MSRL_env_ex.py,
+// simulators/ship_in_transit/obstacle.py).  The map lives in the kernel-argument constant bank: every
+// lane of a warp walks the same edge at the same time, so edge data are uniform operands.
+//
+// shapely / GEOS is an un-vendored, un-pinned dependency of the reference; these follow the
+// published GEOS algorithms (RayCrossingCounter, Distance::pointToSegment) as restated in
+// oracle/geometry.py -- PARITY UNPINNED for this sub-path.
+#pragma once
+#include "ship_core.cuh"
+
+namespace sit {
+
+template <typename R>
+struct MapP {
+    R x1[SIT_MAX_EDGES], y1[SIT_MAX_EDGES], x2[SIT_MAX_EDGES], y2[SIT_MAX_EDGES];
+    R dx[SIT_MAX_EDGES], dy[SIT_MAX_EDGES];
+    R len2[SIT_MAX_EDGES], inv_len2[SIT_MAX_EDGES];
+    uint8_t poly_end[SIT_MAX_EDGES];  // 1 on the last segment of each polygon
+    int32_t n_edges, n_poly;
+};
+
+template <typename R>
+struct EnvP {
+    // PolygonObstacle.map_boundaries obstacle.py:111-124 and the horizons built from them
+    R min_n, max_n, min_e, max_e;                 // is_route_outside_horizon MSRL_env_ex.py:517-542
+    R lo_n[2], hi_n[2], lo_e[2], hi_e[2];         // is_pos_outside_horizon :460-488, per role (L/2 margin)
+    R inv_max_north;                              // reward normalisation :650,697,725
+    R inv_e_tol, e_tol;                           // e_tolerance = 1000 :119
+    R arrive2[2];                                 // largest x with sqrt(x) <= 200 (:754,829), per precision
+    R rpm_max;                                    // 2000 :557
+    double collide2;                              // 50^2 :592
+    R near2;                                      // (L/2 * sqrt2 + slack)^2: beyond it all hull corners share the centre's side
+    double theta, sampling_frequency;             // :125,130
+    R half_len[2];
+};
+
+// env flag bits (state field "flags")
+enum { F_STOP_TEST = 1, F_STOP_OBS = 2, F_NSTORED_SHIFT = 2, F_NSTORED_MASK = 3 << 2, F_IW_BAD = 16, F_FRESH = 32,
+       F_IW_VALID = 64 };
+
+// Literal point-in-any-polygon: obstacle.py:126-129 any(poly.contains(Point(e, n))), interior only.
+template <typename R>
+__device__ __noinline__ bool map_contains(const MapP<R>& m, R py /*north*/, R px /*east*/) {
+    int crossings = 0;
+    bool boundary = false, inside = false;
+    for (int i = 0; i < m.n_edges; ++i) {
+        if (!boundary) {
+            const R x1 = m.x1[i], y1 = m.y1[i], x2 = m.x2[i], y2 = m.y2[i];
+            if (!(x1 < px && x2 < px)) {
+                if (px == x2 && py == y2) {
+                    boundary = true;
+                } else if (y1 == py && y2 == py) {
+                    const R lo = x1 <= x2 ? x1 : x2, hi = x1 <= x2 ? x2 : x1;
+                    if (lo <= px && px <= hi) boundary = true;
+                } else if ((y1 > py && y2 <= py) || (y2 > py && y1 <= py)) {
+                    const R d = m.dx[i] * (py - y1) - m.dy[i] * (px - x1);
+                    if (d == (R)0) boundary = true;
+                    else if ((d > (R)0) != (y2 < y1)) crossings++;
+                }
+            }
+        }
+        if (m.poly_end[i]) {
+            inside |= (!boundary && (crossings & 1));
+            crossings = 0;
+            boundary = false;
+        }
+    }
+    return inside;
+}
+
+// One pass over the ring segments for the hull centre: squared distance to the nearest ring
+// (obstacle.py:138-141 min(poly.exterior.distance)) and containment of the centre, sharing the
+// per-edge cross product.  Valid as the containment of all four hull corners whenever
+// dist2 > near2 (no ring can pass between the centre and a corner).
+template <typename R>
+__device__ __forceinline__ void map_scan(const MapP<R>& m, R py, R px, R& dist2, bool& centre_inside) {
+    R best = (R)3.0e38;
+    uint32_t parity = 0;
+    bool inside = false;
+#pragma unroll 4
+    for (int i = 0; i < m.n_edges; ++i) {
+        const R ex = px - m.x1[i], ey = py - m.y1[i];
+        const R dx = m.dx[i], dy = m.dy[i];
+        const R v2 = ex * ex + ey * ey;               // distance^2 to the segment's first vertex
+        const R dot = ex * dx + ey * dy;
+        const R cr = dx * ey - dy * ex;               // orientation of (a, b, p)
+        const R pr = cr * cr * m.inv_len2[i];         // distance^2 to the supporting line
+        const R cand = (dot > (R)0 && dot < m.len2[i]) ? pr : v2;
+        best = min_(best, cand);
+        const bool straddle = (m.y1[i] > py) != (m.y2[i] > py);
+        parity ^= (straddle && ((cr > (R)0) != (dy < (R)0))) ? 1u : 0u;
+        if (m.poly_end[i]) { inside |= (parity & 1u); parity = 0; }
+    }
+    dist2 = best;
+    centre_inside = inside;
+}
+
+}  // namespace sit

@@ -1,0 +1,978 @@
+// libshipsim.so -- kernels and C ABI of the batched ship-in-transit simulator (see include/shipsim.h).
+// sm_100a only; no CPU fallback.  Reference citations are relative to /root/reference/.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "env_core.cuh"
+
+using namespace sit;
+
+// =================================================================================================
+// Kernel argument blocks
+// =================================================================================================
+template <typename R>
+struct FleetIO {
+    const R* dist; int32_t dist_steps; int32_t avoid; int32_t store; int32_t traj_steps;
+    R* traj; R* log27; R* cmd;
+};
+
+template <typename R>
+struct EnvPtrs {
+    double *prev_n, *prev_e, *eps_dist, *samp_dist;
+    R *ab_seg, *act_n, *act_e, *ep_return;
+    int32_t *flags, *ep_steps;
+    int64_t n_envs;
+};
+
+template <typename R>
+struct EnvIO {
+    const R* action; const uint8_t* sac_update; int32_t act_steps; int32_t init; int32_t auto_reset; int32_t rec_steps;
+    R* obs; R* reward; uint8_t* done; int32_t* status; R* reward_sum; uint8_t* done_any; unsigned long long* stats;
+    const uint8_t* mask;   // init_step only
+};
+
+template <typename R>
+struct EnvKArgs {
+    ShipP<R> P[2];
+    EnvP<R> EP;
+    MapP<R> M;
+};
+
+// =================================================================================================
+// K1: fleet of bare ships, K steps per launch, state in registers
+// =================================================================================================
+template <typename R, bool LOG>
+__global__ void __launch_bounds__(256) fleet_step_kernel(const __grid_constant__ ShipP<R> P, const ShipPtrs<R> g,
+                                                         const int K, const FleetIO<R> io) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t S = g.n_ships;
+    if (i >= S) return;
+    Ship<R> s;
+    load_ship(s, g, i);
+    R w_speed = (R)0, w_dir = (R)0;
+    for (int t = 0; t < K; ++t) {
+        if (io.dist && (t == 0 || io.dist_steps > 1)) {
+            // ship_model.py:154-156: vel_c / wind_speed / wind_dir are plain attributes, assigned per step
+            const R* d = io.dist + (int64_t)(io.dist_steps > 1 ? t : 0) * 4 * S;
+            s.vcn = d[i]; s.vce = d[S + i];
+            w_speed = d[2 * S + i]; w_dir = d[3 * S + i];
+            set_wind(s, w_speed, w_dir);
+        }
+        StepOut<R> o;
+        R lg[SIT_N_LOG];
+        ship_step<R, LOG>(P, s, g, i, io.avoid != 0, io.store != 0, o, (LOG && io.log27) ? lg : nullptr);
+        if (io.traj && (io.traj_steps != 1 || t == K - 1)) {
+            R* tr = io.traj + (int64_t)(io.traj_steps != 1 ? t : 0) * SIT_N_TRAJ * S + i;
+            tr[0] = (R)s.N; tr[S] = (R)s.E; tr[2 * S] = s.psi; tr[3 * S] = s.u;
+            tr[4 * S] = s.v; tr[5 * S] = s.r; tr[6 * S] = s.om; tr[7 * S] = (R)s.k;
+        }
+        if (LOG && io.log27) {
+            R* lo = io.log27 + (int64_t)t * SIT_N_LOG * S + i;
+#pragma unroll
+            for (int c = 0; c < SIT_N_LOG; ++c) lo[(int64_t)c * S] = lg[c];
+        }
+        if (io.cmd) {
+            R* co = io.cmd + (int64_t)t * 2 * S + i;
+            co[0] = o.rud; co[S] = o.thr;
+        }
+    }
+    store_ship(s, g, i);
+    if (io.dist) {
+        g.vc_n[i] = s.vcn; g.vc_e[i] = s.vce; g.wind_speed[i] = w_speed; g.wind_dir[i] = w_dir;
+    }
+}
+
+// =================================================================================================
+// K3: reset / capture_init
+// =================================================================================================
+template <typename R>
+__global__ void capture_init_kernel(const ShipPtrs<R> g, const EnvPtrs<R> ge, const double sampling_frequency,
+                                    const int ships_per_env) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t S = g.n_ships;
+    if (i >= S) return;
+    g.init_north[i] = g.north[i]; g.init_east[i] = g.east[i];
+    g.init_psi[i] = g.psi[i]; g.init_u[i] = g.u[i]; g.init_v[i] = g.v[i]; g.init_r[i] = g.r[i];
+    g.init_vc_n[i] = g.vc_n[i]; g.init_vc_e[i] = g.vc_e[i];
+    g.init_wind_speed[i] = g.wind_speed[i]; g.init_wind_dir[i] = g.wind_dir[i];
+    g.init_u_sp[i] = g.u_sp[i]; g.init_omega[i] = g.omega[i]; g.init_ei_shaft[i] = g.ei_shaft[i];
+    const int32_t n = g.n_wp[i];
+    g.n_wp0[i] = n;
+    for (int j = 0; j < g.max_wp; ++j) {
+        g.wp0_n[(int64_t)j * S + i] = g.wp_n[(int64_t)j * S + i];
+        g.wp0_e[(int64_t)j * S + i] = g.wp_e[(int64_t)j * S + i];
+    }
+    if (ships_per_env == 2 && (i & 1)) {
+        // reward_function_params, MSRL_env_ex.py:122-127: AB = first -> last waypoint of the obstacle route
+        const double dn = (double)g.wp_n[(int64_t)(n - 1) * S + i] - (double)g.wp_n[i];
+        const double de = (double)g.wp_e[(int64_t)(n - 1) * S + i] - (double)g.wp_e[i];
+        ge.ab_seg[i >> 1] = (R)(sqrt(dn * dn + de * de) / sampling_frequency);
+    }
+}
+
+template <typename R>
+__global__ void reset_kernel(const ShipPtrs<R> g, const EnvPtrs<R> ge, const uint8_t* mask, const int hard,
+                             const int ships_per_env) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n_ships) return;
+    const int64_t env = ships_per_env == 2 ? (i >> 1) : i;
+    if (mask && !mask[env]) return;
+    reset_ship_arrays(g, i, hard != 0);
+    if (ships_per_env == 2 && (i & 1)) {
+        // MSRL_env_ex.py:168-183: stop flags, distance counters; the stored-position history is
+        // cleared by ShipModelAST.reset (ship_model.py:708-712)
+        ge.flags[env] = (ge.flags[env] & (F_IW_BAD | F_IW_VALID)) | F_FRESH;
+        ge.eps_dist[env] = 0.0; ge.samp_dist[env] = 0.0;
+        ge.prev_n[env] = 0.0; ge.prev_e[env] = 0.0;
+        ge.ep_return[env] = (R)0; ge.ep_steps[env] = 0;
+    }
+}
+
+// =================================================================================================
+// K2: two-ship AST env.  Lane pair (2j, 2j+1) = (test ship, obstacle ship) of one env.
+// =================================================================================================
+template <typename R>
+__device__ __forceinline__ void reset_ship_regs(Ship<R>& s, const ShipPtrs<R>& g, int64_t i) {
+    const int64_t S = g.n_ships;
+    s.N = g.init_north[i]; s.E = g.init_east[i];
+    s.psi = g.init_psi[i]; s.u = g.init_u[i]; s.v = g.init_v[i]; s.r = g.init_r[i];
+    s.vcn = g.init_vc_n[i]; s.vce = g.init_vc_e[i];
+    const R ws = g.init_wind_speed[i], wd = g.init_wind_dir[i];
+    set_wind(s, ws, wd);
+    g.vc_n[i] = s.vcn; g.vc_e[i] = s.vce; g.wind_speed[i] = ws; g.wind_dir[i] = wd;
+    s.u_sp = g.init_u_sp[i]; g.u_sp[i] = s.u_sp;
+    s.steps = 0; s.k = 1; s.e_ct = (R)0; s.e_int = (R)0;
+    s.n_wp = g.n_wp0[i];
+    for (int j = 0; j < g.max_wp; ++j) {
+        g.wp_n[(int64_t)j * S + i] = g.wp0_n[(int64_t)j * S + i];
+        g.wp_e[(int64_t)j * S + i] = g.wp0_e[(int64_t)j * S + i];
+    }
+    load_segment(s, g, i);
+}
+
+template <typename R>
+__device__ __forceinline__ bool hull_inside(const EnvKArgs<R>& A, R n, R e, R half, R d2, bool centre_inside) {
+    // is_pos_inside_obstacles, MSRL_env_ex.py:490-515: the four corners of the +-L/2 square
+    if (d2 > A.EP.near2) return centre_inside;
+    bool in = map_contains(A.M, n - half, e - half);
+    in |= map_contains(A.M, n - half, e + half);
+    in |= map_contains(A.M, n + half, e - half);
+    in |= map_contains(A.M, n + half, e + half);
+    return in;
+}
+
+template <typename R, bool SAME>
+__global__ void __launch_bounds__(128) env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
+                                                       const EnvPtrs<R> ge, const int K, const EnvIO<R> io) {
+    const unsigned FULL = 0xffffffffu;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t S = g.n_ships, B = ge.n_envs;
+    const bool active = tid < S;
+    const int64_t i = active ? tid : (tid & 1);   // idle lanes of the last warp shadow env 0 and never store
+    const int role = (int)(i & 1);
+    const int64_t env = i >> 1;
+    const bool is_obs = role == SIT_ROLE_OBS;
+    const ShipP<R>& P = SAME ? A.P[0] : A.P[role];
+    const EnvP<R>& EP = A.EP;
+    const int lane = threadIdx.x & 31;
+
+    Ship<R> s;
+    load_ship(s, g, i);
+    // route end point (constant: insertions go before it, controllers.py:298-303)
+    R endN = g.wp_n[(int64_t)(s.n_wp - 1) * S + i], endE = g.wp_e[(int64_t)(s.n_wp - 1) * S + i];
+    int32_t flags = ge.flags[env];
+    bool stop = (flags & (is_obs ? F_STOP_OBS : F_STOP_TEST)) != 0;
+    int nstored = (flags & F_NSTORED_MASK) >> F_NSTORED_SHIFT;
+    bool fresh = (flags & F_FRESH) != 0;
+    bool iw_bad = (flags & F_IW_BAD) != 0, iw_valid = (flags & F_IW_VALID) != 0;
+    double prev_n = ge.prev_n[env], prev_e = ge.prev_e[env];
+    double eps_dist = ge.eps_dist[env], samp_dist = ge.samp_dist[env];
+    R ab_seg = ge.ab_seg[env], act_n = ge.act_n[env], act_e = ge.act_e[env];
+    R ep_return = ge.ep_return[env];
+    int32_t ep_steps = ge.ep_steps[env];
+    R rsum = (R)0;
+    bool any_done = false;
+    unsigned my_cnt = 0;   // lane b < 12 counts status bit b of this warp's envs; lane 12 counts done steps
+
+    for (int t = 0; t < K; ++t) {
+        // ---- inputs: converted_action and SAC_update (MSRL_env_ex.py:402-405) -----------------------
+        bool su = false;
+        if (io.action) {
+            const int64_t ta = io.act_steps > 1 ? t : 0;
+            const R a_n = io.action[(ta * 2 + 0) * B + env], a_e = io.action[(ta * 2 + 1) * B + env];
+            if (!iw_valid || a_n != act_n || a_e != act_e) {
+                // is_route_outside_horizon :517-542 or is_route_inside_obstacles :544-552 of the
+                // action, cached until the action changes
+                act_n = a_n; act_e = a_e;
+                iw_bad = (a_n < EP.min_n || a_n > EP.max_n || a_e < EP.min_e || a_e > EP.max_e) ||
+                         map_contains(A.M, a_n, a_e);
+                iw_valid = true;
+            }
+            if (io.sac_update && (io.act_steps > 1 || t == 0)) su = io.sac_update[ta * B + env] != 0;
+        }
+        const bool init = io.init >= 0 ? (t == 0 && io.init != 0) : fresh;
+        const bool frozen = is_obs && stop;
+        const double pre_n = s.N, pre_e = s.E;
+        StepOut<R> o;
+        o.rpm = (R)0; o.power_me_kw = (R)0; o.avail_me_kw = (R)0;
+        if (!frozen) {
+            if (is_obs && su) {
+                // obs_step :324-338 -> update_route controllers.py:298-303: list.insert(-1, wp)
+                if (s.n_wp < g.max_wp) {
+                    g.wp_n[(int64_t)s.n_wp * S + i] = endN; g.wp_e[(int64_t)s.n_wp * S + i] = endE;
+                    g.wp_n[(int64_t)(s.n_wp - 1) * S + i] = act_n; g.wp_e[(int64_t)(s.n_wp - 1) * S + i] = act_e;
+                    if (s.k == s.n_wp - 1) {   // the segment in use ended at the old last point
+                        s.cN = act_n; s.cE = act_e;
+                        s.alpha = atan2_(s.cE - s.pE, s.cN - s.pN);
+                        sincos_(s.alpha, s.sa, s.ca);
+                    }
+                    s.n_wp += 1;
+                }
+                samp_dist = 0.0;
+            }
+            // test_step :217-283 (avoidance branch always taken) | obs_step :346-373
+            ship_step<R, false>(P, s, g, i, !is_obs, true, o, nullptr);
+        } else {
+            s.steps += 2;   // frozen ship: next_time twice, :294,307
+        }
+        if (is_obs) {
+            if (frozen) {
+                if (nstored >= 1) nstored = 2;   // store_last_simulation_data repeats the last row :292
+            } else {
+                if (!init && nstored >= 1) {      // :391-395, last two *stored* (pre-step) positions
+                    const double dn = pre_n - prev_n, de = pre_e - prev_e;
+                    const double d = sqrt(__dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de)));
+                    eps_dist += d; samp_dist += d;
+                }
+                prev_n = pre_n; prev_e = pre_e;
+                nstored = nstored < 2 ? nstored + 1 : 2;
+            }
+        }
+
+        // ---- exchange post-step positions inside the lane pair ---------------------------------------
+        const double oth_n = __shfl_xor_sync(FULL, s.N, 1), oth_e = __shfl_xor_sync(FULL, s.E, 1);
+        const double n_t = is_obs ? oth_n : s.N, e_t = is_obs ? oth_e : s.E;
+        const double n_o = is_obs ? s.N : oth_n, e_o = is_obs ? s.E : oth_e;
+        const double ddn = n_t - n_o, dde = e_t - e_o;
+        const double ship_d2 = __dadd_rn(__dmul_rn(ddn, ddn), __dmul_rn(dde, dde));
+
+        // ---- own-ship geometry: distance to the nearest ring + hull containment ------------------------
+        const R pn = (R)s.N, pe = (R)s.E;
+        R d2map; bool c_in;
+        map_scan(A.M, pn, pe, d2map, c_in);
+        const bool inside = hull_inside(A, pn, pe, EP.half_len[role], d2map, c_in);
+        const R dmap = sqrt_(d2map);
+        const bool outside = pn < EP.lo_n[role] || pn > EP.hi_n[role] || pe < EP.lo_e[role] || pe > EP.hi_e[role];
+        const double dnE = s.N - (double)endN, deE = s.E - (double)endE;
+        const bool arrived = (R)__dadd_rn(__dmul_rn(dnE, dnE), __dmul_rn(deE, deE)) <= EP.arrive2[role];
+        const R ect = s.e_ct;
+
+        // ---- per-ship reward terms and terminal checks (sequential stop_flag gating) -------------------
+        int st = 0; bool dn_ = false; R part;
+        if (!is_obs) {
+            // test_ship_non_terminal_state_reward :628-664
+            const R ntt = abs_(ect) * EP.inv_e_tol + ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
+            R rt = (R)0;
+            // test_ship_terminal_state_reward :734-809
+            if (arrived) { stop = true; dn_ = true; st |= SIT_ST_TEST_ENDPOINT; }
+            if (outside) { stop = true; dn_ = true; st |= SIT_ST_TEST_HORIZON; }
+            if (inside) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_TERRAIN; }
+            if (abs_(o.rpm) > EP.rpm_max) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_MECH; }
+            if (abs_(ect) > EP.e_tol) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_NAV; }
+            if (o.power_me_kw > o.avail_me_kw) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_BLACKOUT; }
+            part = ntt + rt;
+        } else {
+            // obs_ship_non_terminal_state_reward :666-710 (stop flag from before this step's checks)
+            R nto = (R)0;
+            if (!stop) nto = (R)0.1 + (-(abs_(ect) * EP.inv_e_tol) * (R)0.01) + (-((R)1 - dmap * EP.inv_max_north) * (R)0.01);
+            R ro = (R)0;
+            // obs_ship_terminal_state_reward :811-881
+            if (arrived) { stop = true; st |= SIT_ST_OBS_ENDPOINT; }                       // no done
+            if (outside) { stop = true; dn_ = true; st |= SIT_ST_OBS_HORIZON; }
+            if (inside) { if (!stop) ro -= (R)1000; dn_ = true; st |= SIT_ST_OBS_TERRAIN; } // no stop flag
+            if (iw_bad) { if (!stop) ro -= (R)1000; stop = true; dn_ = true; st |= SIT_ST_OBS_IW; }
+            if (abs_(ect) > EP.e_tol || samp_dist > (double)ab_seg * EP.theta) {
+                if (!stop) ro -= (R)1000; stop = true; dn_ = true; st |= SIT_ST_OBS_NAV;
+            }
+            // shared_non_terminal_state_reward :712-731 (sees the stop flag after the checks above)
+            R snt = (R)0;
+            if (!stop) snt = ((R)1 - (R)sqrt(ship_d2) * EP.inv_max_north) * (R)0.001;
+            part = nto;      // assembled below as ((((ntt+rt) + nto) + ro) + snt) + rs
+            // stash ro, snt in o.* free slots
+            o.rud = ro; o.thr = snt;
+        }
+        // shared_terminal_state_reward :883-904, is_ship_collision :584-603
+        const bool collide = ship_d2 < EP.collide2;
+        if (collide) { stop = true; dn_ = true; st |= SIT_ST_COLLISION; }
+
+        const R part_t = __shfl_xor_sync(FULL, part, 1);
+        const int st_o = __shfl_xor_sync(FULL, st, 1);
+        const bool dn_o = __shfl_xor_sync(FULL, (int)dn_, 1) != 0;
+        const bool done = dn_ || dn_o;
+        const int status = st | st_o;
+        R reward = (R)0;
+        if (is_obs) reward = ((((part_t + part) + o.rud) + o.thr)) + (collide ? (R)2000 : (R)0);   // :970-972
+        rsum += reward; ep_return += reward; ep_steps += 1;
+        any_done |= done;
+        fresh = false;
+
+        // ---- outputs: coalesced SoA rows [step][channel][env] -------------------------------------------
+        if (active && (io.rec_steps > 1 || t == K - 1)) {
+            const int64_t rec = io.rec_steps > 1 ? t : 0;
+            if (io.obs) {
+                R* ob = io.obs + rec * SIT_N_OBS * B + env;
+                if (!is_obs) {   // :424-435: post-step pose, pre-step stored rpm / e_ct / power
+                    ob[0] = pn; ob[B] = pe; ob[2 * B] = s.psi; ob[3 * B] = o.rpm; ob[4 * B] = ect; ob[5 * B] = o.power_me_kw;
+                } else {
+                    ob[6 * B] = pn; ob[7 * B] = pe; ob[8 * B] = s.psi; ob[9 * B] = ect;
+                }
+            }
+            if (is_obs) {
+                if (io.reward) io.reward[rec * B + env] = reward;
+                if (io.done) io.done[rec * B + env] = done ? 1 : 0;
+                if (io.status) io.status[rec * B + env] = status;
+            }
+        }
+        // ---- warp-level reduction of termination / collision flags --------------------------------------
+        if (io.stats) {
+            const bool cnt_lane = active && is_obs;
+            if (__any_sync(FULL, cnt_lane && status != 0)) {
+#pragma unroll
+                for (int b = 0; b < 12; ++b) {
+                    const unsigned bal = __ballot_sync(FULL, cnt_lane && ((status >> b) & 1));
+                    if (lane == b) my_cnt += __popc(bal);
+                }
+                const unsigned bal = __ballot_sync(FULL, cnt_lane && done);
+                if (lane == 12) my_cnt += __popc(bal);
+            }
+        }
+        // ---- in-kernel reset() + init_step() right after a terminal step ---------------------------------
+        if (io.auto_reset && done) {
+            reset_ship_regs(s, g, i);   // MSRL_env_ex.py:145-186 (omega, integrators, fuel kept)
+            endN = g.wp_n[(int64_t)(s.n_wp - 1) * S + i]; endE = g.wp_e[(int64_t)(s.n_wp - 1) * S + i];
+            stop = false; nstored = 0; fresh = true;
+            eps_dist = 0.0; samp_dist = 0.0; prev_n = 0.0; prev_e = 0.0;
+            ep_return = (R)0; ep_steps = 0;
+            StepOut<R> o2;
+            ship_step<R, false>(P, s, g, i, false, false, o2, nullptr);   // init_step :188-215
+        }
+    }
+
+    // ---- write back ------------------------------------------------------------------------------------------
+    const bool stop_t = __shfl_xor_sync(FULL, (int)stop, 1) != 0;   // the test lane's flag, seen by the obs lane
+    if (active) {
+        store_ship(s, g, i);
+        if (is_obs) {
+            int32_t f = (stop_t ? F_STOP_TEST : 0) | (stop ? F_STOP_OBS : 0) | (nstored << F_NSTORED_SHIFT) |
+                        (iw_bad ? F_IW_BAD : 0) | (iw_valid ? F_IW_VALID : 0) | (fresh ? F_FRESH : 0);
+            ge.flags[env] = f;
+            ge.prev_n[env] = prev_n; ge.prev_e[env] = prev_e;
+            ge.eps_dist[env] = eps_dist; ge.samp_dist[env] = samp_dist;
+            ge.act_n[env] = act_n; ge.act_e[env] = act_e;
+            ge.ep_return[env] = ep_return; ge.ep_steps[env] = ep_steps;
+            if (io.reward_sum) io.reward_sum[env] = rsum;
+            if (io.done_any) io.done_any[env] = any_done ? 1 : 0;
+        }
+    }
+    if (io.stats) {
+        if (lane <= 12 && my_cnt) atomicAdd(&io.stats[lane], (unsigned long long)my_cnt);
+        const unsigned n_env_lanes = __popc(__ballot_sync(FULL, active && is_obs));
+        if (lane == 13 && n_env_lanes) atomicAdd(&io.stats[13], (unsigned long long)n_env_lanes * (unsigned long long)K);
+    }
+}
+
+// init_step, MSRL_env_ex.py:188-215: both ships advance one dt without storing, without next_time and
+// without the avoidance branch
+template <typename R, bool SAME>
+__global__ void __launch_bounds__(256) env_init_step_kernel(const __grid_constant__ ShipP<R> P0,
+                                                            const __grid_constant__ ShipP<R> P1, const ShipPtrs<R> g,
+                                                            const uint8_t* mask) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n_ships) return;
+    if (mask && !mask[i >> 1]) return;
+    const ShipP<R>& P = (SAME || !(i & 1)) ? P0 : P1;
+    Ship<R> s;
+    load_ship(s, g, i);
+    StepOut<R> o;
+    ship_step<R, false>(P, s, g, i, false, false, o, nullptr);
+    store_ship(s, g, i);
+}
+
+// =================================================================================================
+// FMA-peak microbenchmark (roofline denominator for the compute-bound step kernels)
+// =================================================================================================
+template <typename R>
+__global__ void __launch_bounds__(256) fma_peak_kernel(R* out, int iters, R a, R b) {
+    R x0 = (R)threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            x0 = x0 * a + b; x1 = x1 * a + b; x2 = x2 * a + b; x3 = x3 * a + b;
+            x4 = x4 * a + b; x5 = x5 * a + b; x6 = x6 * a + b; x7 = x7 * a + b;
+        }
+    }
+    const R sum = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (sum == (R)123456789) out[0] = sum;   // never true: keeps the chain alive
+}
+
+// =================================================================================================
+// Host side
+// =================================================================================================
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CUDA_TRY(x)                                                                                   \
+    do {                                                                                              \
+        cudaError_t e_ = (x);                                                                         \
+        if (e_ != cudaSuccess) return fail(SIT_E_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct FieldDef { const char* name; char kind; int rows; bool env; };   // kind: D f64, R real, I i32
+static const FieldDef kShipFields[] = {
+    {"north", 'D', 1, false}, {"east", 'D', 1, false}, {"init_north", 'D', 1, false}, {"init_east", 'D', 1, false},
+    {"psi", 'R', 1, false}, {"u", 'R', 1, false}, {"v", 'R', 1, false}, {"r", 'R', 1, false}, {"omega", 'R', 1, false},
+    {"ei_speed", 'R', 1, false}, {"ei_shaft", 'R', 1, false}, {"ei_heading", 'R', 1, false}, {"e_prev", 'R', 1, false},
+    {"e_ct", 'R', 1, false}, {"e_ct_int", 'R', 1, false},
+    {"fuel_me", 'R', 1, false}, {"fuel_el", 'R', 1, false}, {"fuel", 'R', 1, false},
+    {"u_sp", 'R', 1, false}, {"vc_n", 'R', 1, false}, {"vc_e", 'R', 1, false}, {"wind_speed", 'R', 1, false},
+    {"wind_dir", 'R', 1, false},
+    {"init_psi", 'R', 1, false}, {"init_u", 'R', 1, false}, {"init_v", 'R', 1, false}, {"init_r", 'R', 1, false},
+    {"init_vc_n", 'R', 1, false}, {"init_vc_e", 'R', 1, false}, {"init_wind_speed", 'R', 1, false},
+    {"init_wind_dir", 'R', 1, false}, {"init_u_sp", 'R', 1, false}, {"init_omega", 'R', 1, false},
+    {"init_ei_shaft", 'R', 1, false},
+    {"k", 'I', 1, false}, {"n_wp", 'I', 1, false}, {"mode", 'I', 1, false}, {"n_wp0", 'I', 1, false},
+    {"steps", 'I', 1, false},
+    {"wp_n", 'R', -1, false}, {"wp_e", 'R', -1, false}, {"wp0_n", 'R', -1, false}, {"wp0_e", 'R', -1, false},
+};
+static const FieldDef kEnvFields[] = {
+    {"prev_n", 'D', 1, true}, {"prev_e", 'D', 1, true}, {"eps_dist", 'D', 1, true}, {"samp_dist", 'D', 1, true},
+    {"ab_seg", 'R', 1, true}, {"act_n", 'R', 1, true}, {"act_e", 'R', 1, true}, {"ep_return", 'R', 1, true},
+    {"flags", 'I', 1, true}, {"ep_steps", 'I', 1, true},
+};
+
+struct SitHandle_ {
+    SitConfig cfg;
+    int64_t n_envs, n_ships;
+    int device, ships_per_env, sm_count;
+    bool same_params;
+    std::vector<SitField> fields;
+    size_t state_bytes;
+    ShipP<double> pd[2]; ShipP<float> pf[2];
+    EnvKArgs<double>* kd; EnvKArgs<float>* kf;   // host copies passed by value at launch
+    // scratch for the *_host entry point
+    void* d_scratch; size_t scratch_bytes;
+    void* h_pinned; size_t pinned_bytes;
+};
+
+template <typename R> struct HostSel;
+template <> struct HostSel<double> {
+    static const ShipP<double>& ship(const SitHandle_* h) { return h->pd[0]; }
+    static const EnvKArgs<double>& env(const SitHandle_* h) { return *h->kd; }
+};
+template <> struct HostSel<float> {
+    static const ShipP<float>& ship(const SitHandle_* h) { return h->pf[0]; }
+    static const EnvKArgs<float>& env(const SitHandle_* h) { return *h->kf; }
+};
+
+static bool params_equal(const SitShipParams& a, const SitShipParams& b) { return std::memcmp(&a, &b, sizeof(a)) == 0; }
+
+template <typename R>
+static R largest_with_sqrt_le(double bound) {
+    // largest x (in R) such that sqrt_R(x) <= bound: lets `sqrt(d2) <= bound` (MSRL_env_ex.py:754,829) be decided
+    // without the square root, bit-for-bit
+    R x = (R)(bound * bound);
+    while (std::sqrt(x) > (R)bound) x = std::nextafter(x, (R)0);
+    for (;;) {
+        R y = std::nextafter(x, (R)INFINITY);
+        if (std::sqrt(y) <= (R)bound) x = y; else break;
+    }
+    return x;
+}
+
+template <typename R>
+static void derive_ship(const SitShipParams& c, ShipP<R>& P) {
+    const double PI = 3.14159265358979323846;
+    // ship_model.py:71-80
+    const double payload = 0.9 * (c.dead_weight_tonnage - c.bunkers);
+    const double lsw = c.dead_weight_tonnage / c.coefficient_of_deadweight_to_displacement - c.dead_weight_tonnage;
+    const double mass = lsw + payload + c.bunkers + c.ballast;
+    const double L = c.length_of_ship, W = c.width_of_ship;
+    const double i_z = mass * (L * L + W * W) / 12;
+    // ship_model.py:193-209
+    const double x_du = mass * c.added_mass_coefficient_in_surge, y_dv = mass * c.added_mass_coefficient_in_sway,
+                 n_dr = i_z * c.added_mass_coefficient_in_yaw;
+    // ship_model.py:123-130
+    const double rho = 1.2, cx = 0.5, cy = 0.7, cn = 0.08, a_f = W * 8.0, a_l = L * 8.0;
+    const double m11 = mass + x_du, m22 = mass + y_dv, m33 = i_z + n_dr;
+    std::memset(&P, 0, sizeof(P));
+    P.dt = (R)c.dt; P.inv_dt = (R)(1.0 / c.dt);
+    P.ra2 = c.radius_of_acceptance * c.radius_of_acceptance;
+    P.look = (R)c.lookahead_distance; P.look2 = (R)(c.lookahead_distance * c.lookahead_distance);
+    P.sat_e = (R)(0.99 * c.lookahead_distance);
+    P.ki_los = (R)c.los_integral_gain; P.windup = (R)c.los_integrator_windup_limit;
+    P.kp_h = (R)c.kp_heading; P.kd_h = (R)c.kd_heading; P.ki_h = (R)c.ki_heading;
+    P.rud_max = (R)(c.max_rudder_angle_degrees * PI / 180); P.rud_bias = (R)(3.0 * PI / 180.0);
+    P.kp_s = (R)c.kp_ship_speed; P.ki_s = (R)c.ki_ship_speed; P.kp_w = (R)c.kp_shaft_speed; P.ki_w = (R)c.ki_shaft_speed;
+    P.hotel = (R)c.hotel_load;
+    for (int j = 0; j < 3; ++j) { P.sfc_me[j] = (R)(c.sfc_me[j] / 3.6e9); P.sfc_dg[j] = (R)(c.sfc_dg[j] / 3.6e9); }
+    const double jp = c.propeller_inertia;
+    P.sh_me = (R)(1.0 / (c.gear_ratio_between_main_engine_and_propeller * jp));
+    P.sh_hsg = (R)(1.0 / (c.gear_ratio_between_hybrid_shaft_generator_and_propeller * jp));
+    P.sh_lin = (R)((c.linear_friction_main_engine / c.gear_ratio_between_main_engine_and_propeller +
+                    c.linear_friction_hybrid_shaft_generator / c.gear_ratio_between_hybrid_shaft_generator_and_propeller) / jp);
+    P.sh_quad = (R)(c.propeller_speed_to_torque_coefficient / jp);
+    const double thrust_coef = std::pow(c.propeller_diameter, 4) * c.propeller_speed_to_thrust_force_coefficient;
+    P.thrust_coef = (R)thrust_coef;
+    P.rad2deg = (R)(180.0 / PI); P.rpm_per_rads = (R)(30.0 / PI);
+    P.au_vr = (R)(mass / m11); P.au_vrr = (R)(y_dv / m11);
+    P.au_lin = (R)(mass / c.mass_over_linear_friction_coefficient_in_surge / m11);
+    P.au_nl = (R)(c.nonlinear_friction_coefficient__in_surge / m11);
+    P.au_wind = (R)(0.5 * rho * cx * a_f / m11); P.au_thr = (R)(thrust_coef / m11);
+    P.av_ur = (R)(mass / m22); P.av_urr = (R)(x_du / m22);
+    P.av_lin = (R)(mass / c.mass_over_linear_friction_coefficient_in_sway / m22);
+    P.av_nl = (R)(c.nonlinear_friction_coefficient__in_sway / m22);
+    P.av_wind = (R)(0.5 * rho * cy * a_l / m22); P.av_rud = (R)(c.rudder_angle_to_sway_force_coefficient / m22);
+    P.ar_ca = (R)((x_du - y_dv) / m33);
+    P.ar_lin = (R)(i_z / c.mass_over_linear_friction_coefficient_in_yaw / m33);
+    P.ar_nl = (R)(c.nonlinear_friction_coefficient__in_yaw / m33);
+    P.ar_wind = (R)(2.0 * 0.5 * rho * cn * a_l * L / m33); P.ar_rud = (R)(c.rudder_angle_to_yaw_force_coefficient / m33);
+    P.half_len = (R)(L / 2);
+    P.n_modes = c.n_modes;
+    for (int j = 0; j < c.n_modes && j < SIT_MAX_MODES; ++j) {
+        ModeP<R>& M = P.mode[j];
+        const double me = c.mode_main_engine_capacity[j], el = c.mode_electrical_capacity[j], hotel = c.hotel_load;
+        const int sg = c.mode_shaft_generator_state[j];
+        double at, ame, ael;   // ship_engine.py:32-44
+        if (sg == SIT_SG_MOTOR) { at = me + el - hotel; ame = me; ael = el - hotel; }
+        else if (sg == SIT_SG_GEN) { at = me - hotel; ame = me - hotel; ael = 0; }
+        else { at = me; ame = me; ael = 0; }
+        M.avail_total = (R)at; M.avail_me = (R)ame; M.avail_el = (R)ael;
+        M.cap_tq_me = (R)(ame / 5 * PI / 30); M.cap_tq_el = (R)(ael / 5 * PI / 30);
+        M.me_cap = (R)me; M.me_cap_kw = (R)(me / 1000); M.el_cap_kw = (R)(el / 1000);
+        M.inv_me_cap = (R)((sg == SIT_SG_MOTOR && me == 0) ? 0.0 : 1.0 / me);
+        M.inv_el_cap = (R)((sg == SIT_SG_GEN && el == 0) ? 0.0 : 1.0 / el);
+        if (sg == SIT_SG_GEN) { const double le = hotel < el ? hotel : el; M.load_me_add = (R)(hotel - le); M.load_el_const = (R)le; }
+        else { M.load_me_add = (R)0; M.load_el_const = (R)hotel; }
+        M.sg = sg;
+    }
+}
+
+template <typename R>
+static void derive_env(const SitConfig& c, EnvKArgs<R>& A) {
+    derive_ship(c.ship[0], A.P[0]);
+    derive_ship(c.ship[1], A.P[1]);
+    const SitMap& m = c.map;
+    MapP<R>& M = A.M;
+    std::memset(&M, 0, sizeof(M));
+    M.n_edges = m.n_edges; M.n_poly = m.n_poly;
+    double mn_n = 1e300, mx_n = -1e300, mn_e = 1e300, mx_e = -1e300;
+    for (int i = 0; i < m.n_edges; ++i) {
+        M.x1[i] = (R)m.x1[i]; M.y1[i] = (R)m.y1[i]; M.x2[i] = (R)m.x2[i]; M.y2[i] = (R)m.y2[i];
+        const double dx = m.x2[i] - m.x1[i], dy = m.y2[i] - m.y1[i], l2 = dx * dx + dy * dy;
+        M.dx[i] = (R)dx; M.dy[i] = (R)dy; M.len2[i] = (R)l2; M.inv_len2[i] = (R)(l2 > 0 ? 1.0 / l2 : 0.0);
+        M.poly_end[i] = (i + 1 == m.n_edges || m.poly[i + 1] != m.poly[i]) ? 1 : 0;
+        mn_e = std::fmin(mn_e, std::fmin(m.x1[i], m.x2[i])); mx_e = std::fmax(mx_e, std::fmax(m.x1[i], m.x2[i]));
+        mn_n = std::fmin(mn_n, std::fmin(m.y1[i], m.y2[i])); mx_n = std::fmax(mx_n, std::fmax(m.y1[i], m.y2[i]));
+    }
+    EnvP<R>& E = A.EP;
+    std::memset(&E, 0, sizeof(E));
+    if (m.n_edges == 0) { mn_n = mn_e = 0; mx_n = mx_e = 1; }
+    E.min_n = (R)mn_n; E.max_n = (R)mx_n; E.min_e = (R)mn_e; E.max_e = (R)mx_e;
+    double hl_max = 0;
+    for (int r = 0; r < 2; ++r) {
+        const double margin = c.ship[r].length_of_ship / 2;
+        E.lo_n[r] = (R)(mn_n + margin); E.hi_n[r] = (R)(mx_n - margin);
+        E.lo_e[r] = (R)(mn_e + margin); E.hi_e[r] = (R)(mx_e - margin);
+        E.half_len[r] = (R)margin;
+        E.arrive2[r] = largest_with_sqrt_le<R>(200.0);
+        hl_max = std::fmax(hl_max, margin);
+    }
+    E.inv_max_north = (R)(1.0 / mx_n);
+    E.e_tol = (R)1000; E.inv_e_tol = (R)(1.0 / 1000);
+    E.rpm_max = (R)2000;
+    E.collide2 = 50.0 * 50.0;
+    const double nr = hl_max * std::sqrt(2.0) + 4.0;
+    E.near2 = (R)(nr * nr);
+    E.theta = c.theta; E.sampling_frequency = c.sampling_frequency;
+}
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+static void build_layout(SitHandle_* h) {
+    size_t off = 0;
+    const bool f32 = h->cfg.precision == SIT_F32;
+    auto add = [&](const FieldDef& d) {
+        SitField f;
+        std::memset(&f, 0, sizeof(f));
+        std::snprintf(f.name, sizeof(f.name), "%s", d.name);
+        f.dtype = d.kind == 'D' ? SIT_DT_F64 : d.kind == 'I' ? SIT_DT_I32 : (f32 ? SIT_DT_F32 : SIT_DT_F64);
+        f.rows = d.rows < 0 ? h->cfg.max_wp : d.rows;
+        f.count = d.env ? h->n_envs : h->n_ships;
+        const size_t esz = f.dtype == SIT_DT_F64 ? 8 : 4;
+        f.offset = (int64_t)off;
+        off = align_up(off + esz * (size_t)f.rows * (size_t)f.count, 256);
+        h->fields.push_back(f);
+    };
+    for (const FieldDef& d : kShipFields) add(d);
+    if (h->cfg.kind == SIT_KIND_ENV)
+        for (const FieldDef& d : kEnvFields) add(d);
+    h->state_bytes = off;
+}
+
+static const SitField* find_field(const SitHandle_* h, const char* name) {
+    for (const SitField& f : h->fields)
+        if (std::strcmp(f.name, name) == 0) return &f;
+    return nullptr;
+}
+
+template <typename T>
+static T* fptr(const SitHandle_* h, void* state, const char* name) {
+    const SitField* f = find_field(h, name);
+    return f ? reinterpret_cast<T*>(static_cast<char*>(state) + f->offset) : nullptr;
+}
+
+template <typename R>
+static ShipPtrs<R> ship_ptrs(const SitHandle_* h, void* st) {
+    ShipPtrs<R> g;
+    g.north = fptr<double>(h, st, "north"); g.east = fptr<double>(h, st, "east");
+    g.init_north = fptr<double>(h, st, "init_north"); g.init_east = fptr<double>(h, st, "init_east");
+#define F_(n) g.n = fptr<R>(h, st, #n)
+    F_(psi); F_(u); F_(v); F_(r); F_(omega); F_(ei_speed); F_(ei_shaft); F_(ei_heading); F_(e_prev); F_(e_ct); F_(e_ct_int);
+    F_(fuel_me); F_(fuel_el); F_(fuel); F_(u_sp); F_(vc_n); F_(vc_e); F_(wind_speed); F_(wind_dir);
+    F_(init_psi); F_(init_u); F_(init_v); F_(init_r); F_(init_vc_n); F_(init_vc_e); F_(init_wind_speed); F_(init_wind_dir);
+    F_(init_u_sp); F_(init_omega); F_(init_ei_shaft);
+    F_(wp_n); F_(wp_e); F_(wp0_n); F_(wp0_e);
+#undef F_
+    g.k = fptr<int32_t>(h, st, "k"); g.n_wp = fptr<int32_t>(h, st, "n_wp"); g.mode = fptr<int32_t>(h, st, "mode");
+    g.n_wp0 = fptr<int32_t>(h, st, "n_wp0"); g.steps = fptr<int32_t>(h, st, "steps");
+    g.n_ships = h->n_ships; g.max_wp = h->cfg.max_wp; g._pad = 0;
+    return g;
+}
+
+template <typename R>
+static EnvPtrs<R> env_ptrs(const SitHandle_* h, void* st) {
+    EnvPtrs<R> e;
+    std::memset(&e, 0, sizeof(e));
+    e.n_envs = h->n_envs;
+    if (h->cfg.kind != SIT_KIND_ENV) return e;
+    e.prev_n = fptr<double>(h, st, "prev_n"); e.prev_e = fptr<double>(h, st, "prev_e");
+    e.eps_dist = fptr<double>(h, st, "eps_dist"); e.samp_dist = fptr<double>(h, st, "samp_dist");
+    e.ab_seg = fptr<R>(h, st, "ab_seg"); e.act_n = fptr<R>(h, st, "act_n"); e.act_e = fptr<R>(h, st, "act_e");
+    e.ep_return = fptr<R>(h, st, "ep_return");
+    e.flags = fptr<int32_t>(h, st, "flags"); e.ep_steps = fptr<int32_t>(h, st, "ep_steps");
+    return e;
+}
+
+static int check_params(const SitShipParams& p, const char* who) {
+    if (!(p.dt > 0)) return fail(SIT_E_INVALID, std::string(who) + ": dt must be > 0");
+    if (p.n_modes < 1 || p.n_modes > SIT_MAX_MODES) return fail(SIT_E_INVALID, std::string(who) + ": n_modes out of range");
+    for (int j = 0; j < p.n_modes; ++j)
+        if (p.mode_shaft_generator_state[j] < 0 || p.mode_shaft_generator_state[j] > 2)
+            return fail(SIT_E_INVALID, std::string(who) + ": bad shaft generator state");
+    if (!(p.lookahead_distance > 0) || !(p.propeller_inertia > 0)) return fail(SIT_E_INVALID, std::string(who) + ": bad parameter");
+    return SIT_OK;
+}
+
+extern "C" {
+
+int sit_abi_version(void) { return SIT_ABI_VERSION; }
+const char* sit_last_error(void) { return g_err.c_str(); }
+
+const char* sit_status_string(int32_t b) {
+    static const char* k[12] = {
+        "|Test ship reaches endpoint|", "|Test ship hits map horizon|", "|Test ship collides with the terrain|",
+        "|Test ship mechanical failure|", "|Test ship navigation failure|", "|Test ship blackout failure|",
+        "|Obstacle ship reaches endpoint|", "|Obstacle ship hits map horizon|", "|Obstacle ship collides with the terrain|",
+        "|Obstacle ship IW sampled in terminal state|", "|Obstacle ship navigation failure|", "|Ship collision|"};
+    return (b >= 0 && b < 12) ? k[b] : "";
+}
+
+int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out) {
+    if (!cfg || !out) return fail(SIT_E_INVALID, "null argument");
+    if (cfg->abi_version != SIT_ABI_VERSION) return fail(SIT_E_INVALID, "SitConfig.abi_version mismatch");
+    if (cfg->kind != SIT_KIND_FLEET && cfg->kind != SIT_KIND_ENV) return fail(SIT_E_INVALID, "bad kind");
+    if (cfg->precision != SIT_F64 && cfg->precision != SIT_F32) return fail(SIT_E_INVALID, "bad precision");
+    if (cfg->max_wp < 2 || cfg->max_wp > SIT_MAX_WP) return fail(SIT_E_INVALID, "max_wp out of range");
+    if (n_envs < 1) return fail(SIT_E_INVALID, "n_envs must be >= 1");
+    int rc = check_params(cfg->ship[0], "ship[0]");
+    if (rc) return rc;
+    if (cfg->kind == SIT_KIND_ENV) {
+        rc = check_params(cfg->ship[1], "ship[1]");
+        if (rc) return rc;
+        if (cfg->map.n_edges < 0 || cfg->map.n_edges > SIT_MAX_EDGES) return fail(SIT_E_INVALID, "map.n_edges out of range");
+        if (!(cfg->sampling_frequency > 0)) return fail(SIT_E_INVALID, "sampling_frequency must be > 0");
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(SIT_E_NODEVICE, "no CUDA device (libshipsim has no CPU fallback)");
+    }
+    if (device < 0 || device >= ndev) return fail(SIT_E_INVALID, "device index out of range");
+    CUDA_TRY(cudaSetDevice(device));
+    SitHandle_* h = new (std::nothrow) SitHandle_();
+    if (!h) return fail(SIT_E_INVALID, "out of host memory");
+    h->cfg = *cfg;
+    h->n_envs = n_envs;
+    h->ships_per_env = cfg->kind == SIT_KIND_ENV ? 2 : 1;
+    h->n_ships = n_envs * h->ships_per_env;
+    h->device = device;
+    h->same_params = cfg->kind == SIT_KIND_FLEET || params_equal(cfg->ship[0], cfg->ship[1]);
+    cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
+    derive_ship(cfg->ship[0], h->pd[0]); derive_ship(cfg->ship[1].dt > 0 ? cfg->ship[1] : cfg->ship[0], h->pd[1]);
+    derive_ship(cfg->ship[0], h->pf[0]); derive_ship(cfg->ship[1].dt > 0 ? cfg->ship[1] : cfg->ship[0], h->pf[1]);
+    h->kd = nullptr; h->kf = nullptr;
+    if (cfg->kind == SIT_KIND_ENV) {
+        if (cfg->precision == SIT_F64) { h->kd = new EnvKArgs<double>(); derive_env(*cfg, *h->kd); }
+        else { h->kf = new EnvKArgs<float>(); derive_env(*cfg, *h->kf); }
+    }
+    h->d_scratch = nullptr; h->scratch_bytes = 0; h->h_pinned = nullptr; h->pinned_bytes = 0;
+    build_layout(h);
+    *out = h;
+    return SIT_OK;
+}
+
+int sit_destroy(SitHandle h) {
+    if (!h) return SIT_OK;
+    if (h->d_scratch) cudaFree(h->d_scratch);
+    if (h->h_pinned) cudaFreeHost(h->h_pinned);
+    delete h->kd; delete h->kf;
+    delete h;
+    return SIT_OK;
+}
+
+int sit_state_bytes(SitHandle h, size_t* nbytes) {
+    if (!h || !nbytes) return fail(SIT_E_INVALID, "null argument");
+    *nbytes = h->state_bytes;
+    return SIT_OK;
+}
+
+int64_t sit_n_ships(SitHandle h) { return h ? h->n_ships : 0; }
+
+int sit_layout(SitHandle h, SitField* fields, int32_t capacity, int32_t* n_fields) {
+    if (!h || !n_fields) return fail(SIT_E_INVALID, "null argument");
+    *n_fields = (int32_t)h->fields.size();
+    if (!fields) return SIT_OK;
+    if (capacity < (int32_t)h->fields.size()) return fail(SIT_E_INVALID, "field array too small");
+    std::memcpy(fields, h->fields.data(), h->fields.size() * sizeof(SitField));
+    return SIT_OK;
+}
+
+static int grid_for(int64_t n, int block) { return (int)((n + block - 1) / block); }
+
+}  // extern "C"
+template <typename R>
+static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, cudaStream_t st) {
+    FleetIO<R> k;
+    std::memset(&k, 0, sizeof(k));
+    k.store = 1;
+    if (io) {
+        k.dist = static_cast<const R*>(io->dist); k.dist_steps = io->dist_steps; k.avoid = io->avoid; k.store = io->store; k.traj_steps = io->traj_steps;
+        k.traj = static_cast<R*>(io->traj); k.log27 = static_cast<R*>(io->log27); k.cmd = static_cast<R*>(io->cmd);
+        if (k.dist && !(k.dist_steps == 1 || k.dist_steps == K)) return fail(SIT_E_INVALID, "dist_steps must be 1 or K");
+        if (!(k.traj_steps == 0 || k.traj_steps == 1 || k.traj_steps == K)) return fail(SIT_E_INVALID, "traj_steps must be 0, 1 or K");
+    }
+    const ShipPtrs<R> g = ship_ptrs<R>(h, state);
+    const ShipP<R>& P = HostSel<R>::ship(h);
+    const int block = 256, grid = grid_for(h->n_ships, block);
+    if (k.log27) fleet_step_kernel<R, true><<<grid, block, 0, st>>>(P, g, K, k);
+    else fleet_step_kernel<R, false><<<grid, block, 0, st>>>(P, g, K, k);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+extern "C" {
+
+int sit_fleet_step_k(SitHandle h, void* state, int32_t K, const SitFleetIO* io, void* stream) {
+    if (!h || !state) return fail(SIT_E_INVALID, "null argument");
+    if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
+    if (h->cfg.kind != SIT_KIND_FLEET) return fail(SIT_E_KIND, "sit_fleet_step_k needs a SIT_KIND_FLEET handle");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    return h->cfg.precision == SIT_F64 ? fleet_step_t<double>(h, state, K, io, st) : fleet_step_t<float>(h, state, K, io, st);
+}
+
+static int ensure_scratch(SitHandle h, size_t total) {
+    if (h->scratch_bytes >= total) return SIT_OK;
+    if (h->d_scratch) cudaFree(h->d_scratch);
+    h->d_scratch = nullptr; h->scratch_bytes = 0;
+    CUDA_TRY(cudaMalloc(&h->d_scratch, total));
+    h->scratch_bytes = total;
+    return SIT_OK;
+}
+
+int sit_fleet_step_host(SitHandle h, void* state, int32_t K, const void* dist_h, int32_t avoid, void* pose_h,
+                        void* stream) {
+    if (!h || !state) return fail(SIT_E_INVALID, "null argument");
+    if (h->cfg.kind != SIT_KIND_FLEET) return fail(SIT_E_KIND, "sit_fleet_step_host needs a SIT_KIND_FLEET handle");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t S = (size_t)h->n_ships, rs = h->cfg.precision == SIT_F64 ? 8 : 4;
+    const size_t o_dist = 0, o_pose = align_up(4 * S * rs, 256), total = o_pose + align_up(SIT_N_TRAJ * S * rs, 256);
+    int rc = ensure_scratch(h, total);
+    if (rc) return rc;
+    char* d = static_cast<char*>(h->d_scratch);
+    if (dist_h) CUDA_TRY(cudaMemcpyAsync(d + o_dist, dist_h, 4 * S * rs, cudaMemcpyHostToDevice, st));
+    SitFleetIO io;
+    std::memset(&io, 0, sizeof(io));
+    io.dist = dist_h ? d + o_dist : nullptr; io.dist_steps = 1; io.avoid = avoid; io.store = 1;
+    io.traj = pose_h ? d + o_pose : nullptr; io.traj_steps = 1;
+    rc = sit_fleet_step_k(h, state, K, &io, stream);
+    if (rc) return rc;
+    if (pose_h) CUDA_TRY(cudaMemcpyAsync(pose_h, d + o_pose, SIT_N_TRAJ * S * rs, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return SIT_OK;
+}
+
+int sit_capture_init(SitHandle h, void* state, void* stream) {
+    if (!h || !state) return fail(SIT_E_INVALID, "null argument");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int block = 256, grid = grid_for(h->n_ships, block);
+    if (h->cfg.precision == SIT_F64)
+        capture_init_kernel<double><<<grid, block, 0, st>>>(ship_ptrs<double>(h, state), env_ptrs<double>(h, state),
+                                                            h->cfg.sampling_frequency, h->ships_per_env);
+    else
+        capture_init_kernel<float><<<grid, block, 0, st>>>(ship_ptrs<float>(h, state), env_ptrs<float>(h, state),
+                                                           h->cfg.sampling_frequency, h->ships_per_env);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+int sit_reset(SitHandle h, void* state, const uint8_t* mask, int32_t hard, void* stream) {
+    if (!h || !state) return fail(SIT_E_INVALID, "null argument");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int block = 256, grid = grid_for(h->n_ships, block);
+    if (h->cfg.precision == SIT_F64)
+        reset_kernel<double><<<grid, block, 0, st>>>(ship_ptrs<double>(h, state), env_ptrs<double>(h, state), mask, hard, h->ships_per_env);
+    else
+        reset_kernel<float><<<grid, block, 0, st>>>(ship_ptrs<float>(h, state), env_ptrs<float>(h, state), mask, hard, h->ships_per_env);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+}  // extern "C"
+template <typename R>
+static int env_init_step_t(SitHandle h, void* state, const uint8_t* mask, cudaStream_t st) {
+    const ShipPtrs<R> g = ship_ptrs<R>(h, state);
+    const EnvKArgs<R>& A = HostSel<R>::env(h);
+    const int block = 256, grid = grid_for(h->n_ships, block);
+    if (h->same_params) env_init_step_kernel<R, true><<<grid, block, 0, st>>>(A.P[0], A.P[1], g, mask);
+    else env_init_step_kernel<R, false><<<grid, block, 0, st>>>(A.P[0], A.P[1], g, mask);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+extern "C" {
+
+int sit_env_init_step(SitHandle h, void* state, const uint8_t* mask, void* stream) {
+    if (!h || !state) return fail(SIT_E_INVALID, "null argument");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_env_init_step needs a SIT_KIND_ENV handle");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    return h->cfg.precision == SIT_F64 ? env_init_step_t<double>(h, state, mask, st) : env_init_step_t<float>(h, state, mask, st);
+}
+
+}  // extern "C"
+template <typename R>
+static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaStream_t st) {
+    EnvIO<R> k;
+    std::memset(&k, 0, sizeof(k));
+    k.init = -1; k.rec_steps = 1; k.act_steps = 1;
+    if (io) {
+        k.action = static_cast<const R*>(io->action); k.sac_update = io->sac_update;
+        k.act_steps = io->act_steps; k.init = io->init; k.auto_reset = io->auto_reset; k.rec_steps = io->rec_steps;
+        k.obs = static_cast<R*>(io->obs); k.reward = static_cast<R*>(io->reward); k.done = io->done; k.status = io->status;
+        k.reward_sum = static_cast<R*>(io->reward_sum); k.done_any = io->done_any; k.stats = io->stats;
+        if (!(k.act_steps == 1 || k.act_steps == K)) return fail(SIT_E_INVALID, "act_steps must be 1 or K");
+        if (!(k.rec_steps == 1 || k.rec_steps == K)) return fail(SIT_E_INVALID, "rec_steps must be 1 or K");
+    }
+    const ShipPtrs<R> g = ship_ptrs<R>(h, state);
+    const EnvPtrs<R> ge = env_ptrs<R>(h, state);
+    const EnvKArgs<R>& A = HostSel<R>::env(h);
+    const int block = 128, grid = grid_for(h->n_ships, block);
+    if (h->same_params) env_step_kernel<R, true><<<grid, block, 0, st>>>(A, g, ge, K, k);
+    else env_step_kernel<R, false><<<grid, block, 0, st>>>(A, g, ge, K, k);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+extern "C" {
+
+int sit_env_step_k(SitHandle h, void* state, int32_t K, const SitEnvIO* io, void* stream) {
+    if (!h || !state) return fail(SIT_E_INVALID, "null argument");
+    if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_env_step_k needs a SIT_KIND_ENV handle");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    return h->cfg.precision == SIT_F64 ? env_step_t<double>(h, state, K, io, st) : env_step_t<float>(h, state, K, io, st);
+}
+
+int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h, const uint8_t* sac_update_h,
+                      int32_t init, void* obs_h, void* reward_h, uint8_t* done_h, int32_t* status_h, void* stream) {
+    if (!h || !state || !action_h) return fail(SIT_E_INVALID, "null argument");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_env_step_host needs a SIT_KIND_ENV handle");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t B = (size_t)h->n_envs, rs = h->cfg.precision == SIT_F64 ? 8 : 4;
+    // device scratch: action [2][B] | obs [10][B] | reward [B] | status [B] i32 | sac [B] u8 | done [B] u8
+    const size_t o_act = 0, o_obs = align_up(o_act + 2 * B * rs, 256), o_rew = align_up(o_obs + SIT_N_OBS * B * rs, 256),
+                 o_st = align_up(o_rew + B * rs, 256), o_sac = align_up(o_st + B * 4, 256), o_done = align_up(o_sac + B, 256),
+                 total = align_up(o_done + B, 256);
+    {
+        int rc0 = ensure_scratch(h, total);
+        if (rc0) return rc0;
+    }
+    char* d = static_cast<char*>(h->d_scratch);
+    CUDA_TRY(cudaMemcpyAsync(d + o_act, action_h, 2 * B * rs, cudaMemcpyHostToDevice, st));
+    if (sac_update_h) CUDA_TRY(cudaMemcpyAsync(d + o_sac, sac_update_h, B, cudaMemcpyHostToDevice, st));
+    SitEnvIO io;
+    std::memset(&io, 0, sizeof(io));
+    io.action = d + o_act; io.sac_update = sac_update_h ? reinterpret_cast<uint8_t*>(d + o_sac) : nullptr;
+    io.act_steps = 1; io.init = init; io.auto_reset = 0; io.rec_steps = 1;
+    io.obs = d + o_obs; io.reward = d + o_rew; io.done = reinterpret_cast<uint8_t*>(d + o_done);
+    io.status = reinterpret_cast<int32_t*>(d + o_st);
+    int rc = sit_env_step_k(h, state, K, &io, stream);
+    if (rc) return rc;
+    if (obs_h) CUDA_TRY(cudaMemcpyAsync(obs_h, d + o_obs, SIT_N_OBS * B * rs, cudaMemcpyDeviceToHost, st));
+    if (reward_h) CUDA_TRY(cudaMemcpyAsync(reward_h, d + o_rew, B * rs, cudaMemcpyDeviceToHost, st));
+    if (done_h) CUDA_TRY(cudaMemcpyAsync(done_h, d + o_done, B, cudaMemcpyDeviceToHost, st));
+    if (status_h) CUDA_TRY(cudaMemcpyAsync(status_h, d + o_st, B * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return SIT_OK;
+}
+
+int sit_measure_fma_peak(int device, int32_t precision, double* tflops, double* ms_out) {
+    if (!tflops) return fail(SIT_E_INVALID, "null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(SIT_E_NODEVICE, "no CUDA device"); }
+    CUDA_TRY(cudaSetDevice(device));
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    void* out = nullptr;
+    CUDA_TRY(cudaMalloc(&out, 64));
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    const int block = 256, grid = sms * 8, iters = precision == SIT_F64 ? 2000 : 4000;
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(e0, 0);
+        if (precision == SIT_F64) fma_peak_kernel<double><<<grid, block>>>(static_cast<double*>(out), iters, 1.0000001, 1e-9);
+        else fma_peak_kernel<float><<<grid, block>>>(static_cast<float*>(out), iters, 1.0000001f, 1e-9f);
+        cudaEventRecord(e1, 0);
+        CUDA_TRY(cudaEventSynchronize(e1));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0 && ms < best) best = ms;
+    }
+    CUDA_TRY(cudaGetLastError());
+    const double flops = 2.0 * 8 * 16 * (double)iters * block * (double)grid;
+    *tflops = flops / (best * 1e-3) / 1e12;
+    if (ms_out) *ms_out = best;
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+    return SIT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,163 @@
+"""GPU parity of kernel K2 (fused two-ship AST env step) through the C ABI against the golden
+fixtures frozen from the REAL reference's MultiShipRLEnv (tests/golden/env_*.npz) and against the CPU
+oracle.  done / status / stop flags bit-exact; observations, rewards and travelled distances within
+1e-9 (fp64)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import helpers as H
+import scenarios as sc
+
+pytestmark = pytest.mark.gpu
+TOL64 = 1e-9
+
+
+def _episodes(s):
+    eps = [("ep1", s["actions"], s["nsteps"])]
+    if "second_episode" in s:
+        eps.append(("ep2", s["second_episode"]["actions"], s["second_episode"]["nsteps"]))
+    return eps
+
+
+@pytest.mark.parametrize("name", list(sc.ENV_SCENARIOS))
+def test_fp64_env_matches_reference_golden_per_step(name):
+    """The reference's own call pattern: reset(), init_step(), then one step() call per step."""
+    import gpu_helpers as G
+    s = sc.ENV_SCENARIOS[name]
+    g = H.golden("env_" + name)
+    env = G.make_env(s, n_envs=2, precision="fp64")
+    for i, (tag, actions, nsteps) in enumerate(_episodes(s)):
+        state0 = env.reset()
+        assert state0.dtype == torch.float32 and tuple(state0.shape) == (2, 10)
+        assert np.allclose(state0[0].cpu().numpy(), g["reset_state" if i == 0 else "reset_state2"], rtol=1e-6)
+        env.init_step()
+        out = G.run_env_episode(env, actions, nsteps, per_step=True)
+        assert np.array_equal(out["done"][:, 0], g[tag + "_done"]), "done must be bit-exact"
+        assert np.array_equal(out["status"][:, 0], g[tag + "_status"]), "status bits must be bit-exact"
+        assert np.array_equal(out["stop"][:, :, 0], g[tag + "_stop"])
+        assert np.array_equal(out["status"][:, 0], out["status"][:, 1])
+        assert H.rel_err(out["obs"][:, :, 0], g[tag + "_obs"], 1e-3).max() <= TOL64
+        assert H.rel_err(out["reward"][:, 0], g[tag + "_reward"], 1.0).max() <= TOL64
+        assert H.rel_err(out["dist"][:, :, 0], g[tag + "_dist"], 1.0).max() <= TOL64
+
+
+@pytest.mark.parametrize("name", ["default", "multi_waypoint", "endpoints", "ship_collision"])
+def test_fp64_env_one_launch_equals_per_step(name):
+    """K steps fused in ONE launch (per-step action stream) == the same episode stepped call by call."""
+    import gpu_helpers as G
+    s = sc.ENV_SCENARIOS[name]
+    g = H.golden("env_" + name)
+    env = G.make_env(s, n_envs=33, precision="fp64")   # odd size: exercises the partial last warp
+    env.reset(); env.init_step()
+    out = G.run_env_episode(env, s["actions"], s["nsteps"], per_step=False)
+    assert np.array_equal(out["done"][:, 0], g["ep1_done"]) and np.array_equal(out["done"][:, 32], g["ep1_done"])
+    assert np.array_equal(out["status"][:, 32], g["ep1_status"])
+    assert H.rel_err(out["obs"][:, :, 32], g["ep1_obs"], 1e-3).max() <= TOL64
+    assert H.rel_err(out["reward"][:, 32], g["ep1_reward"], 1.0).max() <= TOL64
+    stats = env.stats.cpu().numpy()
+    assert stats[13] == 33 * s["nsteps"], "env-step counter (warp-reduced) must equal n_envs * steps"
+    assert stats[12] == 33 * int(g["ep1_done"].sum())
+    for b in range(12):
+        assert stats[b] == 33 * int(((g["ep1_status"] >> b) & 1).sum()), f"status bit {b} count"
+
+
+@pytest.mark.parametrize("name", ["default", "ship_collision", "test_terrain", "blackout_pto"])
+def test_fp32_env_decisions_exact_and_obs_close(name):
+    import gpu_helpers as G
+    s = sc.ENV_SCENARIOS[name]
+    g = H.golden("env_" + name)
+    env = G.make_env(s, n_envs=4, precision="fp32")
+    env.reset(); env.init_step()
+    out = G.run_env_episode(env, s["actions"], s["nsteps"], per_step=False)
+    assert np.array_equal(out["done"][:, 0], g["ep1_done"]), "termination decisions must be bit-exact in fp32"
+    assert np.array_equal(out["status"][:, 0], g["ep1_status"])
+    n = min(1000, s["nsteps"])
+    err = H.rel_err(out["obs"][:n, [0, 1, 2, 6, 7, 8], 0], g["ep1_obs"][:n][:, [0, 1, 2, 6, 7, 8]], 1.0)
+    assert err.max() <= 1e-4, f"fp32 pose rel err {err.max():.3e}"
+
+
+def test_random_envs_match_oracle():
+    """Randomised two-ship envs (per-env set points, headings and intermediate waypoints, some of them
+    inside islands / outside the map) against the CPU oracle: decisions exact, values within 1e-9."""
+    import gpu_helpers as G
+    from oracle import cport
+    B, T = 256, 700
+    s = sc.ENV_SCENARIOS["default"]
+    rng = np.random.default_rng(11)
+    u_t, u_o = rng.uniform(5, 9, B), rng.uniform(5, 9, B)
+    dpsi = np.deg2rad(rng.uniform(-20, 20, (2, B)))
+    act = np.stack([rng.uniform(6000, 10300, B), rng.uniform(5500, 9800, B)], axis=1)   # (north, east)
+    act2 = act + rng.uniform(-900, -300, (B, 2))
+    env = G.make_env(s, n_envs=B, precision="fp64")
+    env.ship[0].u_sp.copy_(torch.as_tensor(u_t)); env.ship[1].u_sp.copy_(torch.as_tensor(u_o))
+    env.ship[0].psi.copy_(torch.as_tensor(s["test_psi0"] + dpsi[0])); env.ship[1].psi.copy_(torch.as_tensor(s["obs_psi0"] + dpsi[1]))
+    env.capture_init()
+    env.reset(); env.init_step()
+    A = torch.zeros((T, B, 2), dtype=torch.float64, device="cuda"); S = torch.zeros((T, B), dtype=torch.uint8, device="cuda")
+    A[:200] = torch.as_tensor(act, device="cuda"); A[200:] = torch.as_tensor(act2, device="cuda"); S[0] = 1; S[200] = 1
+    out = env.step_k(T, A, S, init=True, record_all=True)
+    # oracle
+    L = cport.lib()
+    cfg = H.default_cfg()
+    p = cport.make_params(cfg); m = cport.make_map(sc.DEFAULT_MAP)
+    envs = (cport.OrcEnv * B)()
+    for i in range(B):
+        cport.init_env(envs[i], cfg, s["test_route"], s["obs_route"], s["test_psi0"] + dpsi[0, i], s["obs_psi0"] + dpsi[1, i],
+                       u_t[i], u_o[i])
+        L.orc_env_reset(C.byref(envs[i])); L.orc_env_init_step(C.byref(p), C.byref(p), C.byref(envs[i]))
+    a_h = np.ascontiguousarray(A.cpu().numpy().transpose(0, 2, 1)); s_h = np.ascontiguousarray(S.cpu().numpy())
+    obs = np.zeros((T, 10, B)); rew = np.zeros((T, B)); done = np.zeros((T, B), np.uint8); st = np.zeros((T, B), np.int32)
+    L.orc_run_envs(C.byref(p), C.byref(p), C.byref(m), envs, B, T, a_h.ctypes.data, s_h.ctypes.data, 1,
+                   obs.ctypes.data, rew.ctypes.data, done.ctypes.data, st.ctypes.data, 0)
+    assert np.array_equal(out["done"].cpu().numpy(), done), "done must be bit-exact"
+    assert np.array_equal(out["status"].cpu().numpy(), st), "status must be bit-exact"
+    assert H.rel_err(out["obs"].cpu().numpy(), obs, 1e-3).max() <= TOL64
+    assert H.rel_err(out["reward"].cpu().numpy(), rew, 1.0).max() <= TOL64
+    seen = np.bitwise_or.reduce(st.ravel())
+    assert bin(int(seen)).count("1") >= 3, f"random case should reach several terminal kinds, saw 0x{int(seen):x}"
+
+
+def test_auto_reset_equals_host_reset():
+    """In-kernel reset() + init_step() after a done step == host-side reset()/init_step() between launches."""
+    import gpu_helpers as G
+    s = sc.ENV_SCENARIOS["iw_in_terrain"]     # terminal at the first step -> many resets
+    a = G.make_env(s, n_envs=8, precision="fp64"); b = G.make_env(s, n_envs=8, precision="fp64")
+    for e in (a, b):
+        e.reset(); e.init_step()
+    act = (7000.0, 6500.0)
+    K = 12
+    oa = a.step_k(K, act, True, init=None, auto_reset=True, record_all=True)
+    rew_b, done_b = [], []
+    for t in range(K):
+        ns, r, d, st = b.step(act, True, True)
+        rew_b.append(r.clone()); done_b.append(d.clone())
+        if d.any():
+            b.reset(mask=d); b.init_step(mask=d)
+    assert torch.equal(oa["done"].bool(), torch.stack(done_b)) and oa["done"].all()
+    assert torch.allclose(oa["reward"], torch.stack(rew_b), rtol=1e-12, atol=0)
+    for k in ("north", "psi", "omega", "ei_speed", "fuel"):
+        assert torch.equal(a.f[k], b.f[k]), k
+
+
+def test_status_strings_and_host_step():
+    import gpu_helpers as G
+    import sac_maritime_ast_b200 as sit
+    s = sc.ENV_SCENARIOS["iw_outside_map"]
+    env = G.make_env(s, n_envs=5, precision="fp64")
+    env.reset(); env.init_step()
+    act_h = torch.tensor([[10500.0] * 5, [8600.0] * 5], dtype=torch.float64).pin_memory()
+    sac_h = torch.ones(5, dtype=torch.uint8).pin_memory()
+    out_h = dict(obs=torch.empty((10, 5), dtype=torch.float64).pin_memory(), reward=torch.empty(5, dtype=torch.float64).pin_memory(),
+                 done=torch.empty(5, dtype=torch.uint8).pin_memory(), status=torch.empty(5, dtype=torch.int32).pin_memory())
+    env.step_host(1, act_h, sac_h, True, out_h)
+    g = H.golden("env_iw_outside_map")
+    assert out_h["done"].tolist() == [int(g["ep1_done"][0])] * 5
+    assert out_h["status"].tolist() == [int(g["ep1_status"][0])] * 5
+    assert H.rel_err(out_h["obs"][:, 0].numpy(), g["ep1_obs"][0], 1e-3).max() <= TOL64
+    txt = sit.MultiShipRLEnv.decode_status(out_h["status"][0].item())
+    assert "|Obstacle ship IW sampled in terminal state|" in txt and "|Test ship not in terminal state|" in txt
+    with pytest.raises(TypeError):
+        env.step(None, True, True)
