@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: ship env-steps/s (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (CUDA kernels via libshipsim.so)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port on all host cores
+
+Workload (BASELINE config 3): per GPU 1,048,576 fp32 ships, random routes (2..8 waypoints),
+per-ship set points, current / wind disturbances re-drawn every launch; one bench "step" = ONE launch of
+the fused ship-step kernel advancing every ship K_INNER = 256 simulator steps.  Ships are sharded over the
+GPUs with no data-path collective (weak scaling: the per-GPU fleet is fixed); NCCL only gathers the
+rollout statistics after the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+SEED = 25450            # main_ast.py:61
+F_SHIP = 250.0          # algorithmic FLOP per ship-step
+TRAJ_BYTES_F64 = 64.0   # algorithmic bytes written per ship-step in trajectory mode: 8 channels x 8 B
+METRIC = "ship env-steps/sec"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ships-per-gpu", type=int, default=1 << 20)
+    ap.add_argument("--k-inner", type=int, default=256)
+    ap.add_argument("--max-wp", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the e2e / HBM trajectory / peak legs (profiling runs)")
+    return ap.parse_args()
+
+
+# ---- synthetic workload (shared by both arms: generated with numpy so the CPU arm needs no GPU) ---------------
+def make_routes(n, max_wp, rng):
+    """Random routes: n_wp ~ U{2..max_wp}, start U([500, 9500]^2), segment length U(800, 3000) m,
+    turn U(-60, 60) deg.  float32-representable values (the fp32 kernel and the fp64 oracle see the same)."""
+    n_wp = rng.integers(2, max_wp + 1, n).astype(np.int32)
+    wp_n = np.zeros((max_wp, n), np.float32); wp_e = np.zeros((max_wp, n), np.float32)
+    wp_n[0] = rng.uniform(500, 9500, n); wp_e[0] = rng.uniform(500, 9500, n)
+    heading = rng.uniform(-np.pi, np.pi, n)
+    psi0 = heading.copy()
+    for j in range(1, max_wp):
+        seg = rng.uniform(800, 3000, n)
+        wp_n[j] = wp_n[j - 1] + seg * np.cos(heading); wp_e[j] = wp_e[j - 1] + seg * np.sin(heading)
+        heading = heading + np.deg2rad(rng.uniform(-60, 60, n))
+    for j in range(2, max_wp):      # unused slots repeat the last waypoint (never read: n_wp bounds the index)
+        unused = n_wp <= j
+        wp_n[j, unused] = wp_n[j - 1, unused]; wp_e[j, unused] = wp_e[j - 1, unused]
+    # set points above the ~9.1 m/s the default ship can reach with a 2.8 m/s following current: the reference's
+    # unsaturated throttle PI (controllers.py:138-143) then never unwinds below zero, which would drive the shaft
+    # through the omega = -0.1 singularity of ship_engine.py:374 (the float64 reference blows up there too)
+    u_sp = rng.uniform(9.5, 12.0, n).astype(np.float32)
+    return n_wp, wp_n, wp_e, psi0.astype(np.float32), u_sp
+
+
+def make_dist(n, rng):
+    return np.stack([rng.uniform(-2, 2, n), rng.uniform(-2, 2, n), rng.uniform(0, 15, n),
+                     rng.uniform(-np.pi, np.pi, n)]).astype(np.float32)
+
+
+# ---- CPU arm: the oracle port (plain C float64, OpenMP) on the host cores ----------------------------------------
+def cpu_ship_steps_per_s(n, k_inner, steps, warmup, max_wp, seed, threads=0):
+    """Times orc_run_ships on a bounded sample (n ships) of the same workload; returns (ship-steps/s, cores)."""
+    import helpers as H
+    from oracle import cport
+    L = cport.lib()
+    rng = np.random.default_rng(seed)
+    n_wp, wp_n, wp_e, psi0, u_sp = make_routes(n, max_wp, rng)
+    cfg = H.default_cfg()
+    p = cport.make_params(cfg)
+    ships = (cport.OrcShip * n)()
+    proto = cport.OrcShip()
+    cport.init_ship(proto, cfg, [(0, 0), (1, 1)], 0.0, 8.0)
+    arr = np.ctypeslib.as_array(ships)
+    arr[:] = np.ctypeslib.as_array((cport.OrcShip * 1)(proto))[0]
+    arr["north"], arr["east"], arr["psi"], arr["u_sp"] = wp_n[0], wp_e[0], psi0, u_sp
+    arr["wp_n"][:, :max_wp] = wp_n.T; arr["wp_e"][:, :max_wp] = wp_e.T
+    arr["n_wp"] = n_wp
+    cores = L.orc_max_threads() if threads <= 0 else threads
+    times = []
+    for it in range(warmup + steps):
+        d = np.ascontiguousarray(make_dist(n, rng).astype(np.float64))
+        arr["vc_n"], arr["vc_e"], arr["wind_speed"], arr["wind_dir"] = d[0], d[1], d[2], d[3]
+        t0 = time.perf_counter()
+        L.orc_run_ships(C.byref(p), ships, n, k_inner, 0, None, None, threads)
+        t1 = time.perf_counter()
+        if it >= warmup:
+            times.append(t1 - t0)
+    total = float(np.sum(times))
+    return n * k_inner * steps / total, cores, total
+
+
+def calibrate_cpu_sample(k_inner, max_wp, budget_s):
+    """Pick a ship count so that one CPU step takes about budget_s / 8 seconds."""
+    rate, cores, _ = cpu_ship_steps_per_s(4096, k_inner, 1, 1, max_wp, 1)
+    n = int(rate * (budget_s / 8.0) / k_inner)
+    return max(1024, min(1 << 20, (n // 1024) * 1024))
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    n = calibrate_cpu_sample(args.k_inner, args.max_wp, budget_s=40.0)
+    rate, cores, total = cpu_ship_steps_per_s(n, args.k_inner, args.steps, min(args.warmup, 2), args.max_wp, SEED)
+    sample = f"{n} ships x {args.k_inner} steps per bench step (bounded sample of the {args.ships_per_gpu}-ship fleet), float64 C port of the reference step, OpenMP"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": "ship-steps/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": rate, "unit": "ship-steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "ship-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "the reference is pure Python and cannot travel to the GPU box; this arm times the plain-C float64 "
+                "restatement (oracle/ship_oracle.c), which is ~10^3x faster per core than the reference's own Python",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args):
+    return {"workload": "BASELINE config 3: batched ship envs fp32, random routes (2..%d waypoints), current/wind "
+                        "disturbances re-drawn every %d steps, sharded over GPUs" % (args.max_wp, args.k_inner),
+            "ships_per_gpu": args.ships_per_gpu, "k_inner_steps_per_launch": args.k_inner, "max_wp": args.max_wp,
+            "sharding": "ships split contiguously over ranks, no step-path collective",
+            "l2": "state (~330 MB per GPU at 1M ships) and disturbance ring larger than the 126 MB L2"}
+
+
+# ---- clocks during the timed region (B200_PROFILING.md recipe) -------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                clk, cmax = float(parts[0]), float(parts[1])
+            except ValueError:
+                continue
+            mx = max(mx, cmax)
+            if t0 <= ts <= t1:
+                sm.append(clk)
+                for nm, v in zip(names, parts[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import sac_maritime_ast_b200 as sit
+    from sac_maritime_ast_b200 import _lib
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device and no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    S, KI = args.ships_per_gpu, args.k_inner
+    rng = np.random.default_rng(SEED + 1000 * rank)       # global ship ids differ per rank: independent shards
+    n_wp, wp_n, wp_e, psi0, u_sp = make_routes(S, args.max_wp, rng)
+    sm, tc, ap = sit.default_ship([(0, 0), (1000, 1000)], 0.0)
+    fleet = sit.ShipFleet(sm, tc, ap, 8.0, n_ships=S, device=dev, precision="fp32", max_wp=args.max_wp)
+    fleet.set_routes(torch.from_numpy(wp_n).to(dev), torch.from_numpy(wp_e).to(dev), torch.from_numpy(n_wp).to(dev))
+    fleet.f["north"].copy_(torch.from_numpy(wp_n[0].astype(np.float64))); fleet.f["east"].copy_(torch.from_numpy(wp_e[0].astype(np.float64)))
+    fleet.f["psi"].copy_(torch.from_numpy(psi0)); fleet.f["u_sp"].copy_(torch.from_numpy(u_sp))
+    fleet.capture_init()
+    n_ring = 8                                             # 8 x 16 MB of disturbances, resident in HBM
+    ring_h = [torch.from_numpy(make_dist(S, rng)).pin_memory() for _ in range(n_ring)]
+    ring_d = [t.to(dev) for t in ring_h]
+    pose_h = torch.empty((8, S), dtype=torch.float32).pin_memory()
+    snapshot = fleet.state_dict()
+
+    # ---- device-resident timed region -----------------------------------------------------------------------------
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    t_load0 = time.perf_counter()
+    for w in range(args.warmup):
+        fleet.step(KI, dist=ring_d[w % n_ring])
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = fleet.launches
+    t_wall0 = time.perf_counter()
+    ev0.record()
+    for k in range(args.steps):
+        fleet.step(KI, dist=ring_d[(args.warmup + k) % n_ring])
+    ev1.record()
+    barrier()
+    t_wall1 = time.perf_counter()
+    launches = fleet.launches - l0
+    ms = ev0.elapsed_time(ev1)
+    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms_max = float(tmax.item())
+    finite = bool(torch.isfinite(fleet.f["north"]).all() and torch.isfinite(fleet.f["u"]).all())
+    value = world * S * KI * args.steps / (ms_max * 1e-3)
+
+    line = {"metric": METRIC, "value": value, "unit": "ship-steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
+            "gpu_launches": launches, "state_finite": finite}
+
+    # ---- end-to-end through the C-ABI host-buffer entry point (H2D + kernel + D2H every step) -----------------------
+    if not args.no_extras:
+        fleet.load_state_dict(snapshot)
+        for w in range(min(args.warmup, 3)):
+            fleet.step_host(KI, ring_h[w % n_ring], pose_h)
+        barrier()
+        t0 = time.perf_counter()
+        ev0.record()
+        for k in range(args.steps):
+            fleet.step_host(KI, ring_h[(args.warmup + k) % n_ring], pose_h)
+        ev1.record()
+        barrier()
+        e2e_ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+        line["e2e"] = {"value": world * S * KI * args.steps / (float(e2e_ms.item()) * 1e-3), "unit": "ship-steps/s",
+                       "h2d_bytes_per_step": int(ring_h[0].numel() * 4), "d2h_bytes_per_step": int(pose_h.numel() * 4),
+                       "api": "ShipFleet.step_host -> sit_fleet_step_host (pinned host buffers)"}
+    t_load1 = time.perf_counter()
+    clocks.stop()
+    # sampled over warm-up + timed region + the e2e loop (the same kernel under load throughout); the timed
+    # region alone can be shorter than one nvidia-smi sampling period
+    line["clocks"] = clocks.summary(t_load0, t_load1)
+    line["clocks"]["window_s"] = t_load1 - t_load0
+    line["clocks"]["timed_region_s"] = t_wall1 - t_wall0
+
+    # ---- rollout statistics gathered over NCCL (outside the step path) ------------------------------------------------
+    stats = torch.stack([fleet.f["steps"].sum().double(), fleet.f["k"].double().mean(), fleet.f["u"].double().mean()])
+    if world > 1:
+        gathered = [torch.empty_like(stats) for _ in range(world)]
+        dist.all_gather(gathered, stats)
+        stats = torch.stack(gathered).mean(0)
+    line["rollout_stats"] = {"mean_waypoint_index": float(stats[1]), "mean_speed_mps": float(stats[2])}
+
+    if rank == 0 and not args.no_extras:
+        # ---- roofline of the dominant kernel (fleet_step_kernel<float>): CUDA-core FP32 issue -----------------------
+        L = _lib.lib()
+        tf, pms = C.c_double(), C.c_double()
+        _lib.check(L.sit_measure_fma_peak(local_rank, _lib.F32, C.byref(tf), C.byref(pms)))
+        per_gpu = value / world
+        ach = per_gpu * F_SHIP / 1e12
+        line["roofline"] = {"bound": "fp32", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value,
+                            "traffic": None,
+                            "note": "CUDA-core FP32 pipe bound (no tensor-core or HBM roofline applies to the K-step kernel): "
+                                    "achieved = ship-steps/s/GPU x 250 algorithmic FLOP; peak = FFMA chain measured live on this GPU "
+                                    "(sit_measure_fma_peak); kernel time = ms_per_step (one launch per step, CUDA events)"}
+        # ---- trajectory write-out mode (BASELINE config 2 style, fp64): HBM-write bound ------------------------------
+        line["roofline_hbm"] = traj_roofline(sit, dev)
+        tf64 = C.c_double()
+        _lib.check(L.sit_measure_fma_peak(local_rank, _lib.F64, C.byref(tf64), None))
+        line["fp64_fma_peak_tflops"] = tf64.value
+    if rank == 0 and not args.no_cpu_baseline and not args.no_extras:
+        n = calibrate_cpu_sample(KI, args.max_wp, budget_s=16.0)
+        rate, cores, total = cpu_ship_steps_per_s(n, KI, 4, 1, args.max_wp, SEED)
+        line["cpu_baseline"] = {"value": rate, "unit": "ship-steps/s", "cores": cores, "kind": "port",
+                                "sample": f"{n} ships x {KI} steps x 4 (oracle/ship_oracle.c float64, OpenMP, {total:.1f} s)"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def traj_roofline(sit, dev):
+    """fp64 fleet with full trajectory write-out [K][8][S] (BASELINE config 2 layout): achieved HBM GB/s."""
+    import torch
+    S, K = 1 << 19, 32
+    sm, tc, ap = sit.default_ship([(0, 0), (3000, 3000), (6000, 9000)], np.pi / 4)
+    fl = sit.ShipFleet(sm, tc, ap, 8.0, n_ships=S, device=dev, precision="fp64")
+    fl.f["u_sp"].copy_(4 + 5 * torch.rand(S, device=dev, dtype=torch.float64))
+    out = {}
+    for _ in range(3):
+        fl.step(K, traj=True, out=out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    e0.record()
+    for _ in range(reps):
+        fl.step(K, traj=True, out=out)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    gbs = TRAJ_BYTES_F64 * S * K / (ms * 1e-3) / 1e9
+    peak = 6551.0
+    src = "fallback"
+    try:
+        peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]; src = "MEASURED_PEAKS.json"
+    except Exception:
+        pass
+    return {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+            "kernel": "fleet_step_kernel<double> with trajectory write-out", "ships": S, "k": K, "ms_per_launch": ms,
+            "ship_steps_per_s": S * K / (ms * 1e-3), "peak_source": src,
+            "note": "algorithmic bytes = 64 B written per ship-step (8 fp64 channels); output 1 GiB per launch > L2"}
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

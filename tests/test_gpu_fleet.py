@@ -18,6 +18,7 @@ pytestmark = pytest.mark.gpu
 TOL64 = 1e-9
 TOL32 = 1e-4
 TRAJ_FLOORS = np.array([1.0, 1.0, 1.0, 1.0, 1e-3, 1e-3, 1.0])
+POSE_FLOORS = np.array([100.0, 100.0, 1.0, 1.0])   # N, E [m], psi [rad], u [m/s]
 
 
 @pytest.mark.parametrize("name", list(sc.SHIP_SCENARIOS))
@@ -55,11 +56,12 @@ def test_fp32_within_tolerance_and_decisions_exact(name):
     assert np.array_equal(traj[:, 7, 0].astype(np.int8), g["k"]), "waypoint index must be bit-exact at every step"
     rows = g["rows"]
     upto = rows <= 1000
-    # pose (N, E, psi) and speed (u): relative error with the floors of SURVEY 7.3-H2
-    err = H.rel_err(traj[rows][upto][:, [0, 1, 2, 3], 0], g["state"][upto][:, [0, 1, 2, 3]], 1.0)
+    # pose (N, E, psi) and speed (u): relative error; a coordinate that crosses zero is measured against one
+    # ship length (~100 m) instead of against itself (SURVEY 7.3-H2 floors)
+    err = H.rel_err(traj[rows][upto][:, [0, 1, 2, 3], 0], g["state"][upto][:, [0, 1, 2, 3]], POSE_FLOORS)
     assert err.max() <= TOL32, f"fp32 pose/speed rel err {err.max():.3e} within the first 1000 steps"
-    err_all = H.rel_err(traj[rows][:, [0, 1, 2, 3], 0], g["state"][:, [0, 1, 2, 3]], 1.0)
-    assert err_all.max() <= 10 * TOL32, f"fp32 pose/speed rel err over the whole run {err_all.max():.3e}"
+    err_all = H.rel_err(traj[rows][:, [0, 1, 2, 3], 0], g["state"][:, [0, 1, 2, 3]], POSE_FLOORS)
+    assert err_all.max() <= TOL32, f"fp32 pose/speed rel err over the whole run {err_all.max():.3e}"
 
 
 def _random_fleet_case(n, seed, precision):
@@ -109,7 +111,7 @@ def test_fp32_random_fleet_close_to_oracle():
     cport.lib().orc_run_ships(C.byref(p), ships, n, T, 0, None, ref.ctypes.data, 0)
     got = fleet.step(T, traj=True)["traj"].cpu().numpy().astype(np.float64)
     flips = (got[:, 7] != ref[:, 7]).any(axis=0)
-    err = H.rel_err(got[-1, :4], ref[-1, :4], 1.0)
+    err = H.rel_err(got[-1, :4], ref[-1, :4], POSE_FLOORS[:, None])
     assert err[:, ~flips].max() <= TOL32, f"fp32 rel err after 1000 steps {err.max():.3e}"
     # the switch happens on a ~3 m/step approach; fp32 may move it by one step for a few ships in 10^3
     assert flips.mean() <= 0.01, f"waypoint-switch flips in {flips.sum()} of {n} ships"
