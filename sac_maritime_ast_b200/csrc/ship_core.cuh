@@ -23,23 +23,56 @@
 namespace sit {
 
 // ---- math wrappers ---------------------------------------------------------------------------
+// double: IEEE-rounded library calls (the 1e-9 parity path).  float: branch-free forms with <= 2 ulp error
+// (MUFU approximations, Cody-Waite sin/cos) -- no slow-path calls, so ptxas keeps the uniform parameters in
+// uniform registers across the K-step loop.
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float rsqrt_approx(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float sqrt_approx(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
 __device__ __forceinline__ void sincos_(double x, double& s, double& c) { sincos(x, &s, &c); }
-__device__ __forceinline__ void sincos_(float x, float& s, float& c) { sincosf(x, &s, &c); }
+__device__ __forceinline__ void sincos_(float x, float& s, float& c) {
+    // |x| stays far below 1e5 (the heading is unwrapped but bounded by the turns of a route): three-constant
+    // Cody-Waite reduction by pi/2, then the cephes minimax polynomials on [-pi/4, pi/4]
+    const float t = fmaf(x, 0.636619772f, 12582912.0f);
+    const int q = __float_as_int(t);
+    const float j = t - 12582912.0f;
+    float r = fmaf(j, -1.57079601e+00f, x);
+    r = fmaf(j, -3.13916473e-07f, r);
+    r = fmaf(j, -5.39030253e-15f, r);
+    const float r2 = r * r;
+    float ps = fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f);
+    ps = fmaf(ps, r2, -1.6666654611e-1f);
+    ps = fmaf(ps * r2, r, r);
+    float pc = fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
+    pc = fmaf(pc, r2, 4.166664568298827e-2f);
+    pc = fmaf(pc, r2, -0.5f);
+    pc = fmaf(pc, r2, 1.0f);
+    const bool swap = q & 1;
+    const float ss = swap ? pc : ps, cc = swap ? ps : pc;
+    s = (q & 2) ? -ss : ss;
+    c = ((q + 1) & 2) ? -cc : cc;
+}
 __device__ __forceinline__ double atan_(double x) { return atan(x); }
 __device__ __forceinline__ float atan_(float x) { return atanf(x); }
 __device__ __forceinline__ double atan2_(double y, double x) { return atan2(y, x); }
 __device__ __forceinline__ float atan2_(float y, float x) { return atan2f(y, x); }
 __device__ __forceinline__ double sqrt_(double x) { return sqrt(x); }
-__device__ __forceinline__ float sqrt_(float x) { return sqrtf(x); }
+__device__ __forceinline__ float sqrt_(float x) { return sqrt_approx(x); }
 __device__ __forceinline__ double abs_(double x) { return fabs(x); }
 __device__ __forceinline__ float abs_(float x) { return fabsf(x); }
 __device__ __forceinline__ double min_(double a, double b) { return fmin(a, b); }
 __device__ __forceinline__ float min_(float a, float b) { return fminf(a, b); }
 __device__ __forceinline__ double max_(double a, double b) { return fmax(a, b); }
 __device__ __forceinline__ float max_(float a, float b) { return fmaxf(a, b); }
-// e / sqrt(l2 - e*e): one MUFU.RSQ + refinement in float, exact sqrt + div in double
+// e / sqrt(x): one MUFU.RSQ in float, exact sqrt + div in double
 __device__ __forceinline__ double over_sqrt_(double e, double x) { return e / sqrt(x); }
-__device__ __forceinline__ float over_sqrt_(float e, float x) { return e * rsqrtf(x); }
+__device__ __forceinline__ float over_sqrt_(float e, float x) { return e * rsqrt_approx(x); }
+__device__ __forceinline__ double rcp_(double x) { return 1.0 / x; }
+__device__ __forceinline__ float rcp_(float x) { const float r = rcp_approx(x); return fmaf(fmaf(-x, r, 1.0f), r, r); }
+// load / 1000 (ship_model.py:661): exact division on the float64 parity path, reciprocal multiply in float
+__device__ __forceinline__ double kilo_(double x) { return x / 1000.0; }
+__device__ __forceinline__ float kilo_(float x) { return x * 0.001f; }
 
 // ---- uniform parameters (kernel arguments -> constant bank, one copy per role) -----------------
 template <typename R>
@@ -95,7 +128,8 @@ struct Ship {
     R ei_s, ei_w, ei_h, e_prev, e_ct, e_int;       // controllers.py:49,77-78; LOS_guidance.py:59-60
     R f_me, f_el, f_tot;                           // ship_engine.py:336-338
     R u_sp, vcn, vce, wcb, wsb;                    // set point; current; wind as W cos b, W sin b
-    R pN, pE, cN, cE, alpha, sa, ca;               // cached route segment k-1 -> k
+    double pN, pE, cN, cE;                         // cached route segment k-1 -> k (widened once per switch)
+    R alpha, sa, ca;                               // its angle, sin, cos
     int32_t k, n_wp, mode, steps;
 };
 
@@ -107,7 +141,7 @@ __device__ __forceinline__ void load_segment(Ship<R>& s, const ShipPtrs<R>& g, i
     s.pE = g.wp_e[(int64_t)(s.k - 1) * S + i];
     s.cN = g.wp_n[(int64_t)s.k * S + i];
     s.cE = g.wp_e[(int64_t)s.k * S + i];
-    s.alpha = atan2_(s.cE - s.pE, s.cN - s.pN);
+    s.alpha = atan2_((R)(s.cE - s.pE), (R)(s.cN - s.pN));
     sincos_(s.alpha, s.sa, s.ca);
 }
 
@@ -151,12 +185,12 @@ struct StepOut {
 
 // One ship-step.  avoid: MSRL_env_ex.py:240-249.  store: store_simulation_data + next_time
 // (false reproduces init_step, MSRL_env_ex.py:188-215).  lg: 27 logged channels or nullptr.
-template <typename R, bool LOG>
+template <typename R, bool LOG, bool SINGLE_MODE = false>
 __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const ShipPtrs<R>& g, int64_t i,
                                           bool avoid, bool store, StepOut<R>& o, R* lg) {
     // ---- LOS_guidance.py:88-103 next_wpt: squared distance, <=, end-of-route hold --------------
     {
-        const double dn = (double)s.cN - s.N, de = (double)s.cE - s.E;
+        const double dn = s.cN - s.N, de = s.cE - s.E;
         const double d2 = __dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de));
         if (d2 <= P.ra2 && s.n_wp > s.k + 1) {
             s.k += 1;
@@ -164,7 +198,7 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
         }
     }
     // ---- LOS_guidance.py:105-121 los_guidance ----------------------------------------------------
-    const R en = (R)(s.N - (double)s.pN), ee = (R)(s.E - (double)s.pE);
+    const R en = (R)(s.N - s.pN), ee = (R)(s.E - s.pE);
     R e = ee * s.ca - en * s.sa;
     s.e_ct = abs_(e);
     if (e * e >= P.look2) e = P.sat_e;  // sign lost on purpose (0.99 * lookahead)
@@ -194,9 +228,11 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
     }
     o.rud = rud; o.thr = thr;
 
-    const ModeP<R>& M = P.mode[s.mode];
+    // the reference's default MachineryModes holds ONE mode (main_ast.py:159-161): its constants are then
+    // uniform operands; with several modes the per-ship index makes them per-lane constant loads
+    const ModeP<R>& M = SINGLE_MODE ? P.mode[0] : P.mode[s.mode];
     const R om = s.om;
-    const R inv_om = (R)1 / (om + (R)0.1);
+    const R inv_om = rcp_(om + (R)0.1);
     const R tq_me = min_(thr * M.avail_me * inv_om, M.cap_tq_me);   // ship_engine.py:368-375
     const R tq_hsg = min_(thr * M.avail_el * inv_om, M.cap_tq_el);  // :377-384
     const R thrust_w = om * abs_(om);                               // :363-366 (pre-update omega)
@@ -220,18 +256,18 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
         s.f_el += rate_el * P.dt;
         s.f_tot += (rate_me + rate_el) * P.dt;
         o.rpm = om * P.rpm_per_rads;
-        o.power_me_kw = load_me / (R)1000;
+        o.power_me_kw = kilo_(load_me);
         o.avail_me_kw = M.me_cap_kw;
         if (LOG && lg) {
             lg[0] = (R)s.steps * P.dt;          lg[1] = (R)s.N;                 lg[2] = (R)s.E;
             lg[3] = s.psi * P.rad2deg;          lg[4] = rud * P.rad2deg;        lg[5] = s.u;
             lg[6] = s.v;                        lg[7] = s.r * P.rad2deg;        lg[8] = o.rpm;
             lg[9] = pct_me;                     lg[10] = pct_el;                lg[11] = o.power_me_kw;
-            lg[12] = M.me_cap_kw;               lg[13] = load_el / (R)1000;     lg[14] = M.el_cap_kw;
-            lg[15] = (load_el + load_me) / (R)1000;                             lg[16] = total / (R)1000;
+            lg[12] = M.me_cap_kw;               lg[13] = kilo_(load_el);     lg[14] = M.el_cap_kw;
+            lg[15] = kilo_(load_el + load_me);                                  lg[16] = kilo_(total);
             lg[17] = rate_me;                   lg[18] = rate_el;               lg[19] = rate_me + rate_el;
             lg[20] = s.f_me;                    lg[21] = s.f_el;                lg[22] = s.f_tot;
-            lg[23] = tq_me;                     lg[24] = P.thrust_coef * thrust_w / (R)1000;
+            lg[23] = tq_me;                     lg[24] = kilo_(P.thrust_coef * thrust_w);
             lg[25] = s.e_ct;                    lg[26] = abs_(s.psi - href);    // radians (controllers.py:327-328)
         }
         s.steps += 1;                                               // utils.py:42-48 next_time

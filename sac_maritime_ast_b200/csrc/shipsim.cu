@@ -88,6 +88,33 @@ __global__ void __launch_bounds__(256) fleet_step_kernel(const __grid_constant__
     }
 }
 
+// Fast variant: nothing is read or written per step (disturbances held for the launch, trajectory row of the last
+// step only, no log / command streams), so the K-step loop is pure register arithmetic with compile-time flags.
+template <typename R, bool AVOID, bool SINGLE_MODE>
+__global__ void __launch_bounds__(256) fleet_step_fast_kernel(const __grid_constant__ ShipP<R> P, const ShipPtrs<R> g,
+                                                              const int K, const FleetIO<R> io) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t S = g.n_ships;
+    if (i >= S) return;
+    Ship<R> s;
+    load_ship(s, g, i);
+    if (io.dist) {
+        s.vcn = io.dist[i]; s.vce = io.dist[S + i];
+        const R w_speed = io.dist[2 * S + i], w_dir = io.dist[3 * S + i];
+        set_wind(s, w_speed, w_dir);
+        g.vc_n[i] = s.vcn; g.vc_e[i] = s.vce; g.wind_speed[i] = w_speed; g.wind_dir[i] = w_dir;
+    }
+    StepOut<R> o;
+#pragma unroll 1
+    for (int t = 0; t < K; ++t) ship_step<R, false, SINGLE_MODE>(P, s, g, i, AVOID, true, o, nullptr);
+    if (io.traj) {
+        R* tr = io.traj + i;
+        tr[0] = (R)s.N; tr[S] = (R)s.E; tr[2 * S] = s.psi; tr[3 * S] = s.u;
+        tr[4 * S] = s.v; tr[5 * S] = s.r; tr[6 * S] = s.om; tr[7 * S] = (R)s.k;
+    }
+    store_ship(s, g, i);
+}
+
 // =================================================================================================
 // K3: reset / capture_init
 // =================================================================================================
@@ -229,7 +256,7 @@ __global__ void __launch_bounds__(128) env_step_kernel(const __grid_constant__ E
                     g.wp_n[(int64_t)(s.n_wp - 1) * S + i] = act_n; g.wp_e[(int64_t)(s.n_wp - 1) * S + i] = act_e;
                     if (s.k == s.n_wp - 1) {   // the segment in use ended at the old last point
                         s.cN = act_n; s.cE = act_e;
-                        s.alpha = atan2_(s.cE - s.pE, s.cN - s.pN);
+                        s.alpha = atan2_((R)(s.cE - s.pE), (R)(s.cN - s.pN));
                         sincos_(s.alpha, s.sa, s.ca);
                     }
                     s.n_wp += 1;
@@ -779,7 +806,17 @@ static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, c
     const ShipPtrs<R> g = ship_ptrs<R>(h, state);
     const ShipP<R>& P = HostSel<R>::ship(h);
     const int block = 256, grid = grid_for(h->n_ships, block);
-    if (k.log27) fleet_step_kernel<R, true><<<grid, block, 0, st>>>(P, g, K, k);
+    const bool fast = (!k.dist || k.dist_steps == 1) && (!k.traj || k.traj_steps == 1) && !k.log27 && !k.cmd && k.store;
+    const bool single = P.n_modes == 1;
+    if (fast) {
+        if (k.avoid) {
+            if (single) fleet_step_fast_kernel<R, true, true><<<grid, block, 0, st>>>(P, g, K, k);
+            else fleet_step_fast_kernel<R, true, false><<<grid, block, 0, st>>>(P, g, K, k);
+        } else {
+            if (single) fleet_step_fast_kernel<R, false, true><<<grid, block, 0, st>>>(P, g, K, k);
+            else fleet_step_fast_kernel<R, false, false><<<grid, block, 0, st>>>(P, g, K, k);
+        }
+    } else if (k.log27) fleet_step_kernel<R, true><<<grid, block, 0, st>>>(P, g, K, k);
     else fleet_step_kernel<R, false><<<grid, block, 0, st>>>(P, g, K, k);
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
