@@ -37,7 +37,7 @@ METRIC = "ship env-steps/sec"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--ships-per-gpu", type=int, default=1 << 20)
@@ -108,18 +108,19 @@ def cpu_ship_steps_per_s(n, k_inner, steps, warmup, max_wp, seed, threads=0):
     return n * k_inner * steps / total, cores, total
 
 
-def calibrate_cpu_sample(k_inner, max_wp, budget_s):
-    """Pick a ship count so that one CPU step takes about budget_s / 8 seconds."""
-    rate, cores, _ = cpu_ship_steps_per_s(4096, k_inner, 1, 1, max_wp, 1)
-    n = int(rate * (budget_s / 8.0) / k_inner)
+def calibrate_cpu_sample(k_inner, max_wp, per_step_s):
+    """Pick a ship count so that one CPU bench step (k_inner simulator steps of every ship) takes about per_step_s."""
+    rate, cores, _ = cpu_ship_steps_per_s(8192, k_inner, 1, 1, max_wp, 1)
+    n = int(rate * per_step_s / k_inner)
     return max(1024, min(1 << 20, (n // 1024) * 1024))
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    n = calibrate_cpu_sample(args.k_inner, args.max_wp, budget_s=40.0)
-    rate, cores, total = cpu_ship_steps_per_s(n, args.k_inner, args.steps, min(args.warmup, 2), args.max_wp, SEED)
+    wu = min(args.warmup, 2)
+    n = calibrate_cpu_sample(args.k_inner, args.max_wp, per_step_s=60.0 / (args.steps + wu))   # whole run ~1 minute
+    rate, cores, total = cpu_ship_steps_per_s(n, args.k_inner, args.steps, wu, args.max_wp, SEED)
     sample = f"{n} ships x {args.k_inner} steps per bench step (bounded sample of the {args.ships_per_gpu}-ship fleet), float64 C port of the reference step, OpenMP"
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": "ship-steps/s", "n_gpus": args.gpus,
@@ -307,8 +308,14 @@ def run_b200(args, rank, world, local_rank):
         tf64 = C.c_double()
         _lib.check(L.sit_measure_fma_peak(local_rank, _lib.F64, C.byref(tf64), None))
         line["fp64_fma_peak_tflops"] = tf64.value
+        # ---- two-ship AST env step (BASELINE configs 4/5): env-steps/s, last-step record and every-step record ----------
+        ast = env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", record_all=False)
+        ast["roofline_frac_fp32"] = ast["algorithmic_tflops"] / tf.value
+        line["ast_env"] = ast
+        ast_rec = env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", record_all=True)
+        line["ast_env_recorded"] = {k: ast_rec[k] for k in ("value", "unit", "ms_per_launch", "write_gbs")}
     if rank == 0 and not args.no_cpu_baseline and not args.no_extras:
-        n = calibrate_cpu_sample(KI, args.max_wp, budget_s=16.0)
+        n = calibrate_cpu_sample(KI, args.max_wp, per_step_s=4.0)
         rate, cores, total = cpu_ship_steps_per_s(n, KI, 4, 1, args.max_wp, SEED)
         line["cpu_baseline"] = {"value": rate, "unit": "ship-steps/s", "cores": cores, "kind": "port",
                                 "sample": f"{n} ships x {KI} steps x 4 (oracle/ship_oracle.c float64, OpenMP, {total:.1f} s)"}
@@ -349,6 +356,83 @@ def traj_roofline(sit, dev):
             "kernel": "fleet_step_kernel<double> with trajectory write-out", "ships": S, "k": K, "ms_per_launch": ms,
             "ship_steps_per_s": S * K / (ms * 1e-3), "peak_source": src,
             "note": "algorithmic bytes = 64 B written per ship-step (8 fp64 channels); output 1 GiB per launch > L2"}
+
+
+DEFAULT_MAP = [
+    [(0, 10000), (5500, 10000), (5300, 9000), (4800, 8500), (4200, 7300), (4000, 5700), (4300, 4900),
+     (4900, 4400), (4400, 4000), (3200, 4100), (2000, 4500), (1000, 4000), (900, 3500), (500, 2600), (0, 2350)],
+    [(10000, 0), (4000, 0), (4250, 250), (5000, 400), (6000, 900), (8000, 1100), (8500, 1500), (9000, 2250),
+     (9500, 3500), (10000, 4000)],
+    [(5500, 5500), (5700, 7000), (6200, 8100), (7500, 8000), (7800, 7000), (7600, 5500), (6900, 4700), (6000, 5000)],
+    [(2000, 2000), (2500, 2300), (4000, 2500), (5000, 3000), (4200, 2100), (3400, 1900)],
+]   # main_ast.py:200-205
+F_ENV = 4800.0   # algorithmic FLOP per AST env-step on the default 39-edge map
+
+
+def make_bench_env(sit, dev, B, precision, seed, modes=("PTO", "PTI", "MEC")):
+    """BASELINE config 4/5 style two-ship envs on the default map: per-env set points and machinery modes so
+    that lanes diverge like a real rollout batch does."""
+    import torch
+    from types import SimpleNamespace
+    kw = dict(mode_names=modes, mode_index=1)
+    t = sit.default_ship([(500, 500), (9500, 9500)], np.pi / 4, **kw)
+    o = sit.default_ship([(9500, 9000), (1000, 1000)], -3 * np.pi / 4, **kw)
+    assets = [sit.ShipAssets(*t, 8.0, [], [], "test_ship", False), sit.ShipAssets(*o, 8.0, [], [], "obs_ship", False)]
+    env = sit.MultiShipRLEnv(assets=assets, map=sit.PolygonObstacle(DEFAULT_MAP), ship_draw=False,
+                             time_since_last_ship_drawing=30, args=SimpleNamespace(sampling_frequency=7, theta=2),
+                             n_envs=B, device=dev, precision=precision)
+    g = torch.Generator(device=dev); g.manual_seed(seed)
+    for role in (0, 1):
+        v = env.ship[role]
+        v.u_sp.copy_(6.0 + 4.0 * torch.rand(B, generator=g, device=dev, dtype=env.real))
+        v.mode.copy_(torch.randint(1, 3, (B,), generator=g, device=dev, dtype=torch.int32))   # PTI / MEC
+    env.capture_init()
+    env.reset(); env.init_step()
+    return env, g
+
+
+def draw_waypoints(env, g, dev):
+    """Intermediate waypoints (north, east) for every env: a point on the obstacle ship's A->B line plus a lateral
+    offset (the role of agent.convert_action_to_simu_input, main_ast.py:367; its code is absent from the reference)."""
+    import torch
+    B = env.n_envs
+    s = torch.rand(B, generator=g, device=dev, dtype=env.real)
+    lat = 1600.0 * (torch.rand(B, generator=g, device=dev, dtype=env.real) - 0.5)
+    a = torch.empty((B, 2), dtype=env.real, device=dev)
+    a[:, 0] = 9500.0 - 8500.0 * s + 0.686 * lat
+    a[:, 1] = 9000.0 - 8000.0 * s - 0.728 * lat
+    return a
+
+
+def env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", record_all=False):
+    """AST env-steps/s: K MultiShipRLEnv.step per launch for B two-ship envs, in-kernel auto-reset, a fresh
+    intermediate waypoint (SAC_update) per launch."""
+    import torch
+    env, g = make_bench_env(sit, dev, B, precision, SEED)
+    acts = [draw_waypoints(env, g, dev) for _ in range(8)]
+    sac = torch.ones(B, dtype=torch.uint8, device=dev)
+    out = {}
+    for w in range(warmup):
+        env.step_k(K, acts[w % 8], sac, init=None, auto_reset=True, record_all=record_all, out=out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    env.stats.zero_()
+    e0.record()
+    for k in range(steps):
+        env.step_k(K, acts[(warmup + k) % 8], sac, init=None, auto_reset=True, record_all=record_all, out=out)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    st = env.stats.cpu().numpy()
+    rate = B * K / (ms * 1e-3)
+    rec_bytes = (10 * 4 + 4 + 1 + 4) if precision == "fp32" else (10 * 8 + 8 + 1 + 4)
+    return {"metric": "AST env-steps/s (MultiShipRLEnv.step, 2 ships + reward + termination)", "value": rate,
+            "unit": "env-steps/s", "envs": B, "k_per_launch": K, "ms_per_launch": ms, "dtype": precision,
+            "record_every_step": bool(record_all),
+            "algorithmic_tflops": rate * F_ENV / 1e12,
+            "write_gbs": (rate * rec_bytes / 1e9) if record_all else None,
+            "episodes_done": int(st[12]), "env_steps_counted": int(st[13]),
+            "status_counts": {i: int(st[i]) for i in range(12)}}
 
 
 def main():

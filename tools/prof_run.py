@@ -1,0 +1,20 @@
+"""Small single-GPU driver for ncu captures: a few launches of each hot kernel at bench sizes.
+    python tools/prof_run.py fleet32|traj64|env32|env32rec|env64"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+import numpy as np
+import torch
+import bench
+import sac_maritime_ast_b200 as sit
+
+which = sys.argv[1]
+dev = torch.device("cuda", 0)
+if which == "traj64":
+    print(bench.traj_roofline(sit, dev))
+elif which.startswith("env"):
+    prec = "fp64" if "64" in which else "fp32"
+    print(bench.env_leg(sit, dev, B=1 << 18 if prec == "fp32" else 1 << 16, K=64, steps=3, warmup=3, precision=prec,
+                        record_all=which.endswith("rec")))
+else:
+    raise SystemExit("fleet32 is `python bench.py --steps 3 --warmup 3 --no-extras`")
