@@ -385,7 +385,9 @@ def make_bench_env(sit, dev, B, precision, seed, modes=("PTO", "PTI", "MEC")):
     for role in (0, 1):
         v = env.ship[role]
         v.u_sp.copy_(6.0 + 4.0 * torch.rand(B, generator=g, device=dev, dtype=env.real))
-        v.mode.copy_(torch.randint(1, 3, (B,), generator=g, device=dev, dtype=torch.int32))   # PTI / MEC
+    # the test ship stays in PTI (the reference default, main_ast.py:159-161): with the always-on avoidance branch its
+    # throttle sits at 1.1, which is an immediate blackout failure in PTO / MEC; the obstacle ship mixes PTI / MEC
+    env.ship[1].mode.copy_(torch.randint(1, 3, (B,), generator=g, device=dev, dtype=torch.int32))
     env.capture_init()
     env.reset(); env.init_step()
     return env, g
@@ -401,6 +403,17 @@ def draw_waypoints(env, g, dev):
     a = torch.empty((B, 2), dtype=env.real, device=dev)
     a[:, 0] = 9500.0 - 8500.0 * s + 0.686 * lat
     a[:, 1] = 9000.0 - 8000.0 * s - 0.728 * lat
+    # validity resampling (main_ast.py:47-51 max_route_resampling): redraw the waypoints that fall inside an island or
+    # off the map, checked by the product's own map kernel (sit_map_query)
+    for _ in range(20):
+        bad = env.map_query(a[:, 0], a[:, 1]) != 0
+        nb = int(bad.sum())
+        if nb == 0:
+            break
+        s2 = torch.rand(nb, generator=g, device=dev, dtype=env.real)
+        l2 = 1600.0 * (torch.rand(nb, generator=g, device=dev, dtype=env.real) - 0.5)
+        a[bad, 0] = 9500.0 - 8500.0 * s2 + 0.686 * l2
+        a[bad, 1] = 9000.0 - 8000.0 * s2 - 0.728 * l2
     return a
 
 

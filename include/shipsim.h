@@ -194,6 +194,11 @@ int sit_env_step_k(SitHandle h, void* state, int32_t K, const SitEnvIO* io, void
 int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h, const uint8_t* sac_update_h,
                       int32_t init, void* obs_h, void* reward_h, uint8_t* done_h, int32_t* status_h, void* stream);
 
+/* Map predicates for n candidate waypoints (device arrays of reals): flags[i] bit 0 = inside an obstacle polygon
+ * (is_route_inside_obstacles MSRL_env_ex.py:544-552 -> obstacle.py:131-136), bit 1 = outside the map AABB
+ * (is_route_outside_horizon :517-542); dist[i] = obstacles_distance (obstacle.py:138-141).  flags / dist may be NULL. */
+int sit_map_query(SitHandle h, int64_t n, const void* north, const void* east, uint8_t* flags, void* dist, void* stream);
+
 /* ---- misc ------------------------------------------------------------------------------------ */
 const char* sit_last_error(void);
 const char* sit_status_string(int32_t bit_index);  /* exact reference strings, MSRL_env_ex.py:760-899 */

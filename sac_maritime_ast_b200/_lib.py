@@ -78,7 +78,7 @@ class SitEnvIO(C.Structure):
 
 
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host",
-           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host",
+           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query",
            "sit_last_error", "sit_status_string", "sit_abi_version", "sit_measure_fma_peak")
 
 _lib = None
@@ -111,6 +111,7 @@ def lib():
     L.sit_env_init_step.argtypes = [vp, vp, vp, vp]
     L.sit_env_step_k.argtypes = [vp, vp, I32, P(SitEnvIO), vp]
     L.sit_env_step_host.argtypes = [vp, vp, I32, vp, vp, I32, vp, vp, vp, vp, vp]
+    L.sit_map_query.argtypes = [vp, I64, vp, vp, vp, vp, vp]
     L.sit_last_error.restype = C.c_char_p
     L.sit_status_string.argtypes = [I32]
     L.sit_status_string.restype = C.c_char_p

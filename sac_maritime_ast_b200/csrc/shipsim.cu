@@ -431,6 +431,27 @@ __global__ void __launch_bounds__(256) env_init_step_kernel(const __grid_constan
     store_ship(s, g, i);
 }
 
+// Map queries for a batch of candidate waypoints: is_route_outside_horizon (MSRL_env_ex.py:517-542), is_route_inside_obstacles
+// (:544-552 -> obstacle.py:131-136) and obstacles_distance (obstacle.py:138-141).  Used by the waypoint sampler to
+// reject invalid intermediate waypoints before they reach step().
+template <typename R>
+__global__ void __launch_bounds__(256) map_query_kernel(const __grid_constant__ EnvKArgs<R> A, const int64_t n, const R* north,
+                                                        const R* east, uint8_t* flags, R* dist) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const R pn = north[i], pe = east[i];
+    const EnvP<R>& EP = A.EP;
+    uint8_t f = 0;
+    if (map_contains(A.M, pn, pe)) f |= 1;
+    if (pn < EP.min_n || pn > EP.max_n || pe < EP.min_e || pe > EP.max_e) f |= 2;
+    if (flags) flags[i] = f;
+    if (dist) {
+        R d2; bool in;
+        map_scan(A.M, pn, pe, d2, in);
+        dist[i] = sqrt_(d2);
+    }
+}
+
 // =================================================================================================
 // FMA-peak microbenchmark (roofline denominator for the compute-bound step kernels)
 // =================================================================================================
@@ -978,6 +999,24 @@ int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h,
     if (done_h) CUDA_TRY(cudaMemcpyAsync(done_h, d + o_done, B, cudaMemcpyDeviceToHost, st));
     if (status_h) CUDA_TRY(cudaMemcpyAsync(status_h, d + o_st, B * 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    return SIT_OK;
+}
+
+int sit_map_query(SitHandle h, int64_t n, const void* north, const void* east, uint8_t* flags, void* dist, void* stream) {
+    if (!h || !north || !east) return fail(SIT_E_INVALID, "null argument");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_map_query needs a SIT_KIND_ENV handle");
+    if (n < 0) return fail(SIT_E_INVALID, "n must be >= 0");
+    if (n == 0) return SIT_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int block = 256, grid = grid_for(n, block);
+    if (h->cfg.precision == SIT_F64)
+        map_query_kernel<double><<<grid, block, 0, st>>>(*h->kd, n, static_cast<const double*>(north), static_cast<const double*>(east),
+                                                         flags, static_cast<double*>(dist));
+    else
+        map_query_kernel<float><<<grid, block, 0, st>>>(*h->kf, n, static_cast<const float*>(north), static_cast<const float*>(east),
+                                                        flags, static_cast<float*>(dist));
+    CUDA_TRY(cudaGetLastError());
     return SIT_OK;
 }
 

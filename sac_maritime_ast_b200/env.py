@@ -242,6 +242,18 @@ class MultiShipRLEnv(SimCore):
         self.launches += 1
         return out_host
 
+    def map_query(self, north: torch.Tensor, east: torch.Tensor, want_dist: bool = False):
+        """Waypoint validity for n points: flags uint8 (bit 0 = inside an obstacle, MSRL_env_ex.py:544-552; bit 1 =
+        outside the map, :517-542) and optionally the distance to the nearest obstacle ring (obstacle.py:138-141)."""
+        north = north.to(device=self.device, dtype=self.real).contiguous()
+        east = east.to(device=self.device, dtype=self.real).contiguous()
+        assert north.shape == east.shape
+        flags = torch.empty(north.shape, dtype=torch.uint8, device=self.device)
+        dist = torch.empty(north.shape, dtype=self.real, device=self.device) if want_dist else None
+        _lib.check(self.L.sit_map_query(self.h, north.numel(), ptr(north), ptr(east), ptr(flags), ptr(dist), self.stream()))
+        self.launches += 1
+        return (flags, dist) if want_dist else flags
+
     # ---- status ---------------------------------------------------------------------------------------------------
     @staticmethod
     def decode_status(mask: int) -> str:

@@ -161,3 +161,28 @@ def test_status_strings_and_host_step():
     assert "|Obstacle ship IW sampled in terminal state|" in txt and "|Test ship not in terminal state|" in txt
     with pytest.raises(TypeError):
         env.step(None, True, True)
+
+
+def test_map_query_matches_geometry_oracle():
+    """sit_map_query (waypoint validity: obstacle.py:126-141, MSRL_env_ex.py:517-552) against the CPU restatement of
+    the shapely calls, on random points plus vertices / edge points (boundary is NOT contained)."""
+    import gpu_helpers as G
+    from oracle import geometry as geo
+    env = G.make_env(sc.ENV_SCENARIOS["default"], n_envs=1, precision="fp64")
+    rng = np.random.default_rng(5)
+    pts = rng.uniform(-500, 10500, (4000, 2))                      # (north, east)
+    verts = np.array([(y, x) for poly in sc.DEFAULT_MAP for (x, y) in poly], dtype=np.float64)
+    mids = np.array([((poly[i][1] + poly[(i + 1) % len(poly)][1]) / 2, (poly[i][0] + poly[(i + 1) % len(poly)][0]) / 2)
+                     for poly in sc.DEFAULT_MAP for i in range(len(poly))])
+    pts = np.concatenate([pts, verts, mids])
+    flags, dist = env.map_query(torch.from_numpy(pts[:, 0].copy()), torch.from_numpy(pts[:, 1].copy()), want_dist=True)
+    flags, dist = flags.cpu().numpy(), dist.cpu().numpy()
+    polys = [geo.Polygon(p) for p in sc.DEFAULT_MAP]
+    for j, (n, e) in enumerate(pts):
+        pt = geo.Point(e, n)
+        inside = any(p.contains(pt) for p in polys)
+        outside = n < 0 or n > 10000 or e < 0 or e > 10000
+        assert bool(flags[j] & 1) == inside, (j, n, e)
+        assert bool(flags[j] & 2) == outside, (j, n, e)
+        d = min(p.exterior.distance(pt) for p in polys)
+        assert abs(dist[j] - d) <= 1e-9 * max(1.0, d), (j, n, e, dist[j], d)
