@@ -168,7 +168,8 @@ typedef struct SitEnvIO {
     int32_t act_steps;       /* 1: action held for the launch, sac_update applies to its first step; or K */
     int32_t init;            /* `init` argument of step(): 1/0 for the first step of the launch, -1 = per-env
                                 "first step since reset" flag */
-    int32_t auto_reset;      /* 1: reset() + init_step() inside the kernel right after a done step */
+    int32_t auto_reset;      /* 1: reset() + init_step() inside the kernel right after a done step (reference
+                                semantics: omega, integrators, fuel survive, quirk Q3); 2: same with a hard reset */
     int32_t rec_steps;       /* outputs hold rec_steps = K (every step) or 1 (last step of the launch) */
     /* outputs (device), may be NULL */
     void* obs;               /* [rec_steps][SIT_N_OBS][n_envs] reals */

@@ -14,7 +14,7 @@ SG = {"MOTOR": 0, "GEN": 1, "OFF": 2}
 DT_F64, DT_F32, DT_I32 = 0, 1, 2
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libshipsim.so")
+LIB_PATH = os.environ.get("SIT_LIBSHIPSIM", os.path.join(_HERE, "libshipsim.so"))   # override: kernel experiments
 
 D, I32, I64 = C.c_double, C.c_int32, C.c_int64
 

@@ -38,6 +38,35 @@ struct EnvP {
 enum { F_STOP_TEST = 1, F_STOP_OBS = 2, F_NSTORED_SHIFT = 2, F_NSTORED_MASK = 3 << 2, F_IW_BAD = 16, F_FRESH = 32,
        F_IW_VALID = 64 };
 
+// One ring segment as the kernels read it: staged once per CTA from the constant bank into shared memory so the
+// edge loop issues two 128-bit broadcast LDS per edge (float) instead of eight indexed constant loads.
+template <typename R> struct IntOf;
+template <> struct IntOf<float> { typedef int32_t type; };
+template <> struct IntOf<double> { typedef int64_t type; };
+
+template <typename R>
+struct __align__(16) EdgeRec {
+    R x1, y1, dx, dy;
+    R len2, inv_len2, y2;
+    typename IntOf<R>::type pbit;   // 1 << (polygon id & 31) ... per-polygon crossing parity lives in one 32-bit mask
+};
+
+template <typename R>
+__device__ __forceinline__ void stage_edges(const MapP<R>& m, EdgeRec<R>* sm) {
+    int poly = 0;
+    // polygon ids are a running count of poly_end flags: recomputed per thread from the (tiny) uniform array
+    for (int i = threadIdx.x; i < m.n_edges; i += blockDim.x) {
+        poly = 0;
+        for (int j = 0; j < i; ++j) poly += m.poly_end[j];
+        EdgeRec<R> e;
+        e.x1 = m.x1[i]; e.y1 = m.y1[i]; e.dx = m.dx[i]; e.dy = m.dy[i];
+        e.len2 = m.len2[i]; e.inv_len2 = m.inv_len2[i]; e.y2 = m.y2[i];
+        e.pbit = (typename IntOf<R>::type)(1u << (poly & 31));
+        sm[i] = e;
+    }
+    __syncthreads();
+}
+
 // Literal point-in-any-polygon: obstacle.py:126-129 any(poly.contains(Point(e, n))), interior only.
 template <typename R>
 __device__ __noinline__ bool map_contains(const MapP<R>& m, R py /*north*/, R px /*east*/) {
@@ -71,28 +100,32 @@ __device__ __noinline__ bool map_contains(const MapP<R>& m, R py /*north*/, R px
 // One pass over the ring segments for the hull centre: squared distance to the nearest ring
 // (obstacle.py:138-141 min(poly.exterior.distance)) and containment of the centre, sharing the
 // per-edge cross product.  Valid as the containment of all four hull corners whenever
-// dist2 > near2 (no ring can pass between the centre and a corner).
+// dist2 > near2 (no ring can pass between the centre and a corner).  Polygons sharing a parity bit
+// (more than 32 polygons) would alias: sit_create rejects such maps.
 template <typename R>
-__device__ __forceinline__ void map_scan(const MapP<R>& m, R py, R px, R& dist2, bool& centre_inside) {
-    R best = (R)3.0e38;
+__device__ __forceinline__ void map_scan(const EdgeRec<R>* __restrict__ E, const int n_edges, R py, R px, R& dist2,
+                                         bool& centre_inside) {
+    R best0 = (R)3.0e38, best1 = (R)3.0e38;
     uint32_t parity = 0;
-    bool inside = false;
-#pragma unroll 4
-    for (int i = 0; i < m.n_edges; ++i) {
-        const R ex = px - m.x1[i], ey = py - m.y1[i];
-        const R dx = m.dx[i], dy = m.dy[i];
+#ifndef SIT_SCAN_UNROLL
+#define SIT_SCAN_UNROLL 8
+#endif
+    constexpr int kUnroll = SIT_SCAN_UNROLL;
+#pragma unroll kUnroll
+    for (int i = 0; i < n_edges; ++i) {
+        const EdgeRec<R> e = E[i];
+        const R ex = px - e.x1, ey = py - e.y1;
         const R v2 = ex * ex + ey * ey;               // distance^2 to the segment's first vertex
-        const R dot = ex * dx + ey * dy;
-        const R cr = dx * ey - dy * ex;               // orientation of (a, b, p)
-        const R pr = cr * cr * m.inv_len2[i];         // distance^2 to the supporting line
-        const R cand = (dot > (R)0 && dot < m.len2[i]) ? pr : v2;
-        best = min_(best, cand);
-        const bool straddle = (m.y1[i] > py) != (m.y2[i] > py);
-        parity ^= (straddle && ((cr > (R)0) != (dy < (R)0))) ? 1u : 0u;
-        if (m.poly_end[i]) { inside |= (parity & 1u); parity = 0; }
+        const R dot = ex * e.dx + ey * e.dy;
+        const R cr = e.dx * ey - e.dy * ex;           // orientation of (a, b, p)
+        const R pr = cr * cr * e.inv_len2;            // distance^2 to the supporting line
+        const R cand = (dot > (R)0 && dot < e.len2) ? pr : v2;
+        if (i & 1) best1 = min_(best1, cand); else best0 = min_(best0, cand);
+        const bool straddle = (e.y1 > py) != (e.y2 > py);
+        parity ^= (straddle && ((cr > (R)0) != (e.dy < (R)0))) ? (uint32_t)e.pbit : 0u;
     }
-    dist2 = best;
-    centre_inside = inside;
+    dist2 = min_(best0, best1);
+    centre_inside = parity != 0u;
 }
 
 }  // namespace sit

@@ -165,7 +165,7 @@ __global__ void reset_kernel(const ShipPtrs<R> g, const EnvPtrs<R> ge, const uin
 // K2: two-ship AST env.  Lane pair (2j, 2j+1) = (test ship, obstacle ship) of one env.
 // =================================================================================================
 template <typename R>
-__device__ __forceinline__ void reset_ship_regs(Ship<R>& s, const ShipPtrs<R>& g, int64_t i) {
+__device__ __forceinline__ void reset_ship_regs(Ship<R>& s, const ShipPtrs<R>& g, int64_t i, bool hard) {
     const int64_t S = g.n_ships;
     s.N = g.init_north[i]; s.E = g.init_east[i];
     s.psi = g.init_psi[i]; s.u = g.init_u[i]; s.v = g.init_v[i]; s.r = g.init_r[i];
@@ -181,6 +181,11 @@ __device__ __forceinline__ void reset_ship_regs(Ship<R>& s, const ShipPtrs<R>& g
         g.wp_e[(int64_t)j * S + i] = g.wp0_e[(int64_t)j * S + i];
     }
     load_segment(s, g, i);
+    if (hard) {   // what the reference's reset() leaves alone (quirk Q3): a fresh construction
+        s.om = g.init_omega[i];
+        s.ei_s = (R)0; s.ei_w = g.init_ei_shaft[i]; s.ei_h = (R)0; s.e_prev = (R)0;
+        s.f_me = (R)0; s.f_el = (R)0; s.f_tot = (R)0;
+    }
 }
 
 template <typename R>
@@ -194,10 +199,16 @@ __device__ __forceinline__ bool hull_inside(const EnvKArgs<R>& A, R n, R e, R ha
     return in;
 }
 
+#ifndef SIT_ENV_MINB_F32
+#define SIT_ENV_MINB_F32 4
+#endif
 template <typename R, bool SAME>
-__global__ void __launch_bounds__(128) env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
+__global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
                                                        const EnvPtrs<R> ge, const int K, const EnvIO<R> io) {
     const unsigned FULL = 0xffffffffu;
+    __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
+    stage_edges(A.M, s_edges);
+    const int n_edges = A.M.n_edges;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t S = g.n_ships, B = ge.n_envs;
     const bool active = tid < S;
@@ -292,7 +303,7 @@ __global__ void __launch_bounds__(128) env_step_kernel(const __grid_constant__ E
         // ---- own-ship geometry: distance to the nearest ring + hull containment ------------------------
         const R pn = (R)s.N, pe = (R)s.E;
         R d2map; bool c_in;
-        map_scan(A.M, pn, pe, d2map, c_in);
+        map_scan(s_edges, n_edges, pn, pe, d2map, c_in);
         const bool inside = hull_inside(A, pn, pe, EP.half_len[role], d2map, c_in);
         const R dmap = sqrt_(d2map);
         const bool outside = pn < EP.lo_n[role] || pn > EP.hi_n[role] || pe < EP.lo_e[role] || pe > EP.hi_e[role];
@@ -381,7 +392,7 @@ __global__ void __launch_bounds__(128) env_step_kernel(const __grid_constant__ E
         }
         // ---- in-kernel reset() + init_step() right after a terminal step ---------------------------------
         if (io.auto_reset && done) {
-            reset_ship_regs(s, g, i);   // MSRL_env_ex.py:145-186 (omega, integrators, fuel kept)
+            reset_ship_regs(s, g, i, io.auto_reset == 2);   // MSRL_env_ex.py:145-186 (omega, integrators, fuel kept unless hard)
             endN = g.wp_n[(int64_t)(s.n_wp - 1) * S + i]; endE = g.wp_e[(int64_t)(s.n_wp - 1) * S + i];
             stop = false; nstored = 0; fresh = true;
             eps_dist = 0.0; samp_dist = 0.0; prev_n = 0.0; prev_e = 0.0;
@@ -437,6 +448,8 @@ __global__ void __launch_bounds__(256) env_init_step_kernel(const __grid_constan
 template <typename R>
 __global__ void __launch_bounds__(256) map_query_kernel(const __grid_constant__ EnvKArgs<R> A, const int64_t n, const R* north,
                                                         const R* east, uint8_t* flags, R* dist) {
+    __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
+    stage_edges(A.M, s_edges);
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const R pn = north[i], pe = east[i];
@@ -447,7 +460,7 @@ __global__ void __launch_bounds__(256) map_query_kernel(const __grid_constant__ 
     if (flags) flags[i] = f;
     if (dist) {
         R d2; bool in;
-        map_scan(A.M, pn, pe, d2, in);
+        map_scan(s_edges, A.M.n_edges, pn, pe, d2, in);
         dist[i] = sqrt_(d2);
     }
 }
@@ -754,6 +767,10 @@ int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out)
         if (rc) return rc;
         if (cfg->map.n_edges < 0 || cfg->map.n_edges > SIT_MAX_EDGES) return fail(SIT_E_INVALID, "map.n_edges out of range");
         if (!(cfg->sampling_frequency > 0)) return fail(SIT_E_INVALID, "sampling_frequency must be > 0");
+        int np_ = 0;
+        for (int i = 0; i < cfg->map.n_edges; ++i)
+            if (i + 1 == cfg->map.n_edges || cfg->map.poly[i + 1] != cfg->map.poly[i]) ++np_;
+        if (np_ > 32) return fail(SIT_E_INVALID, "map has more than 32 polygons");
     }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {

@@ -195,7 +195,8 @@ class MultiShipRLEnv(SimCore):
                want_sums=False, out: Optional[dict] = None):
         """K env steps in ONE launch.  converted_action [n_envs, 2] (held for the launch; SAC_update applies to
         its first step) or [K, n_envs, 2] with SAC_update [K, n_envs].  init: True / False for the first
-        step, None = per-env first-step-since-reset flag.  Outputs are SoA: obs [rec, 10, n_envs],
+        step, None = per-env first-step-since-reset flag.  auto_reset: False, True (reference reset semantics,
+        quirk Q3) or "hard" (integrators, shaft speed and fuel restored too).  Outputs are SoA: obs [rec, 10, n_envs],
         reward / done / status [rec, n_envs] with rec = K (record_all) or 1 (last step)."""
         io = _lib.SitEnvIO()
         act = self._as_action(converted_action, K)
@@ -205,7 +206,7 @@ class MultiShipRLEnv(SimCore):
             sac = sac.expand(act.shape[0], self.n_envs).contiguous()
         io.action, io.sac_update, io.act_steps = act.data_ptr(), sac.data_ptr(), act.shape[0]
         io.init = -1 if init is None else int(bool(init))
-        io.auto_reset = int(bool(auto_reset))
+        io.auto_reset = 2 if auto_reset == "hard" else int(bool(auto_reset))
         rec = K if record_all else 1
         io.rec_steps = rec
         res = out if out is not None else {}
