@@ -195,6 +195,57 @@ int sit_env_step_k(SitHandle h, void* state, int32_t K, const SitEnvIO* io, void
 int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h, const uint8_t* sac_update_h,
                       int32_t init, void* obs_h, void* reward_h, uint8_t* done_h, int32_t* status_h, void* stream);
 
+/* ---- device-resident rollout (the role of the empty ast_core/samplers/intermediate_waypoint_sampler.py; loop
+ * contract of test_beds/main_ast.py:310-412).  The agent-side pieces the reference imports from the absent `ast_sac`
+ * package (select_action, convert_action_to_simu_input) are DEFINED here -- parity unpinned, see DESIGN.md:
+ *   decision event  = first step of an episode, or the obstacle ship is within the radius of acceptance of its
+ *                     current intermediate waypoint (controllers.py:317-325) and fewer than sampling_frequency
+ *                     decisions were taken this episode (main_ast.py:47);
+ *   action          = a in [-1, 1]: UniformPolicy (policies/uniform_policy.py:21-22) or the tanh-Gaussian policy
+ *                     (nn_models/mlp.py:95-148, distributions/normal.py:14-15,78-98, policies/gaussian_policy.py:116-117);
+ *   conversion      = scoping angle a * pi/6 (action_space, MSRL_env_ex.py:79-83) around AB_alpha, one
+ *                     AB_segment_length (MSRL_env_ex.py:122-127) ahead of the previous intermediate waypoint
+ *                     (of the route start for the first), redrawn up to max_route_resampling times while it falls
+ *                     inside an obstacle or off the map (main_ast.py:49-51);
+ *   transition      = (state[10], action, reward, next_state[10], mask) of the decision step only
+ *                     (main_ast.py:387,395-396), mask = 1 if episode_steps == num_steps_episode else !done.
+ * An env that reaches a decision event stops stepping ("pending") until sit_rollout_policy has given it an action,
+ * so the policy runs batched over the pending subset between step launches and nothing returns to the host. */
+#define SIT_TR_FLOATS 24   /* replay row: s[0..9], a[10], r[11], s'[12..21], mask[22], global env id as int32 bits [23] */
+enum { SIT_POLICY_UNIFORM = 0, SIT_POLICY_GAUSSIAN = 1, SIT_POLICY_MEAN = 2 };
+enum { SIT_RC_TRANSITIONS = 0, SIT_RC_DECISIONS = 1, SIT_RC_RESAMPLES = 2, SIT_RC_EPISODES = 3, SIT_RC_N = 8 };
+
+typedef struct SitPolicy {
+    int32_t mode;              /* SIT_POLICY_* */
+    int32_t hidden;            /* width H of both hidden layers (multiple of 32, <= 256); ignored for UNIFORM */
+    const float* w0;           /* [10][H] row-major: layer0 = relu(b0 + obs . w0)   (device pointers, fp32) */
+    const float* b0;           /* [H] */
+    const float* w1;           /* [H][H]:  layer1 = relu(b1 + layer0 . w1) */
+    const float* b1;           /* [H] */
+    const float* w2;           /* [H][2]:  (mu, log_sigma) = b2 + layer1 . w2, log_sigma clipped to [-20, 2] */
+    const float* b2;           /* [2] */
+} SitPolicy;
+
+typedef struct SitRollout {
+    uint64_t seed;             /* Philox key; draws are keyed by (global env id, decision serial, resample index) */
+    int64_t env_id_offset;     /* global id of env 0 of this handle: results do not depend on the sharding */
+    int32_t max_episode_steps; /* num_steps_episode cap (0 = none): reset after that many steps */
+    int32_t max_route_resampling;
+    float* replay;             /* [capacity][SIT_TR_FLOATS] device ring, capacity >= n_envs */
+    int64_t capacity;
+    unsigned long long* counters; /* [SIT_RC_N] device counters, accumulated */
+} SitRollout;
+
+/* give every pending env an action: policy forward on its current observation, sample, convert, validate, open
+ * the replay row.  Enqueues only. */
+int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const SitRollout* ro, void* stream);
+/* K x step for every env that is not pending (pending envs with a fresh action consume it first); closes replay
+ * rows, auto-resets finished episodes (io->auto_reset: 1 reference reset, 2 hard) and marks new decision events.
+ * io may carry the usual outputs (rec_steps must be 1) and stats; io->action / sac_update / init are ignored. */
+int sit_rollout_step_k(SitHandle h, void* state, int32_t K, const SitRollout* ro, const SitEnvIO* io, void* stream);
+/* mark every env pending at the start of a rollout (after sit_reset + sit_env_init_step) */
+int sit_rollout_begin(SitHandle h, void* state, void* stream);
+
 /* Map predicates for n candidate waypoints (device arrays of reals): flags[i] bit 0 = inside an obstacle polygon
  * (is_route_inside_obstacles MSRL_env_ex.py:544-552 -> obstacle.py:131-136), bit 1 = outside the map AABB
  * (is_route_outside_horizon :517-542); dist[i] = obstacles_distance (obstacle.py:138-141).  flags / dist may be NULL. */

@@ -77,8 +77,22 @@ class SitEnvIO(C.Structure):
                 ("reward_sum", C.c_void_p), ("done_any", C.c_void_p), ("stats", C.c_void_p)]
 
 
+class SitPolicy(C.Structure):
+    _fields_ = [("mode", I32), ("hidden", I32), ("w0", C.c_void_p), ("b0", C.c_void_p), ("w1", C.c_void_p),
+                ("b1", C.c_void_p), ("w2", C.c_void_p), ("b2", C.c_void_p)]
+
+
+class SitRollout(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("env_id_offset", I64), ("max_episode_steps", I32),
+                ("max_route_resampling", I32), ("replay", C.c_void_p), ("capacity", I64), ("counters", C.c_void_p)]
+
+
+TR_FLOATS = 24
+POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
+RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_N = 0, 1, 2, 3, 8
+
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host",
-           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query",
+           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_policy", "sit_rollout_step_k",
            "sit_last_error", "sit_status_string", "sit_abi_version", "sit_measure_fma_peak")
 
 _lib = None
@@ -111,6 +125,9 @@ def lib():
     L.sit_env_init_step.argtypes = [vp, vp, vp, vp]
     L.sit_env_step_k.argtypes = [vp, vp, I32, P(SitEnvIO), vp]
     L.sit_env_step_host.argtypes = [vp, vp, I32, vp, vp, I32, vp, vp, vp, vp, vp]
+    L.sit_rollout_begin.argtypes = [vp, vp, vp]
+    L.sit_rollout_policy.argtypes = [vp, vp, P(SitPolicy), P(SitRollout), vp]
+    L.sit_rollout_step_k.argtypes = [vp, vp, I32, P(SitRollout), P(SitEnvIO), vp]
     L.sit_map_query.argtypes = [vp, I64, vp, vp, vp, vp, vp]
     L.sit_last_error.restype = C.c_char_p
     L.sit_status_string.argtypes = [I32]

@@ -36,7 +36,7 @@ struct EnvP {
 
 // env flag bits (state field "flags")
 enum { F_STOP_TEST = 1, F_STOP_OBS = 2, F_NSTORED_SHIFT = 2, F_NSTORED_MASK = 3 << 2, F_IW_BAD = 16, F_FRESH = 32,
-       F_IW_VALID = 64 };
+       F_IW_VALID = 64, F_PENDING = 128, F_HAVE_ACT = 256 };
 
 // One ring segment as the kernels read it: staged once per CTA from the constant bank into shared memory so the
 // edge loop issues two 128-bit broadcast LDS per edge (float) instead of eight indexed constant loads.

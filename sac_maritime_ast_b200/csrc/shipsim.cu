@@ -26,8 +26,16 @@ template <typename R>
 struct EnvPtrs {
     double *prev_n, *prev_e, *eps_dist, *samp_dist;
     R *ab_seg, *act_n, *act_e, *ep_return;
+    R *ab_alpha, *cur_obs;                       // rollout: AB heading (MSRL_env_ex.py:125), observation held for the policy [10][B]
     int32_t *flags, *ep_steps;
+    int32_t *n_dec, *dec_serial, *tr_slot;       // rollout: decisions this episode / ever, open replay row
     int64_t n_envs;
+};
+
+struct RollArgs {   // device-resident rollout (include/shipsim.h SitRollout), by value
+    float* replay; int64_t capacity; unsigned long long* counters;
+    uint64_t seed; int64_t env_id_offset;
+    int32_t max_episode_steps, max_route_resampling, sampling_frequency, _pad;
 };
 
 template <typename R>
@@ -140,6 +148,7 @@ __global__ void capture_init_kernel(const ShipPtrs<R> g, const EnvPtrs<R> ge, co
         const double dn = (double)g.wp_n[(int64_t)(n - 1) * S + i] - (double)g.wp_n[i];
         const double de = (double)g.wp_e[(int64_t)(n - 1) * S + i] - (double)g.wp_e[i];
         ge.ab_seg[i >> 1] = (R)(sqrt(dn * dn + de * de) / sampling_frequency);
+        ge.ab_alpha[i >> 1] = (R)atan2(de, dn);
     }
 }
 
@@ -158,6 +167,7 @@ __global__ void reset_kernel(const ShipPtrs<R> g, const EnvPtrs<R> ge, const uin
         ge.eps_dist[env] = 0.0; ge.samp_dist[env] = 0.0;
         ge.prev_n[env] = 0.0; ge.prev_e[env] = 0.0;
         ge.ep_return[env] = (R)0; ge.ep_steps[env] = 0;
+        ge.n_dec[env] = 0;
     }
 }
 
@@ -202,9 +212,13 @@ __device__ __forceinline__ bool hull_inside(const EnvKArgs<R>& A, R n, R e, R ha
 #ifndef SIT_ENV_MINB_F32
 #define SIT_ENV_MINB_F32 4
 #endif
-template <typename R, bool SAME>
-__global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
-                                                       const EnvPtrs<R> ge, const int K, const EnvIO<R> io) {
+// ROLL: device-resident rollout (sit_rollout_step_k): envs waiting for a policy action do not step, the decision
+// step's transition is completed in the replay ring, finished episodes restart in-kernel and new decision events are
+// detected after every step.  Lanes of one env always take the same branches, so the pair exchanges use a two-lane mask.
+template <typename R, bool SAME, bool ROLL>
+__global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2)
+env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, const EnvPtrs<R> ge, const int K,
+                const EnvIO<R> io, const RollArgs ro) {
     const unsigned FULL = 0xffffffffu;
     __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
     stage_edges(A.M, s_edges);
@@ -219,6 +233,7 @@ __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) en
     const ShipP<R>& P = SAME ? A.P[0] : A.P[role];
     const EnvP<R>& EP = A.EP;
     const int lane = threadIdx.x & 31;
+    const unsigned PAIR = 3u << (lane & 30);
 
     Ship<R> s;
     load_ship(s, g, i);
@@ -229,19 +244,28 @@ __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) en
     int nstored = (flags & F_NSTORED_MASK) >> F_NSTORED_SHIFT;
     bool fresh = (flags & F_FRESH) != 0;
     bool iw_bad = (flags & F_IW_BAD) != 0, iw_valid = (flags & F_IW_VALID) != 0;
+    bool pending = ROLL && (flags & F_PENDING) != 0, have_act = ROLL && (flags & F_HAVE_ACT) != 0, tr_open = false;
     double prev_n = ge.prev_n[env], prev_e = ge.prev_e[env];
     double eps_dist = ge.eps_dist[env], samp_dist = ge.samp_dist[env];
     R ab_seg = ge.ab_seg[env], act_n = ge.act_n[env], act_e = ge.act_e[env];
     R ep_return = ge.ep_return[env];
     int32_t ep_steps = ge.ep_steps[env];
+    int32_t n_dec = ROLL ? ge.n_dec[env] : 0;
     R rsum = (R)0;
     bool any_done = false;
     unsigned my_cnt = 0;   // lane b < 12 counts status bit b of this warp's envs; lane 12 counts done steps
+    unsigned n_live = 0;   // env-steps actually executed by this lane (ROLL: pending envs do not step)
 
     for (int t = 0; t < K; ++t) {
         // ---- inputs: converted_action and SAC_update (MSRL_env_ex.py:402-405) -----------------------
-        bool su = false;
-        if (io.action) {
+        bool su = false, live = true;
+        if (ROLL) {
+            if (pending) {
+                if (have_act) { su = true; pending = false; have_act = false; tr_open = true; }   // action from sit_rollout_policy
+                else live = false;
+            }
+            if (!__any_sync(FULL, live && active)) break;
+        } else if (io.action) {
             const int64_t ta = io.act_steps > 1 ? t : 0;
             const R a_n = io.action[(ta * 2 + 0) * B + env], a_e = io.action[(ta * 2 + 1) * B + env];
             if (!iw_valid || a_n != act_n || a_e != act_e) {
@@ -254,7 +278,11 @@ __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) en
             }
             if (io.sac_update && (io.act_steps > 1 || t == 0)) su = io.sac_update[ta * B + env] != 0;
         }
-        const bool init = io.init >= 0 ? (t == 0 && io.init != 0) : fresh;
+        int status = 0;
+        bool done = false;
+        if (live) {
+        n_live += 1;
+        const bool init = (ROLL || io.init < 0) ? fresh : (t == 0 && io.init != 0);
         const bool frozen = is_obs && stop;
         const double pre_n = s.N, pre_e = s.E;
         StepOut<R> o;
@@ -294,7 +322,7 @@ __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) en
         }
 
         // ---- exchange post-step positions inside the lane pair ---------------------------------------
-        const double oth_n = __shfl_xor_sync(FULL, s.N, 1), oth_e = __shfl_xor_sync(FULL, s.E, 1);
+        const double oth_n = __shfl_xor_sync(PAIR, s.N, 1), oth_e = __shfl_xor_sync(PAIR, s.E, 1);
         const double n_t = is_obs ? oth_n : s.N, e_t = is_obs ? oth_e : s.E;
         const double n_o = is_obs ? s.N : oth_n, e_o = is_obs ? s.E : oth_e;
         const double ddn = n_t - n_o, dde = e_t - e_o;
@@ -329,31 +357,31 @@ __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) en
             // obs_ship_non_terminal_state_reward :666-710 (stop flag from before this step's checks)
             R nto = (R)0;
             if (!stop) nto = (R)0.1 + (-(abs_(ect) * EP.inv_e_tol) * (R)0.01) + (-((R)1 - dmap * EP.inv_max_north) * (R)0.01);
-            R ro = (R)0;
+            R ro_ = (R)0;
             // obs_ship_terminal_state_reward :811-881
             if (arrived) { stop = true; st |= SIT_ST_OBS_ENDPOINT; }                       // no done
             if (outside) { stop = true; dn_ = true; st |= SIT_ST_OBS_HORIZON; }
-            if (inside) { if (!stop) ro -= (R)1000; dn_ = true; st |= SIT_ST_OBS_TERRAIN; } // no stop flag
-            if (iw_bad) { if (!stop) ro -= (R)1000; stop = true; dn_ = true; st |= SIT_ST_OBS_IW; }
+            if (inside) { if (!stop) ro_ -= (R)1000; dn_ = true; st |= SIT_ST_OBS_TERRAIN; } // no stop flag
+            if (iw_bad) { if (!stop) ro_ -= (R)1000; stop = true; dn_ = true; st |= SIT_ST_OBS_IW; }
             if (abs_(ect) > EP.e_tol || samp_dist > (double)ab_seg * EP.theta) {
-                if (!stop) ro -= (R)1000; stop = true; dn_ = true; st |= SIT_ST_OBS_NAV;
+                if (!stop) ro_ -= (R)1000; stop = true; dn_ = true; st |= SIT_ST_OBS_NAV;
             }
             // shared_non_terminal_state_reward :712-731 (sees the stop flag after the checks above)
             R snt = (R)0;
             if (!stop) snt = ((R)1 - (R)sqrt(ship_d2) * EP.inv_max_north) * (R)0.001;
             part = nto;      // assembled below as ((((ntt+rt) + nto) + ro) + snt) + rs
             // stash ro, snt in o.* free slots
-            o.rud = ro; o.thr = snt;
+            o.rud = ro_; o.thr = snt;
         }
         // shared_terminal_state_reward :883-904, is_ship_collision :584-603
         const bool collide = ship_d2 < EP.collide2;
         if (collide) { stop = true; dn_ = true; st |= SIT_ST_COLLISION; }
 
-        const R part_t = __shfl_xor_sync(FULL, part, 1);
-        const int st_o = __shfl_xor_sync(FULL, st, 1);
-        const bool dn_o = __shfl_xor_sync(FULL, (int)dn_, 1) != 0;
-        const bool done = dn_ || dn_o;
-        const int status = st | st_o;
+        const R part_t = __shfl_xor_sync(PAIR, part, 1);
+        const int st_o = __shfl_xor_sync(PAIR, st, 1);
+        const bool dn_o = __shfl_xor_sync(PAIR, (int)dn_, 1) != 0;
+        done = dn_ || dn_o;
+        status = st | st_o;
         R reward = (R)0;
         if (is_obs) reward = ((((part_t + part) + o.rud) + o.thr)) + (collide ? (R)2000 : (R)0);   // :970-972
         rsum += reward; ep_return += reward; ep_steps += 1;
@@ -377,9 +405,74 @@ __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) en
                 if (io.status) io.status[rec * B + env] = status;
             }
         }
+        bool episode_end = done && io.auto_reset != 0;
+        if (ROLL) {
+            // main_ast.py:387: mask = 1 if episode_steps == num_steps_episode else float(not done); the reference's
+            // episode_steps counts init_step as 1, so it equals ep_steps + 1 here
+            const bool timeup = ro.max_episode_steps > 0 && ep_steps + 1 >= ro.max_episode_steps;
+            if (tr_open) {   // close the replay row opened by sit_rollout_policy: (reward, next_state, mask), :395-396
+                if (active) {
+                    float* row = ro.replay + (int64_t)ge.tr_slot[env] * SIT_TR_FLOATS;
+                    if (!is_obs) {
+                        row[12] = (float)pn; row[13] = (float)pe; row[14] = (float)s.psi; row[15] = (float)o.rpm;
+                        row[16] = (float)ect; row[17] = (float)o.power_me_kw;
+                    } else {
+                        row[18] = (float)pn; row[19] = (float)pe; row[20] = (float)s.psi; row[21] = (float)ect;
+                        row[11] = (float)reward; row[22] = timeup ? 1.0f : (done ? 0.0f : 1.0f);
+                    }
+                }
+                tr_open = false;
+            }
+            episode_end = done || timeup;
+        }
+        // ---- in-kernel reset() + init_step() right after a terminal step ---------------------------------
+        if (episode_end) {
+            reset_ship_regs(s, g, i, io.auto_reset == 2);   // MSRL_env_ex.py:145-186 (omega, integrators, fuel kept unless hard)
+            endN = g.wp_n[(int64_t)(s.n_wp - 1) * S + i]; endE = g.wp_e[(int64_t)(s.n_wp - 1) * S + i];
+            stop = false; nstored = 0; fresh = true;
+            eps_dist = 0.0; samp_dist = 0.0; prev_n = 0.0; prev_e = 0.0;
+            ep_return = (R)0; ep_steps = 0;
+            StepOut<R> o2;
+            ship_step<R, false>(P, s, g, i, false, false, o2, nullptr);   // init_step :188-215
+            if (ROLL) {
+                // the new episode's first decision acts on reset()'s float32 initial state (MSRL_env_ex.py:86-90,186)
+                pending = true; n_dec = 0;
+                if (active) {
+                    R* co = ge.cur_obs + env;
+                    if (!is_obs) {
+                        co[0] = (R)(float)g.init_north[i]; co[B] = (R)(float)g.init_east[i]; co[2 * B] = (R)(float)g.init_psi[i];
+                        co[3 * B] = (R)0; co[4 * B] = (R)0; co[5 * B] = (R)0;
+                    } else {
+                        co[6 * B] = (R)(float)g.init_north[i]; co[7 * B] = (R)(float)g.init_east[i];
+                        co[8 * B] = (R)(float)g.init_psi[i]; co[9 * B] = (R)0;
+                    }
+                }
+            }
+        } else if (ROLL) {
+            // decision event: the obstacle ship is inside the radius of acceptance of its current intermediate
+            // waypoint (controllers.py:317-325; the same squared test as the waypoint switch, LOS_guidance.py:96)
+            bool dec = false;
+            if (is_obs && !stop && n_dec < ro.sampling_frequency && s.k < s.n_wp - 1) {
+                const double dn = s.cN - s.N, de = s.cE - s.E;
+                dec = __dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de)) <= P.ra2;
+            }
+            dec = __shfl_sync(PAIR, (int)dec, lane | 1) != 0;
+            if (dec) {
+                pending = true;
+                if (active) {
+                    R* co = ge.cur_obs + env;
+                    if (!is_obs) {
+                        co[0] = pn; co[B] = pe; co[2 * B] = s.psi; co[3 * B] = o.rpm; co[4 * B] = ect; co[5 * B] = o.power_me_kw;
+                    } else {
+                        co[6 * B] = pn; co[7 * B] = pe; co[8 * B] = s.psi; co[9 * B] = ect;
+                    }
+                }
+            }
+        }
+        }   // live
         // ---- warp-level reduction of termination / collision flags --------------------------------------
         if (io.stats) {
-            const bool cnt_lane = active && is_obs;
+            const bool cnt_lane = active && is_obs && live;
             if (__any_sync(FULL, cnt_lane && status != 0)) {
 #pragma unroll
                 for (int b = 0; b < 12; ++b) {
@@ -390,16 +483,6 @@ __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) en
                 if (lane == 12) my_cnt += __popc(bal);
             }
         }
-        // ---- in-kernel reset() + init_step() right after a terminal step ---------------------------------
-        if (io.auto_reset && done) {
-            reset_ship_regs(s, g, i, io.auto_reset == 2);   // MSRL_env_ex.py:145-186 (omega, integrators, fuel kept unless hard)
-            endN = g.wp_n[(int64_t)(s.n_wp - 1) * S + i]; endE = g.wp_e[(int64_t)(s.n_wp - 1) * S + i];
-            stop = false; nstored = 0; fresh = true;
-            eps_dist = 0.0; samp_dist = 0.0; prev_n = 0.0; prev_e = 0.0;
-            ep_return = (R)0; ep_steps = 0;
-            StepOut<R> o2;
-            ship_step<R, false>(P, s, g, i, false, false, o2, nullptr);   // init_step :188-215
-        }
     }
 
     // ---- write back ------------------------------------------------------------------------------------------
@@ -408,20 +491,24 @@ __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2) en
         store_ship(s, g, i);
         if (is_obs) {
             int32_t f = (stop_t ? F_STOP_TEST : 0) | (stop ? F_STOP_OBS : 0) | (nstored << F_NSTORED_SHIFT) |
-                        (iw_bad ? F_IW_BAD : 0) | (iw_valid ? F_IW_VALID : 0) | (fresh ? F_FRESH : 0);
+                        (iw_bad ? F_IW_BAD : 0) | (iw_valid ? F_IW_VALID : 0) | (fresh ? F_FRESH : 0) |
+                        (pending ? F_PENDING : 0) | (have_act ? F_HAVE_ACT : 0);
             ge.flags[env] = f;
             ge.prev_n[env] = prev_n; ge.prev_e[env] = prev_e;
             ge.eps_dist[env] = eps_dist; ge.samp_dist[env] = samp_dist;
             ge.act_n[env] = act_n; ge.act_e[env] = act_e;
             ge.ep_return[env] = ep_return; ge.ep_steps[env] = ep_steps;
+            if (ROLL) ge.n_dec[env] = n_dec;
             if (io.reward_sum) io.reward_sum[env] = rsum;
             if (io.done_any) io.done_any[env] = any_done ? 1 : 0;
         }
     }
     if (io.stats) {
         if (lane <= 12 && my_cnt) atomicAdd(&io.stats[lane], (unsigned long long)my_cnt);
-        const unsigned n_env_lanes = __popc(__ballot_sync(FULL, active && is_obs));
-        if (lane == 13 && n_env_lanes) atomicAdd(&io.stats[13], (unsigned long long)n_env_lanes * (unsigned long long)K);
+        unsigned steps = (active && is_obs) ? n_live : 0u;   // env-steps executed by this warp
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) steps += __shfl_xor_sync(FULL, steps, d);
+        if (lane == 13 && steps) atomicAdd(&io.stats[13], (unsigned long long)steps);
     }
 }
 
@@ -440,6 +527,184 @@ __global__ void __launch_bounds__(256) env_init_step_kernel(const __grid_constan
     StepOut<R> o;
     ship_step<R, false>(P, s, g, i, false, false, o, nullptr);
     store_ship(s, g, i);
+}
+
+// =================================================================================================
+// K4: rollout policy -- for every pending env: tanh-Gaussian / uniform policy on its held observation, scoping
+// angle -> intermediate waypoint, validity resampling, replay row head.  One CTA scans 256 envs, compacts the
+// pending ones (deterministic order) and runs the MLP in tiles of 16 envs: thread j owns hidden unit j, the
+// 16 activations of each unit sit in shared memory as one 64-byte row read back with broadcast 128-bit loads.
+// =================================================================================================
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
+                                              uint32_t out[4]) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+struct PolicyArgs { int32_t mode, hidden; const float *w0, *b0, *w1, *b1, *w2, *b2; };
+
+#define POL_TILE 16
+template <typename R>
+__global__ void __launch_bounds__(256) rollout_policy_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
+                                                             const EnvPtrs<R> ge, const PolicyArgs pol, const RollArgs ro) {
+    __shared__ int s_list[256];
+    __shared__ int s_warp_cnt[8];
+    __shared__ int s_n;
+    __shared__ long long s_slot0;
+    __shared__ float s_obs[POL_TILE][SIT_N_OBS];
+    __shared__ __align__(16) float s_h[2][256][POL_TILE];   // [layer][unit][env]
+    __shared__ float s_out[POL_TILE][2];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t B = ge.n_envs, S = g.n_ships;
+    const int64_t env = (int64_t)blockIdx.x * 256 + tid;
+    // ---- deterministic compaction of the pending envs of this CTA ----------------------------------------------
+    int32_t fl = env < B ? ge.flags[env] : 0;
+    const bool pend = (fl & F_PENDING) && !(fl & F_HAVE_ACT);
+    const unsigned bal = __ballot_sync(0xffffffffu, pend);
+    if (lane == 0) s_warp_cnt[wid] = __popc(bal);
+    __syncthreads();
+    int off = 0, total = 0;
+    for (int w = 0; w < 8; ++w) { if (w < wid) off += s_warp_cnt[w]; total += s_warp_cnt[w]; }
+    if (pend) s_list[off + __popc(bal & ((1u << lane) - 1u))] = tid;
+    if (tid == 0) {
+        s_n = total;
+        s_slot0 = total ? (long long)atomicAdd(&ro.counters[SIT_RC_TRANSITIONS], (unsigned long long)total) : 0;
+        if (total) atomicAdd(&ro.counters[SIT_RC_DECISIONS], (unsigned long long)total);
+    }
+    __syncthreads();
+    const int n = s_n;
+    const int H = pol.hidden;
+    for (int t0 = 0; t0 < n; t0 += POL_TILE) {
+        const int nt = min(POL_TILE, n - t0);
+        // held observations of the tile (MSRL_env_ex.py:424-435 layout), as float32 like the reference's policy input
+        if (tid < POL_TILE * SIT_N_OBS) {
+            const int e = tid / SIT_N_OBS, c = tid % SIT_N_OBS;
+            s_obs[e][c] = e < nt ? (float)ge.cur_obs[(int64_t)c * B + (int64_t)blockIdx.x * 256 + s_list[t0 + e]] : 0.0f;
+        }
+        __syncthreads();
+        if (pol.mode != SIT_POLICY_UNIFORM) {
+            // layer 0: relu(b0 + obs . w0)   (nn_models/mlp.py:121-133)
+            if (tid < H) {
+                float acc[POL_TILE];
+                const float b = pol.b0[tid];
+#pragma unroll
+                for (int e = 0; e < POL_TILE; ++e) acc[e] = b;
+                for (int c = 0; c < SIT_N_OBS; ++c) {
+                    const float w = pol.w0[c * H + tid];
+#pragma unroll
+                    for (int e = 0; e < POL_TILE; ++e) acc[e] = fmaf(s_obs[e][c], w, acc[e]);
+                }
+#pragma unroll
+                for (int e = 0; e < POL_TILE; ++e) s_h[0][tid][e] = fmaxf(acc[e], 0.0f);
+            }
+            __syncthreads();
+            // layer 1: relu(b1 + h0 . w1)   (:135-142)
+            if (tid < H) {
+                float acc[POL_TILE];
+                const float b = pol.b1[tid];
+#pragma unroll
+                for (int e = 0; e < POL_TILE; ++e) acc[e] = b;
+                for (int k = 0; k < H; ++k) {
+                    const float w = pol.w1[(int64_t)k * H + tid];
+                    const float4* hp = reinterpret_cast<const float4*>(&s_h[0][k][0]);
+#pragma unroll
+                    for (int q = 0; q < POL_TILE / 4; ++q) {
+                        const float4 hv = hp[q];
+                        acc[4 * q + 0] = fmaf(hv.x, w, acc[4 * q + 0]); acc[4 * q + 1] = fmaf(hv.y, w, acc[4 * q + 1]);
+                        acc[4 * q + 2] = fmaf(hv.z, w, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(hv.w, w, acc[4 * q + 3]);
+                    }
+                }
+#pragma unroll
+                for (int e = 0; e < POL_TILE; ++e) s_h[1][tid][e] = fmaxf(acc[e], 0.0f);
+            }
+            __syncthreads();
+            // output layer: (mu, log_sigma) = b2 + h1 . w2, no output nonlinearity (distributions/normal.py:78-83)
+            if (tid < POL_TILE * 2) {
+                const int e = tid >> 1, c = tid & 1;
+                float acc = pol.b2[c];
+                for (int k = 0; k < H; ++k) acc = fmaf(s_h[1][k][e], pol.w2[k * 2 + c], acc);
+                s_out[e][c] = acc;
+            }
+            __syncthreads();
+        }
+        // ---- sample, convert, validate, publish: one thread per env of the tile ------------------------------------
+        if (tid < nt) {
+            const int64_t e = (int64_t)blockIdx.x * 256 + s_list[t0 + tid];
+            const int64_t gid = ro.env_id_offset + e;
+            const int32_t serial = ge.dec_serial[e];
+            const int32_t ndec = ge.n_dec[e];
+            const int64_t io_ = 2 * e + 1;                        // obstacle ship slot
+            // previous intermediate waypoint, or the route start for the first decision of the episode
+            const R base_n = ndec == 0 ? g.wp0_n[io_] : ge.act_n[e];
+            const R base_e = ndec == 0 ? g.wp0_e[io_] : ge.act_e[e];
+            const R L = ge.ab_seg[e], alpha = ge.ab_alpha[e];
+            float mu = 0.0f, sig = 0.0f;
+            if (pol.mode != SIT_POLICY_UNIFORM) {
+                mu = s_out[tid][0];
+                sig = expf(fminf(fmaxf(s_out[tid][1], -20.0f), 2.0f));   // LOG_SIG_CAP_MIN / MAX, normal.py:14-15,86-87
+            }
+            float a = 0.0f;
+            R wn = (R)0, we = (R)0;
+            bool bad = true;
+            int tries = 0;
+            const int max_tries = 1 + max(ro.max_route_resampling, 0);
+            while (bad && tries < max_tries) {
+                uint32_t x[4];
+                philox4x32_10((uint32_t)gid, (uint32_t)((uint64_t)gid >> 32), (uint32_t)serial, (uint32_t)tries,
+                              (uint32_t)ro.seed, (uint32_t)(ro.seed >> 32), x);
+                const double u1 = ((double)x[0] + 0.5) * (1.0 / 4294967296.0), u2 = ((double)x[1] + 0.5) * (1.0 / 4294967296.0);
+                if (pol.mode == SIT_POLICY_UNIFORM) {
+                    a = (float)(2.0 * u1 - 1.0);                      // policies/uniform_policy.py:21-22
+                } else if (pol.mode == SIT_POLICY_MEAN) {
+                    a = tanhf(mu);                                    // deterministic branch, gaussian_policy.py:129-141
+                } else {
+                    const float eps = (float)(sqrt(-2.0 * log(u1)) * cospi(2.0 * u2));
+                    a = tanhf(fmaf(sig, eps, mu));                    // normal.py:91-93, gaussian_policy.py:116-117
+                }
+                R sn, cs;
+                sincos_(alpha + (R)a * (R)0.52359877559829887308, sn, cs);   // scoping angle a * pi/6 about AB_alpha
+                wn = base_n + L * cs; we = base_e + L * sn;
+                bad = (wn < A.EP.min_n || wn > A.EP.max_n || we < A.EP.min_e || we > A.EP.max_e) || map_contains(A.M, wn, we);
+                ++tries;
+                if (pol.mode == SIT_POLICY_MEAN) break;               // nothing to redraw
+            }
+            if (tries > 1) atomicAdd(&ro.counters[SIT_RC_RESAMPLES], (unsigned long long)(tries - 1));
+            ge.act_n[e] = wn; ge.act_e[e] = we;
+            ge.flags[e] = (ge.flags[e] & ~F_IW_BAD) | F_HAVE_ACT | F_IW_VALID | (bad ? F_IW_BAD : 0);
+            ge.n_dec[e] = ndec + 1; ge.dec_serial[e] = serial + 1;
+            const long long slot = (s_slot0 + t0 + tid) % ro.capacity;
+            ge.tr_slot[e] = (int32_t)slot;
+            float* row = ro.replay + slot * SIT_TR_FLOATS;
+#pragma unroll
+            for (int c = 0; c < SIT_N_OBS; ++c) row[c] = s_obs[tid][c];
+            row[10] = a;
+            row[23] = __int_as_float((int32_t)gid);
+        }
+        __syncthreads();
+    }
+}
+
+// arm a rollout: every env pending on reset()'s float32 initial state (MSRL_env_ex.py:86-90,186)
+template <typename R>
+__global__ void rollout_begin_kernel(const ShipPtrs<R> g, const EnvPtrs<R> ge) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t B = ge.n_envs;
+    if (e >= B) return;
+    ge.flags[e] = (ge.flags[e] & ~F_HAVE_ACT) | F_PENDING;
+    ge.n_dec[e] = 0;
+    R* co = ge.cur_obs + e;
+    const int64_t it = 2 * e, io_ = 2 * e + 1;
+    co[0] = (R)(float)g.init_north[it]; co[B] = (R)(float)g.init_east[it]; co[2 * B] = (R)(float)g.init_psi[it];
+    co[3 * B] = (R)0; co[4 * B] = (R)0; co[5 * B] = (R)0;
+    co[6 * B] = (R)(float)g.init_north[io_]; co[7 * B] = (R)(float)g.init_east[io_]; co[8 * B] = (R)(float)g.init_psi[io_];
+    co[9 * B] = (R)0;
 }
 
 // Map queries for a batch of candidate waypoints: is_route_outside_horizon (MSRL_env_ex.py:517-542), is_route_inside_obstacles
@@ -514,6 +779,8 @@ static const FieldDef kEnvFields[] = {
     {"prev_n", 'D', 1, true}, {"prev_e", 'D', 1, true}, {"eps_dist", 'D', 1, true}, {"samp_dist", 'D', 1, true},
     {"ab_seg", 'R', 1, true}, {"act_n", 'R', 1, true}, {"act_e", 'R', 1, true}, {"ep_return", 'R', 1, true},
     {"flags", 'I', 1, true}, {"ep_steps", 'I', 1, true},
+    {"ab_alpha", 'R', 1, true}, {"cur_obs", 'R', SIT_N_OBS, true},
+    {"n_dec", 'I', 1, true}, {"dec_serial", 'I', 1, true}, {"tr_slot", 'I', 1, true},
 };
 
 struct SitHandle_ {
@@ -726,6 +993,9 @@ static EnvPtrs<R> env_ptrs(const SitHandle_* h, void* st) {
     e.ab_seg = fptr<R>(h, st, "ab_seg"); e.act_n = fptr<R>(h, st, "act_n"); e.act_e = fptr<R>(h, st, "act_e");
     e.ep_return = fptr<R>(h, st, "ep_return");
     e.flags = fptr<int32_t>(h, st, "flags"); e.ep_steps = fptr<int32_t>(h, st, "ep_steps");
+    e.ab_alpha = fptr<R>(h, st, "ab_alpha"); e.cur_obs = fptr<R>(h, st, "cur_obs");
+    e.n_dec = fptr<int32_t>(h, st, "n_dec"); e.dec_serial = fptr<int32_t>(h, st, "dec_serial");
+    e.tr_slot = fptr<int32_t>(h, st, "tr_slot");
     return e;
 }
 
@@ -969,11 +1239,99 @@ static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaS
     const EnvPtrs<R> ge = env_ptrs<R>(h, state);
     const EnvKArgs<R>& A = HostSel<R>::env(h);
     const int block = 128, grid = grid_for(h->n_ships, block);
-    if (h->same_params) env_step_kernel<R, true><<<grid, block, 0, st>>>(A, g, ge, K, k);
-    else env_step_kernel<R, false><<<grid, block, 0, st>>>(A, g, ge, K, k);
+    RollArgs ra;
+    std::memset(&ra, 0, sizeof(ra));
+    if (h->same_params) env_step_kernel<R, true, false><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
+    else env_step_kernel<R, false, false><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
 }
+static int roll_args(SitHandle h, const SitRollout* ro, RollArgs& ra) {
+    if (!ro || !ro->replay || !ro->counters) return fail(SIT_E_INVALID, "SitRollout needs replay and counters");
+    if (ro->capacity < h->n_envs) return fail(SIT_E_INVALID, "replay capacity must be >= n_envs");
+    if (ro->capacity > 0x7fffffffLL) return fail(SIT_E_INVALID, "replay capacity too large");
+    std::memset(&ra, 0, sizeof(ra));
+    ra.replay = ro->replay; ra.capacity = ro->capacity; ra.counters = ro->counters;
+    ra.seed = ro->seed; ra.env_id_offset = ro->env_id_offset;
+    ra.max_episode_steps = ro->max_episode_steps; ra.max_route_resampling = ro->max_route_resampling;
+    ra.sampling_frequency = (int32_t)h->cfg.sampling_frequency;
+    return SIT_OK;
+}
+
+template <typename R>
+static int rollout_step_t(SitHandle h, void* state, int K, const RollArgs& ra, const SitEnvIO* io, cudaStream_t st) {
+    EnvIO<R> k;
+    std::memset(&k, 0, sizeof(k));
+    k.init = -1; k.rec_steps = 1; k.act_steps = 1; k.auto_reset = 1;
+    if (io) {
+        if (io->rec_steps > 1) return fail(SIT_E_INVALID, "sit_rollout_step_k records the last step only (rec_steps <= 1)");
+        k.auto_reset = io->auto_reset == 2 ? 2 : 1;
+        k.obs = static_cast<R*>(io->obs); k.reward = static_cast<R*>(io->reward); k.done = io->done; k.status = io->status;
+        k.reward_sum = static_cast<R*>(io->reward_sum); k.done_any = io->done_any; k.stats = io->stats;
+    }
+    const ShipPtrs<R> g = ship_ptrs<R>(h, state);
+    const EnvPtrs<R> ge = env_ptrs<R>(h, state);
+    const EnvKArgs<R>& A = HostSel<R>::env(h);
+    const int block = 128, grid = grid_for(h->n_ships, block);
+    if (h->same_params) env_step_kernel<R, true, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
+    else env_step_kernel<R, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+extern "C" {
+
+int sit_rollout_begin(SitHandle h, void* state, void* stream) {
+    if (!h || !state) return fail(SIT_E_INVALID, "null argument");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_rollout_begin needs a SIT_KIND_ENV handle");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int block = 256, grid = grid_for(h->n_envs, block);
+    if (h->cfg.precision == SIT_F64) rollout_begin_kernel<double><<<grid, block, 0, st>>>(ship_ptrs<double>(h, state), env_ptrs<double>(h, state));
+    else rollout_begin_kernel<float><<<grid, block, 0, st>>>(ship_ptrs<float>(h, state), env_ptrs<float>(h, state));
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const SitRollout* ro, void* stream) {
+    if (!h || !state || !pol) return fail(SIT_E_INVALID, "null argument");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_rollout_policy needs a SIT_KIND_ENV handle");
+    if (pol->mode < SIT_POLICY_UNIFORM || pol->mode > SIT_POLICY_MEAN) return fail(SIT_E_INVALID, "bad policy mode");
+    PolicyArgs pa;
+    std::memset(&pa, 0, sizeof(pa));
+    pa.mode = pol->mode; pa.hidden = pol->hidden;
+    if (pol->mode != SIT_POLICY_UNIFORM) {
+        if (pol->hidden < 32 || pol->hidden > 256 || pol->hidden % 32) return fail(SIT_E_INVALID, "policy hidden width must be a multiple of 32 in [32, 256]");
+        if (!pol->w0 || !pol->b0 || !pol->w1 || !pol->b1 || !pol->w2 || !pol->b2) return fail(SIT_E_INVALID, "policy weights missing");
+        pa.w0 = pol->w0; pa.b0 = pol->b0; pa.w1 = pol->w1; pa.b1 = pol->b1; pa.w2 = pol->w2; pa.b2 = pol->b2;
+    }
+    RollArgs ra;
+    int rc = roll_args(h, ro, ra);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int block = 256, grid = grid_for(h->n_envs, block);
+    if (h->cfg.precision == SIT_F64)
+        rollout_policy_kernel<double><<<grid, block, 0, st>>>(*h->kd, ship_ptrs<double>(h, state), env_ptrs<double>(h, state), pa, ra);
+    else
+        rollout_policy_kernel<float><<<grid, block, 0, st>>>(*h->kf, ship_ptrs<float>(h, state), env_ptrs<float>(h, state), pa, ra);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+int sit_rollout_step_k(SitHandle h, void* state, int32_t K, const SitRollout* ro, const SitEnvIO* io, void* stream) {
+    if (!h || !state) return fail(SIT_E_INVALID, "null argument");
+    if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_rollout_step_k needs a SIT_KIND_ENV handle");
+    RollArgs ra;
+    int rc = roll_args(h, ro, ra);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    return h->cfg.precision == SIT_F64 ? rollout_step_t<double>(h, state, K, ra, io, st) : rollout_step_t<float>(h, state, K, ra, io, st);
+}
+
+}  // extern "C"
 extern "C" {
 
 int sit_env_step_k(SitHandle h, void* state, int32_t K, const SitEnvIO* io, void* stream) {

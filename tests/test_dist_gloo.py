@@ -1,0 +1,58 @@
+"""World-size-2 `gloo` tests (CPU) of the only collectives of the framework: the post-segment gather of compacted
+replay rows and the reduction of the episode counters (sac_maritime_ast_b200/rollout.py)."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from sac_maritime_ast_b200.rollout import gather_replay, reduce_stats, shard_range
+    n_total = 11
+    lo, hi = shard_range(n_total, rank, world)
+    # rank r holds a different number of rows; row content encodes (global env id, index)
+    n = (hi - lo) * (rank + 1)
+    rows = torch.zeros((n, 24), dtype=torch.float32)
+    for j in range(n):
+        rows[j, 0], rows[j, 1] = lo + j % (hi - lo), j
+        rows[j, 23] = torch.tensor(lo + j % (hi - lo), dtype=torch.int32).view(torch.float32)
+    allrows = gather_replay(rows)
+    stats = torch.arange(16, dtype=torch.int64) * (rank + 1)
+    tot = reduce_stats(stats)
+    empty = gather_replay(torch.zeros((0, 24)) if rank == 0 else rows[:2])   # ragged incl. an empty rank
+    q.put((rank, allrows.clone(), tot.clone(), empty.shape[0], n))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gather_replay_and_reduce_stats_world2():
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda x: x[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    n_rows = [r[4] for r in res]
+    for rank, allrows, tot, n_empty, _ in res:
+        assert allrows.shape == (sum(n_rows), 24)
+        assert torch.equal(allrows, res[0][1])                       # same on every rank
+        assert torch.equal(tot, torch.arange(16, dtype=torch.int64) * 3)
+        assert n_empty == 2
+    # rank order preserved: first block is rank 0's rows
+    a = res[0][1]
+    assert torch.equal(a[:n_rows[0], 1], torch.arange(n_rows[0], dtype=torch.float32))
+    ids = a[:, 23].contiguous().view(torch.int32)
+    assert int(ids.min()) == 0 and int(ids.max()) == 10
