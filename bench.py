@@ -314,6 +314,10 @@ def run_b200(args, rank, world, local_rank):
         line["ast_env"] = ast
         ast_rec = env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", record_all=True)
         line["ast_env_recorded"] = {k: ast_rec[k] for k in ("value", "unit", "ms_per_launch", "write_gbs")}
+        # ---- SAC-AST rollout (BASELINE config 4): policy fused into the device loop, samples/s --------------------------
+        rl = rollout_leg(sit, dev)
+        rl.pop("sampler")
+        line["rollout"] = rl
     if rank == 0 and not args.no_cpu_baseline and not args.no_extras:
         n = calibrate_cpu_sample(KI, args.max_wp, per_step_s=4.0)
         rate, cores, total = cpu_ship_steps_per_s(n, KI, 4, 1, args.max_wp, SEED)
@@ -449,6 +453,42 @@ def env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", rec
             "auto_reset": "hard (fresh construction; the reference's reset keeps integrators, quirk Q3)",
             "episodes_done": int(st[12]), "env_steps_counted": int(st[13]),
             "status_counts": {i: int(st[i]) for i in range(12)}}
+
+
+def rollout_leg(sit, dev, B=65536, K=16, iters=40, warm_iters=20, hidden=256, precision="fp32", mode="gaussian",
+                env_id_offset=0):
+    """BASELINE config 4: SAC-AST rollout, policy MLP 10 -> 256 -> 256 -> 2 with fixed seeded weights evaluated on the
+    decision-event subset between step launches, transitions compacted into a device replay ring.  Returns
+    samples/s (pushed transitions) and env-steps/s actually executed (pending envs do not step)."""
+    import torch
+    from sac_maritime_ast_b200 import rollout as ro
+    env, g = make_bench_env(sit, dev, B, precision, SEED)
+    if mode == "uniform":
+        pol = ro.UniformPolicy()
+    else:
+        pol = ro.GaussianPolicy(hidden_size=hidden, device=dev, seed=SEED, mode=mode)
+        pol.w0.mul_(1e-4)      # raw observations are ~1e4 m (the reference feeds them unnormalised): keep layer 0 O(1)
+    smp = ro.IntermediateWaypointSampler(env, pol, capacity=max(B * 4, 1 << 16), seed=SEED, env_id_offset=env_id_offset,
+                                         num_steps_episode=600, max_route_resampling=1000, auto_reset="hard")
+    smp.begin()
+    smp.collect(warm_iters, K)
+    torch.cuda.synchronize()
+    c0, s0, l0 = smp.counters.clone(), env.stats.clone(), smp.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    smp.collect(iters, K)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    dc, ds = (smp.counters - c0).cpu().numpy(), (env.stats - s0).cpu().numpy()
+    rows = smp.replay[:min(smp.n_transitions(), smp.capacity)]
+    return {"metric": "SAC-AST rollout samples/s", "value": float(dc[0]) / (ms * 1e-3), "unit": "samples/s",
+            "env_steps_per_s": float(ds[13]) / (ms * 1e-3), "envs": B, "k_per_launch": K, "iterations": iters,
+            "ms_per_iteration": ms / iters, "policy": f"{mode} MLP 10-{hidden}-{hidden}-2" if mode != "uniform" else "uniform",
+            "dtype": precision, "samples": int(dc[0]), "env_steps": int(ds[13]), "resamples": int(dc[2]),
+            "episodes": int(ds[12]), "lane_utilisation": float(ds[13]) / (B * K * iters),
+            "launches": smp.launches - l0, "bytes_per_sample": 96,
+            "replay_finite": bool(torch.isfinite(rows[:, :23]).all()), "sampler": smp}
 
 
 def main():

@@ -49,6 +49,7 @@ struct __align__(16) EdgeRec {
     R x1, y1, dx, dy;
     R len2, inv_len2, y2;
     typename IntOf<R>::type pbit;   // 1 << (polygon id & 31) ... per-polygon crossing parity lives in one 32-bit mask
+    R x2, _p0, _p1, _p2;            // third 128-bit word: only the containment test reads it
 };
 
 template <typename R>
@@ -61,40 +62,51 @@ __device__ __forceinline__ void stage_edges(const MapP<R>& m, EdgeRec<R>* sm) {
         EdgeRec<R> e;
         e.x1 = m.x1[i]; e.y1 = m.y1[i]; e.dx = m.dx[i]; e.dy = m.dy[i];
         e.len2 = m.len2[i]; e.inv_len2 = m.inv_len2[i]; e.y2 = m.y2[i];
+        e.x2 = m.x2[i]; e._p0 = e._p1 = e._p2 = (R)0;
         e.pbit = (typename IntOf<R>::type)(1u << (poly & 31));
         sm[i] = e;
     }
     __syncthreads();
 }
 
-// Literal point-in-any-polygon: obstacle.py:126-129 any(poly.contains(Point(e, n))), interior only.
-template <typename R>
-__device__ __noinline__ bool map_contains(const MapP<R>& m, R py /*north*/, R px /*east*/) {
-    int crossings = 0;
-    bool boundary = false, inside = false;
-    for (int i = 0; i < m.n_edges; ++i) {
-        if (!boundary) {
-            const R x1 = m.x1[i], y1 = m.y1[i], x2 = m.x2[i], y2 = m.y2[i];
-            if (!(x1 < px && x2 < px)) {
-                if (px == x2 && py == y2) {
-                    boundary = true;
-                } else if (y1 == py && y2 == py) {
-                    const R lo = x1 <= x2 ? x1 : x2, hi = x1 <= x2 ? x2 : x1;
-                    if (lo <= px && px <= hi) boundary = true;
-                } else if ((y1 > py && y2 <= py) || (y2 > py && y1 <= py)) {
-                    const R d = m.dx[i] * (py - y1) - m.dy[i] * (px - x1);
-                    if (d == (R)0) boundary = true;
-                    else if ((d > (R)0) != (y2 < y1)) crossings++;
-                }
-            }
-        }
-        if (m.poly_end[i]) {
-            inside |= (!boundary && (crossings & 1));
-            crossings = 0;
-            boundary = false;
+// Point-in-any-polygon for NP points at once: obstacle.py:126-129 any(poly.contains(Point(e, n))), interior only
+// (a point on a ring segment or vertex is boundary, hence not contained -- GEOS RayCrossingCounter, restated in
+// oracle/geometry.py ring_locate).  Branch-free form of the per-edge if / else-if chain: the three boundary cases are
+// mutually exclusive with a counted crossing, so they are OR-ed into a per-polygon boundary mask that vetoes the
+// polygon's parity bit at the end.
+template <typename R, int NP>
+__device__ __forceinline__ void map_contains_n(const EdgeRec<R>* __restrict__ E, const int n_edges, const R (&py)[NP],
+                                               const R (&px)[NP], bool (&inside)[NP]) {
+    uint32_t parity[NP], bmask[NP];
+#pragma unroll
+    for (int q = 0; q < NP; ++q) { parity[q] = 0u; bmask[q] = 0u; }
+#pragma unroll 2
+    for (int i = 0; i < n_edges; ++i) {
+        const EdgeRec<R> e = E[i];
+        const uint32_t pbit = (uint32_t)e.pbit;
+        const bool down = e.y2 < e.y1, horiz = e.y1 == e.y2;
+        const R lo = e.x1 <= e.x2 ? e.x1 : e.x2, hi = e.x1 <= e.x2 ? e.x2 : e.x1;
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const bool right = !(e.x1 < px[q] && e.x2 < px[q]);     // segments strictly left of the point never count
+            const bool straddle = (e.y1 > py[q] && e.y2 <= py[q]) || (e.y2 > py[q] && e.y1 <= py[q]);
+            const R d = e.dx * (py[q] - e.y1) - e.dy * (px[q] - e.x1);
+            const bool on = (px[q] == e.x2 && py[q] == e.y2) || (horiz && e.y1 == py[q] && lo <= px[q] && px[q] <= hi) ||
+                            (straddle && d == (R)0);
+            bmask[q] |= (right && on) ? pbit : 0u;
+            parity[q] ^= (right && straddle && ((d > (R)0) != down)) ? pbit : 0u;
         }
     }
-    return inside;
+#pragma unroll
+    for (int q = 0; q < NP; ++q) inside[q] = (parity[q] & ~bmask[q]) != 0u;
+}
+
+template <typename R>
+__device__ __forceinline__ bool map_contains(const EdgeRec<R>* __restrict__ E, const int n_edges, R py /*north*/, R px /*east*/) {
+    const R ay[1] = {py}, ax[1] = {px};
+    bool in[1];
+    map_contains_n<R, 1>(E, n_edges, ay, ax, in);
+    return in[0];
 }
 
 // One pass over the ring segments for the hull centre: squared distance to the nearest ring

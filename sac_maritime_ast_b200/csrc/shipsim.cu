@@ -199,14 +199,13 @@ __device__ __forceinline__ void reset_ship_regs(Ship<R>& s, const ShipPtrs<R>& g
 }
 
 template <typename R>
-__device__ __forceinline__ bool hull_inside(const EnvKArgs<R>& A, R n, R e, R half, R d2, bool centre_inside) {
+__device__ __forceinline__ bool hull_inside(const EdgeRec<R>* E, int n_edges, R near2, R n, R e, R half, R d2, bool centre_inside) {
     // is_pos_inside_obstacles, MSRL_env_ex.py:490-515: the four corners of the +-L/2 square
-    if (d2 > A.EP.near2) return centre_inside;
-    bool in = map_contains(A.M, n - half, e - half);
-    in |= map_contains(A.M, n - half, e + half);
-    in |= map_contains(A.M, n + half, e - half);
-    in |= map_contains(A.M, n + half, e + half);
-    return in;
+    if (d2 > near2) return centre_inside;
+    const R py[4] = {n - half, n - half, n + half, n + half}, px[4] = {e - half, e + half, e - half, e + half};
+    bool in[4];
+    map_contains_n<R, 4>(E, n_edges, py, px, in);
+    return in[0] | in[1] | in[2] | in[3];
 }
 
 #ifndef SIT_ENV_MINB_F32
@@ -273,7 +272,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
                 // action, cached until the action changes
                 act_n = a_n; act_e = a_e;
                 iw_bad = (a_n < EP.min_n || a_n > EP.max_n || a_e < EP.min_e || a_e > EP.max_e) ||
-                         map_contains(A.M, a_n, a_e);
+                         map_contains(s_edges, n_edges, a_n, a_e);
                 iw_valid = true;
             }
             if (io.sac_update && (io.act_steps > 1 || t == 0)) su = io.sac_update[ta * B + env] != 0;
@@ -332,7 +331,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         const R pn = (R)s.N, pe = (R)s.E;
         R d2map; bool c_in;
         map_scan(s_edges, n_edges, pn, pe, d2map, c_in);
-        const bool inside = hull_inside(A, pn, pe, EP.half_len[role], d2map, c_in);
+        const bool inside = hull_inside(s_edges, n_edges, EP.near2, pn, pe, EP.half_len[role], d2map, c_in);
         const R dmap = sqrt_(d2map);
         const bool outside = pn < EP.lo_n[role] || pn > EP.hi_n[role] || pe < EP.lo_e[role] || pe > EP.hi_e[role];
         const double dnE = s.N - (double)endN, deE = s.E - (double)endE;
@@ -561,6 +560,9 @@ __global__ void __launch_bounds__(256) rollout_policy_kernel(const __grid_consta
     __shared__ float s_obs[POL_TILE][SIT_N_OBS];
     __shared__ __align__(16) float s_h[2][256][POL_TILE];   // [layer][unit][env]
     __shared__ float s_out[POL_TILE][2];
+    __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
+    stage_edges(A.M, s_edges);
+    const int n_edges = A.M.n_edges;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int64_t B = ge.n_envs, S = g.n_ships;
     const int64_t env = (int64_t)blockIdx.x * 256 + tid;
@@ -634,9 +636,10 @@ __global__ void __launch_bounds__(256) rollout_policy_kernel(const __grid_consta
             }
             __syncthreads();
         }
-        // ---- sample, convert, validate, publish: one thread per env of the tile ------------------------------------
-        if (tid < nt) {
-            const int64_t e = (int64_t)blockIdx.x * 256 + s_list[t0 + tid];
+        // ---- sample, convert, validate, publish: one warp per env of the tile, lanes = resampling tries -------------
+        // (the first valid try in draw order wins, exactly as a sequential redraw loop would pick it)
+        for (int te = wid; te < nt; te += 8) {
+            const int64_t e = (int64_t)blockIdx.x * 256 + s_list[t0 + te];
             const int64_t gid = ro.env_id_offset + e;
             const int32_t serial = ge.dec_serial[e];
             const int32_t ndec = ge.n_dec[e];
@@ -647,45 +650,57 @@ __global__ void __launch_bounds__(256) rollout_policy_kernel(const __grid_consta
             const R L = ge.ab_seg[e], alpha = ge.ab_alpha[e];
             float mu = 0.0f, sig = 0.0f;
             if (pol.mode != SIT_POLICY_UNIFORM) {
-                mu = s_out[tid][0];
-                sig = expf(fminf(fmaxf(s_out[tid][1], -20.0f), 2.0f));   // LOG_SIG_CAP_MIN / MAX, normal.py:14-15,86-87
+                mu = s_out[te][0];
+                sig = expf(fminf(fmaxf(s_out[te][1], -20.0f), 2.0f));   // LOG_SIG_CAP_MIN / MAX, normal.py:14-15,86-87
             }
+            const int max_tries = pol.mode == SIT_POLICY_MEAN ? 1 : 1 + max(ro.max_route_resampling, 0);
             float a = 0.0f;
             R wn = (R)0, we = (R)0;
             bool bad = true;
             int tries = 0;
-            const int max_tries = 1 + max(ro.max_route_resampling, 0);
-            while (bad && tries < max_tries) {
+            for (int r0 = 0; r0 < max_tries && bad; r0 += 32) {
+                const int tr = r0 + lane;
                 uint32_t x[4];
-                philox4x32_10((uint32_t)gid, (uint32_t)((uint64_t)gid >> 32), (uint32_t)serial, (uint32_t)tries,
+                philox4x32_10((uint32_t)gid, (uint32_t)((uint64_t)gid >> 32), (uint32_t)serial, (uint32_t)tr,
                               (uint32_t)ro.seed, (uint32_t)(ro.seed >> 32), x);
                 const double u1 = ((double)x[0] + 0.5) * (1.0 / 4294967296.0), u2 = ((double)x[1] + 0.5) * (1.0 / 4294967296.0);
+                float la;
                 if (pol.mode == SIT_POLICY_UNIFORM) {
-                    a = (float)(2.0 * u1 - 1.0);                      // policies/uniform_policy.py:21-22
+                    la = (float)(2.0 * u1 - 1.0);                     // policies/uniform_policy.py:21-22
                 } else if (pol.mode == SIT_POLICY_MEAN) {
-                    a = tanhf(mu);                                    // deterministic branch, gaussian_policy.py:129-141
+                    la = tanhf(mu);                                   // deterministic branch, gaussian_policy.py:129-141
                 } else {
                     const float eps = (float)(sqrt(-2.0 * log(u1)) * cospi(2.0 * u2));
-                    a = tanhf(fmaf(sig, eps, mu));                    // normal.py:91-93, gaussian_policy.py:116-117
+                    la = tanhf(fmaf(sig, eps, mu));                   // normal.py:91-93, gaussian_policy.py:116-117
                 }
                 R sn, cs;
-                sincos_(alpha + (R)a * (R)0.52359877559829887308, sn, cs);   // scoping angle a * pi/6 about AB_alpha
-                wn = base_n + L * cs; we = base_e + L * sn;
-                bad = (wn < A.EP.min_n || wn > A.EP.max_n || we < A.EP.min_e || we > A.EP.max_e) || map_contains(A.M, wn, we);
-                ++tries;
-                if (pol.mode == SIT_POLICY_MEAN) break;               // nothing to redraw
+                sincos_(alpha + (R)la * (R)0.52359877559829887308, sn, cs);   // scoping angle a * pi/6 about AB_alpha
+                const R ln = base_n + L * cs, le = base_e + L * sn;
+                const bool lbad = (ln < A.EP.min_n || ln > A.EP.max_n || le < A.EP.min_e || le > A.EP.max_e) ||
+                                  map_contains(s_edges, n_edges, ln, le);
+                const unsigned ok = __ballot_sync(0xffffffffu, !lbad && tr < max_tries);
+                // winner: first valid try of this round, else the last try allowed (what a sequential loop ends on)
+                const int last = min(31, max_tries - 1 - r0);
+                const int src = ok ? (__ffs(ok) - 1) : last;
+                a = __shfl_sync(0xffffffffu, la, src);
+                wn = __shfl_sync(0xffffffffu, ln, src);
+                we = __shfl_sync(0xffffffffu, le, src);
+                bad = ok == 0u;
+                tries = r0 + src + 1;
             }
-            if (tries > 1) atomicAdd(&ro.counters[SIT_RC_RESAMPLES], (unsigned long long)(tries - 1));
-            ge.act_n[e] = wn; ge.act_e[e] = we;
-            ge.flags[e] = (ge.flags[e] & ~F_IW_BAD) | F_HAVE_ACT | F_IW_VALID | (bad ? F_IW_BAD : 0);
-            ge.n_dec[e] = ndec + 1; ge.dec_serial[e] = serial + 1;
-            const long long slot = (s_slot0 + t0 + tid) % ro.capacity;
-            ge.tr_slot[e] = (int32_t)slot;
-            float* row = ro.replay + slot * SIT_TR_FLOATS;
+            if (lane == 0) {
+                if (tries > 1) atomicAdd(&ro.counters[SIT_RC_RESAMPLES], (unsigned long long)(tries - 1));
+                ge.act_n[e] = wn; ge.act_e[e] = we;
+                ge.flags[e] = (ge.flags[e] & ~F_IW_BAD) | F_HAVE_ACT | F_IW_VALID | (bad ? F_IW_BAD : 0);
+                ge.n_dec[e] = ndec + 1; ge.dec_serial[e] = serial + 1;
+                const long long slot = (s_slot0 + t0 + te) % ro.capacity;
+                ge.tr_slot[e] = (int32_t)slot;
+                float* row = ro.replay + slot * SIT_TR_FLOATS;
 #pragma unroll
-            for (int c = 0; c < SIT_N_OBS; ++c) row[c] = s_obs[tid][c];
-            row[10] = a;
-            row[23] = __int_as_float((int32_t)gid);
+                for (int c = 0; c < SIT_N_OBS; ++c) row[c] = s_obs[te][c];
+                row[10] = a;
+                row[23] = __int_as_float((int32_t)gid);
+            }
         }
         __syncthreads();
     }
@@ -720,7 +735,7 @@ __global__ void __launch_bounds__(256) map_query_kernel(const __grid_constant__ 
     const R pn = north[i], pe = east[i];
     const EnvP<R>& EP = A.EP;
     uint8_t f = 0;
-    if (map_contains(A.M, pn, pe)) f |= 1;
+    if (map_contains(s_edges, A.M.n_edges, pn, pe)) f |= 1;
     if (pn < EP.min_n || pn > EP.max_n || pe < EP.min_e || pe > EP.max_e) f |= 2;
     if (flags) flags[i] = f;
     if (dist) {

@@ -12,6 +12,12 @@ which = sys.argv[1]
 dev = torch.device("cuda", 0)
 if which == "traj64":
     print(bench.traj_roofline(sit, dev))
+elif which.startswith("roll"):
+    kw = {}
+    for a in sys.argv[2:]:
+        k, v = a.split("=")
+        kw[k] = v if k in ("precision", "mode") else int(v)
+    r = bench.rollout_leg(sit, dev, **kw); r.pop("sampler"); print(r)
 elif which.startswith("env"):
     prec = "fp64" if "64" in which else "fp32"
     print(bench.env_leg(sit, dev, B=1 << 18 if prec == "fp32" else 1 << 16, K=64, steps=3, warmup=3, precision=prec,
