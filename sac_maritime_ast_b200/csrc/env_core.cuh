@@ -140,4 +140,123 @@ __device__ __forceinline__ void map_scan(const EdgeRec<R>* __restrict__ E, const
     centre_inside = parity != 0u;
 }
 
+// ---- nearest-ring cache ------------------------------------------------------------------------------------------
+// A ship moves a few metres per step while the rings are hundreds of metres away, so the edge that realises
+// obstacles_distance (obstacle.py:138-141) stays among the same few edges for tens of steps.  Each lane keeps the 4
+// edges nearest to the position p0 of its last scan and a displacement budget b = min((d5 - d1) / 2, d1) - 1 m
+// (d1, d5 = nearest / fifth-nearest segment distance at p0).  While |p - p0| < b the nearest segment at p is one of the
+// cached four (every other segment is at least d5 - |p - p0| away, segment distance being 1-Lipschitz) and the ship
+// cannot have crossed a ring (|p - p0| < d1), so the distance is the minimum over four segments and the containment
+// of the centre is the cached one -- bit-identical to the full scan.  A lane whose budget is spent is rescanned by the
+// WHOLE warp: lanes take 32 edges at a time, top-5 by five REDUX.MIN over (distance bits | edge index) keys, crossing
+// parity by one REDUX.XOR.
+struct MapCache {
+    uint32_t idx;      // four edge indices, 8 bits each
+    float p0n, p0e;    // position of the last scan
+    float b2;          // squared displacement budget; negative: the centre was inside a polygon at p0; 0: invalid
+};
+
+// squared distance to segment i (GEOS Distance::pointToSegment cases) and the orientation product
+template <typename R>
+__device__ __forceinline__ R segment_dist2(const EdgeRec<R>& e, R py, R px, R& cr) {
+    const R ex = px - e.x1, ey = py - e.y1;
+    const R v2 = ex * ex + ey * ey;
+    const R dot = ex * e.dx + ey * e.dy;
+    cr = e.dx * ey - e.dy * ex;
+    const R pr = cr * cr * e.inv_len2;
+    const R fx = px - e.x2, fy = py - e.y2;
+    const R w2 = fx * fx + fy * fy;                   // the next segment's first vertex: same bits as its v2
+    return dot <= (R)0 ? v2 : (dot >= e.len2 ? w2 : pr);
+}
+
+__device__ __forceinline__ float f32_down(double x) { return __double2float_rd(x); }
+__device__ __forceinline__ float f32_down(float x) { return x; }
+
+// all 32 lanes: scan the map for the point (py, px) of one lane; every lane gets the same result
+template <typename R>
+__device__ __forceinline__ MapCache coop_scan(const EdgeRec<R>* __restrict__ E, const int n_edges, R py, R px, int lane) {
+    const unsigned FULL = 0xffffffffu;
+    uint32_t key[SIT_MAX_EDGES / 32];
+    uint32_t parity = 0u;
+#pragma unroll
+    for (int m = 0; m < SIT_MAX_EDGES / 32; ++m) {
+        const int j = lane + 32 * m;
+        key[m] = 0xffffffffu;
+        if (32 * m < n_edges) {             // warp-uniform
+            if (j < n_edges) {
+                const EdgeRec<R> e = E[j];
+                R cr;
+                const R d2 = segment_dist2(e, py, px, cr);
+                key[m] = (__float_as_uint(f32_down(d2)) & 0xffffff80u) | (uint32_t)j;
+                const bool straddle = (e.y1 > py) != (e.y2 > py);
+                parity ^= (straddle && ((cr > (R)0) != (e.dy < (R)0))) ? (uint32_t)e.pbit : 0u;
+            }
+        }
+    }
+    uint32_t g[5];
+#pragma unroll
+    for (int r = 0; r < 5; ++r) {
+        uint32_t loc = key[0];
+#pragma unroll
+        for (int m = 1; m < SIT_MAX_EDGES / 32; ++m) loc = min(loc, key[m]);
+        g[r] = __reduce_min_sync(FULL, loc);
+#pragma unroll
+        for (int m = 0; m < SIT_MAX_EDGES / 32; ++m) key[m] = key[m] == g[r] ? 0xffffffffu : key[m];
+    }
+    parity = __reduce_xor_sync(FULL, parity);
+    MapCache c;
+    const uint32_t i0 = g[0] & 0x7fu;
+    c.idx = i0 | ((g[1] == 0xffffffffu ? i0 : (g[1] & 0x7fu)) << 8) | ((g[2] == 0xffffffffu ? i0 : (g[2] & 0x7fu)) << 16) |
+            ((g[3] == 0xffffffffu ? i0 : (g[3] & 0x7fu)) << 24);
+    c.p0n = (float)py; c.p0e = (float)px;
+    const float d1 = sqrtf(__uint_as_float(g[0] | 0x7fu));                                   // rounded up
+    const float d5 = g[4] == 0xffffffffu ? 1.0e6f : sqrtf(__uint_as_float(g[4] & 0xffffff80u));   // rounded down
+    const float b = fminf(0.5f * (d5 - d1), d1) - 1.0f;     // 1 m covers the float copies of p0 and of the keys
+    const float b2 = b > 0.0f ? b * b : 0.0f;
+    c.b2 = copysignf(b2, parity != 0u ? -1.0f : 1.0f);   // the sign bit survives b2 == 0
+    if (n_edges == 0 || g[0] == 0xffffffffu) { c.idx = 0u; c.b2 = 0.0f; }
+    return c;
+}
+
+// per lane: obstacles_distance^2 from the four cached segments
+template <typename R>
+__device__ __forceinline__ R cached_dist2(const EdgeRec<R>* __restrict__ E, uint32_t idx, R py, R px) {
+    R best = (R)3.0e38;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        R cr;
+        best = min_(best, segment_dist2(E[(idx >> (8 * r)) & 0xffu], py, px, cr));
+    }
+    return best;
+}
+
+// all 32 lanes: is any of the four hull corners of one lane's ship inside a polygon (MSRL_env_ex.py:490-515)
+template <typename R>
+__device__ __forceinline__ bool coop_hull_inside(const EdgeRec<R>* __restrict__ E, const int n_edges, R n, R e_, R half, int lane) {
+    const unsigned FULL = 0xffffffffu;
+    const R py[4] = {n - half, n - half, n + half, n + half}, px[4] = {e_ - half, e_ + half, e_ - half, e_ + half};
+    uint32_t parity[4] = {0u, 0u, 0u, 0u}, bmask[4] = {0u, 0u, 0u, 0u};
+    for (int j = lane; j < n_edges; j += 32) {
+        const EdgeRec<R> e = E[j];
+        const uint32_t pbit = (uint32_t)e.pbit;
+        const bool down = e.y2 < e.y1, horiz = e.y1 == e.y2;
+        const R lo = e.x1 <= e.x2 ? e.x1 : e.x2, hi = e.x1 <= e.x2 ? e.x2 : e.x1;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const bool right = !(e.x1 < px[q] && e.x2 < px[q]);
+            const bool straddle = (e.y1 > py[q] && e.y2 <= py[q]) || (e.y2 > py[q] && e.y1 <= py[q]);
+            const R d = e.dx * (py[q] - e.y1) - e.dy * (px[q] - e.x1);
+            const bool on = (px[q] == e.x2 && py[q] == e.y2) || (horiz && e.y1 == py[q] && lo <= px[q] && px[q] <= hi) ||
+                            (straddle && d == (R)0);
+            bmask[q] |= (right && on) ? pbit : 0u;
+            parity[q] ^= (right && straddle && ((d > (R)0) != down)) ? pbit : 0u;
+        }
+    }
+    bool in = false;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+        in |= (__reduce_xor_sync(FULL, parity[q]) & ~__reduce_or_sync(FULL, bmask[q])) != 0u;
+    return in;
+}
+
 }  // namespace sit

@@ -116,6 +116,7 @@ struct ShipPtrs {
         *init_u_sp, *init_omega, *init_ei_shaft;
     int32_t *k, *n_wp, *mode, *n_wp0, *steps;
     R *wp_n, *wp_e, *wp0_n, *wp0_e;  // [max_wp][n_ships]
+    int32_t* mc_idx; float *mc_n, *mc_e, *mc_b2;   // nearest-ring cache (env kernel)
     int64_t n_ships;
     int32_t max_wp, _pad;
 };

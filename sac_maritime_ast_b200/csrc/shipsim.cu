@@ -198,16 +198,6 @@ __device__ __forceinline__ void reset_ship_regs(Ship<R>& s, const ShipPtrs<R>& g
     }
 }
 
-template <typename R>
-__device__ __forceinline__ bool hull_inside(const EdgeRec<R>* E, int n_edges, R near2, R n, R e, R half, R d2, bool centre_inside) {
-    // is_pos_inside_obstacles, MSRL_env_ex.py:490-515: the four corners of the +-L/2 square
-    if (d2 > near2) return centre_inside;
-    const R py[4] = {n - half, n - half, n + half, n + half}, px[4] = {e - half, e + half, e - half, e + half};
-    bool in[4];
-    map_contains_n<R, 4>(E, n_edges, py, px, in);
-    return in[0] | in[1] | in[2] | in[3];
-}
-
 #ifndef SIT_ENV_MINB_F32
 #define SIT_ENV_MINB_F32 4
 #endif
@@ -254,6 +244,8 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     bool any_done = false;
     unsigned my_cnt = 0;   // lane b < 12 counts status bit b of this warp's envs; lane 12 counts done steps
     unsigned n_live = 0;   // env-steps actually executed by this lane (ROLL: pending envs do not step)
+    MapCache mc;           // nearest-ring cache, carried across launches in the state buffer
+    mc.idx = (uint32_t)g.mc_idx[i]; mc.p0n = g.mc_n[i]; mc.p0e = g.mc_e[i]; mc.b2 = g.mc_b2[i];
 
     for (int t = 0; t < K; ++t) {
         // ---- inputs: converted_action and SAC_update (MSRL_env_ex.py:402-405) -----------------------
@@ -279,13 +271,14 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         }
         int status = 0;
         bool done = false;
-        if (live) {
+        StepOut<R> o;
+        o.rpm = (R)0; o.power_me_kw = (R)0; o.avail_me_kw = (R)0; o.rud = (R)0; o.thr = (R)0;
+        double ship_d2 = 0.0;
+        if (live) {   // ---- phase A: the two ship steps ------------------------------------------------------
         n_live += 1;
         const bool init = (ROLL || io.init < 0) ? fresh : (t == 0 && io.init != 0);
         const bool frozen = is_obs && stop;
         const double pre_n = s.N, pre_e = s.E;
-        StepOut<R> o;
-        o.rpm = (R)0; o.power_me_kw = (R)0; o.avail_me_kw = (R)0;
         if (!frozen) {
             if (is_obs && su) {
                 // obs_step :324-338 -> update_route controllers.py:298-303: list.insert(-1, wp)
@@ -325,13 +318,35 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         const double n_t = is_obs ? oth_n : s.N, e_t = is_obs ? oth_e : s.E;
         const double n_o = is_obs ? s.N : oth_n, e_o = is_obs ? s.E : oth_e;
         const double ddn = n_t - n_o, dde = e_t - e_o;
-        const double ship_d2 = __dadd_rn(__dmul_rn(ddn, ddn), __dmul_rn(dde, dde));
+        ship_d2 = __dadd_rn(__dmul_rn(ddn, ddn), __dmul_rn(dde, dde));
+        }
 
-        // ---- own-ship geometry: distance to the nearest ring + hull containment ------------------------
+        // ---- phase B (whole warp): distance to the nearest ring + hull containment, nearest-ring cache -------
         const R pn = (R)s.N, pe = (R)s.E;
-        R d2map; bool c_in;
-        map_scan(s_edges, n_edges, pn, pe, d2map, c_in);
-        const bool inside = hull_inside(s_edges, n_edges, EP.near2, pn, pe, EP.half_len[role], d2map, c_in);
+        R d2map = (R)3.0e38;
+        bool inside = false;
+        if (n_edges > 0) {
+            const float ddn_ = (float)pn - mc.p0n, dde_ = (float)pe - mc.p0e;
+            unsigned nb = __ballot_sync(FULL, live && !(ddn_ * ddn_ + dde_ * dde_ < fabsf(mc.b2)));
+            while (nb) {   // budget spent: the whole warp rescans that lane's position
+                const int L = __ffs(nb) - 1;
+                nb &= nb - 1;
+                const MapCache c = coop_scan(s_edges, n_edges, __shfl_sync(FULL, pn, L), __shfl_sync(FULL, pe, L), lane);
+                if (lane == L) mc = c;
+            }
+            d2map = cached_dist2(s_edges, mc.idx, pn, pe);
+            inside = (__float_as_uint(mc.b2) >> 31) != 0u;   // far from every ring all four corners share the centre's side
+            unsigned hb = __ballot_sync(FULL, live && d2map <= EP.near2);
+            while (hb) {   // is_pos_inside_obstacles, MSRL_env_ex.py:490-515: the four corners of the +-L/2 square
+                const int L = __ffs(hb) - 1;
+                hb &= hb - 1;
+                const bool in = coop_hull_inside(s_edges, n_edges, __shfl_sync(FULL, pn, L), __shfl_sync(FULL, pe, L),
+                                                 __shfl_sync(FULL, EP.half_len[role], L), lane);
+                if (lane == L) inside = in;
+            }
+        }
+
+        if (live) {   // ---- phase C: rewards, terminal checks, outputs, episode restart ------------------------------
         const R dmap = sqrt_(d2map);
         const bool outside = pn < EP.lo_n[role] || pn > EP.hi_n[role] || pe < EP.lo_e[role] || pe > EP.hi_e[role];
         const double dnE = s.N - (double)endN, deE = s.E - (double)endE;
@@ -488,6 +503,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     const bool stop_t = __shfl_xor_sync(FULL, (int)stop, 1) != 0;   // the test lane's flag, seen by the obs lane
     if (active) {
         store_ship(s, g, i);
+        g.mc_idx[i] = (int32_t)mc.idx; g.mc_n[i] = mc.p0n; g.mc_e[i] = mc.p0e; g.mc_b2[i] = mc.b2;
         if (is_obs) {
             int32_t f = (stop_t ? F_STOP_TEST : 0) | (stop ? F_STOP_OBS : 0) | (nstored << F_NSTORED_SHIFT) |
                         (iw_bad ? F_IW_BAD : 0) | (iw_valid ? F_IW_VALID : 0) | (fresh ? F_FRESH : 0) |
@@ -789,6 +805,8 @@ static const FieldDef kShipFields[] = {
     {"k", 'I', 1, false}, {"n_wp", 'I', 1, false}, {"mode", 'I', 1, false}, {"n_wp0", 'I', 1, false},
     {"steps", 'I', 1, false},
     {"wp_n", 'R', -1, false}, {"wp_e", 'R', -1, false}, {"wp0_n", 'R', -1, false}, {"wp0_e", 'R', -1, false},
+    // nearest-ring cache of the env kernel (env_core.cuh MapCache): always float32
+    {"mc_idx", 'I', 1, false}, {"mc_n", 'F', 1, false}, {"mc_e", 'F', 1, false}, {"mc_b2", 'F', 1, false},
 };
 static const FieldDef kEnvFields[] = {
     {"prev_n", 'D', 1, true}, {"prev_e", 'D', 1, true}, {"eps_dist", 'D', 1, true}, {"samp_dist", 'D', 1, true},
@@ -953,7 +971,7 @@ static void build_layout(SitHandle_* h) {
         SitField f;
         std::memset(&f, 0, sizeof(f));
         std::snprintf(f.name, sizeof(f.name), "%s", d.name);
-        f.dtype = d.kind == 'D' ? SIT_DT_F64 : d.kind == 'I' ? SIT_DT_I32 : (f32 ? SIT_DT_F32 : SIT_DT_F64);
+        f.dtype = d.kind == 'D' ? SIT_DT_F64 : d.kind == 'I' ? SIT_DT_I32 : d.kind == 'F' ? SIT_DT_F32 : (f32 ? SIT_DT_F32 : SIT_DT_F64);
         f.rows = d.rows < 0 ? h->cfg.max_wp : d.rows;
         f.count = d.env ? h->n_envs : h->n_ships;
         const size_t esz = f.dtype == SIT_DT_F64 ? 8 : 4;
@@ -993,6 +1011,8 @@ static ShipPtrs<R> ship_ptrs(const SitHandle_* h, void* st) {
 #undef F_
     g.k = fptr<int32_t>(h, st, "k"); g.n_wp = fptr<int32_t>(h, st, "n_wp"); g.mode = fptr<int32_t>(h, st, "mode");
     g.n_wp0 = fptr<int32_t>(h, st, "n_wp0"); g.steps = fptr<int32_t>(h, st, "steps");
+    g.mc_idx = fptr<int32_t>(h, st, "mc_idx"); g.mc_n = fptr<float>(h, st, "mc_n"); g.mc_e = fptr<float>(h, st, "mc_e");
+    g.mc_b2 = fptr<float>(h, st, "mc_b2");
     g.n_ships = h->n_ships; g.max_wp = h->cfg.max_wp; g._pad = 0;
     return g;
 }
