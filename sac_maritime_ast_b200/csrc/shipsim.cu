@@ -564,161 +564,180 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
 }
 
 struct PolicyArgs { int32_t mode, hidden; const float *w0, *b0, *w1, *b1, *w2, *b2; };
+// scratch of one sit_rollout_policy call (device, owned by the handle): compact list of the pending envs
+struct PolScratch { unsigned int* n_pending; int32_t* env; float* obs; float* out; };   // env [B], obs [B][10], out [B][2]
 
-#define POL_TILE 16
+// ---- K4a: compact the pending envs, open their replay rows ---------------------------------------------------------
 template <typename R>
-__global__ void __launch_bounds__(256) rollout_policy_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
-                                                             const EnvPtrs<R> ge, const PolicyArgs pol, const RollArgs ro) {
-    __shared__ int s_list[256];
+__global__ void __launch_bounds__(256) rollout_gather_kernel(const EnvPtrs<R> ge, const RollArgs ro, const PolScratch sc) {
     __shared__ int s_warp_cnt[8];
-    __shared__ int s_n;
-    __shared__ long long s_slot0;
-    __shared__ float s_obs[POL_TILE][SIT_N_OBS];
-    __shared__ __align__(16) float s_h[2][256][POL_TILE];   // [layer][unit][env]
-    __shared__ float s_out[POL_TILE][2];
-    __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
-    stage_edges(A.M, s_edges);
-    const int n_edges = A.M.n_edges;
+    __shared__ unsigned int s_base;
+    __shared__ unsigned long long s_slot0;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int64_t B = ge.n_envs, S = g.n_ships;
+    const int64_t B = ge.n_envs;
     const int64_t env = (int64_t)blockIdx.x * 256 + tid;
-    // ---- deterministic compaction of the pending envs of this CTA ----------------------------------------------
-    int32_t fl = env < B ? ge.flags[env] : 0;
+    const int32_t fl = env < B ? ge.flags[env] : 0;
     const bool pend = (fl & F_PENDING) && !(fl & F_HAVE_ACT);
     const unsigned bal = __ballot_sync(0xffffffffu, pend);
     if (lane == 0) s_warp_cnt[wid] = __popc(bal);
     __syncthreads();
     int off = 0, total = 0;
     for (int w = 0; w < 8; ++w) { if (w < wid) off += s_warp_cnt[w]; total += s_warp_cnt[w]; }
-    if (pend) s_list[off + __popc(bal & ((1u << lane) - 1u))] = tid;
-    if (tid == 0) {
-        s_n = total;
-        s_slot0 = total ? (long long)atomicAdd(&ro.counters[SIT_RC_TRANSITIONS], (unsigned long long)total) : 0;
-        if (total) atomicAdd(&ro.counters[SIT_RC_DECISIONS], (unsigned long long)total);
+    if (tid == 0 && total) {
+        s_base = atomicAdd(sc.n_pending, (unsigned int)total);
+        s_slot0 = atomicAdd(&ro.counters[SIT_RC_TRANSITIONS], (unsigned long long)total);
+        atomicAdd(&ro.counters[SIT_RC_DECISIONS], (unsigned long long)total);
     }
     __syncthreads();
-    const int n = s_n;
+    if (!pend) return;
+    const unsigned int r = off + __popc(bal & ((1u << lane) - 1u));
+    const unsigned int p = s_base + r;
+    sc.env[p] = (int32_t)env;
+    const long long slot = (long long)((s_slot0 + r) % (unsigned long long)ro.capacity);
+    ge.tr_slot[env] = (int32_t)slot;
+    float* row = ro.replay + slot * SIT_TR_FLOATS;
+    // held observation (MSRL_env_ex.py:424-435 layout) as float32, like the reference's policy input and replay state
+#pragma unroll
+    for (int c = 0; c < SIT_N_OBS; ++c) {
+        const float v = (float)ge.cur_obs[(int64_t)c * B + env];
+        sc.obs[(int64_t)p * SIT_N_OBS + c] = v;
+        row[c] = v;
+    }
+    row[23] = __int_as_float((int32_t)(ro.env_id_offset + env));
+}
+
+// ---- K4b: policy MLP on the compact list, tiles of 16 rows: thread j owns hidden unit j, the 16 activations of each
+// unit sit in shared memory as one 64-byte row read back with broadcast 128-bit loads ------------------------------
+#define POL_TILE 16
+__global__ void __launch_bounds__(256) rollout_mlp_kernel(const PolicyArgs pol, const PolScratch sc) {
+    __shared__ float s_obs[POL_TILE][SIT_N_OBS];
+    __shared__ __align__(16) float s_h[2][256][POL_TILE];   // [layer][unit][row]
+    const int tid = threadIdx.x;
+    const int n = (int)*sc.n_pending;
     const int H = pol.hidden;
-    for (int t0 = 0; t0 < n; t0 += POL_TILE) {
+    for (int t0 = blockIdx.x * POL_TILE; t0 < n; t0 += gridDim.x * POL_TILE) {
         const int nt = min(POL_TILE, n - t0);
-        // held observations of the tile (MSRL_env_ex.py:424-435 layout), as float32 like the reference's policy input
         if (tid < POL_TILE * SIT_N_OBS) {
             const int e = tid / SIT_N_OBS, c = tid % SIT_N_OBS;
-            s_obs[e][c] = e < nt ? (float)ge.cur_obs[(int64_t)c * B + (int64_t)blockIdx.x * 256 + s_list[t0 + e]] : 0.0f;
+            s_obs[e][c] = e < nt ? sc.obs[(int64_t)(t0 + e) * SIT_N_OBS + c] : 0.0f;
         }
         __syncthreads();
+        // layer 0: relu(b0 + obs . w0)   (nn_models/mlp.py:121-133)
+        if (tid < H) {
+            float acc[POL_TILE];
+            const float b = pol.b0[tid];
+#pragma unroll
+            for (int e = 0; e < POL_TILE; ++e) acc[e] = b;
+            for (int c = 0; c < SIT_N_OBS; ++c) {
+                const float w = pol.w0[c * H + tid];
+#pragma unroll
+                for (int e = 0; e < POL_TILE; ++e) acc[e] = fmaf(s_obs[e][c], w, acc[e]);
+            }
+#pragma unroll
+            for (int e = 0; e < POL_TILE; ++e) s_h[0][tid][e] = fmaxf(acc[e], 0.0f);
+        }
+        __syncthreads();
+        // layer 1: relu(b1 + h0 . w1)   (:135-142)
+        if (tid < H) {
+            float acc[POL_TILE];
+            const float b = pol.b1[tid];
+#pragma unroll
+            for (int e = 0; e < POL_TILE; ++e) acc[e] = b;
+#pragma unroll 4
+            for (int k = 0; k < H; ++k) {
+                const float w = pol.w1[(int64_t)k * H + tid];
+                const float4* hp = reinterpret_cast<const float4*>(&s_h[0][k][0]);
+#pragma unroll
+                for (int q = 0; q < POL_TILE / 4; ++q) {
+                    const float4 hv = hp[q];
+                    acc[4 * q + 0] = fmaf(hv.x, w, acc[4 * q + 0]); acc[4 * q + 1] = fmaf(hv.y, w, acc[4 * q + 1]);
+                    acc[4 * q + 2] = fmaf(hv.z, w, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(hv.w, w, acc[4 * q + 3]);
+                }
+            }
+#pragma unroll
+            for (int e = 0; e < POL_TILE; ++e) s_h[1][tid][e] = fmaxf(acc[e], 0.0f);
+        }
+        __syncthreads();
+        // output layer: (mu, log_sigma) = b2 + h1 . w2, no output nonlinearity (distributions/normal.py:78-83)
+        if (tid < POL_TILE * 2) {
+            const int e = tid >> 1, c = tid & 1;
+            float acc = pol.b2[c];
+            for (int k = 0; k < H; ++k) acc = fmaf(s_h[1][k][e], pol.w2[k * 2 + c], acc);
+            if (e < nt) sc.out[(int64_t)(t0 + e) * 2 + c] = acc;
+        }
+        __syncthreads();
+    }
+}
+
+// ---- K4c: sample, convert, validate, publish: one warp per pending env, lanes = resampling tries (the first valid try
+// in draw order wins, exactly as a sequential redraw loop would pick it) -----------------------------------------------
+template <typename R>
+__global__ void __launch_bounds__(256) rollout_sample_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
+                                                             const EnvPtrs<R> ge, const PolicyArgs pol, const RollArgs ro,
+                                                             const PolScratch sc) {
+    __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
+    stage_edges(A.M, s_edges);
+    const int n_edges = A.M.n_edges;
+    const int lane = threadIdx.x & 31;
+    const int n = (int)*sc.n_pending;
+    const int warps = gridDim.x * (blockDim.x >> 5);
+    for (int p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < n; p += warps) {
+        const int64_t e = sc.env[p];
+        const int64_t gid = ro.env_id_offset + e;
+        const int32_t serial = ge.dec_serial[e];
+        const int32_t ndec = ge.n_dec[e];
+        const int64_t io_ = 2 * e + 1;                        // obstacle ship slot
+        // previous intermediate waypoint, or the route start for the first decision of the episode
+        const R base_n = ndec == 0 ? g.wp0_n[io_] : ge.act_n[e];
+        const R base_e = ndec == 0 ? g.wp0_e[io_] : ge.act_e[e];
+        const R L = ge.ab_seg[e], alpha = ge.ab_alpha[e];
+        float mu = 0.0f, sig = 0.0f;
         if (pol.mode != SIT_POLICY_UNIFORM) {
-            // layer 0: relu(b0 + obs . w0)   (nn_models/mlp.py:121-133)
-            if (tid < H) {
-                float acc[POL_TILE];
-                const float b = pol.b0[tid];
-#pragma unroll
-                for (int e = 0; e < POL_TILE; ++e) acc[e] = b;
-                for (int c = 0; c < SIT_N_OBS; ++c) {
-                    const float w = pol.w0[c * H + tid];
-#pragma unroll
-                    for (int e = 0; e < POL_TILE; ++e) acc[e] = fmaf(s_obs[e][c], w, acc[e]);
-                }
-#pragma unroll
-                for (int e = 0; e < POL_TILE; ++e) s_h[0][tid][e] = fmaxf(acc[e], 0.0f);
-            }
-            __syncthreads();
-            // layer 1: relu(b1 + h0 . w1)   (:135-142)
-            if (tid < H) {
-                float acc[POL_TILE];
-                const float b = pol.b1[tid];
-#pragma unroll
-                for (int e = 0; e < POL_TILE; ++e) acc[e] = b;
-                for (int k = 0; k < H; ++k) {
-                    const float w = pol.w1[(int64_t)k * H + tid];
-                    const float4* hp = reinterpret_cast<const float4*>(&s_h[0][k][0]);
-#pragma unroll
-                    for (int q = 0; q < POL_TILE / 4; ++q) {
-                        const float4 hv = hp[q];
-                        acc[4 * q + 0] = fmaf(hv.x, w, acc[4 * q + 0]); acc[4 * q + 1] = fmaf(hv.y, w, acc[4 * q + 1]);
-                        acc[4 * q + 2] = fmaf(hv.z, w, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(hv.w, w, acc[4 * q + 3]);
-                    }
-                }
-#pragma unroll
-                for (int e = 0; e < POL_TILE; ++e) s_h[1][tid][e] = fmaxf(acc[e], 0.0f);
-            }
-            __syncthreads();
-            // output layer: (mu, log_sigma) = b2 + h1 . w2, no output nonlinearity (distributions/normal.py:78-83)
-            if (tid < POL_TILE * 2) {
-                const int e = tid >> 1, c = tid & 1;
-                float acc = pol.b2[c];
-                for (int k = 0; k < H; ++k) acc = fmaf(s_h[1][k][e], pol.w2[k * 2 + c], acc);
-                s_out[e][c] = acc;
-            }
-            __syncthreads();
+            mu = sc.out[(int64_t)p * 2];
+            sig = expf(fminf(fmaxf(sc.out[(int64_t)p * 2 + 1], -20.0f), 2.0f));   // LOG_SIG_CAP_MIN / MAX, normal.py:14-15,86-87
         }
-        // ---- sample, convert, validate, publish: one warp per env of the tile, lanes = resampling tries -------------
-        // (the first valid try in draw order wins, exactly as a sequential redraw loop would pick it)
-        for (int te = wid; te < nt; te += 8) {
-            const int64_t e = (int64_t)blockIdx.x * 256 + s_list[t0 + te];
-            const int64_t gid = ro.env_id_offset + e;
-            const int32_t serial = ge.dec_serial[e];
-            const int32_t ndec = ge.n_dec[e];
-            const int64_t io_ = 2 * e + 1;                        // obstacle ship slot
-            // previous intermediate waypoint, or the route start for the first decision of the episode
-            const R base_n = ndec == 0 ? g.wp0_n[io_] : ge.act_n[e];
-            const R base_e = ndec == 0 ? g.wp0_e[io_] : ge.act_e[e];
-            const R L = ge.ab_seg[e], alpha = ge.ab_alpha[e];
-            float mu = 0.0f, sig = 0.0f;
-            if (pol.mode != SIT_POLICY_UNIFORM) {
-                mu = s_out[te][0];
-                sig = expf(fminf(fmaxf(s_out[te][1], -20.0f), 2.0f));   // LOG_SIG_CAP_MIN / MAX, normal.py:14-15,86-87
+        const int max_tries = pol.mode == SIT_POLICY_MEAN ? 1 : 1 + max(ro.max_route_resampling, 0);
+        float a = 0.0f;
+        R wn = (R)0, we = (R)0;
+        bool bad = true;
+        int tries = 0;
+        for (int r0 = 0; r0 < max_tries && bad; r0 += 32) {
+            const int tr = r0 + lane;
+            uint32_t x[4];
+            philox4x32_10((uint32_t)gid, (uint32_t)((uint64_t)gid >> 32), (uint32_t)serial, (uint32_t)tr,
+                          (uint32_t)ro.seed, (uint32_t)(ro.seed >> 32), x);
+            const double u1 = ((double)x[0] + 0.5) * (1.0 / 4294967296.0), u2 = ((double)x[1] + 0.5) * (1.0 / 4294967296.0);
+            float la;
+            if (pol.mode == SIT_POLICY_UNIFORM) {
+                la = (float)(2.0 * u1 - 1.0);                     // policies/uniform_policy.py:21-22
+            } else if (pol.mode == SIT_POLICY_MEAN) {
+                la = tanhf(mu);                                   // deterministic branch, gaussian_policy.py:129-141
+            } else {
+                const float eps = (float)(sqrt(-2.0 * log(u1)) * cospi(2.0 * u2));
+                la = tanhf(fmaf(sig, eps, mu));                   // normal.py:91-93, gaussian_policy.py:116-117
             }
-            const int max_tries = pol.mode == SIT_POLICY_MEAN ? 1 : 1 + max(ro.max_route_resampling, 0);
-            float a = 0.0f;
-            R wn = (R)0, we = (R)0;
-            bool bad = true;
-            int tries = 0;
-            for (int r0 = 0; r0 < max_tries && bad; r0 += 32) {
-                const int tr = r0 + lane;
-                uint32_t x[4];
-                philox4x32_10((uint32_t)gid, (uint32_t)((uint64_t)gid >> 32), (uint32_t)serial, (uint32_t)tr,
-                              (uint32_t)ro.seed, (uint32_t)(ro.seed >> 32), x);
-                const double u1 = ((double)x[0] + 0.5) * (1.0 / 4294967296.0), u2 = ((double)x[1] + 0.5) * (1.0 / 4294967296.0);
-                float la;
-                if (pol.mode == SIT_POLICY_UNIFORM) {
-                    la = (float)(2.0 * u1 - 1.0);                     // policies/uniform_policy.py:21-22
-                } else if (pol.mode == SIT_POLICY_MEAN) {
-                    la = tanhf(mu);                                   // deterministic branch, gaussian_policy.py:129-141
-                } else {
-                    const float eps = (float)(sqrt(-2.0 * log(u1)) * cospi(2.0 * u2));
-                    la = tanhf(fmaf(sig, eps, mu));                   // normal.py:91-93, gaussian_policy.py:116-117
-                }
-                R sn, cs;
-                sincos_(alpha + (R)la * (R)0.52359877559829887308, sn, cs);   // scoping angle a * pi/6 about AB_alpha
-                const R ln = base_n + L * cs, le = base_e + L * sn;
-                const bool lbad = (ln < A.EP.min_n || ln > A.EP.max_n || le < A.EP.min_e || le > A.EP.max_e) ||
-                                  map_contains(s_edges, n_edges, ln, le);
-                const unsigned ok = __ballot_sync(0xffffffffu, !lbad && tr < max_tries);
-                // winner: first valid try of this round, else the last try allowed (what a sequential loop ends on)
-                const int last = min(31, max_tries - 1 - r0);
-                const int src = ok ? (__ffs(ok) - 1) : last;
-                a = __shfl_sync(0xffffffffu, la, src);
-                wn = __shfl_sync(0xffffffffu, ln, src);
-                we = __shfl_sync(0xffffffffu, le, src);
-                bad = ok == 0u;
-                tries = r0 + src + 1;
-            }
-            if (lane == 0) {
-                if (tries > 1) atomicAdd(&ro.counters[SIT_RC_RESAMPLES], (unsigned long long)(tries - 1));
-                ge.act_n[e] = wn; ge.act_e[e] = we;
-                ge.flags[e] = (ge.flags[e] & ~F_IW_BAD) | F_HAVE_ACT | F_IW_VALID | (bad ? F_IW_BAD : 0);
-                ge.n_dec[e] = ndec + 1; ge.dec_serial[e] = serial + 1;
-                const long long slot = (s_slot0 + t0 + te) % ro.capacity;
-                ge.tr_slot[e] = (int32_t)slot;
-                float* row = ro.replay + slot * SIT_TR_FLOATS;
-#pragma unroll
-                for (int c = 0; c < SIT_N_OBS; ++c) row[c] = s_obs[te][c];
-                row[10] = a;
-                row[23] = __int_as_float((int32_t)gid);
-            }
+            R sn, cs;
+            sincos_(alpha + (R)la * (R)0.52359877559829887308, sn, cs);   // scoping angle a * pi/6 about AB_alpha
+            const R ln = base_n + L * cs, le = base_e + L * sn;
+            const bool lbad = (ln < A.EP.min_n || ln > A.EP.max_n || le < A.EP.min_e || le > A.EP.max_e) ||
+                              map_contains(s_edges, n_edges, ln, le);
+            const unsigned ok = __ballot_sync(0xffffffffu, !lbad && tr < max_tries);
+            // winner: first valid try of this round, else the last try allowed (what a sequential loop ends on)
+            const int last = min(31, max_tries - 1 - r0);
+            const int src = ok ? (__ffs(ok) - 1) : last;
+            a = __shfl_sync(0xffffffffu, la, src);
+            wn = __shfl_sync(0xffffffffu, ln, src);
+            we = __shfl_sync(0xffffffffu, le, src);
+            bad = ok == 0u;
+            tries = r0 + src + 1;
         }
-        __syncthreads();
+        if (lane == 0) {
+            if (tries > 1) atomicAdd(&ro.counters[SIT_RC_RESAMPLES], (unsigned long long)(tries - 1));
+            ge.act_n[e] = wn; ge.act_e[e] = we;
+            ge.flags[e] = (ge.flags[e] & ~F_IW_BAD) | F_HAVE_ACT | F_IW_VALID | (bad ? F_IW_BAD : 0);
+            ge.n_dec[e] = ndec + 1; ge.dec_serial[e] = serial + 1;
+            ro.replay[(int64_t)ge.tr_slot[e] * SIT_TR_FLOATS + 10] = a;
+        }
     }
 }
 
@@ -827,6 +846,7 @@ struct SitHandle_ {
     EnvKArgs<double>* kd; EnvKArgs<float>* kf;   // host copies passed by value at launch
     // scratch for the *_host entry point
     void* d_scratch; size_t scratch_bytes;
+    void* d_pol; size_t pol_bytes;               // sit_rollout_policy scratch
     void* h_pinned; size_t pinned_bytes;
 };
 
@@ -1101,6 +1121,7 @@ int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out)
         else { h->kf = new EnvKArgs<float>(); derive_env(*cfg, *h->kf); }
     }
     h->d_scratch = nullptr; h->scratch_bytes = 0; h->h_pinned = nullptr; h->pinned_bytes = 0;
+    h->d_pol = nullptr; h->pol_bytes = 0;
     build_layout(h);
     *out = h;
     return SIT_OK;
@@ -1109,6 +1130,7 @@ int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out)
 int sit_destroy(SitHandle h) {
     if (!h) return SIT_OK;
     if (h->d_scratch) cudaFree(h->d_scratch);
+    if (h->d_pol) cudaFree(h->d_pol);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     delete h->kd; delete h->kf;
     delete h;
@@ -1181,6 +1203,15 @@ static int ensure_scratch(SitHandle h, size_t total) {
     h->d_scratch = nullptr; h->scratch_bytes = 0;
     CUDA_TRY(cudaMalloc(&h->d_scratch, total));
     h->scratch_bytes = total;
+    return SIT_OK;
+}
+
+static int ensure_pol_scratch(SitHandle h, size_t total) {
+    if (h->pol_bytes >= total) return SIT_OK;
+    if (h->d_pol) cudaFree(h->d_pol);
+    h->d_pol = nullptr; h->pol_bytes = 0;
+    CUDA_TRY(cudaMalloc(&h->d_pol, total));
+    h->pol_bytes = total;
     return SIT_OK;
 }
 
@@ -1345,11 +1376,26 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
     if (rc) return rc;
     CUDA_TRY(cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const int block = 256, grid = grid_for(h->n_envs, block);
+    // scratch: pending counter | env list [B] | obs [B][10] | out [B][2]
+    const size_t B = (size_t)h->n_envs;
+    const size_t o_env = 256, o_obs = align_up(o_env + B * 4, 256), o_out = align_up(o_obs + B * SIT_N_OBS * 4, 256),
+                 total = align_up(o_out + B * 2 * 4, 256);
+    rc = ensure_pol_scratch(h, total);
+    if (rc) return rc;
+    char* d = static_cast<char*>(h->d_pol);
+    PolScratch sc;
+    sc.n_pending = reinterpret_cast<unsigned int*>(d); sc.env = reinterpret_cast<int32_t*>(d + o_env);
+    sc.obs = reinterpret_cast<float*>(d + o_obs); sc.out = reinterpret_cast<float*>(d + o_out);
+    CUDA_TRY(cudaMemsetAsync(sc.n_pending, 0, sizeof(unsigned int), st));
+    const int gather_grid = grid_for(h->n_envs, 256);
+    const int work_grid = h->sm_count * 4;   // persistent: tiles / warps stride over the pending list
+    if (h->cfg.precision == SIT_F64) rollout_gather_kernel<double><<<gather_grid, 256, 0, st>>>(env_ptrs<double>(h, state), ra, sc);
+    else rollout_gather_kernel<float><<<gather_grid, 256, 0, st>>>(env_ptrs<float>(h, state), ra, sc);
+    if (pa.mode != SIT_POLICY_UNIFORM) rollout_mlp_kernel<<<work_grid, 256, 0, st>>>(pa, sc);
     if (h->cfg.precision == SIT_F64)
-        rollout_policy_kernel<double><<<grid, block, 0, st>>>(*h->kd, ship_ptrs<double>(h, state), env_ptrs<double>(h, state), pa, ra);
+        rollout_sample_kernel<double><<<work_grid, 256, 0, st>>>(*h->kd, ship_ptrs<double>(h, state), env_ptrs<double>(h, state), pa, ra, sc);
     else
-        rollout_policy_kernel<float><<<grid, block, 0, st>>>(*h->kf, ship_ptrs<float>(h, state), env_ptrs<float>(h, state), pa, ra);
+        rollout_sample_kernel<float><<<work_grid, 256, 0, st>>>(*h->kf, ship_ptrs<float>(h, state), env_ptrs<float>(h, state), pa, ra, sc);
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
 }
