@@ -565,7 +565,7 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
 
 struct PolicyArgs { int32_t mode, hidden; const float *w0, *b0, *w1, *b1, *w2, *b2; };
 // scratch of one sit_rollout_policy call (device, owned by the handle): compact list of the pending envs
-struct PolScratch { unsigned int* n_pending; int32_t* env; float* obs; float* out; };   // env [B], obs [B][10], out [B][2]
+struct PolScratch { unsigned int *n_pending, *n_retry; int32_t *env, *retry; float *obs, *out; };   // env / retry [B], obs [B][10], out [B][2]
 
 // ---- K4a: compact the pending envs, open their replay rows ---------------------------------------------------------
 template <typename R>
@@ -669,8 +669,62 @@ __global__ void __launch_bounds__(256) rollout_mlp_kernel(const PolicyArgs pol, 
     }
 }
 
-// ---- K4c: sample, convert, validate, publish: one warp per pending env, lanes = resampling tries (the first valid try
-// in draw order wins, exactly as a sequential redraw loop would pick it) -----------------------------------------------
+// ---- K4c / K4d: sample, convert, validate, publish.  The first valid try in draw order wins, exactly as a sequential
+// redraw loop would pick it.  K4c: one warp per pending env, lanes = tries 0..31 (most envs finish here).  K4d: one CTA
+// per env that found no valid waypoint yet, threads = the next 256 tries per round (main_ast.py:49-51 allows 1000). -------
+template <typename R>
+struct TryCtx { int64_t gid; int32_t serial; R base_n, base_e, L, alpha; float mu, sig; };
+
+template <typename R>
+__device__ __forceinline__ void load_try_ctx(TryCtx<R>& c, const ShipPtrs<R>& g, const EnvPtrs<R>& ge, const PolicyArgs& pol,
+                                             const RollArgs& ro, const PolScratch& sc, int p, int64_t e) {
+    c.gid = ro.env_id_offset + e;
+    c.serial = ge.dec_serial[e];
+    const int64_t io_ = 2 * e + 1;                        // obstacle ship slot
+    // previous intermediate waypoint, or the route start for the first decision of the episode
+    const bool first = ge.n_dec[e] == 0;
+    c.base_n = first ? g.wp0_n[io_] : ge.act_n[e];
+    c.base_e = first ? g.wp0_e[io_] : ge.act_e[e];
+    c.L = ge.ab_seg[e]; c.alpha = ge.ab_alpha[e];
+    c.mu = 0.0f; c.sig = 0.0f;
+    if (pol.mode != SIT_POLICY_UNIFORM) {
+        c.mu = sc.out[(int64_t)p * 2];
+        c.sig = expf(fminf(fmaxf(sc.out[(int64_t)p * 2 + 1], -20.0f), 2.0f));   // LOG_SIG_CAP_MIN / MAX, normal.py:14-15,86-87
+    }
+}
+
+// try number tr of one decision: action, waypoint, validity
+template <typename R>
+__device__ __forceinline__ bool try_waypoint(const TryCtx<R>& c, const EnvKArgs<R>& A, const EdgeRec<R>* E, int n_edges,
+                                             int mode, uint64_t seed, int tr, float& la, R& ln, R& le) {
+    uint32_t x[4];
+    philox4x32_10((uint32_t)c.gid, (uint32_t)((uint64_t)c.gid >> 32), (uint32_t)c.serial, (uint32_t)tr, (uint32_t)seed,
+                  (uint32_t)(seed >> 32), x);
+    const double u1 = ((double)x[0] + 0.5) * (1.0 / 4294967296.0), u2 = ((double)x[1] + 0.5) * (1.0 / 4294967296.0);
+    if (mode == SIT_POLICY_UNIFORM) {
+        la = (float)(2.0 * u1 - 1.0);                     // policies/uniform_policy.py:21-22
+    } else if (mode == SIT_POLICY_MEAN) {
+        la = tanhf(c.mu);                                 // deterministic branch, gaussian_policy.py:129-141
+    } else {
+        const float eps = (float)(sqrt(-2.0 * log(u1)) * cospi(2.0 * u2));
+        la = tanhf(fmaf(c.sig, eps, c.mu));               // normal.py:91-93, gaussian_policy.py:116-117
+    }
+    R sn, cs;
+    sincos_(c.alpha + (R)la * (R)0.52359877559829887308, sn, cs);   // scoping angle a * pi/6 about AB_alpha
+    ln = c.base_n + c.L * cs; le = c.base_e + c.L * sn;
+    return (ln < A.EP.min_n || ln > A.EP.max_n || le < A.EP.min_e || le > A.EP.max_e) || map_contains(E, n_edges, ln, le);
+}
+
+template <typename R>
+__device__ __forceinline__ void publish_action(const EnvPtrs<R>& ge, const RollArgs& ro, int64_t e, float a, R wn, R we, bool bad,
+                                               int tries) {
+    if (tries > 1) atomicAdd(&ro.counters[SIT_RC_RESAMPLES], (unsigned long long)(tries - 1));
+    ge.act_n[e] = wn; ge.act_e[e] = we;
+    ge.flags[e] = (ge.flags[e] & ~F_IW_BAD) | F_HAVE_ACT | F_IW_VALID | (bad ? F_IW_BAD : 0);
+    ge.n_dec[e] += 1; ge.dec_serial[e] += 1;
+    ro.replay[(int64_t)ge.tr_slot[e] * SIT_TR_FLOATS + 10] = a;
+}
+
 template <typename R>
 __global__ void __launch_bounds__(256) rollout_sample_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
                                                              const EnvPtrs<R> ge, const PolicyArgs pol, const RollArgs ro,
@@ -681,63 +735,58 @@ __global__ void __launch_bounds__(256) rollout_sample_kernel(const __grid_consta
     const int lane = threadIdx.x & 31;
     const int n = (int)*sc.n_pending;
     const int warps = gridDim.x * (blockDim.x >> 5);
+    const int max_tries = pol.mode == SIT_POLICY_MEAN ? 1 : 1 + max(ro.max_route_resampling, 0);
     for (int p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); p < n; p += warps) {
         const int64_t e = sc.env[p];
-        const int64_t gid = ro.env_id_offset + e;
-        const int32_t serial = ge.dec_serial[e];
-        const int32_t ndec = ge.n_dec[e];
-        const int64_t io_ = 2 * e + 1;                        // obstacle ship slot
-        // previous intermediate waypoint, or the route start for the first decision of the episode
-        const R base_n = ndec == 0 ? g.wp0_n[io_] : ge.act_n[e];
-        const R base_e = ndec == 0 ? g.wp0_e[io_] : ge.act_e[e];
-        const R L = ge.ab_seg[e], alpha = ge.ab_alpha[e];
-        float mu = 0.0f, sig = 0.0f;
-        if (pol.mode != SIT_POLICY_UNIFORM) {
-            mu = sc.out[(int64_t)p * 2];
-            sig = expf(fminf(fmaxf(sc.out[(int64_t)p * 2 + 1], -20.0f), 2.0f));   // LOG_SIG_CAP_MIN / MAX, normal.py:14-15,86-87
+        TryCtx<R> c;
+        load_try_ctx(c, g, ge, pol, ro, sc, p, e);
+        float la; R ln, le;
+        const bool lbad = try_waypoint(c, A, s_edges, n_edges, pol.mode, ro.seed, lane, la, ln, le);
+        const unsigned ok = __ballot_sync(0xffffffffu, !lbad && lane < max_tries);
+        if (!ok && max_tries > 32) {              // no valid waypoint among the first 32 draws: CTA-wide rounds (K4d)
+            if (lane == 0) sc.retry[atomicAdd(sc.n_retry, 1u)] = p;
+            continue;
         }
-        const int max_tries = pol.mode == SIT_POLICY_MEAN ? 1 : 1 + max(ro.max_route_resampling, 0);
-        float a = 0.0f;
-        R wn = (R)0, we = (R)0;
-        bool bad = true;
-        int tries = 0;
-        for (int r0 = 0; r0 < max_tries && bad; r0 += 32) {
-            const int tr = r0 + lane;
-            uint32_t x[4];
-            philox4x32_10((uint32_t)gid, (uint32_t)((uint64_t)gid >> 32), (uint32_t)serial, (uint32_t)tr,
-                          (uint32_t)ro.seed, (uint32_t)(ro.seed >> 32), x);
-            const double u1 = ((double)x[0] + 0.5) * (1.0 / 4294967296.0), u2 = ((double)x[1] + 0.5) * (1.0 / 4294967296.0);
-            float la;
-            if (pol.mode == SIT_POLICY_UNIFORM) {
-                la = (float)(2.0 * u1 - 1.0);                     // policies/uniform_policy.py:21-22
-            } else if (pol.mode == SIT_POLICY_MEAN) {
-                la = tanhf(mu);                                   // deterministic branch, gaussian_policy.py:129-141
-            } else {
-                const float eps = (float)(sqrt(-2.0 * log(u1)) * cospi(2.0 * u2));
-                la = tanhf(fmaf(sig, eps, mu));                   // normal.py:91-93, gaussian_policy.py:116-117
+        const int src = ok ? (__ffs(ok) - 1) : (max_tries - 1);
+        if (lane == src) publish_action(ge, ro, e, la, ln, le, ok == 0u, src + 1);
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256) rollout_resample_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g,
+                                                               const EnvPtrs<R> ge, const PolicyArgs pol, const RollArgs ro,
+                                                               const PolScratch sc) {
+    __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
+    __shared__ int s_best;
+    stage_edges(A.M, s_edges);
+    const int n_edges = A.M.n_edges;
+    const int n = (int)*sc.n_retry;
+    const int max_tries = 1 + max(ro.max_route_resampling, 0);
+    for (int q = blockIdx.x; q < n; q += gridDim.x) {
+        const int p = sc.retry[q];
+        const int64_t e = sc.env[p];
+        TryCtx<R> c;
+        load_try_ctx(c, g, ge, pol, ro, sc, p, e);
+        if (threadIdx.x == 0) s_best = 0x7fffffff;
+        __syncthreads();
+        for (int r0 = 32; r0 < max_tries; r0 += 256) {
+            const int tr = r0 + threadIdx.x;
+            float la = 0.0f; R ln = (R)0, le = (R)0;
+            bool lbad = true;
+            if (tr < max_tries) {
+                lbad = try_waypoint(c, A, s_edges, n_edges, pol.mode, ro.seed, tr, la, ln, le);
+                if (!lbad) atomicMin(&s_best, tr);
             }
-            R sn, cs;
-            sincos_(alpha + (R)la * (R)0.52359877559829887308, sn, cs);   // scoping angle a * pi/6 about AB_alpha
-            const R ln = base_n + L * cs, le = base_e + L * sn;
-            const bool lbad = (ln < A.EP.min_n || ln > A.EP.max_n || le < A.EP.min_e || le > A.EP.max_e) ||
-                              map_contains(s_edges, n_edges, ln, le);
-            const unsigned ok = __ballot_sync(0xffffffffu, !lbad && tr < max_tries);
-            // winner: first valid try of this round, else the last try allowed (what a sequential loop ends on)
-            const int last = min(31, max_tries - 1 - r0);
-            const int src = ok ? (__ffs(ok) - 1) : last;
-            a = __shfl_sync(0xffffffffu, la, src);
-            wn = __shfl_sync(0xffffffffu, ln, src);
-            we = __shfl_sync(0xffffffffu, le, src);
-            bad = ok == 0u;
-            tries = r0 + src + 1;
+            __syncthreads();
+            const int best = s_best;
+            __syncthreads();   // everyone has read this round's verdict before the next round's atomicMin
+            if (best != 0x7fffffff) {
+                if (tr == best) publish_action(ge, ro, e, la, ln, le, false, tr + 1);
+                break;
+            }
+            if (tr == max_tries - 1) publish_action(ge, ro, e, la, ln, le, true, max_tries);   // every draw was invalid
         }
-        if (lane == 0) {
-            if (tries > 1) atomicAdd(&ro.counters[SIT_RC_RESAMPLES], (unsigned long long)(tries - 1));
-            ge.act_n[e] = wn; ge.act_e[e] = we;
-            ge.flags[e] = (ge.flags[e] & ~F_IW_BAD) | F_HAVE_ACT | F_IW_VALID | (bad ? F_IW_BAD : 0);
-            ge.n_dec[e] = ndec + 1; ge.dec_serial[e] = serial + 1;
-            ro.replay[(int64_t)ge.tr_slot[e] * SIT_TR_FLOATS + 10] = a;
-        }
+        __syncthreads();
     }
 }
 
@@ -1379,14 +1428,15 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
     // scratch: pending counter | env list [B] | obs [B][10] | out [B][2]
     const size_t B = (size_t)h->n_envs;
     const size_t o_env = 256, o_obs = align_up(o_env + B * 4, 256), o_out = align_up(o_obs + B * SIT_N_OBS * 4, 256),
-                 total = align_up(o_out + B * 2 * 4, 256);
+                 o_retry = align_up(o_out + B * 2 * 4, 256), total = align_up(o_retry + B * 4, 256);
     rc = ensure_pol_scratch(h, total);
     if (rc) return rc;
     char* d = static_cast<char*>(h->d_pol);
     PolScratch sc;
-    sc.n_pending = reinterpret_cast<unsigned int*>(d); sc.env = reinterpret_cast<int32_t*>(d + o_env);
+    sc.n_pending = reinterpret_cast<unsigned int*>(d); sc.n_retry = sc.n_pending + 1;
+    sc.env = reinterpret_cast<int32_t*>(d + o_env); sc.retry = reinterpret_cast<int32_t*>(d + o_retry);
     sc.obs = reinterpret_cast<float*>(d + o_obs); sc.out = reinterpret_cast<float*>(d + o_out);
-    CUDA_TRY(cudaMemsetAsync(sc.n_pending, 0, sizeof(unsigned int), st));
+    CUDA_TRY(cudaMemsetAsync(sc.n_pending, 0, 2 * sizeof(unsigned int), st));
     const int gather_grid = grid_for(h->n_envs, 256);
     const int work_grid = h->sm_count * 4;   // persistent: tiles / warps stride over the pending list
     if (h->cfg.precision == SIT_F64) rollout_gather_kernel<double><<<gather_grid, 256, 0, st>>>(env_ptrs<double>(h, state), ra, sc);
@@ -1396,6 +1446,12 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
         rollout_sample_kernel<double><<<work_grid, 256, 0, st>>>(*h->kd, ship_ptrs<double>(h, state), env_ptrs<double>(h, state), pa, ra, sc);
     else
         rollout_sample_kernel<float><<<work_grid, 256, 0, st>>>(*h->kf, ship_ptrs<float>(h, state), env_ptrs<float>(h, state), pa, ra, sc);
+    if (pa.mode != SIT_POLICY_MEAN && ra.max_route_resampling >= 32) {
+        if (h->cfg.precision == SIT_F64)
+            rollout_resample_kernel<double><<<work_grid, 256, 0, st>>>(*h->kd, ship_ptrs<double>(h, state), env_ptrs<double>(h, state), pa, ra, sc);
+        else
+            rollout_resample_kernel<float><<<work_grid, 256, 0, st>>>(*h->kf, ship_ptrs<float>(h, state), env_ptrs<float>(h, state), pa, ra, sc);
+    }
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
 }
