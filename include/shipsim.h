@@ -243,6 +243,11 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
  * rows, auto-resets finished episodes (io->auto_reset: 1 reference reset, 2 hard) and marks new decision events.
  * io may carry the usual outputs (rec_steps must be 1) and stats; io->action / sac_update / init are ignored. */
 int sit_rollout_step_k(SitHandle h, void* state, int32_t K, const SitRollout* ro, const SitEnvIO* io, void* stream);
+/* `iterations` x (sit_rollout_policy, sit_rollout_step_k(K)): the inner loop of main_ast.py:320-412 between two learner
+ * updates.  use_graph != 0 (and a non-default stream): one iteration is captured into a CUDA graph once and replayed, so
+ * the host pays one graph launch per iteration; the graph is re-captured when any argument changes.  Enqueues only. */
+int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K, const SitPolicy* pol, const SitRollout* ro,
+                        const SitEnvIO* io, int32_t use_graph, void* stream);
 /* mark every env pending at the start of a rollout (after sit_reset + sit_env_init_step) */
 int sit_rollout_begin(SitHandle h, void* state, void* stream);
 
@@ -250,6 +255,52 @@ int sit_rollout_begin(SitHandle h, void* state, void* stream);
  * (is_route_inside_obstacles MSRL_env_ex.py:544-552 -> obstacle.py:131-136), bit 1 = outside the map AABB
  * (is_route_outside_horizon :517-542); dist[i] = obstacles_distance (obstacle.py:138-141).  flags / dist may be NULL. */
 int sit_map_query(SitHandle h, int64_t n, const void* north, const void* east, uint8_t* flags, void* dist, void* stream);
+
+/* ---- SAC learner (the step after the path: the empty ast_core/algorithms/sac.py; call contract
+ * `critic_1_loss, critic_2_loss, policy_loss, ent_loss, alpha = agent.update_parameters(memory, batch_size, updates)`
+ * main_ast.py:350-357; hyper-parameters main_ast.py:41-68).  The reference's `ast_sac` agent is absent, so the update
+ * rule is DEFINED here as standard soft actor-critic with twin Q networks -- parity unpinned, checked against a plain
+ * PyTorch autograd restatement in tests/:
+ *   (s, a, r, s', mask) ~ uniform rows of the replay ring (SIT_TR_FLOATS layout above);
+ *   a' = tanh(mu(s') + sigma(s') eps'), log pi' = log N(eps') - log sigma - log(1 - a'^2 + 1e-6);
+ *   y = r + mask * gamma * (min(Q1t, Q2t)(s', a') - alpha log pi');     critic loss = mse(Q1(s,a), y) + mse(Q2(s,a), y);
+ *   policy loss = mean(alpha log pi(a~|s) - min(Q1, Q2)(s, a~)) with the updated critics, reparameterised;
+ *   alpha loss  = -mean(log_alpha * (log pi + target_entropy)), target_entropy = -1 (one action); alpha = exp(log_alpha)
+ *                 takes effect from the next update (the first update uses SitSacConfig.alpha);
+ *   Adam (beta 0.9 / 0.999, eps 1e-8) on policy, critics and log_alpha;  target <- (1 - tau) target + tau critic every
+ *   target_update_interval updates.
+ * Networks: policy 10 -> H -> H -> (mu, log sigma), Q(s, a) 11 -> H -> H -> 1, ReLU, Glorot-uniform weights, zero biases.
+ * The policy block has the SitPolicy layout, so the rollout kernels read the weights the learner is updating.
+ * All device memory is ONE caller-owned workspace (sit_sac_workspace_bytes, sit_sac_field); an update is ~35 small
+ * kernels captured once into a CUDA graph and replayed; every random draw is Philox keyed by (seed, update index). */
+typedef struct SitSacConfig {
+    int32_t hidden;                    /* H: multiple of 32 in [32, 256] (main_ast.py:67: 256) */
+    int32_t batch_size;                /* main_ast.py:63: 64; any 1..65536 */
+    float gamma, tau, lr, alpha;       /* main_ast.py:41-58: 0.99, 0.005, 3e-4, 0.2 */
+    int32_t automatic_entropy_tuning;  /* main_ast.py:59 */
+    int32_t target_update_interval;    /* main_ast.py:84 */
+    uint64_t seed;                     /* main_ast.py:61 */
+} SitSacConfig;
+typedef struct SitSac_* SitSac;
+enum { SIT_SAC_LOSS_Q1 = 0, SIT_SAC_LOSS_Q2 = 1, SIT_SAC_LOSS_POLICY = 2, SIT_SAC_LOSS_ALPHA = 3, SIT_SAC_ALPHA = 4,
+       SIT_SAC_MEAN_LOGPI = 5, SIT_SAC_MEAN_Q = 6, SIT_SAC_N_LOSS = 8 };
+
+int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out);
+int sit_sac_destroy(SitSac h);
+int sit_sac_workspace_bytes(SitSac h, size_t* nbytes);
+/* named float32 / int32 region of the workspace: "policy", "q1", "q2", "q1_target", "q2_target", "log_alpha", "alpha",
+ * "grad", "adam_m", "adam_v", "idx", "eps_next", "eps_cur", "losses", "updates".  offset in bytes, count in elements. */
+int sit_sac_field(SitSac h, const char* name, int64_t* offset, int64_t* count);
+/* Glorot-uniform weights (Philox, cfg.seed), zero biases, targets = critics, log_alpha = 0, Adam state and counter 0 */
+int sit_sac_init(SitSac h, void* workspace, void* stream);
+/* fill a SitPolicy (mode GAUSSIAN) with pointers into the workspace's policy block */
+int sit_sac_policy(SitSac h, void* workspace, SitPolicy* out);
+/* n_updates x update_parameters on batches drawn from replay[0 .. min(*n_rows, capacity)) (n_rows: device counter, e.g.
+ * SitRollout.counters + SIT_RC_TRANSITIONS; NULL = all `capacity` rows are valid).  losses (device, may be NULL)
+ * receives [SIT_SAC_N_LOSS] floats of the LAST update.  Enqueues only; fails if fewer rows than one batch is NOT checked
+ * on the host (the counter lives on the device): an empty replay draws row 0. */
+int sit_sac_update(SitSac h, void* workspace, const float* replay, int64_t capacity, const unsigned long long* n_rows,
+                   int32_t n_updates, float* losses, int32_t use_graph, void* stream);
 
 /* ---- misc ------------------------------------------------------------------------------------ */
 const char* sit_last_error(void);

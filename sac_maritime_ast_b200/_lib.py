@@ -92,7 +92,7 @@ POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
 RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_N = 0, 1, 2, 3, 8
 
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host",
-           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_policy", "sit_rollout_step_k",
+           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
            "sit_last_error", "sit_status_string", "sit_abi_version", "sit_measure_fma_peak")
 
 _lib = None
@@ -128,6 +128,7 @@ def lib():
     L.sit_rollout_begin.argtypes = [vp, vp, vp]
     L.sit_rollout_policy.argtypes = [vp, vp, P(SitPolicy), P(SitRollout), vp]
     L.sit_rollout_step_k.argtypes = [vp, vp, I32, P(SitRollout), P(SitEnvIO), vp]
+    L.sit_rollout_collect.argtypes = [vp, vp, I32, I32, P(SitPolicy), P(SitRollout), P(SitEnvIO), I32, vp]
     L.sit_map_query.argtypes = [vp, I64, vp, vp, vp, vp, vp]
     L.sit_last_error.restype = C.c_char_p
     L.sit_status_string.argtypes = [I32]

@@ -897,6 +897,8 @@ struct SitHandle_ {
     void* d_scratch; size_t scratch_bytes;
     void* d_pol; size_t pol_bytes;               // sit_rollout_policy scratch
     void* h_pinned; size_t pinned_bytes;
+    // sit_rollout_collect: instantiated CUDA graph of one (policy + K steps) iteration and the arguments it was captured for
+    cudaGraphExec_t roll_graph; std::string roll_key;
 };
 
 template <typename R> struct HostSel;
@@ -1171,6 +1173,7 @@ int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out)
     }
     h->d_scratch = nullptr; h->scratch_bytes = 0; h->h_pinned = nullptr; h->pinned_bytes = 0;
     h->d_pol = nullptr; h->pol_bytes = 0;
+    h->roll_graph = nullptr;
     build_layout(h);
     *out = h;
     return SIT_OK;
@@ -1181,6 +1184,7 @@ int sit_destroy(SitHandle h) {
     if (h->d_scratch) cudaFree(h->d_scratch);
     if (h->d_pol) cudaFree(h->d_pol);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
+    if (h->roll_graph) cudaGraphExecDestroy(h->roll_graph);
     delete h->kd; delete h->kf;
     delete h;
     return SIT_OK;
@@ -1466,6 +1470,62 @@ int sit_rollout_step_k(SitHandle h, void* state, int32_t K, const SitRollout* ro
     CUDA_TRY(cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     return h->cfg.precision == SIT_F64 ? rollout_step_t<double>(h, state, K, ra, io, st) : rollout_step_t<float>(h, state, K, ra, io, st);
+}
+
+// `iterations` x (sit_rollout_policy, sit_rollout_step_k(K)).  One iteration is captured once into a CUDA graph
+// (6 nodes) and replayed, so the loop costs one graph launch per iteration instead of six kernel launches through
+// the caller's language binding; the graph is re-captured when any argument changes.  use_graph == 0: plain launches.
+int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K, const SitPolicy* pol, const SitRollout* ro,
+                        const SitEnvIO* io, int32_t use_graph, void* stream) {
+    if (!h || !state || !pol || !ro) return fail(SIT_E_INVALID, "null argument");
+    if (iterations < 0 || K < 1) return fail(SIT_E_INVALID, "iterations must be >= 0 and K >= 1");
+    if (iterations == 0) return SIT_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (st != nullptr) CUDA_TRY(cudaStreamIsCapturing(st, &cs));
+    if (!use_graph || st == nullptr || cs != cudaStreamCaptureStatusNone) {   // legacy stream cannot be captured
+        for (int it = 0; it < iterations; ++it) {
+            int rc = sit_rollout_policy(h, state, pol, ro, stream);
+            if (rc) return rc;
+            rc = sit_rollout_step_k(h, state, K, ro, io, stream);
+            if (rc) return rc;
+        }
+        return SIT_OK;
+    }
+    std::string key;
+    key.append(reinterpret_cast<const char*>(&state), sizeof(state));
+    key.append(reinterpret_cast<const char*>(&K), sizeof(K));
+    key.append(reinterpret_cast<const char*>(pol), sizeof(*pol));
+    key.append(reinterpret_cast<const char*>(ro), sizeof(*ro));
+    SitEnvIO io0;
+    std::memset(&io0, 0, sizeof(io0));
+    if (io) io0 = *io;
+    key.append(reinterpret_cast<const char*>(&io0), sizeof(io0));
+    if (!h->roll_graph || key != h->roll_key) {
+        if (h->roll_graph) { cudaGraphExecDestroy(h->roll_graph); h->roll_graph = nullptr; }
+        // one eager iteration first: validates the arguments and sizes the scratch outside the capture
+        int rc = sit_rollout_policy(h, state, pol, ro, stream);
+        if (rc) return rc;
+        rc = sit_rollout_step_k(h, state, K, ro, io, stream);
+        if (rc) return rc;
+        if (--iterations == 0) return SIT_OK;
+        CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        rc = sit_rollout_policy(h, state, pol, ro, stream);
+        if (!rc) rc = sit_rollout_step_k(h, state, K, ro, io, stream);
+        cudaGraph_t graph = nullptr;
+        cudaError_t ce = cudaStreamEndCapture(st, &graph);
+        if (rc || ce != cudaSuccess) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc ? rc : fail(SIT_E_CUDA, std::string("graph capture: ") + cudaGetErrorString(ce));
+        }
+        ce = cudaGraphInstantiate(&h->roll_graph, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ce != cudaSuccess) { h->roll_graph = nullptr; return fail(SIT_E_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(ce)); }
+        h->roll_key = key;
+    }
+    for (int it = 0; it < iterations; ++it) CUDA_TRY(cudaGraphLaunch(h->roll_graph, st));
+    return SIT_OK;
 }
 
 }  // extern "C"

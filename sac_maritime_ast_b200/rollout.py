@@ -109,6 +109,7 @@ class IntermediateWaypointSampler:
         self.io.rec_steps = 1
         self.io.stats = env.stats.data_ptr()
         self.launches = 0
+        self._side = None
         self._pol = policy.struct()
 
     def set_policy(self, policy):
@@ -132,11 +133,26 @@ class IntermediateWaypointSampler:
         _lib.check(e.L.sit_rollout_step_k(e.h, e.state_ptr(), int(K), C.byref(self.ro), C.byref(self.io), e.stream()))
         self.launches += 1
 
-    def collect(self, iterations: int, K: int = 16):
-        """`iterations` x (policy on the pending envs, then K env steps).  Enqueues only."""
-        for _ in range(iterations):
-            self.policy_step()
-            self.env_steps(K)
+    def collect(self, iterations: int, K: int = 16, graph: bool = True):
+        """`iterations` x (policy on the pending envs, then K env steps).  Enqueues only.  With ``graph`` the loop runs
+        inside libshipsim (sit_rollout_collect): one iteration is captured into a CUDA graph on a side stream (the
+        legacy default stream cannot be captured) and replayed."""
+        e = self.env
+        if iterations <= 0:
+            return
+        if not graph:
+            for _ in range(iterations):
+                self.policy_step()
+                self.env_steps(K)
+            return
+        cur = torch.cuda.current_stream(e.device)
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=e.device)
+        self._side.wait_stream(cur)
+        _lib.check(e.L.sit_rollout_collect(e.h, e.state_ptr(), int(iterations), int(K), C.byref(self._pol), C.byref(self.ro),
+                                           C.byref(self.io), 1, self._side.cuda_stream))
+        cur.wait_stream(self._side)
+        self.launches += 5 * iterations       # gather + mlp + sample + resample + step kernels per iteration
 
     # ---- results ----------------------------------------------------------------------------------------------
     def n_transitions(self) -> int:

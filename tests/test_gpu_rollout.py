@@ -134,3 +134,22 @@ def test_shard_invariance_and_fp32_consistency():
     assert set(np.unique(rows[:, 22])) <= {0.0, 1.0}
     assert (np.abs(rows[:, 10]) <= 1.0).all()
     assert 0 < int(s32.env.stats[13].item()) <= 512 * 40 * 16
+
+
+def test_graph_collect_equals_eager_collect():
+    """sit_rollout_collect (CUDA graph of one iteration, replayed) == the same launches issued one by one: replay rows,
+    counters and env state bit-identical; changing K re-captures the graph."""
+    from sac_maritime_ast_b200 import rollout as ro
+    pol = ro.GaussianPolicy(hidden_size=64, device="cuda:0", seed=5)
+    pol.w0.mul_(1e-4)
+    a, b = _make(96, "fp32", pol, cap=200, auto_reset="hard"), _make(96, "fp32", pol, cap=200, auto_reset="hard")
+    for s, graph in ((a, True), (b, False)):
+        s.begin()
+        s.collect(iterations=25, K=16, graph=graph)
+        s.collect(iterations=10, K=8, graph=graph)
+    torch.cuda.synchronize()
+    assert a.n_transitions() == b.n_transitions() > 96
+    assert torch.equal(a.counters, b.counters) and torch.equal(a.env.stats, b.env.stats)
+    assert torch.equal(a.replay.view(torch.int32), b.replay.view(torch.int32))
+    for k in ("north", "east", "psi", "u", "omega", "flags", "ep_steps"):
+        assert torch.equal(a.env.f[k], b.env.f[k]), k
