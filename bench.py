@@ -316,8 +316,9 @@ def run_b200(args, rank, world, local_rank):
         line["ast_env_recorded"] = {k: ast_rec[k] for k in ("value", "unit", "ms_per_launch", "write_gbs")}
         # ---- SAC-AST rollout (BASELINE config 4): policy fused into the device loop, samples/s --------------------------
         rl = rollout_leg(sit, dev)
-        rl.pop("sampler")
+        smp_keep = rl.pop("sampler")
         line["rollout"] = rl
+        line["learner"] = learner_leg(sit, dev, smp_keep)
     if rank == 0 and not args.no_cpu_baseline and not args.no_extras:
         n = calibrate_cpu_sample(KI, args.max_wp, per_step_s=4.0)
         rate, cores, total = cpu_ship_steps_per_s(n, KI, 4, 1, args.max_wp, SEED)
@@ -489,6 +490,33 @@ def rollout_leg(sit, dev, B=65536, K=16, iters=40, warm_iters=20, hidden=256, pr
             "episodes": int(ds[12]), "lane_utilisation": float(ds[13]) / (B * K * iters),
             "launches": smp.launches - l0, "bytes_per_sample": 96,
             "replay_finite": bool(torch.isfinite(rows[:, :23]).all()), "sampler": smp}
+
+
+def learner_leg(sit, dev, sampler, batch=64, hidden=256, n=400, warm=50):
+    """SAC update_parameters/s (main_ast.py:354) on the replay ring the rollout leg filled: twin-Q SAC, policy and critics
+    10/11 -> 256 -> 256, batch 64 (main_ast.py:63-67), one CUDA-graph replay (35 kernels) per update."""
+    import torch
+    from sac_maritime_ast_b200 import sac
+    mem = sac.ReplayMemory.from_sampler(sampler)
+    out = {}
+    for b in (batch, 4096):
+        agent = sac.SAC(10, None, None, device=dev, hidden_size=hidden, batch_size=b, seed=SEED)
+        agent.update(mem, warm)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ls = agent.update(mem, n)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        flop = 3 * 2 * b * (2 * (11 * hidden + hidden * hidden + 2 * hidden) + 4 * (12 * hidden + hidden * hidden + hidden))
+        out[f"batch_{b}"] = {"updates_per_s": n / (ms * 1e-3), "us_per_update": ms * 1e3 / n, "samples_per_s": n * b / (ms * 1e-3),
+                             "approx_tflops": flop * n / (ms * 1e-3) / 1e12, "kernels_per_update": 35,
+                             "losses_finite": bool(torch.isfinite(ls).all()), "alpha": float(ls[4])}
+        agent.close()
+    out["replay_rows"] = len(mem)
+    out["metric"] = "SAC update_parameters/s (twin-Q, auto-alpha, Adam, soft target update), fp32, CUDA graph"
+    return out
 
 
 def main():

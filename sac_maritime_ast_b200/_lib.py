@@ -87,12 +87,20 @@ class SitRollout(C.Structure):
                 ("max_route_resampling", I32), ("replay", C.c_void_p), ("capacity", I64), ("counters", C.c_void_p)]
 
 
+class SitSacConfig(C.Structure):
+    _fields_ = [("hidden", I32), ("batch_size", I32), ("gamma", C.c_float), ("tau", C.c_float), ("lr", C.c_float),
+                ("alpha", C.c_float), ("automatic_entropy_tuning", I32), ("target_update_interval", I32),
+                ("seed", C.c_uint64)]
+
+
 TR_FLOATS = 24
 POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
 RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_N = 0, 1, 2, 3, 8
 
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host",
            "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
+           "sit_sac_create", "sit_sac_destroy", "sit_sac_workspace_bytes", "sit_sac_field", "sit_sac_init", "sit_sac_policy",
+           "sit_sac_update",
            "sit_last_error", "sit_status_string", "sit_abi_version", "sit_measure_fma_peak")
 
 _lib = None
@@ -130,6 +138,13 @@ def lib():
     L.sit_rollout_step_k.argtypes = [vp, vp, I32, P(SitRollout), P(SitEnvIO), vp]
     L.sit_rollout_collect.argtypes = [vp, vp, I32, I32, P(SitPolicy), P(SitRollout), P(SitEnvIO), I32, vp]
     L.sit_map_query.argtypes = [vp, I64, vp, vp, vp, vp, vp]
+    L.sit_sac_create.argtypes = [P(SitSacConfig), C.c_int, P(vp)]
+    L.sit_sac_destroy.argtypes = [vp]
+    L.sit_sac_workspace_bytes.argtypes = [vp, P(C.c_size_t)]
+    L.sit_sac_field.argtypes = [vp, C.c_char_p, P(I64), P(I64)]
+    L.sit_sac_init.argtypes = [vp, vp, vp]
+    L.sit_sac_policy.argtypes = [vp, vp, P(SitPolicy)]
+    L.sit_sac_update.argtypes = [vp, vp, vp, I64, vp, I32, vp, I32, vp]
     L.sit_last_error.restype = C.c_char_p
     L.sit_status_string.argtypes = [I32]
     L.sit_status_string.restype = C.c_char_p

@@ -1624,3 +1624,4 @@ int sit_measure_fma_peak(int device, int32_t precision, double* tflops, double* 
 }
 
 }  // extern "C"
+#include "sac_learner.cuh"

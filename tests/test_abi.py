@@ -32,14 +32,14 @@ def test_library_exports_every_declared_symbol():
 def test_ctypes_struct_sizes_match_the_header(tmp_path):
     from sac_maritime_ast_b200 import _lib
     prog = tmp_path / "sz.c"
-    prog.write_text('#include <stdio.h>\n#include "shipsim.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n",'
+    prog.write_text('#include <stdio.h>\n#include "shipsim.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
                     "sizeof(SitShipParams),sizeof(SitMap),sizeof(SitConfig),sizeof(SitField),sizeof(SitFleetIO),"
-                    "sizeof(SitEnvIO),sizeof(SitPolicy),sizeof(SitRollout));return 0;}\n")
+                    "sizeof(SitEnvIO),sizeof(SitPolicy),sizeof(SitRollout),sizeof(SitSacConfig));return 0;}\n")
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(prog)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     want = [C.sizeof(t) for t in (_lib.SitShipParams, _lib.SitMap, _lib.SitConfig, _lib.SitField, _lib.SitFleetIO,
-                                  _lib.SitEnvIO, _lib.SitPolicy, _lib.SitRollout)]
+                                  _lib.SitEnvIO, _lib.SitPolicy, _lib.SitRollout, _lib.SitSacConfig)]
     assert got == want
 
 

@@ -17,7 +17,9 @@ elif which.startswith("roll"):
     for a in sys.argv[2:]:
         k, v = a.split("=")
         kw[k] = v if k in ("precision", "mode") else int(v)
-    r = bench.rollout_leg(sit, dev, **kw); r.pop("sampler"); print(r)
+    r = bench.rollout_leg(sit, dev, **kw); smp = r.pop("sampler"); print(r)
+    if which == "roll_learn":
+        print(bench.learner_leg(sit, dev, smp))
 elif which.startswith("env"):
     prec = "fp64" if "64" in which else "fp32"
     print(bench.env_leg(sit, dev, B=1 << 18 if prec == "fp32" else 1 << 16, K=64, steps=3, warmup=3, precision=prec,
