@@ -457,7 +457,7 @@ def env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", rec
 
 
 def rollout_leg(sit, dev, B=65536, K=16, iters=40, warm_iters=20, hidden=256, precision="fp32", mode="gaussian",
-                env_id_offset=0):
+                env_id_offset=0, tc=1):
     """BASELINE config 4: SAC-AST rollout, policy MLP 10 -> 256 -> 256 -> 2 with fixed seeded weights evaluated on the
     decision-event subset between step launches, transitions compacted into a device replay ring.  Returns
     samples/s (pushed transitions) and env-steps/s actually executed (pending envs do not step)."""
@@ -467,7 +467,7 @@ def rollout_leg(sit, dev, B=65536, K=16, iters=40, warm_iters=20, hidden=256, pr
     if mode == "uniform":
         pol = ro.UniformPolicy()
     else:
-        pol = ro.GaussianPolicy(hidden_size=hidden, device=dev, seed=SEED, mode=mode)
+        pol = ro.GaussianPolicy(hidden_size=hidden, device=dev, seed=SEED, mode=mode, tensor_cores=bool(tc))
         pol.w0.mul_(1e-4)      # raw observations are ~1e4 m (the reference feeds them unnormalised): keep layer 0 O(1)
     smp = ro.IntermediateWaypointSampler(env, pol, capacity=max(B * 4, 1 << 16), seed=SEED, env_id_offset=env_id_offset,
                                          num_steps_episode=600, max_route_resampling=1000, auto_reset="hard")
@@ -486,6 +486,7 @@ def rollout_leg(sit, dev, B=65536, K=16, iters=40, warm_iters=20, hidden=256, pr
     return {"metric": "SAC-AST rollout samples/s", "value": float(dc[0]) / (ms * 1e-3), "unit": "samples/s",
             "env_steps_per_s": float(ds[13]) / (ms * 1e-3), "envs": B, "k_per_launch": K, "iterations": iters,
             "ms_per_iteration": ms / iters, "policy": f"{mode} MLP 10-{hidden}-{hidden}-2" if mode != "uniform" else "uniform",
+            "policy_hidden_layer": "tcgen05 bf16 x bf16 -> fp32 (TMEM)" if (tc and mode != "uniform") else "fp32 CUDA cores",
             "dtype": precision, "samples": int(dc[0]), "env_steps": int(ds[13]), "resamples": int(dc[2]),
             "episodes": int(ds[12]), "lane_utilisation": float(ds[13]) / (B * K * iters),
             "launches": smp.launches - l0, "bytes_per_sample": 96,

@@ -213,6 +213,10 @@ int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h,
  * so the policy runs batched over the pending subset between step launches and nothing returns to the host. */
 #define SIT_TR_FLOATS 24   /* replay row: s[0..9], a[10], r[11], s'[12..21], mask[22], global env id as int32 bits [23] */
 enum { SIT_POLICY_UNIFORM = 0, SIT_POLICY_GAUSSIAN = 1, SIT_POLICY_MEAN = 2 };
+/* OR into SitPolicy.mode: run the H x H hidden layer on the tensor cores (tcgen05.mma, bf16 operands -- layer-0 activations
+ * and w1 rounded to nearest-even bf16 -- fp32 accumulate in TMEM); everything else stays fp32.  Without it the whole MLP
+ * is fp32 on the CUDA cores. */
+enum { SIT_POLICY_TC_BF16 = 0x100 };
 enum { SIT_RC_TRANSITIONS = 0, SIT_RC_DECISIONS = 1, SIT_RC_RESAMPLES = 2, SIT_RC_EPISODES = 3, SIT_RC_N = 8 };
 
 typedef struct SitPolicy {

@@ -95,6 +95,7 @@ class SitSacConfig(C.Structure):
 
 TR_FLOATS = 24
 POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
+POLICY_TC_BF16 = 0x100
 RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_N = 0, 1, 2, 3, 8
 
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host",

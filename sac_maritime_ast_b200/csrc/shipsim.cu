@@ -669,6 +669,137 @@ __global__ void __launch_bounds__(256) rollout_mlp_kernel(const PolicyArgs pol, 
     }
 }
 
+// ---- K4b (tensor cores): the same MLP with the H x H hidden layer on tcgen05.  One CTA = one 128-row tile of pending
+// envs (persistent over tiles).  Layer 0 (K = 10) runs on the CUDA cores and writes relu(h0) as bf16 straight into shared
+// memory in the UMMA canonical K-major layout (8 x 16-byte core matrices, no swizzle); W1 is staged once per CTA as the
+// bf16 B operand (N x K, K-major, i.e. transposed on the way in).  One elected thread issues H/16 tcgen05.mma
+// (M = 128, N = H, K = 16, fp32 accumulate in TMEM) and commits to an mbarrier; the epilogue reads the accumulator rows
+// back with tcgen05.ld (thread = TMEM lane = env), applies bias + ReLU and folds the 2-wide output layer into the same
+// pass.  Numerics: bf16 inputs to the hidden-layer product (h0 and W1 rounded to nearest even), fp32 everywhere else.
+#define TC_M 128
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint64_t umma_desc_kmajor_noswizzle(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    // cute::UMMA::SmemDescriptor: start >> 4 [0,14) | LBO >> 4 [16,30) | SBO >> 4 [32,46) | version 1 [46,48) | layout NONE [61,64)
+    return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46);
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+
+__global__ void __launch_bounds__(256, 1) rollout_mlp_tc_kernel(const PolicyArgs pol, const PolScratch sc, const int tmem_cols) {
+    extern __shared__ __align__(128) unsigned char tc_smem[];
+    const int H = pol.hidden;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int n = (int)*sc.n_pending;
+    if ((int)blockIdx.x * TC_M >= n) return;                         // nothing for this CTA: leave before staging W1
+    unsigned char* sA = tc_smem;                                      // [128/8][H/8][8][8] bf16
+    unsigned char* sB = sA + (size_t)TC_M * H * 2;                    // [H/8][H/8][8][8] bf16, rows = output unit n
+    float* s_w2 = reinterpret_cast<float*>(sB + (size_t)H * H * 2);   // [H][2]
+    float* s_b1 = s_w2 + 2 * H;                                       // [H]
+    float* s_part = s_b1 + H;                                         // [128][2] partial output sums of the upper column half
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + 2 * TC_M);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 1);
+    const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;               // next 8-row group | next 16-byte K chunk
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    if (tid == 32) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::);
+    }
+    // W1 [k][n] (n contiguous) -> B operand: thread owns output unit nn and 8 consecutive k per 16-byte store
+    for (int item = tid; item < H * (H >> 3); item += 256) {
+        const int nn = item % H, kc = item / H;
+        const float* w = pol.w1 + (size_t)(kc * 8) * H + nn;
+        uint4 v;
+        v.x = pack_bf16x2(w[0], w[H]); v.y = pack_bf16x2(w[2 * H], w[3 * H]);
+        v.z = pack_bf16x2(w[4 * H], w[5 * H]); v.w = pack_bf16x2(w[6 * H], w[7 * H]);
+        *reinterpret_cast<uint4*>(sB + (size_t)(nn >> 3) * sbo + (size_t)kc * lbo + (nn & 7) * 16) = v;
+    }
+    for (int i = tid; i < 2 * H; i += 256) s_w2[i] = pol.w2[i];
+    for (int i = tid; i < H; i += 256) s_b1[i] = pol.b1[i];
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+    const uint32_t tmem_base = *s_tmem;
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(H >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
+    const int row = tid & (TC_M - 1), half = tid >> 7;                // TMEM lane / env of the tile | column half
+    const int kh = H >> 1;                                            // columns per half (multiple of 16)
+    uint32_t parity = 0;
+    for (int t0 = blockIdx.x * TC_M; t0 < n; t0 += gridDim.x * TC_M) {
+        // layer 0 on the CUDA cores: relu(b0 + obs . w0) for this thread's row and column half (nn_models/mlp.py:121-133)
+        float o[SIT_N_OBS];
+#pragma unroll
+        for (int c = 0; c < SIT_N_OBS; ++c) o[c] = (t0 + row) < n ? sc.obs[(int64_t)(t0 + row) * SIT_N_OBS + c] : 0.0f;
+        for (int k0 = half * kh; k0 < (half + 1) * kh; k0 += 8) {
+            float a[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = pol.b0[k0 + j];
+#pragma unroll
+            for (int c = 0; c < SIT_N_OBS; ++c) {
+                const float4 wa = *reinterpret_cast<const float4*>(pol.w0 + c * H + k0);
+                const float4 wb = *reinterpret_cast<const float4*>(pol.w0 + c * H + k0 + 4);
+                a[0] = fmaf(o[c], wa.x, a[0]); a[1] = fmaf(o[c], wa.y, a[1]); a[2] = fmaf(o[c], wa.z, a[2]); a[3] = fmaf(o[c], wa.w, a[3]);
+                a[4] = fmaf(o[c], wb.x, a[4]); a[5] = fmaf(o[c], wb.y, a[5]); a[6] = fmaf(o[c], wb.z, a[6]); a[7] = fmaf(o[c], wb.w, a[7]);
+            }
+            uint4 v;
+            v.x = pack_bf16x2(fmaxf(a[0], 0.f), fmaxf(a[1], 0.f)); v.y = pack_bf16x2(fmaxf(a[2], 0.f), fmaxf(a[3], 0.f));
+            v.z = pack_bf16x2(fmaxf(a[4], 0.f), fmaxf(a[5], 0.f)); v.w = pack_bf16x2(fmaxf(a[6], 0.f), fmaxf(a[7], 0.f));
+            *reinterpret_cast<uint4*>(sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16) = v;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy smem writes -> visible to the MMA's async proxy
+        __syncthreads();
+        // layer 1 on the tensor cores: D[128 x H] (TMEM, fp32) = A[128 x H] . B[H x H]
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::);
+            const uint64_t da = umma_desc_kmajor_noswizzle(smem_u32(sA), lbo, sbo), db = umma_desc_kmajor_noswizzle(smem_u32(sB), lbo, sbo);
+            for (int ks = 0; ks < (H >> 4); ++ks) {
+                const uint64_t adv = (uint64_t)((ks * 2 * lbo) >> 4);           // 16 bf16 = two core matrices along K
+                const uint32_t acc = ks > 0 ? 1u : 0u;
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                             "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                             ::"r"(tmem_base), "l"(da + adv), "l"(db + adv), "r"(idesc), "r"(acc) : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(s_bar)) : "memory");
+        }
+        asm volatile("{\n\t.reg .pred P1;\n\tLAB_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t@P1 bra DONE;\n\t"
+                     "bra LAB_WAIT;\n\tDONE:\n\t}" ::"r"(smem_u32(s_bar)), "r"(parity) : "memory");
+        parity ^= 1u;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::);
+        // epilogue: relu(b1 + D) folded into the output layer (mlp.py:135-142, normal.py:78-83)
+        float mu = 0.0f, ls = 0.0f;
+        const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        for (int c0 = half * kh; c0 < (half + 1) * kh; c0 += 16) {
+            uint32_t r[16];
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                         : "r"(taddr + (uint32_t)c0));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float h1 = fmaxf(__uint_as_float(r[j]) + s_b1[c0 + j], 0.0f);
+                mu = fmaf(h1, s_w2[2 * (c0 + j)], mu);
+                ls = fmaf(h1, s_w2[2 * (c0 + j) + 1], ls);
+            }
+        }
+        if (half == 1) { s_part[2 * row] = mu; s_part[2 * row + 1] = ls; }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::);
+        __syncthreads();                                                // accumulator fully read: the next tile may overwrite it
+        if (half == 0 && (t0 + row) < n) {
+            sc.out[(int64_t)(t0 + row) * 2] = mu + s_part[2 * row] + pol.b2[0];
+            sc.out[(int64_t)(t0 + row) * 2 + 1] = ls + s_part[2 * row + 1] + pol.b2[1];
+        }
+    }
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols));
+}
+
 // ---- K4c / K4d: sample, convert, validate, publish.  The first valid try in draw order wins, exactly as a sequential
 // redraw loop would pick it.  K4c: one warp per pending env, lanes = tries 0..31 (most envs finish here).  K4d: one CTA
 // per env that found no valid waypoint yet, threads = the next 256 tries per round (main_ast.py:49-51 allows 1000). -------
@@ -899,6 +1030,7 @@ struct SitHandle_ {
     void* h_pinned; size_t pinned_bytes;
     // sit_rollout_collect: instantiated CUDA graph of one (policy + K steps) iteration and the arguments it was captured for
     cudaGraphExec_t roll_graph; std::string roll_key;
+    size_t tc_smem_set;                          // dynamic shared memory opted in for rollout_mlp_tc_kernel
 };
 
 template <typename R> struct HostSel;
@@ -1173,7 +1305,7 @@ int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out)
     }
     h->d_scratch = nullptr; h->scratch_bytes = 0; h->h_pinned = nullptr; h->pinned_bytes = 0;
     h->d_pol = nullptr; h->pol_bytes = 0;
-    h->roll_graph = nullptr;
+    h->roll_graph = nullptr; h->tc_smem_set = 0;
     build_layout(h);
     *out = h;
     return SIT_OK;
@@ -1415,11 +1547,13 @@ int sit_rollout_begin(SitHandle h, void* state, void* stream) {
 int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const SitRollout* ro, void* stream) {
     if (!h || !state || !pol) return fail(SIT_E_INVALID, "null argument");
     if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_rollout_policy needs a SIT_KIND_ENV handle");
-    if (pol->mode < SIT_POLICY_UNIFORM || pol->mode > SIT_POLICY_MEAN) return fail(SIT_E_INVALID, "bad policy mode");
+    const int base_mode = pol->mode & 0xff;
+    const bool tensor_cores = (pol->mode & SIT_POLICY_TC_BF16) != 0;
+    if ((pol->mode & ~(0xff | SIT_POLICY_TC_BF16)) || base_mode > SIT_POLICY_MEAN) return fail(SIT_E_INVALID, "bad policy mode");
     PolicyArgs pa;
     std::memset(&pa, 0, sizeof(pa));
-    pa.mode = pol->mode; pa.hidden = pol->hidden;
-    if (pol->mode != SIT_POLICY_UNIFORM) {
+    pa.mode = base_mode; pa.hidden = pol->hidden;
+    if (base_mode != SIT_POLICY_UNIFORM) {
         if (pol->hidden < 32 || pol->hidden > 256 || pol->hidden % 32) return fail(SIT_E_INVALID, "policy hidden width must be a multiple of 32 in [32, 256]");
         if (!pol->w0 || !pol->b0 || !pol->w1 || !pol->b1 || !pol->w2 || !pol->b2) return fail(SIT_E_INVALID, "policy weights missing");
         pa.w0 = pol->w0; pa.b0 = pol->b0; pa.w1 = pol->w1; pa.b1 = pol->b1; pa.w2 = pol->w2; pa.b2 = pol->b2;
@@ -1445,7 +1579,21 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
     const int work_grid = h->sm_count * 4;   // persistent: tiles / warps stride over the pending list
     if (h->cfg.precision == SIT_F64) rollout_gather_kernel<double><<<gather_grid, 256, 0, st>>>(env_ptrs<double>(h, state), ra, sc);
     else rollout_gather_kernel<float><<<gather_grid, 256, 0, st>>>(env_ptrs<float>(h, state), ra, sc);
-    if (pa.mode != SIT_POLICY_UNIFORM) rollout_mlp_kernel<<<work_grid, 256, 0, st>>>(pa, sc);
+    if (pa.mode != SIT_POLICY_UNIFORM) {
+        if (tensor_cores) {
+            const int H = pa.hidden;
+            const size_t smem = (size_t)TC_M * H * 2 + (size_t)H * H * 2 + (size_t)(3 * H + 2 * TC_M) * 4 + 16;
+            int cols = 32;
+            while (cols < H) cols <<= 1;
+            if (h->tc_smem_set < smem) {
+                CUDA_TRY(cudaFuncSetAttribute(rollout_mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                h->tc_smem_set = smem;
+            }
+            rollout_mlp_tc_kernel<<<h->sm_count, 256, smem, st>>>(pa, sc, cols);
+        } else {
+            rollout_mlp_kernel<<<work_grid, 256, 0, st>>>(pa, sc);
+        }
+    }
     if (h->cfg.precision == SIT_F64)
         rollout_sample_kernel<double><<<work_grid, 256, 0, st>>>(*h->kd, ship_ptrs<double>(h, state), env_ptrs<double>(h, state), pa, ra, sc);
     else

@@ -39,10 +39,13 @@ class GaussianPolicy:
     like ``_weight_variable`` / ``_bias_variable`` (mlp.py:13-51).  Both hidden layers share one width H
     (multiple of 32, <= 256: main_ast.py:67 uses 256, the class default is (100, 100) -> use 128 or 96)."""
 
-    def __init__(self, hidden_size: int = 256, device=None, seed: int = 25450, mode: str = "gaussian"):
+    def __init__(self, hidden_size: int = 256, device=None, seed: int = 25450, mode: str = "gaussian",
+                 tensor_cores: bool = False):
         if hidden_size % 32 or not 32 <= hidden_size <= 256:
             raise ValueError("hidden_size must be a multiple of 32 in [32, 256]")
         self.hidden, self.device, self.mode = hidden_size, torch.device(device or "cuda"), mode
+        # tensor_cores: hidden layer as tcgen05.mma with bf16 operands / fp32 accumulate (SIT_POLICY_TC_BF16)
+        self.tensor_cores = bool(tensor_cores)
         g = torch.Generator().manual_seed(seed)
 
         def glorot(fan_in, fan_out):
@@ -59,6 +62,8 @@ class GaussianPolicy:
     def struct(self) -> "_lib.SitPolicy":
         p = _lib.SitPolicy()
         p.mode = {"uniform": _lib.POLICY_UNIFORM, "gaussian": _lib.POLICY_GAUSSIAN, "mean": _lib.POLICY_MEAN}[self.mode]
+        if self.tensor_cores and self.mode != "uniform":
+            p.mode |= _lib.POLICY_TC_BF16
         p.hidden = self.hidden
         for n in ("w0", "b0", "w1", "b1", "w2", "b2"):
             t = getattr(self, n)
@@ -69,7 +74,10 @@ class GaussianPolicy:
     # plain torch restatement (used by the tests as the fp32 reference of the policy kernel)
     def mu_logsig(self, obs: torch.Tensor):
         h = torch.relu(obs.float() @ self.w0 + self.b0)
-        h = torch.relu(h @ self.w1 + self.b1)
+        if self.tensor_cores:     # the kernel rounds both operands of the hidden-layer product to bf16 (fp32 accumulate)
+            h = torch.relu(h.bfloat16().float() @ self.w1.bfloat16().float() + self.b1)
+        else:
+            h = torch.relu(h @ self.w1 + self.b1)
         out = h @ self.w2 + self.b2
         return out[:, 0], out[:, 1].clamp(LOG_SIG_CAP_MIN, LOG_SIG_CAP_MAX)
 

@@ -129,24 +129,26 @@ class SAC:
             o += (K + 1) * N
         return out
 
-    def policy_struct(self, mode: str = "gaussian") -> "_lib.SitPolicy":
+    def policy_struct(self, mode: str = "gaussian", tensor_cores: bool = False) -> "_lib.SitPolicy":
         """SitPolicy pointing INTO the workspace: the rollout kernels read the weights the learner updates."""
         p = _lib.SitPolicy()
         _lib.check(self.L.sit_sac_policy(self.h, self.ws.data_ptr(), C.byref(p)))
         p.mode = {"gaussian": _lib.POLICY_GAUSSIAN, "mean": _lib.POLICY_MEAN}[mode]
+        if tensor_cores:
+            p.mode |= _lib.POLICY_TC_BF16
         return p
 
-    def policy(self, mode: str = "gaussian"):
+    def policy(self, mode: str = "gaussian", tensor_cores: bool = False):
         agent = self
 
         class _LivePolicy:
             hidden = agent.hidden
 
             def __init__(self):
-                self.mode = mode
+                self.mode, self.tensor_cores = mode, tensor_cores
 
             def struct(self):
-                return agent.policy_struct(self.mode)
+                return agent.policy_struct(self.mode, self.tensor_cores)
         return _LivePolicy()
 
     @property
