@@ -305,6 +305,7 @@ def run_b200(args, rank, world, local_rank):
                                     "(sit_measure_fma_peak); kernel time = ms_per_step (one launch per step, CUDA events)"}
         # ---- trajectory write-out mode (BASELINE config 2 style, fp64): HBM-write bound ------------------------------
         line["roofline_hbm"] = traj_roofline(sit, dev)
+        line["roofline_hbm_fp32"] = traj_roofline(sit, dev, "fp32")
         tf64 = C.c_double()
         _lib.check(L.sit_measure_fma_peak(local_rank, _lib.F64, C.byref(tf64), None))
         line["fp64_fma_peak_tflops"] = tf64.value
@@ -331,13 +332,15 @@ def run_b200(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
-def traj_roofline(sit, dev):
-    """fp64 fleet with full trajectory write-out [K][8][S] (BASELINE config 2 layout): achieved HBM GB/s."""
+def traj_roofline(sit, dev, precision="fp64"):
+    """Fleet with full trajectory write-out [K][8][S] (BASELINE config 2 layout): achieved HBM GB/s.  fp64: 64 B per
+    ship-step (the config-2 kernel, co-bound by the FP64 pipe); fp32: 32 B per ship-step (the config-3 arithmetic)."""
     import torch
-    S, K = 1 << 19, 32
+    f64 = precision == "fp64"
+    S, K = 148 * 4096, (32 if f64 else 64)      # 148 SMs x 16 CTAs of 256 ships: whole waves at 2 or 4 CTAs per SM
     sm, tc, ap = sit.default_ship([(0, 0), (3000, 3000), (6000, 9000)], np.pi / 4)
-    fl = sit.ShipFleet(sm, tc, ap, 8.0, n_ships=S, device=dev, precision="fp64")
-    fl.f["u_sp"].copy_(4 + 5 * torch.rand(S, device=dev, dtype=torch.float64))
+    fl = sit.ShipFleet(sm, tc, ap, 8.0, n_ships=S, device=dev, precision=precision)
+    fl.f["u_sp"].copy_(4 + 5 * torch.rand(S, device=dev, dtype=torch.float64 if f64 else torch.float32))
     out = {}
     for _ in range(3):
         fl.step(K, traj=True, out=out)
@@ -350,7 +353,8 @@ def traj_roofline(sit, dev):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
-    gbs = TRAJ_BYTES_F64 * S * K / (ms * 1e-3) / 1e9
+    bytes_per_step = TRAJ_BYTES_F64 if f64 else TRAJ_BYTES_F64 // 2
+    gbs = bytes_per_step * S * K / (ms * 1e-3) / 1e9
     peak = 6551.0
     src = "fallback"
     try:
@@ -358,9 +362,9 @@ def traj_roofline(sit, dev):
     except Exception:
         pass
     return {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
-            "kernel": "fleet_step_kernel<double> with trajectory write-out", "ships": S, "k": K, "ms_per_launch": ms,
-            "ship_steps_per_s": S * K / (ms * 1e-3), "peak_source": src,
-            "note": "algorithmic bytes = 64 B written per ship-step (8 fp64 channels); output 1 GiB per launch > L2"}
+            "kernel": f"fleet_step_fast_kernel<{'double' if f64 else 'float'}, TRAJ> (every-step trajectory write-out)", "ships": S, "k": K,
+            "ms_per_launch": ms, "ship_steps_per_s": S * K / (ms * 1e-3), "peak_source": src,
+            "note": f"algorithmic bytes = {bytes_per_step} B written per ship-step (8 {precision} channels); output ~1.2 GB per launch > L2"}
 
 
 DEFAULT_MAP = [

@@ -77,13 +77,14 @@ __global__ void __launch_bounds__(256) fleet_step_kernel(const __grid_constant__
         ship_step<R, LOG>(P, s, g, i, io.avoid != 0, io.store != 0, o, (LOG && io.log27) ? lg : nullptr);
         if (io.traj && (io.traj_steps != 1 || t == K - 1)) {
             R* tr = io.traj + (int64_t)(io.traj_steps != 1 ? t : 0) * SIT_N_TRAJ * S + i;
-            tr[0] = (R)s.N; tr[S] = (R)s.E; tr[2 * S] = s.psi; tr[3 * S] = s.u;
-            tr[4 * S] = s.v; tr[5 * S] = s.r; tr[6 * S] = s.om; tr[7 * S] = (R)s.k;
+            // streaming stores (st.global.cs): the trajectory is written once and never read back by the kernel
+            __stcs(tr, (R)s.N); __stcs(tr + S, (R)s.E); __stcs(tr + 2 * S, s.psi); __stcs(tr + 3 * S, s.u);
+            __stcs(tr + 4 * S, s.v); __stcs(tr + 5 * S, s.r); __stcs(tr + 6 * S, s.om); __stcs(tr + 7 * S, (R)s.k);
         }
         if (LOG && io.log27) {
             R* lo = io.log27 + (int64_t)t * SIT_N_LOG * S + i;
 #pragma unroll
-            for (int c = 0; c < SIT_N_LOG; ++c) lo[(int64_t)c * S] = lg[c];
+            for (int c = 0; c < SIT_N_LOG; ++c) __stcs(lo + (int64_t)c * S, lg[c]);
         }
         if (io.cmd) {
             R* co = io.cmd + (int64_t)t * 2 * S + i;
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(256) fleet_step_kernel(const __grid_constant__
 
 // Fast variant: nothing is read or written per step (disturbances held for the launch, trajectory row of the last
 // step only, no log / command streams), so the K-step loop is pure register arithmetic with compile-time flags.
-template <typename R, bool AVOID, bool SINGLE_MODE>
+template <typename R, bool AVOID, bool SINGLE_MODE, bool TRAJ = false>
 __global__ void __launch_bounds__(256) fleet_step_fast_kernel(const __grid_constant__ ShipP<R> P, const ShipPtrs<R> g,
                                                               const int K, const FleetIO<R> io) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -114,8 +115,15 @@ __global__ void __launch_bounds__(256) fleet_step_fast_kernel(const __grid_const
     }
     StepOut<R> o;
 #pragma unroll 1
-    for (int t = 0; t < K; ++t) ship_step<R, false, SINGLE_MODE>(P, s, g, i, AVOID, true, o, nullptr);
-    if (io.traj) {
+    for (int t = 0; t < K; ++t) {
+        ship_step<R, false, SINGLE_MODE>(P, s, g, i, AVOID, true, o, nullptr);
+        if (TRAJ) {   // every-step trajectory [K][8][S]: coalesced streaming stores, the only memory traffic of the loop
+            R* tr = io.traj + (int64_t)t * SIT_N_TRAJ * S + i;
+            __stcs(tr, (R)s.N); __stcs(tr + S, (R)s.E); __stcs(tr + 2 * S, s.psi); __stcs(tr + 3 * S, s.u);
+            __stcs(tr + 4 * S, s.v); __stcs(tr + 5 * S, s.r); __stcs(tr + 6 * S, s.om); __stcs(tr + 7 * S, (R)s.k);
+        }
+    }
+    if (!TRAJ && io.traj) {
         R* tr = io.traj + i;
         tr[0] = (R)s.N; tr[S] = (R)s.E; tr[2 * S] = s.psi; tr[3 * S] = s.u;
         tr[4 * S] = s.v; tr[5 * S] = s.r; tr[6 * S] = s.om; tr[7 * S] = (R)s.k;
@@ -565,7 +573,7 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
 
 struct PolicyArgs { int32_t mode, hidden; const float *w0, *b0, *w1, *b1, *w2, *b2; };
 // scratch of one sit_rollout_policy call (device, owned by the handle): compact list of the pending envs
-struct PolScratch { unsigned int *n_pending, *n_retry; int32_t *env, *retry; float *obs, *out; };   // env / retry [B], obs [B][10], out [B][2]
+struct PolScratch { unsigned int *n_pending, *n_retry; int32_t *env, *retry; float *obs, *out; unsigned char* w1p; };   // env / retry [B], obs [B][10], out [B][2]
 
 // ---- K4a: compact the pending envs, open their replay rows ---------------------------------------------------------
 template <typename R>
@@ -689,6 +697,21 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     return r;
 }
 
+// W1 [k][n] fp32 (n contiguous) -> the bf16 B-operand image (N x K, K-major canonical layout) in global scratch, once per
+// policy call (the learner may have changed the weights); every CTA then pulls the whole image with ONE bulk async copy.
+__global__ void __launch_bounds__(256) rollout_pack_w1_kernel(const PolicyArgs pol, const PolScratch sc) {
+    const int H = pol.hidden;
+    const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;
+    for (int item = blockIdx.x * 256 + threadIdx.x; item < H * (H >> 3); item += gridDim.x * 256) {
+        const int nn = item % H, kc = item / H;
+        const float* w = pol.w1 + (size_t)(kc * 8) * H + nn;
+        uint4 v;
+        v.x = pack_bf16x2(w[0], w[H]); v.y = pack_bf16x2(w[2 * H], w[3 * H]);
+        v.z = pack_bf16x2(w[4 * H], w[5 * H]); v.w = pack_bf16x2(w[6 * H], w[7 * H]);
+        *reinterpret_cast<uint4*>(sc.w1p + (size_t)(nn >> 3) * sbo + (size_t)kc * lbo + (nn & 7) * 16) = v;
+    }
+}
+
 __global__ void __launch_bounds__(256, 1) rollout_mlp_tc_kernel(const PolicyArgs pol, const PolScratch sc, const int tmem_cols) {
     extern __shared__ __align__(128) unsigned char tc_smem[];
     const int H = pol.hidden;
@@ -700,8 +723,8 @@ __global__ void __launch_bounds__(256, 1) rollout_mlp_tc_kernel(const PolicyArgs
     float* s_w2 = reinterpret_cast<float*>(sB + (size_t)H * H * 2);   // [H][2]
     float* s_b1 = s_w2 + 2 * H;                                       // [H]
     float* s_part = s_b1 + H;                                         // [128][2] partial output sums of the upper column half
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + 2 * TC_M);
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 1);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + 2 * TC_M);   // [0]: MMAs of a tile done, [1]: W1 image landed
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2);
     const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;               // next 8-row group | next 16-byte K chunk
 
     if (warp == 0) {
@@ -710,16 +733,14 @@ __global__ void __launch_bounds__(256, 1) rollout_mlp_tc_kernel(const PolicyArgs
     }
     if (tid == 32) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar + 1)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::);
-    }
-    // W1 [k][n] (n contiguous) -> B operand: thread owns output unit nn and 8 consecutive k per 16-byte store
-    for (int item = tid; item < H * (H >> 3); item += 256) {
-        const int nn = item % H, kc = item / H;
-        const float* w = pol.w1 + (size_t)(kc * 8) * H + nn;
-        uint4 v;
-        v.x = pack_bf16x2(w[0], w[H]); v.y = pack_bf16x2(w[2 * H], w[3 * H]);
-        v.z = pack_bf16x2(w[4 * H], w[5 * H]); v.w = pack_bf16x2(w[6 * H], w[7 * H]);
-        *reinterpret_cast<uint4*>(sB + (size_t)(nn >> 3) * sbo + (size_t)kc * lbo + (nn & 7) * 16) = v;
+        // B operand: the packed bf16 image of W1 (rollout_pack_w1_kernel) in one bulk async copy, landing on s_bar[1] while
+        // the CTA computes layer 0 of its first tile
+        const uint32_t bytes = (uint32_t)H * (uint32_t)H * 2u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(s_bar + 1)), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(sB)), "l"(sc.w1p), "r"(bytes), "r"(smem_u32(s_bar + 1)) : "memory");
     }
     for (int i = tid; i < 2 * H; i += 256) s_w2[i] = pol.w2[i];
     for (int i = tid; i < H; i += 256) s_b1[i] = pol.b1[i];
@@ -731,6 +752,7 @@ __global__ void __launch_bounds__(256, 1) rollout_mlp_tc_kernel(const PolicyArgs
     const int row = tid & (TC_M - 1), half = tid >> 7;                // TMEM lane / env of the tile | column half
     const int kh = H >> 1;                                            // columns per half (multiple of 16)
     uint32_t parity = 0;
+    bool b_ready = false;
     for (int t0 = blockIdx.x * TC_M; t0 < n; t0 += gridDim.x * TC_M) {
         // layer 0 on the CUDA cores: relu(b0 + obs . w0) for this thread's row and column half (nn_models/mlp.py:121-133)
         float o[SIT_N_OBS];
@@ -756,6 +778,11 @@ __global__ void __launch_bounds__(256, 1) rollout_mlp_tc_kernel(const PolicyArgs
         __syncthreads();
         // layer 1 on the tensor cores: D[128 x H] (TMEM, fp32) = A[128 x H] . B[H x H]
         if (tid == 0) {
+            if (!b_ready) {   // first tile: wait for the W1 image
+                asm volatile("{\n\t.reg .pred P1;\n\tLAB_WAITB:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t@P1 bra DONEB;\n\t"
+                             "bra LAB_WAITB;\n\tDONEB:\n\t}" ::"r"(smem_u32(s_bar + 1)), "r"(0u) : "memory");
+                b_ready = true;
+            }
             asm volatile("tcgen05.fence::after_thread_sync;" ::);
             const uint64_t da = umma_desc_kmajor_noswizzle(smem_u32(sA), lbo, sbo), db = umma_desc_kmajor_noswizzle(smem_u32(sB), lbo, sbo);
             for (int ks = 0; ks < (H >> 4); ++ks) {
@@ -784,8 +811,9 @@ __global__ void __launch_bounds__(256, 1) rollout_mlp_tc_kernel(const PolicyArgs
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
                 const float h1 = fmaxf(__uint_as_float(r[j]) + s_b1[c0 + j], 0.0f);
-                mu = fmaf(h1, s_w2[2 * (c0 + j)], mu);
-                ls = fmaf(h1, s_w2[2 * (c0 + j) + 1], ls);
+                const float2 w = reinterpret_cast<const float2*>(s_w2)[c0 + j];
+                mu = fmaf(h1, w.x, mu);
+                ls = fmaf(h1, w.y, ls);
             }
         }
         if (half == 1) { s_part[2 * row] = mu; s_part[2 * row + 1] = ls; }
@@ -1356,9 +1384,18 @@ static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, c
     const ShipPtrs<R> g = ship_ptrs<R>(h, state);
     const ShipP<R>& P = HostSel<R>::ship(h);
     const int block = 256, grid = grid_for(h->n_ships, block);
-    const bool fast = (!k.dist || k.dist_steps == 1) && (!k.traj || k.traj_steps == 1) && !k.log27 && !k.cmd && k.store;
+    const bool quiet = (!k.dist || k.dist_steps == 1) && !k.log27 && !k.cmd && k.store;
+    const bool fast = quiet && (!k.traj || k.traj_steps == 1);
     const bool single = P.n_modes == 1;
-    if (fast) {
+    if (quiet && k.traj && k.traj_steps == K && K > 1) {   // every-step trajectory on the specialised compute path
+        if (k.avoid) {
+            if (single) fleet_step_fast_kernel<R, true, true, true><<<grid, block, 0, st>>>(P, g, K, k);
+            else fleet_step_fast_kernel<R, true, false, true><<<grid, block, 0, st>>>(P, g, K, k);
+        } else {
+            if (single) fleet_step_fast_kernel<R, false, true, true><<<grid, block, 0, st>>>(P, g, K, k);
+            else fleet_step_fast_kernel<R, false, false, true><<<grid, block, 0, st>>>(P, g, K, k);
+        }
+    } else if (fast) {
         if (k.avoid) {
             if (single) fleet_step_fast_kernel<R, true, true><<<grid, block, 0, st>>>(P, g, K, k);
             else fleet_step_fast_kernel<R, true, false><<<grid, block, 0, st>>>(P, g, K, k);
@@ -1566,7 +1603,8 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
     // scratch: pending counter | env list [B] | obs [B][10] | out [B][2]
     const size_t B = (size_t)h->n_envs;
     const size_t o_env = 256, o_obs = align_up(o_env + B * 4, 256), o_out = align_up(o_obs + B * SIT_N_OBS * 4, 256),
-                 o_retry = align_up(o_out + B * 2 * 4, 256), total = align_up(o_retry + B * 4, 256);
+                 o_retry = align_up(o_out + B * 2 * 4, 256), o_w1p = align_up(o_retry + B * 4, 256),
+                 total = o_w1p + 256 * 256 * 2;
     rc = ensure_pol_scratch(h, total);
     if (rc) return rc;
     char* d = static_cast<char*>(h->d_pol);
@@ -1574,6 +1612,7 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
     sc.n_pending = reinterpret_cast<unsigned int*>(d); sc.n_retry = sc.n_pending + 1;
     sc.env = reinterpret_cast<int32_t*>(d + o_env); sc.retry = reinterpret_cast<int32_t*>(d + o_retry);
     sc.obs = reinterpret_cast<float*>(d + o_obs); sc.out = reinterpret_cast<float*>(d + o_out);
+    sc.w1p = reinterpret_cast<unsigned char*>(d + o_w1p);
     CUDA_TRY(cudaMemsetAsync(sc.n_pending, 0, 2 * sizeof(unsigned int), st));
     const int gather_grid = grid_for(h->n_envs, 256);
     const int work_grid = h->sm_count * 4;   // persistent: tiles / warps stride over the pending list
@@ -1582,13 +1621,14 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
     if (pa.mode != SIT_POLICY_UNIFORM) {
         if (tensor_cores) {
             const int H = pa.hidden;
-            const size_t smem = (size_t)TC_M * H * 2 + (size_t)H * H * 2 + (size_t)(3 * H + 2 * TC_M) * 4 + 16;
+            const size_t smem = (size_t)TC_M * H * 2 + (size_t)H * H * 2 + (size_t)(3 * H + 2 * TC_M) * 4 + 32;
             int cols = 32;
             while (cols < H) cols <<= 1;
             if (h->tc_smem_set < smem) {
                 CUDA_TRY(cudaFuncSetAttribute(rollout_mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
                 h->tc_smem_set = smem;
             }
+            rollout_pack_w1_kernel<<<(H * (H >> 3) + 255) / 256, 256, 0, st>>>(pa, sc);
             rollout_mlp_tc_kernel<<<h->sm_count, 256, smem, st>>>(pa, sc, cols);
         } else {
             rollout_mlp_kernel<<<work_grid, 256, 0, st>>>(pa, sc);

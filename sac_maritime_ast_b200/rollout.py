@@ -160,7 +160,8 @@ class IntermediateWaypointSampler:
         _lib.check(e.L.sit_rollout_collect(e.h, e.state_ptr(), int(iterations), int(K), C.byref(self._pol), C.byref(self.ro),
                                            C.byref(self.io), 1, self._side.cuda_stream))
         cur.wait_stream(self._side)
-        self.launches += 5 * iterations       # gather + mlp + sample + resample + step kernels per iteration
+        # gather + (w1 pack) + mlp + sample + resample + step kernels per iteration
+        self.launches += (6 if getattr(self.policy, 'tensor_cores', False) else 5) * iterations
 
     # ---- results ----------------------------------------------------------------------------------------------
     def n_transitions(self) -> int:

@@ -12,6 +12,8 @@ which = sys.argv[1]
 dev = torch.device("cuda", 0)
 if which == "traj64":
     print(bench.traj_roofline(sit, dev))
+elif which == "traj32":
+    print(bench.traj_roofline(sit, dev, "fp32"))
 elif which.startswith("roll"):
     kw = {}
     for a in sys.argv[2:]:
