@@ -2,6 +2,7 @@
 // sm_100a only; no CPU fallback.  Reference citations are relative to /root/reference/.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -20,6 +21,7 @@ template <typename R>
 struct FleetIO {
     const R* dist; int32_t dist_steps; int32_t avoid; int32_t store; int32_t traj_steps;
     R* traj; R* log27; R* cmd;
+    int64_t first, count;    // ship sub-range [first, first + count) of this launch (the host-buffer pipeline launches chunks)
 };
 
 template <typename R>
@@ -58,9 +60,9 @@ struct EnvKArgs {
 template <typename R, bool LOG>
 __global__ void __launch_bounds__(256) fleet_step_kernel(const __grid_constant__ ShipP<R> P, const ShipPtrs<R> g,
                                                          const int K, const FleetIO<R> io) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t S = g.n_ships;
-    if (i >= S) return;
+    const int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t S = g.n_ships, i = io.first + li;
+    if (li >= io.count) return;
     Ship<R> s;
     load_ship(s, g, i);
     R w_speed = (R)0, w_dir = (R)0;
@@ -102,9 +104,9 @@ __global__ void __launch_bounds__(256) fleet_step_kernel(const __grid_constant__
 template <typename R, bool AVOID, bool SINGLE_MODE, bool TRAJ = false>
 __global__ void __launch_bounds__(256) fleet_step_fast_kernel(const __grid_constant__ ShipP<R> P, const ShipPtrs<R> g,
                                                               const int K, const FleetIO<R> io) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t S = g.n_ships;
-    if (i >= S) return;
+    const int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t S = g.n_ships, i = io.first + li;
+    if (li >= io.count) return;
     Ship<R> s;
     load_ship(s, g, i);
     if (io.dist) {
@@ -1043,6 +1045,7 @@ static const FieldDef kEnvFields[] = {
     {"n_dec", 'I', 1, true}, {"dec_serial", 'I', 1, true}, {"tr_slot", 'I', 1, true},
 };
 
+#define SIT_PIPE 4
 struct SitHandle_ {
     SitConfig cfg;
     int64_t n_envs, n_ships;
@@ -1059,6 +1062,8 @@ struct SitHandle_ {
     // sit_rollout_collect: instantiated CUDA graph of one (policy + K steps) iteration and the arguments it was captured for
     cudaGraphExec_t roll_graph; std::string roll_key;
     size_t tc_smem_set;                          // dynamic shared memory opted in for rollout_mlp_tc_kernel
+    // sit_fleet_step_host: chunk pipeline over internal streams
+    bool pipe_ready; cudaStream_t pipe[SIT_PIPE]; cudaEvent_t pipe_done[SIT_PIPE], pipe_in;
 };
 
 template <typename R> struct HostSel;
@@ -1333,7 +1338,7 @@ int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out)
     }
     h->d_scratch = nullptr; h->scratch_bytes = 0; h->h_pinned = nullptr; h->pinned_bytes = 0;
     h->d_pol = nullptr; h->pol_bytes = 0;
-    h->roll_graph = nullptr; h->tc_smem_set = 0;
+    h->roll_graph = nullptr; h->tc_smem_set = 0; h->pipe_ready = false;
     build_layout(h);
     *out = h;
     return SIT_OK;
@@ -1345,6 +1350,10 @@ int sit_destroy(SitHandle h) {
     if (h->d_pol) cudaFree(h->d_pol);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     if (h->roll_graph) cudaGraphExecDestroy(h->roll_graph);
+    if (h->pipe_ready) {
+        for (int j = 0; j < SIT_PIPE; ++j) { cudaStreamDestroy(h->pipe[j]); cudaEventDestroy(h->pipe_done[j]); }
+        cudaEventDestroy(h->pipe_in);
+    }
     delete h->kd; delete h->kf;
     delete h;
     return SIT_OK;
@@ -1371,10 +1380,12 @@ static int grid_for(int64_t n, int block) { return (int)((n + block - 1) / block
 
 }  // extern "C"
 template <typename R>
-static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, cudaStream_t st) {
+static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, cudaStream_t st, int64_t first = 0,
+                        int64_t count = -1) {
     FleetIO<R> k;
     std::memset(&k, 0, sizeof(k));
     k.store = 1;
+    k.first = first; k.count = count < 0 ? h->n_ships : count;
     if (io) {
         k.dist = static_cast<const R*>(io->dist); k.dist_steps = io->dist_steps; k.avoid = io->avoid; k.store = io->store; k.traj_steps = io->traj_steps;
         k.traj = static_cast<R*>(io->traj); k.log27 = static_cast<R*>(io->log27); k.cmd = static_cast<R*>(io->cmd);
@@ -1383,7 +1394,7 @@ static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, c
     }
     const ShipPtrs<R> g = ship_ptrs<R>(h, state);
     const ShipP<R>& P = HostSel<R>::ship(h);
-    const int block = 256, grid = grid_for(h->n_ships, block);
+    const int block = 256, grid = grid_for(k.count, block);
     const bool quiet = (!k.dist || k.dist_steps == 1) && !k.log27 && !k.cmd && k.store;
     const bool fast = quiet && (!k.traj || k.traj_steps == 1);
     const bool single = P.n_modes == 1;
@@ -1448,14 +1459,54 @@ int sit_fleet_step_host(SitHandle h, void* state, int32_t K, const void* dist_h,
     int rc = ensure_scratch(h, total);
     if (rc) return rc;
     char* d = static_cast<char*>(h->d_scratch);
-    if (dist_h) CUDA_TRY(cudaMemcpyAsync(d + o_dist, dist_h, 4 * S * rs, cudaMemcpyHostToDevice, st));
     SitFleetIO io;
     std::memset(&io, 0, sizeof(io));
     io.dist = dist_h ? d + o_dist : nullptr; io.dist_steps = 1; io.avoid = avoid; io.store = 1;
     io.traj = pose_h ? d + o_pose : nullptr; io.traj_steps = 1;
-    rc = sit_fleet_step_k(h, state, K, &io, stream);
-    if (rc) return rc;
-    if (pose_h) CUDA_TRY(cudaMemcpyAsync(pose_h, d + o_pose, SIT_N_TRAJ * S * rs, cudaMemcpyDeviceToHost, st));
+    // Large fleets: the ships are cut into chunks that travel through SIT_PIPE internal streams, so the H2D copy of
+    // chunk c+1 and the D2H copy of chunk c-1 run on the two copy engines while chunk c computes (ships are independent,
+    // so a chunk is a complete unit of work).  Small fleets: one copy-in, one launch, one copy-out on the caller's stream.
+    const int64_t min_chunk = 65536;
+    int n_chunks = (int)std::min<int64_t>(8, (int64_t)S / min_chunk);
+    if (n_chunks < 2 || (!dist_h && !pose_h)) {
+        if (dist_h) CUDA_TRY(cudaMemcpyAsync(d + o_dist, dist_h, 4 * S * rs, cudaMemcpyHostToDevice, st));
+        rc = sit_fleet_step_k(h, state, K, &io, stream);
+        if (rc) return rc;
+        if (pose_h) CUDA_TRY(cudaMemcpyAsync(pose_h, d + o_pose, SIT_N_TRAJ * S * rs, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        return SIT_OK;
+    }
+    if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
+    if (!h->pipe_ready) {
+        for (int j = 0; j < SIT_PIPE; ++j) {
+            CUDA_TRY(cudaStreamCreateWithFlags(&h->pipe[j], cudaStreamNonBlocking));
+            CUDA_TRY(cudaEventCreateWithFlags(&h->pipe_done[j], cudaEventDisableTiming));
+        }
+        CUDA_TRY(cudaEventCreateWithFlags(&h->pipe_in, cudaEventDisableTiming));
+        h->pipe_ready = true;
+    }
+    CUDA_TRY(cudaEventRecord(h->pipe_in, st));
+    for (int j = 0; j < SIT_PIPE; ++j) CUDA_TRY(cudaStreamWaitEvent(h->pipe[j], h->pipe_in, 0));
+    const int64_t chunk = ((int64_t)S / n_chunks + 255) / 256 * 256;
+    const size_t pitch = S * rs;
+    int c = 0;
+    for (int64_t first = 0; first < (int64_t)S; first += chunk, ++c) {
+        const int64_t cnt = std::min<int64_t>(chunk, (int64_t)S - first);
+        cudaStream_t ps = h->pipe[c % SIT_PIPE];
+        if (dist_h)
+            CUDA_TRY(cudaMemcpy2DAsync(d + o_dist + first * rs, pitch, static_cast<const char*>(dist_h) + first * rs, pitch,
+                                       cnt * rs, 4, cudaMemcpyHostToDevice, ps));
+        rc = h->cfg.precision == SIT_F64 ? fleet_step_t<double>(h, state, K, &io, ps, first, cnt)
+                                         : fleet_step_t<float>(h, state, K, &io, ps, first, cnt);
+        if (rc) return rc;
+        if (pose_h)
+            CUDA_TRY(cudaMemcpy2DAsync(static_cast<char*>(pose_h) + first * rs, pitch, d + o_pose + first * rs, pitch,
+                                       cnt * rs, SIT_N_TRAJ, cudaMemcpyDeviceToHost, ps));
+    }
+    for (int j = 0; j < SIT_PIPE; ++j) {
+        CUDA_TRY(cudaEventRecord(h->pipe_done[j], h->pipe[j]));
+        CUDA_TRY(cudaStreamWaitEvent(st, h->pipe_done[j], 0));
+    }
     CUDA_TRY(cudaStreamSynchronize(st));
     return SIT_OK;
 }

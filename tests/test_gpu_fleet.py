@@ -153,3 +153,26 @@ def test_reset_semantics():
     fl.reset(hard=True)
     again = fl.step(300, traj=True)["traj"].cpu().numpy()
     assert np.array_equal(first, again), "hard reset must reproduce the first episode bit-for-bit"
+
+
+@pytest.mark.parametrize("n", [1000, 200_003, 1 << 20])
+def test_host_buffer_path_equals_device_path(n):
+    """sit_fleet_step_host (pinned host disturbances in, host pose out; large fleets are cut into chunks that are
+    pipelined over internal streams) == sit_fleet_step_k on device tensors, bit-for-bit, including a ragged tail."""
+    import gpu_helpers as G
+    s = sc.SHIP_SCENARIOS["default"]
+    a = G.make_fleet(s, n_ships=n, precision="fp32")
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    a.f["u_sp"].copy_(4 + 5 * torch.rand(n, generator=gen, device="cuda"))
+    snap = a.state_dict()
+    dist = torch.empty((4, n), dtype=torch.float32).uniform_(-2, 2, generator=torch.Generator().manual_seed(4))
+    want = a.step(64, dist=dist.cuda(), traj=False)
+    want_pose = torch.stack([a.f[k].to(torch.float32) for k in ("north", "east", "psi", "u", "v", "r", "omega", "k")])
+    a.load_state_dict(snap)
+    dist_h, pose_h = dist.pin_memory(), torch.empty((8, n), dtype=torch.float32).pin_memory()
+    pose_h.fill_(float("nan"))
+    a.step_host(64, dist_h, pose_h)
+    assert torch.equal(pose_h, want_pose.cpu()), "host-buffer path differs from the device path"
+    assert torch.equal(a.f["vc_n"].cpu(), dist[0]) and torch.equal(a.f["wind_dir"].cpu(), dist[3])
+    a.step_host(3, None, pose_h)          # no disturbance update: held values stay
+    assert (a.f["steps"] == 67).all() and torch.isfinite(pose_h).all()
