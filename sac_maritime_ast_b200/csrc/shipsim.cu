@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -38,6 +39,7 @@ struct RollArgs {   // device-resident rollout (include/shipsim.h SitRollout), b
     float* replay; int64_t capacity; unsigned long long* counters;
     uint64_t seed; int64_t env_id_offset;
     int32_t max_episode_steps, max_route_resampling, sampling_frequency, _pad;
+    int64_t env_first, env_count;   // env sub-range of this launch (sit_rollout_collect pipelines env groups)
 };
 
 template <typename R>
@@ -222,9 +224,9 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
     stage_edges(A.M, s_edges);
     const int n_edges = A.M.n_edges;
-    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x + (ROLL ? 2 * ro.env_first : 0);
     const int64_t S = g.n_ships, B = ge.n_envs;
-    const bool active = tid < S;
+    const bool active = tid < (ROLL ? 2 * (ro.env_first + ro.env_count) : S);
     const int64_t i = active ? tid : (tid & 1);   // idle lanes of the last warp shadow env 0 and never store
     const int role = (int)(i & 1);
     const int64_t env = i >> 1;
@@ -585,8 +587,8 @@ __global__ void __launch_bounds__(256) rollout_gather_kernel(const EnvPtrs<R> ge
     __shared__ unsigned long long s_slot0;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int64_t B = ge.n_envs;
-    const int64_t env = (int64_t)blockIdx.x * 256 + tid;
-    const int32_t fl = env < B ? ge.flags[env] : 0;
+    const int64_t env = ro.env_first + (int64_t)blockIdx.x * 256 + tid;
+    const int32_t fl = env < ro.env_first + ro.env_count ? ge.flags[env] : 0;
     const bool pend = (fl & F_PENDING) && !(fl & F_HAVE_ACT);
     const unsigned bal = __ballot_sync(0xffffffffu, pend);
     if (lane == 0) s_warp_cnt[wid] = __popc(bal);
@@ -1430,6 +1432,7 @@ int sit_fleet_step_k(SitHandle h, void* state, int32_t K, const SitFleetIO* io, 
     return h->cfg.precision == SIT_F64 ? fleet_step_t<double>(h, state, K, io, st) : fleet_step_t<float>(h, state, K, io, st);
 }
 
+static int ensure_pipe(SitHandle h);
 static int ensure_scratch(SitHandle h, size_t total) {
     if (h->scratch_bytes >= total) return SIT_OK;
     if (h->d_scratch) cudaFree(h->d_scratch);
@@ -1477,14 +1480,7 @@ int sit_fleet_step_host(SitHandle h, void* state, int32_t K, const void* dist_h,
         return SIT_OK;
     }
     if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
-    if (!h->pipe_ready) {
-        for (int j = 0; j < SIT_PIPE; ++j) {
-            CUDA_TRY(cudaStreamCreateWithFlags(&h->pipe[j], cudaStreamNonBlocking));
-            CUDA_TRY(cudaEventCreateWithFlags(&h->pipe_done[j], cudaEventDisableTiming));
-        }
-        CUDA_TRY(cudaEventCreateWithFlags(&h->pipe_in, cudaEventDisableTiming));
-        h->pipe_ready = true;
-    }
+    if ((rc = ensure_pipe(h))) return rc;
     CUDA_TRY(cudaEventRecord(h->pipe_in, st));
     for (int j = 0; j < SIT_PIPE; ++j) CUDA_TRY(cudaStreamWaitEvent(h->pipe[j], h->pipe_in, 0));
     const int64_t chunk = ((int64_t)S / n_chunks + 255) / 256 * 256;
@@ -1594,6 +1590,7 @@ static int roll_args(SitHandle h, const SitRollout* ro, RollArgs& ra) {
     ra.seed = ro->seed; ra.env_id_offset = ro->env_id_offset;
     ra.max_episode_steps = ro->max_episode_steps; ra.max_route_resampling = ro->max_route_resampling;
     ra.sampling_frequency = (int32_t)h->cfg.sampling_frequency;
+    ra.env_first = 0; ra.env_count = h->n_envs;
     return SIT_OK;
 }
 
@@ -1611,7 +1608,7 @@ static int rollout_step_t(SitHandle h, void* state, int K, const RollArgs& ra, c
     const ShipPtrs<R> g = ship_ptrs<R>(h, state);
     const EnvPtrs<R> ge = env_ptrs<R>(h, state);
     const EnvKArgs<R>& A = HostSel<R>::env(h);
-    const int block = 128, grid = grid_for(h->n_ships, block);
+    const int block = 128, grid = grid_for(2 * ra.env_count, block);
     if (h->same_params) env_step_kernel<R, true, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     else env_step_kernel<R, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     CUDA_TRY(cudaGetLastError());
@@ -1632,43 +1629,68 @@ int sit_rollout_begin(SitHandle h, void* state, void* stream) {
     return SIT_OK;
 }
 
-int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const SitRollout* ro, void* stream) {
-    if (!h || !state || !pol) return fail(SIT_E_INVALID, "null argument");
-    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_rollout_policy needs a SIT_KIND_ENV handle");
+}  // extern "C"
+
+#define SIT_ROLL_GROUPS_MAX 8
+static int policy_args(const SitPolicy* pol, PolicyArgs& pa, bool& tensor_cores) {
     const int base_mode = pol->mode & 0xff;
-    const bool tensor_cores = (pol->mode & SIT_POLICY_TC_BF16) != 0;
+    tensor_cores = (pol->mode & SIT_POLICY_TC_BF16) != 0;
     if ((pol->mode & ~(0xff | SIT_POLICY_TC_BF16)) || base_mode > SIT_POLICY_MEAN) return fail(SIT_E_INVALID, "bad policy mode");
-    PolicyArgs pa;
     std::memset(&pa, 0, sizeof(pa));
     pa.mode = base_mode; pa.hidden = pol->hidden;
     if (base_mode != SIT_POLICY_UNIFORM) {
         if (pol->hidden < 32 || pol->hidden > 256 || pol->hidden % 32) return fail(SIT_E_INVALID, "policy hidden width must be a multiple of 32 in [32, 256]");
         if (!pol->w0 || !pol->b0 || !pol->w1 || !pol->b1 || !pol->w2 || !pol->b2) return fail(SIT_E_INVALID, "policy weights missing");
         pa.w0 = pol->w0; pa.b0 = pol->b0; pa.w1 = pol->w1; pa.b1 = pol->b1; pa.w2 = pol->w2; pa.b2 = pol->b2;
+    } else {
+        tensor_cores = false;
     }
-    RollArgs ra;
-    int rc = roll_args(h, ro, ra);
-    if (rc) return rc;
-    CUDA_TRY(cudaSetDevice(h->device));
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    // scratch: pending counter | env list [B] | obs [B][10] | out [B][2]
+    return SIT_OK;
+}
+
+// Policy scratch: counters [SIT_ROLL_GROUPS_MAX][2] | env list [B] | obs [B][10] | out [B][2] | retry list [B] | packed W1.
+// The lists are sized for the whole handle; an env group [first, first + count) uses the slices that start at `first`,
+// so groups that run concurrently never share a row.
+static int pol_scratch(SitHandle h, int group, int64_t first, PolScratch& sc) {
     const size_t B = (size_t)h->n_envs;
     const size_t o_env = 256, o_obs = align_up(o_env + B * 4, 256), o_out = align_up(o_obs + B * SIT_N_OBS * 4, 256),
                  o_retry = align_up(o_out + B * 2 * 4, 256), o_w1p = align_up(o_retry + B * 4, 256),
                  total = o_w1p + 256 * 256 * 2;
-    rc = ensure_pol_scratch(h, total);
+    int rc = ensure_pol_scratch(h, total);
     if (rc) return rc;
     char* d = static_cast<char*>(h->d_pol);
-    PolScratch sc;
-    sc.n_pending = reinterpret_cast<unsigned int*>(d); sc.n_retry = sc.n_pending + 1;
-    sc.env = reinterpret_cast<int32_t*>(d + o_env); sc.retry = reinterpret_cast<int32_t*>(d + o_retry);
-    sc.obs = reinterpret_cast<float*>(d + o_obs); sc.out = reinterpret_cast<float*>(d + o_out);
+    sc.n_pending = reinterpret_cast<unsigned int*>(d) + 2 * group; sc.n_retry = sc.n_pending + 1;
+    sc.env = reinterpret_cast<int32_t*>(d + o_env) + first; sc.retry = reinterpret_cast<int32_t*>(d + o_retry) + first;
+    sc.obs = reinterpret_cast<float*>(d + o_obs) + first * SIT_N_OBS; sc.out = reinterpret_cast<float*>(d + o_out) + first * 2;
     sc.w1p = reinterpret_cast<unsigned char*>(d + o_w1p);
+    return SIT_OK;
+}
+
+static int pack_w1(SitHandle h, const PolicyArgs& pa, cudaStream_t st) {
+    PolScratch sc;
+    int rc = pol_scratch(h, 0, 0, sc);
+    if (rc) return rc;
+    const int H = pa.hidden;
+    rollout_pack_w1_kernel<<<(H * (H >> 3) + 255) / 256, 256, 0, st>>>(pa, sc);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+// gather -> MLP -> sample -> resample for the env range of `ra`; the packed W1 image must already be in the scratch
+template <typename R>
+static int rollout_policy_t(SitHandle h, void* state, const PolicyArgs& pa, bool tensor_cores, const RollArgs& ra, int group,
+                            cudaStream_t st) {
+    PolScratch sc;
+    int rc = pol_scratch(h, group, ra.env_first, sc);
+    if (rc) return rc;
     CUDA_TRY(cudaMemsetAsync(sc.n_pending, 0, 2 * sizeof(unsigned int), st));
-    const int gather_grid = grid_for(h->n_envs, 256);
-    const int work_grid = h->sm_count * 4;   // persistent: tiles / warps stride over the pending list
-    if (h->cfg.precision == SIT_F64) rollout_gather_kernel<double><<<gather_grid, 256, 0, st>>>(env_ptrs<double>(h, state), ra, sc);
-    else rollout_gather_kernel<float><<<gather_grid, 256, 0, st>>>(env_ptrs<float>(h, state), ra, sc);
+    const ShipPtrs<R> g = ship_ptrs<R>(h, state);
+    const EnvPtrs<R> ge = env_ptrs<R>(h, state);
+    const EnvKArgs<R>& A = HostSel<R>::env(h);
+    const int gather_grid = grid_for(ra.env_count, 256);
+    // persistent: tiles / warps stride over the pending list (a small share of the group's envs)
+    const int work_grid = h->sm_count * 4;
+    rollout_gather_kernel<R><<<gather_grid, 256, 0, st>>>(ge, ra, sc);
     if (pa.mode != SIT_POLICY_UNIFORM) {
         if (tensor_cores) {
             const int H = pa.hidden;
@@ -1679,24 +1701,39 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
                 CUDA_TRY(cudaFuncSetAttribute(rollout_mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
                 h->tc_smem_set = smem;
             }
-            rollout_pack_w1_kernel<<<(H * (H >> 3) + 255) / 256, 256, 0, st>>>(pa, sc);
-            rollout_mlp_tc_kernel<<<h->sm_count, 256, smem, st>>>(pa, sc, cols);
+            const int tiles = (int)std::min<int64_t>(h->sm_count, (ra.env_count + TC_M - 1) / TC_M);
+            rollout_mlp_tc_kernel<<<tiles, 256, smem, st>>>(pa, sc, cols);
         } else {
             rollout_mlp_kernel<<<work_grid, 256, 0, st>>>(pa, sc);
         }
     }
-    if (h->cfg.precision == SIT_F64)
-        rollout_sample_kernel<double><<<work_grid, 256, 0, st>>>(*h->kd, ship_ptrs<double>(h, state), env_ptrs<double>(h, state), pa, ra, sc);
-    else
-        rollout_sample_kernel<float><<<work_grid, 256, 0, st>>>(*h->kf, ship_ptrs<float>(h, state), env_ptrs<float>(h, state), pa, ra, sc);
-    if (pa.mode != SIT_POLICY_MEAN && ra.max_route_resampling >= 32) {
-        if (h->cfg.precision == SIT_F64)
-            rollout_resample_kernel<double><<<work_grid, 256, 0, st>>>(*h->kd, ship_ptrs<double>(h, state), env_ptrs<double>(h, state), pa, ra, sc);
-        else
-            rollout_resample_kernel<float><<<work_grid, 256, 0, st>>>(*h->kf, ship_ptrs<float>(h, state), env_ptrs<float>(h, state), pa, ra, sc);
-    }
+    rollout_sample_kernel<R><<<work_grid, 256, 0, st>>>(A, g, ge, pa, ra, sc);
+    if (pa.mode != SIT_POLICY_MEAN && ra.max_route_resampling >= 32)
+        rollout_resample_kernel<R><<<work_grid, 256, 0, st>>>(A, g, ge, pa, ra, sc);
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
+}
+
+extern "C" {
+
+int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const SitRollout* ro, void* stream) {
+    if (!h || !state || !pol) return fail(SIT_E_INVALID, "null argument");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_rollout_policy needs a SIT_KIND_ENV handle");
+    PolicyArgs pa;
+    bool tensor_cores = false;
+    int rc = policy_args(pol, pa, tensor_cores);
+    if (rc) return rc;
+    RollArgs ra;
+    rc = roll_args(h, ro, ra);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (tensor_cores) {
+        rc = pack_w1(h, pa, st);
+        if (rc) return rc;
+    }
+    return h->cfg.precision == SIT_F64 ? rollout_policy_t<double>(h, state, pa, tensor_cores, ra, 0, st)
+                                       : rollout_policy_t<float>(h, state, pa, tensor_cores, ra, 0, st);
 }
 
 int sit_rollout_step_k(SitHandle h, void* state, int32_t K, const SitRollout* ro, const SitEnvIO* io, void* stream) {
@@ -1711,30 +1748,100 @@ int sit_rollout_step_k(SitHandle h, void* state, int32_t K, const SitRollout* ro
     return h->cfg.precision == SIT_F64 ? rollout_step_t<double>(h, state, K, ra, io, st) : rollout_step_t<float>(h, state, K, ra, io, st);
 }
 
-// `iterations` x (sit_rollout_policy, sit_rollout_step_k(K)).  One iteration is captured once into a CUDA graph
-// (6 nodes) and replayed, so the loop costs one graph launch per iteration instead of six kernel launches through
-// the caller's language binding; the graph is re-captured when any argument changes.  use_graph == 0: plain launches.
+}  // extern "C"
+
+static int ensure_pipe(SitHandle h) {
+    if (h->pipe_ready) return SIT_OK;
+    for (int j = 0; j < SIT_PIPE; ++j) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&h->pipe[j], cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&h->pipe_done[j], cudaEventDisableTiming));
+    }
+    CUDA_TRY(cudaEventCreateWithFlags(&h->pipe_in, cudaEventDisableTiming));
+    h->pipe_ready = true;
+    return SIT_OK;
+}
+
+// Number of env groups one rollout iteration is cut into (SIT_ROLLOUT_GROUPS overrides).  The policy chain of a group
+// (gather -> MLP -> sample -> resample) is short, dependent and touches only the few envs at a decision event, so on its
+// own it leaves the GPU almost idle; with several groups in flight the chain of one group runs under the env-step kernel of
+// the others.  Envs are independent and every draw is keyed by (global env id, decision serial, try), so the grouping
+// does not change any env's trajectory.
+static int rollout_groups(SitHandle h) {
+    int g = h->n_envs >= 32768 ? 4 : (h->n_envs >= 8192 ? 2 : 1);
+    if (const char* e = std::getenv("SIT_ROLLOUT_GROUPS")) g = std::atoi(e);
+    g = std::max(1, std::min(g, std::min(SIT_ROLL_GROUPS_MAX, SIT_PIPE + 1)));
+    while (g > 1 && h->n_envs / g < 256) --g;
+    return g;
+}
+
+// one iteration = policy + K steps for every env, as `groups` independent chains: group 0 on the caller's stream, the others
+// forked onto the handle's internal streams and joined back (works eagerly and under stream capture alike)
+static int rollout_iteration(SitHandle h, void* state, int K, const PolicyArgs& pa, bool tensor_cores, const RollArgs& ra0,
+                             const SitEnvIO* io, int groups, cudaStream_t st) {
+    int rc = SIT_OK;
+    if (tensor_cores && (rc = pack_w1(h, pa, st))) return rc;
+    const int64_t B = h->n_envs, per = ((B + groups - 1) / groups + 255) / 256 * 256;
+    if (groups > 1) {
+        CUDA_TRY(cudaEventRecord(h->pipe_in, st));
+        for (int gi = 1; gi < groups; ++gi) CUDA_TRY(cudaStreamWaitEvent(h->pipe[gi - 1], h->pipe_in, 0));
+    }
+    for (int gi = 0; gi < groups; ++gi) {
+        RollArgs ra = ra0;
+        ra.env_first = std::min<int64_t>(B, gi * per);
+        ra.env_count = std::min<int64_t>(B, (gi + 1) * per) - ra.env_first;
+        if (ra.env_count <= 0) continue;
+        cudaStream_t gs = gi == 0 ? st : h->pipe[gi - 1];
+        if (h->cfg.precision == SIT_F64) {
+            rc = rollout_policy_t<double>(h, state, pa, tensor_cores, ra, gi, gs);
+            if (!rc) rc = rollout_step_t<double>(h, state, K, ra, io, gs);
+        } else {
+            rc = rollout_policy_t<float>(h, state, pa, tensor_cores, ra, gi, gs);
+            if (!rc) rc = rollout_step_t<float>(h, state, K, ra, io, gs);
+        }
+        if (rc) return rc;
+    }
+    for (int gi = 1; gi < groups; ++gi) {
+        CUDA_TRY(cudaEventRecord(h->pipe_done[gi - 1], h->pipe[gi - 1]));
+        CUDA_TRY(cudaStreamWaitEvent(st, h->pipe_done[gi - 1], 0));
+    }
+    return SIT_OK;
+}
+
+extern "C" {
+
+// `iterations` x (sit_rollout_policy, sit_rollout_step_k(K)), each iteration cut into env groups whose chains overlap
+// (rollout_groups above).  One iteration is captured once into a CUDA graph and replayed, so the loop costs one graph launch
+// per iteration instead of ~7 launches per group through the caller's language binding; the graph is re-captured when any
+// argument changes.  use_graph == 0: plain launches.
 int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K, const SitPolicy* pol, const SitRollout* ro,
                         const SitEnvIO* io, int32_t use_graph, void* stream) {
     if (!h || !state || !pol || !ro) return fail(SIT_E_INVALID, "null argument");
     if (iterations < 0 || K < 1) return fail(SIT_E_INVALID, "iterations must be >= 0 and K >= 1");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_rollout_collect needs a SIT_KIND_ENV handle");
+    if (io && io->rec_steps > 1) return fail(SIT_E_INVALID, "sit_rollout_collect records the last step only (rec_steps <= 1)");
     if (iterations == 0) return SIT_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CUDA_TRY(cudaSetDevice(h->device));
+    PolicyArgs pa;
+    bool tensor_cores = false;
+    int rc = policy_args(pol, pa, tensor_cores);
+    if (rc) return rc;
+    RollArgs ra;
+    rc = roll_args(h, ro, ra);
+    if (rc) return rc;
+    const int groups = rollout_groups(h);
+    if (groups > 1 && (rc = ensure_pipe(h))) return rc;
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (st != nullptr) CUDA_TRY(cudaStreamIsCapturing(st, &cs));
     if (!use_graph || st == nullptr || cs != cudaStreamCaptureStatusNone) {   // legacy stream cannot be captured
-        for (int it = 0; it < iterations; ++it) {
-            int rc = sit_rollout_policy(h, state, pol, ro, stream);
-            if (rc) return rc;
-            rc = sit_rollout_step_k(h, state, K, ro, io, stream);
-            if (rc) return rc;
-        }
+        for (int it = 0; it < iterations; ++it)
+            if ((rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, groups, st))) return rc;
         return SIT_OK;
     }
     std::string key;
     key.append(reinterpret_cast<const char*>(&state), sizeof(state));
     key.append(reinterpret_cast<const char*>(&K), sizeof(K));
+    key.append(reinterpret_cast<const char*>(&groups), sizeof(groups));
     key.append(reinterpret_cast<const char*>(pol), sizeof(*pol));
     key.append(reinterpret_cast<const char*>(ro), sizeof(*ro));
     SitEnvIO io0;
@@ -1744,14 +1851,10 @@ int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K,
     if (!h->roll_graph || key != h->roll_key) {
         if (h->roll_graph) { cudaGraphExecDestroy(h->roll_graph); h->roll_graph = nullptr; }
         // one eager iteration first: validates the arguments and sizes the scratch outside the capture
-        int rc = sit_rollout_policy(h, state, pol, ro, stream);
-        if (rc) return rc;
-        rc = sit_rollout_step_k(h, state, K, ro, io, stream);
-        if (rc) return rc;
+        if ((rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, groups, st))) return rc;
         if (--iterations == 0) return SIT_OK;
         CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        rc = sit_rollout_policy(h, state, pol, ro, stream);
-        if (!rc) rc = sit_rollout_step_k(h, state, K, ro, io, stream);
+        rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, groups, st);
         cudaGraph_t graph = nullptr;
         cudaError_t ce = cudaStreamEndCapture(st, &graph);
         if (rc || ce != cudaSuccess) {
