@@ -199,6 +199,7 @@ def run_b200(args, rank, world, local_rank):
     import torch.distributed as dist
     import sac_maritime_ast_b200 as sit
     from sac_maritime_ast_b200 import _lib
+    from sac_maritime_ast_b200 import rollout as ro_mod
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device and no CPU fallback (use --impl reference for the CPU arm)")
@@ -315,11 +316,40 @@ def run_b200(args, rank, world, local_rank):
         line["ast_env"] = ast
         ast_rec = env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", record_all=True)
         line["ast_env_recorded"] = {k: ast_rec[k] for k in ("value", "unit", "ms_per_launch", "write_gbs")}
-        # ---- SAC-AST rollout (BASELINE config 4): policy fused into the device loop, samples/s --------------------------
-        rl = rollout_leg(sit, dev)
+    if not args.no_extras:
+        # ---- SAC-AST rollout (BASELINE config 4): policy fused into the device loop, samples/s.  Every rank rolls out its
+        # own shard of envs (global env ids rank*B ..), then the replay rows of the timed segment are all-gathered and the
+        # episode counters all-reduced over NCCL -- the only collectives of the framework, after the segment ----------------
+        B_roll = 65536
+        rl = rollout_leg(sit, dev, B=B_roll, env_id_offset=rank * B_roll)
         smp_keep = rl.pop("sampler")
-        line["rollout"] = rl
-        line["learner"] = learner_leg(sit, dev, smp_keep)
+        rows = smp_keep.transitions()[:min(rl["samples"], smp_keep.capacity)]
+        barrier()
+        ev0.record()
+        allrows = ro_mod.gather_replay(rows)
+        tot_stats = ro_mod.reduce_stats(smp_keep.env.stats)
+        ev1.record()
+        barrier()
+        agg = torch.tensor([rl["samples"], rl["env_steps"], rows.shape[0]], dtype=torch.float64, device=dev)
+        tm = torch.tensor([rl["ms_total"], ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        ids = allrows[:, 23].contiguous().view(torch.int32)
+        rl.update({"n_gpus": world, "envs": world * B_roll, "envs_per_gpu": B_roll, "samples": int(agg[0].item()),
+                   "env_steps": int(agg[1].item()), "ms_total": float(tm[0].item()), "gather_ms": float(tm[1].item()),
+                   "gathered_rows": int(allrows.shape[0]), "gathered_bytes": int(allrows.numel() * 4),
+                   "gather_complete": bool(allrows.shape[0] == int(agg[2].item()) and int(ids.min()) >= 0
+                                           and int(ids.max()) < world * B_roll and int(tot_stats[13].item()) > 0),
+                   "value": float(agg[0].item()) / ((float(tm[0].item()) + float(tm[1].item())) * 1e-3),
+                   "value_without_gather": float(agg[0].item()) / (float(tm[0].item()) * 1e-3),
+                   "env_steps_per_s": float(agg[1].item()) / (float(tm[0].item()) * 1e-3),
+                   "collective": "NCCL all_gather of replay rows + all_reduce of 16 counters after the segment"
+                                 if world > 1 else "none (one rank)"})
+        del allrows
+        if rank == 0:
+            line["rollout"] = rl
+            line["learner"] = learner_leg(sit, dev, smp_keep)
     if rank == 0 and not args.no_cpu_baseline and not args.no_extras:
         n = calibrate_cpu_sample(KI, args.max_wp, per_step_s=4.0)
         rate, cores, total = cpu_ship_steps_per_s(n, KI, 4, 1, args.max_wp, SEED)
@@ -460,7 +490,7 @@ def env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", rec
             "status_counts": {i: int(st[i]) for i in range(12)}}
 
 
-def rollout_leg(sit, dev, B=65536, K=16, iters=40, warm_iters=20, hidden=256, precision="fp32", mode="gaussian",
+def rollout_leg(sit, dev, B=65536, K=32, iters=40, warm_iters=20, hidden=256, precision="fp32", mode="gaussian",
                 env_id_offset=0, tc=1):
     """BASELINE config 4: SAC-AST rollout, policy MLP 10 -> 256 -> 256 -> 2 with fixed seeded weights evaluated on the
     decision-event subset between step launches, transitions compacted into a device replay ring.  Returns
@@ -489,7 +519,7 @@ def rollout_leg(sit, dev, B=65536, K=16, iters=40, warm_iters=20, hidden=256, pr
     rows = smp.replay[:min(smp.n_transitions(), smp.capacity)]
     return {"metric": "SAC-AST rollout samples/s", "value": float(dc[0]) / (ms * 1e-3), "unit": "samples/s",
             "env_steps_per_s": float(ds[13]) / (ms * 1e-3), "envs": B, "k_per_launch": K, "iterations": iters,
-            "ms_per_iteration": ms / iters, "policy": f"{mode} MLP 10-{hidden}-{hidden}-2" if mode != "uniform" else "uniform",
+            "ms_per_iteration": ms / iters, "ms_total": ms, "policy": f"{mode} MLP 10-{hidden}-{hidden}-2" if mode != "uniform" else "uniform",
             "policy_hidden_layer": "tcgen05 bf16 x bf16 -> fp32 (TMEM)" if (tc and mode != "uniform") else "fp32 CUDA cores",
             "dtype": precision, "samples": int(dc[0]), "env_steps": int(ds[13]), "resamples": int(dc[2]),
             "episodes": int(ds[12]), "lane_utilisation": float(ds[13]) / (B * K * iters),

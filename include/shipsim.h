@@ -254,6 +254,11 @@ int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K,
                         const SitEnvIO* io, int32_t use_graph, void* stream);
 /* mark every env pending at the start of a rollout (after sit_reset + sit_env_init_step) */
 int sit_rollout_begin(SitHandle h, void* state, void* stream);
+/* number of env groups sit_rollout_collect pipelines one iteration over (1 = a single chain on the caller's stream; more:
+ * the groups' chains run on internal streams forked from and joined to the caller's, inside the same CUDA graph).  Envs are
+ * independent and every random draw is keyed by (global env id, decision serial, try), so no env's trajectory depends on
+ * it.  Chosen from n_envs; the environment variable SIT_ROLLOUT_GROUPS overrides. */
+int sit_rollout_group_count(SitHandle h, int32_t* groups);
 
 /* Map predicates for n candidate waypoints (device arrays of reals): flags[i] bit 0 = inside an obstacle polygon
  * (is_route_inside_obstacles MSRL_env_ex.py:544-552 -> obstacle.py:131-136), bit 1 = outside the map AABB

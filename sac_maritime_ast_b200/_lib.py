@@ -99,7 +99,7 @@ POLICY_TC_BF16 = 0x100
 RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_N = 0, 1, 2, 3, 8
 
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host",
-           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
+           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_group_count", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
            "sit_sac_create", "sit_sac_destroy", "sit_sac_workspace_bytes", "sit_sac_field", "sit_sac_init", "sit_sac_policy",
            "sit_sac_update",
            "sit_last_error", "sit_status_string", "sit_abi_version", "sit_measure_fma_peak")
@@ -135,6 +135,7 @@ def lib():
     L.sit_env_step_k.argtypes = [vp, vp, I32, P(SitEnvIO), vp]
     L.sit_env_step_host.argtypes = [vp, vp, I32, vp, vp, I32, vp, vp, vp, vp, vp]
     L.sit_rollout_begin.argtypes = [vp, vp, vp]
+    L.sit_rollout_group_count.argtypes = [vp, C.POINTER(C.c_int32)]
     L.sit_rollout_policy.argtypes = [vp, vp, P(SitPolicy), P(SitRollout), vp]
     L.sit_rollout_step_k.argtypes = [vp, vp, I32, P(SitRollout), P(SitEnvIO), vp]
     L.sit_rollout_collect.argtypes = [vp, vp, I32, I32, P(SitPolicy), P(SitRollout), P(SitEnvIO), I32, vp]

@@ -160,8 +160,12 @@ class IntermediateWaypointSampler:
         _lib.check(e.L.sit_rollout_collect(e.h, e.state_ptr(), int(iterations), int(K), C.byref(self._pol), C.byref(self.ro),
                                            C.byref(self.io), 1, self._side.cuda_stream))
         cur.wait_stream(self._side)
-        # gather + (w1 pack) + mlp + sample + resample + step kernels per iteration
-        self.launches += (6 if getattr(self.policy, 'tensor_cores', False) else 5) * iterations
+        # per env group: gather + mlp + sample + resample + step kernels; plus one w1 pack per iteration (tensor cores)
+        groups = C.c_int32(1)
+        _lib.check(e.L.sit_rollout_group_count(e.h, C.byref(groups)))
+        tc = bool(getattr(self.policy, 'tensor_cores', False))
+        per_group = 4 + (0 if isinstance(self.policy, UniformPolicy) else 1)
+        self.launches += (per_group * groups.value + (1 if tc else 0)) * iterations
 
     # ---- results ----------------------------------------------------------------------------------------------
     def n_transitions(self) -> int:
