@@ -94,7 +94,11 @@ def cpu_ship_steps_per_s(n, k_inner, steps, warmup, max_wp, seed, threads=0):
     arr["north"], arr["east"], arr["psi"], arr["u_sp"] = wp_n[0], wp_e[0], psi0, u_sp
     arr["wp_n"][:, :max_wp] = wp_n.T; arr["wp_e"][:, :max_wp] = wp_e.T
     arr["n_wp"] = n_wp
-    cores = L.orc_max_threads() if threads <= 0 else threads
+    if threads <= 0:
+        # all host cores this process may run on (torchrun exports OMP_NUM_THREADS=1, which would otherwise make the
+        # OpenMP port single-threaded)
+        threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = threads
     times = []
     for it in range(warmup + steps):
         d = np.ascontiguousarray(make_dist(n, rng).astype(np.float64))
@@ -206,6 +210,7 @@ def run_b200(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -300,7 +305,8 @@ def run_b200(args, rank, world, local_rank):
         per_gpu = value / world
         ach = per_gpu * F_SHIP / 1e12
         line["roofline"] = {"bound": "fp32", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value,
-                            "traffic": None,
+                            "traffic": ncu_traffic("fleet32") if (S == 1 << 20 and KI == 256) else None,
+                            "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r01_traffic.json)",
                             "note": "CUDA-core FP32 pipe bound (no tensor-core or HBM roofline applies to the K-step kernel): "
                                     "achieved = ship-steps/s/GPU x 250 algorithmic FLOP; peak = FFMA chain measured live on this GPU "
                                     "(sit_measure_fma_peak); kernel time = ms_per_step (one launch per step, CUDA events)"}
@@ -362,6 +368,15 @@ def run_b200(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def ncu_traffic(label):
+    """DRAM bytes per launch of the kernel `label` from the committed `ncu --set full` capture of the same workload
+    (profiles/r01_traffic.json, written by tools/ncu_traffic.py), or None."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))[label]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def traj_roofline(sit, dev, precision="fp64"):
     """Fleet with full trajectory write-out [K][8][S] (BASELINE config 2 layout): achieved HBM GB/s.  fp64: 64 B per
     ship-step (the config-2 kernel, co-bound by the FP64 pipe); fp32: 32 B per ship-step (the config-3 arithmetic)."""
@@ -391,7 +406,8 @@ def traj_roofline(sit, dev, precision="fp64"):
         peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]; src = "MEASURED_PEAKS.json"
     except Exception:
         pass
-    return {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+    return {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+            "traffic": ncu_traffic("traj64" if f64 else "traj32"), "algorithmic_bytes_per_launch": bytes_per_step * S * K,
             "kernel": f"fleet_step_fast_kernel<{'double' if f64 else 'float'}, TRAJ> (every-step trajectory write-out)", "ships": S, "k": K,
             "ms_per_launch": ms, "ship_steps_per_s": S * K / (ms * 1e-3), "peak_source": src,
             "note": f"algorithmic bytes = {bytes_per_step} B written per ship-step (8 {precision} channels); output ~1.2 GB per launch > L2"}
