@@ -24,11 +24,12 @@
 extern "C" {
 #endif
 
-#define SIT_ABI_VERSION 1
+#define SIT_ABI_VERSION 2
 #define SIT_MAX_WP 16     /* route capacity per ship: 2 + sampling_frequency (main_ast.py:47) fits */
 #define SIT_MAX_MODES 4   /* machinery modes per ship (PTO / PTI / MEC, main_ast.py:136-158) */
 #define SIT_MAX_EDGES 128 /* polygon ring segments of the map (default map: 39, main_ast.py:200-205) */
 #define SIT_N_OBS 10      /* observation vector, MSRL_env_ex.py:424-435 */
+#define SIT_N_REWARD_PARTS 8
 #define SIT_N_TRAJ 8      /* trajectory channels N, E, psi, u, v, r, omega, k */
 #define SIT_N_LOG 27      /* simulation_results channels, ship_model.py:645-684 */
 #define SIT_N_STATS 16    /* 12 status-bit counters + done, steps, decisions, reserved */
@@ -180,6 +181,11 @@ typedef struct SitEnvIO {
     uint8_t* done_any;       /* [n_envs]: any step of this launch was done */
     unsigned long long* stats; /* [SIT_N_STATS] accumulated with warp-reduced atomics: counts of each status
                                 bit (0..11), done steps (12), env-steps (13) */
+    void* reward_parts;      /* [rec_steps][SIT_N_REWARD_PARTS][n_envs] reals, may be NULL: the per-step increments of the
+                                reference's cumulative `reward_results` lists (MSRL_env_ex.py:133-141, appended in
+                                reward_function :924-964): test_ship reward_e_ct, reward_near_col, total_non_terminal;
+                                obs_ship reward_base, reward_e_ct, reward_near_col, total_non_terminal; shared
+                                total_non_terminal */
 } SitEnvIO;
 
 /* MultiShipRLEnv.reset (MSRL_env_ex.py:145-186): same as sit_reset on an env handle */

@@ -14,6 +14,6 @@ from .config import (  # noqa: F401
     default_ship, ship_params)
 from .env import MultiShipRLEnv, ShipAssets  # noqa: F401
 from .fleet import ShipFleet  # noqa: F401
-from .results import LOG_KEYS, SimulationResults  # noqa: F401
+from .results import LOG_KEYS, REWARD_KEYS, RewardResults, SimulationResults  # noqa: F401
 
-__all__ = ["ShipFleet", "MultiShipRLEnv", "ShipAssets", "PolygonObstacle", "default_ship", "ShipSimError", "SimulationResults"]
+__all__ = ["ShipFleet", "MultiShipRLEnv", "ShipAssets", "PolygonObstacle", "default_ship", "ShipSimError", "SimulationResults", "RewardResults"]

@@ -7,7 +7,7 @@ import os
 
 MAX_WP, MAX_MODES, MAX_EDGES = 16, 4, 128
 N_OBS, N_TRAJ, N_LOG, N_STATS = 10, 8, 27, 16
-ABI_VERSION = 1
+ABI_VERSION = 2
 F64, F32 = 0, 1
 KIND_FLEET, KIND_ENV = 1, 2
 SG = {"MOTOR": 0, "GEN": 1, "OFF": 2}
@@ -74,7 +74,8 @@ class SitEnvIO(C.Structure):
     _fields_ = [("action", C.c_void_p), ("sac_update", C.c_void_p), ("act_steps", I32), ("init", I32),
                 ("auto_reset", I32), ("rec_steps", I32),
                 ("obs", C.c_void_p), ("reward", C.c_void_p), ("done", C.c_void_p), ("status", C.c_void_p),
-                ("reward_sum", C.c_void_p), ("done_any", C.c_void_p), ("stats", C.c_void_p)]
+                ("reward_sum", C.c_void_p), ("done_any", C.c_void_p), ("stats", C.c_void_p),
+                ("reward_parts", C.c_void_p)]
 
 
 class SitPolicy(C.Structure):
@@ -93,6 +94,7 @@ class SitSacConfig(C.Structure):
                 ("seed", C.c_uint64)]
 
 
+N_REWARD_PARTS = 8
 TR_FLOATS = 24
 POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
 POLICY_TC_BF16 = 0x100

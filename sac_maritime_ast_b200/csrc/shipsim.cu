@@ -47,6 +47,7 @@ struct EnvIO {
     const R* action; const uint8_t* sac_update; int32_t act_steps; int32_t init; int32_t auto_reset; int32_t rec_steps;
     R* obs; R* reward; uint8_t* done; int32_t* status; R* reward_sum; uint8_t* done_any; unsigned long long* stats;
     const uint8_t* mask;   // init_step only
+    R* rew_parts;          // [rec][SIT_N_REWARD_PARTS][B] per-step increments of reward_results (MSRL_env_ex.py:924-964)
 };
 
 template <typename R>
@@ -366,9 +367,11 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         const R ect = s.e_ct;
 
         // ---- per-ship reward terms and terminal checks (sequential stop_flag gating) -------------------
-        int st = 0; bool dn_ = false; R part;
+        int st = 0; bool dn_ = false; R part, part_own_nt;
+        R rp0 = (R)0, rp1 = (R)0, rp2 = (R)0;   // reward_results increments of this ship (written only when asked for)
         if (!is_obs) {
             // test_ship_non_terminal_state_reward :628-664
+            rp0 = abs_(ect) * EP.inv_e_tol; rp1 = ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
             const R ntt = abs_(ect) * EP.inv_e_tol + ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
             R rt = (R)0;
             // test_ship_terminal_state_reward :734-809
@@ -378,11 +381,14 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             if (abs_(o.rpm) > EP.rpm_max) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_MECH; }
             if (abs_(ect) > EP.e_tol) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_NAV; }
             if (o.power_me_kw > o.avail_me_kw) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_BLACKOUT; }
-            part = ntt + rt;
+            part = ntt + rt; part_own_nt = ntt;
         } else {
             // obs_ship_non_terminal_state_reward :666-710 (stop flag from before this step's checks)
             R nto = (R)0;
-            if (!stop) nto = (R)0.1 + (-(abs_(ect) * EP.inv_e_tol) * (R)0.01) + (-((R)1 - dmap * EP.inv_max_north) * (R)0.01);
+            if (!stop) {
+                nto = (R)0.1 + (-(abs_(ect) * EP.inv_e_tol) * (R)0.01) + (-((R)1 - dmap * EP.inv_max_north) * (R)0.01);
+                rp0 = (R)0.1; rp1 = -(abs_(ect) * EP.inv_e_tol) * (R)0.01; rp2 = -((R)1 - dmap * EP.inv_max_north) * (R)0.01;
+            }
             R ro_ = (R)0;
             // obs_ship_terminal_state_reward :811-881
             if (arrived) { stop = true; st |= SIT_ST_OBS_ENDPOINT; }                       // no done
@@ -395,7 +401,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             // shared_non_terminal_state_reward :712-731 (sees the stop flag after the checks above)
             R snt = (R)0;
             if (!stop) snt = ((R)1 - (R)sqrt(ship_d2) * EP.inv_max_north) * (R)0.001;
-            part = nto;      // assembled below as ((((ntt+rt) + nto) + ro) + snt) + rs
+            part = nto; part_own_nt = nto;      // assembled below as ((((ntt+rt) + nto) + ro) + snt) + rs
             // stash ro, snt in o.* free slots
             o.rud = ro_; o.thr = snt;
         }
@@ -424,6 +430,11 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
                 } else {
                     ob[6 * B] = pn; ob[7 * B] = pe; ob[8 * B] = s.psi; ob[9 * B] = ect;
                 }
+            }
+            if (io.rew_parts) {
+                R* rp = io.rew_parts + rec * SIT_N_REWARD_PARTS * B + env;
+                if (!is_obs) { rp[0] = rp0; rp[B] = rp1; rp[2 * B] = part_own_nt; }
+                else { rp[3 * B] = rp0; rp[4 * B] = rp1; rp[5 * B] = rp2; rp[6 * B] = part_own_nt; rp[7 * B] = o.thr; }
             }
             if (is_obs) {
                 if (io.reward) io.reward[rec * B + env] = reward;
@@ -1567,6 +1578,7 @@ static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaS
         k.act_steps = io->act_steps; k.init = io->init; k.auto_reset = io->auto_reset; k.rec_steps = io->rec_steps;
         k.obs = static_cast<R*>(io->obs); k.reward = static_cast<R*>(io->reward); k.done = io->done; k.status = io->status;
         k.reward_sum = static_cast<R*>(io->reward_sum); k.done_any = io->done_any; k.stats = io->stats;
+        k.rew_parts = static_cast<R*>(io->reward_parts);
         if (!(k.act_steps == 1 || k.act_steps == K)) return fail(SIT_E_INVALID, "act_steps must be 1 or K");
         if (!(k.rec_steps == 1 || k.rec_steps == K)) return fail(SIT_E_INVALID, "rec_steps must be 1 or K");
     }

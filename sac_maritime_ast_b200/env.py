@@ -192,12 +192,13 @@ class MultiShipRLEnv(SimCore):
         return out["obs"][0].t(), out["reward"][0], out["done"][0].bool(), out["status"][0]
 
     def step_k(self, K, converted_action, SAC_update=False, init=None, auto_reset=False, record_all=True,
-               want_sums=False, out: Optional[dict] = None):
+               want_sums=False, out: Optional[dict] = None, reward_parts=False):
         """K env steps in ONE launch.  converted_action [n_envs, 2] (held for the launch; SAC_update applies to
         its first step) or [K, n_envs, 2] with SAC_update [K, n_envs].  init: True / False for the first
         step, None = per-env first-step-since-reset flag.  auto_reset: False, True (reference reset semantics,
         quirk Q3) or "hard" (integrators, shaft speed and fuel restored too).  Outputs are SoA: obs [rec, 10, n_envs],
-        reward / done / status [rec, n_envs] with rec = K (record_all) or 1 (last step)."""
+        reward / done / status [rec, n_envs] with rec = K (record_all) or 1 (last step); reward_parts adds
+        ``reward_parts`` [rec, 8, n_envs], the per-step increments of the reference's ``reward_results`` lists."""
         io = _lib.SitEnvIO()
         act = self._as_action(converted_action, K)
         sac = self._as_mask(SAC_update, K)
@@ -213,6 +214,8 @@ class MultiShipRLEnv(SimCore):
         B = self.n_envs
         spec = (("obs", (rec, _lib.N_OBS, B), self.real), ("reward", (rec, B), self.real),
                 ("done", (rec, B), torch.uint8), ("status", (rec, B), torch.int32))
+        if reward_parts:
+            spec += (("reward_parts", (rec, _lib.N_REWARD_PARTS, B), self.real),)
         for name, shape, dt in spec:
             t = res.get(name)
             if t is None or tuple(t.shape) != shape:

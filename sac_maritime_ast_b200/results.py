@@ -68,3 +68,54 @@ class SimulationResults:
 
     def reset(self):
         self.chunks = []
+
+
+# (ship, key) order of MultiShipRLEnv.reward_results, MSRL_env_ex.py:133-141 (== channel order of SIT_N_REWARD_PARTS)
+REWARD_KEYS = (("test_ship", "reward_e_ct"), ("test_ship", "reward_near_col"), ("test_ship", "total_non_terminal"),
+               ("obs_ship", "reward_base"), ("obs_ship", "reward_e_ct"), ("obs_ship", "reward_near_col"),
+               ("obs_ship", "total_non_terminal"), ("shared", "total_non_terminal"))
+
+
+class RewardResults:
+    """Recorder around a ``MultiShipRLEnv``: the reference's ``reward_results`` -- cumulative sums of the non-terminal reward
+    terms, one entry appended per ``step`` (reward_function, MSRL_env_ex.py:924-964), lists re-created by ``reset()``
+    (through reward_function_params, :174) -- as a device buffer of per-step increments ``[steps][8][n_envs]`` written by the
+    env-step kernel; the running sums are formed when an exporter is called.  ``reset()`` here resets the env and clears the
+    record, like the reference's ``env.reset()`` does."""
+
+    def __init__(self, env, envs: Optional[torch.Tensor] = None):
+        self.env = env
+        self.envs = None if envs is None else torch.as_tensor(envs, dtype=torch.long, device=env.device)
+        self.chunks: List[torch.Tensor] = []
+
+    def step_k(self, K, converted_action, SAC_update=False, **kw):
+        out = self.env.step_k(K, converted_action, SAC_update, record_all=True, reward_parts=True, **kw)
+        rp = out["reward_parts"]
+        self.chunks.append(rp.clone() if self.envs is None else rp.index_select(2, self.envs))
+        return out
+
+    def reset(self, **kw):
+        self.chunks = []
+        return self.env.reset(**kw)
+
+    def __len__(self) -> int:
+        return sum(c.shape[0] for c in self.chunks)
+
+    def increments(self) -> torch.Tensor:
+        """[steps, 8, n_kept_envs] device tensor of per-step increments."""
+        if not self.chunks:
+            n = self.env.n_envs if self.envs is None else self.envs.numel()
+            return torch.empty((0, len(REWARD_KEYS), n), dtype=self.env.real, device=self.env.device)
+        if len(self.chunks) > 1:
+            self.chunks = [torch.cat(self.chunks, dim=0)]
+        return self.chunks[0]
+
+    def to_dict(self, env: int = 0) -> Dict[str, Dict[str, List[float]]]:
+        """The reference's nested ``reward_results`` dict of one (kept) env: running sums in float64, added in step order
+        exactly like ``prev + r`` (numpy's cumsum is sequential)."""
+        inc = self.increments()[:, :, env].double().cpu().numpy()
+        cum = np.cumsum(inc, axis=0)
+        res: Dict[str, Dict[str, List[float]]] = {"test_ship": {}, "obs_ship": {}, "shared": {}}
+        for c, (ship, key) in enumerate(REWARD_KEYS):
+            res[ship][key] = cum[:, c].tolist()
+        return res
