@@ -109,6 +109,29 @@ __device__ __forceinline__ bool map_contains(const EdgeRec<R>* __restrict__ E, c
     return in[0];
 }
 
+// Same test over a subset of the ring segments (indices in `list`).  Exact whenever every skipped segment can contribute
+// neither a crossing nor a boundary hit for the point: its y-range does not reach py, or it lies strictly left of px
+// (see arc_edge_list in shipsim.cu, which builds such a subset once for all candidate waypoints of one decision).
+template <typename R>
+__device__ __forceinline__ bool map_contains_list(const EdgeRec<R>* __restrict__ E, const uint8_t* __restrict__ list,
+                                                  const int n_list, const R py, const R px) {
+    uint32_t parity = 0u, bmask = 0u;
+#pragma unroll 2
+    for (int j = 0; j < n_list; ++j) {
+        const EdgeRec<R> e = E[list[j]];
+        const uint32_t pbit = (uint32_t)e.pbit;
+        const bool down = e.y2 < e.y1, horiz = e.y1 == e.y2;
+        const R lo = e.x1 <= e.x2 ? e.x1 : e.x2, hi = e.x1 <= e.x2 ? e.x2 : e.x1;
+        const bool right = !(e.x1 < px && e.x2 < px);
+        const bool straddle = (e.y1 > py && e.y2 <= py) || (e.y2 > py && e.y1 <= py);
+        const R d = e.dx * (py - e.y1) - e.dy * (px - e.x1);
+        const bool on = (px == e.x2 && py == e.y2) || (horiz && e.y1 == py && lo <= px && px <= hi) || (straddle && d == (R)0);
+        bmask |= (right && on) ? pbit : 0u;
+        parity ^= (right && straddle && ((d > (R)0) != down)) ? pbit : 0u;
+    }
+    return (parity & ~bmask) != 0u;
+}
+
 // One pass over the ring segments for the hull centre: squared distance to the nearest ring
 // (obstacle.py:138-141 min(poly.exterior.distance)) and containment of the centre, sharing the
 // per-edge cross product.  Valid as the containment of all four hull corners whenever
