@@ -353,7 +353,24 @@ def run_b200(args, rank, world, local_rank):
                    "collective": "NCCL all_gather of replay rows + all_reduce of 16 counters after the segment"
                                  if world > 1 else "none (one rank)"})
         del allrows
+        # ---- long horizon (BASELINE config 5): 10 000 steps, run-time machinery-mode switching, all checks on; every rank
+        # runs its own envs, the termination histogram is summed over ranks with one all-reduce after the run ---------------
+        barrier()
+        lh = long_horizon_leg(sit, dev, rank)
+        barrier()
+        lh_ms = torch.tensor([lh["ms"]], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(lh_ms, op=dist.ReduceOp.MAX)
+        lh_stats = ro_mod.reduce_stats(lh["stats"]).cpu().numpy()
         if rank == 0:
+            line["long_horizon"] = {
+                "metric": "AST env-steps/s over a 10 000-step horizon with machinery-mode switching (config 5)",
+                "value": float(lh_stats[13]) / (float(lh_ms.item()) * 1e-3), "unit": "env-steps/s", "n_gpus": world,
+                "envs_per_gpu": lh["envs"], "steps": lh["steps"], "launches_per_gpu": lh["launches"],
+                "ms_total": float(lh_ms.item()), "mode_redraw_every": 512, "modes": ["PTO", "PTI", "MEC"],
+                "env_steps_counted": int(lh_stats[13]), "episodes_done": int(lh_stats[12]),
+                "status_counts": {i: int(lh_stats[i]) for i in range(12)}, "state_finite": lh["finite"],
+                "collective": "one all_reduce of 16 counters after the run" if world > 1 else "none (one rank)"}
             line["rollout"] = rl
             line["learner"] = learner_leg(sit, dev, smp_keep)
     if rank == 0 and not args.no_cpu_baseline and not args.no_extras:
@@ -504,6 +521,37 @@ def env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", rec
             "auto_reset": "hard (fresh construction; the reference's reset keeps integrators, quirk Q3)",
             "episodes_done": int(st[12]), "env_steps_counted": int(st[13]),
             "status_counts": {i: int(st[i]) for i in range(12)}}
+
+
+def long_horizon_leg(sit, dev, rank, B=65536, K=64, total_steps=10000, mode_every=512, precision="fp32"):
+    """BASELINE config 5: 10 000-step horizon with every termination / collision check on, in-kernel auto-reset, and the
+    obstacle ship's machinery mode re-drawn per env from {PTO, PTI, MEC} every `mode_every` steps (run-time mode switch =
+    mode_selector, ship_engine.py:233-237; the test ship stays in PTI, see make_bench_env).  Returns this rank's timing and
+    the 16 episode counters (the caller reduces them over ranks)."""
+    import torch
+    env, g = make_bench_env(sit, dev, B, precision, SEED + 17 * rank)
+    acts = [draw_waypoints(env, g, dev) for _ in range(8)]
+    sac = torch.ones(B, dtype=torch.uint8, device=dev)
+    n_draws = (total_steps + mode_every - 1) // mode_every
+    modes = torch.randint(0, 3, (n_draws, B), generator=g, device=dev, dtype=torch.int32)
+    out = {}
+    for w in range(3):
+        env.step_k(K, acts[w % 8], sac, init=None, auto_reset="hard", record_all=False, out=out)
+    torch.cuda.synchronize()
+    env.stats.zero_()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches, done_steps = 0, 0
+    e0.record()
+    while done_steps < total_steps:
+        if done_steps % mode_every == 0:
+            env.ship[1].mode.copy_(modes[done_steps // mode_every])
+        k = min(K, total_steps - done_steps, mode_every - done_steps % mode_every)
+        env.step_k(k, acts[launches % 8], sac, init=None, auto_reset="hard", record_all=False, out=out)
+        launches += 1; done_steps += k
+    e1.record()
+    torch.cuda.synchronize()
+    return {"ms": e0.elapsed_time(e1), "launches": launches, "stats": env.stats.clone(), "envs": B, "steps": total_steps,
+            "finite": bool(torch.isfinite(env.f["north"]).all() and torch.isfinite(env.f["omega"]).all())}
 
 
 def rollout_leg(sit, dev, B=65536, K=32, iters=40, warm_iters=20, hidden=256, precision="fp32", mode="gaussian",

@@ -1822,7 +1822,7 @@ static int ensure_pipe(SitHandle h) {
 // the others.  Envs are independent and every draw is keyed by (global env id, decision serial, try), so the grouping
 // does not change any env's trajectory.
 static int rollout_groups(SitHandle h) {
-    int g = h->n_envs >= 32768 ? 2 : 1;   // measured on B200, 65 536 envs: 2 groups +2..5 %, more groups lose it again
+    int g = 1;   // measured on B200, 65 536 envs: 2..3 groups within 1 % of one group once the re-draw chain was made cheap
     if (const char* e = std::getenv("SIT_ROLLOUT_GROUPS")) g = std::atoi(e);
     g = std::max(1, std::min(g, std::min(SIT_ROLL_GROUPS_MAX, SIT_PIPE + 1)));
     while (g > 1 && h->n_envs / g < 256) --g;
