@@ -119,17 +119,18 @@ __global__ void __launch_bounds__(256) fleet_step_fast_kernel(const __grid_const
         g.vc_n[i] = s.vcn; g.vc_e[i] = s.vce; g.wind_speed[i] = w_speed; g.wind_dir[i] = w_dir;
     }
     StepOut<R> o;
+    R* tr = io.traj + i;   // running row pointer of the every-step trajectory: one 64-bit add chain per step, no multiplies
 #pragma unroll 1
     for (int t = 0; t < K; ++t) {
         ship_step<R, false, SINGLE_MODE>(P, s, g, i, AVOID, true, o, nullptr);
         if (TRAJ) {   // every-step trajectory [K][8][S]: coalesced streaming stores, the only memory traffic of the loop
-            R* tr = io.traj + (int64_t)t * SIT_N_TRAJ * S + i;
-            __stcs(tr, (R)s.N); __stcs(tr + S, (R)s.E); __stcs(tr + 2 * S, s.psi); __stcs(tr + 3 * S, s.u);
-            __stcs(tr + 4 * S, s.v); __stcs(tr + 5 * S, s.r); __stcs(tr + 6 * S, s.om); __stcs(tr + 7 * S, (R)s.k);
+            R* q = tr;
+            __stcs(q, (R)s.N); q += S; __stcs(q, (R)s.E); q += S; __stcs(q, s.psi); q += S; __stcs(q, s.u); q += S;
+            __stcs(q, s.v); q += S; __stcs(q, s.r); q += S; __stcs(q, s.om); q += S; __stcs(q, (R)s.k);
+            tr = q + S;
         }
     }
     if (!TRAJ && io.traj) {
-        R* tr = io.traj + i;
         tr[0] = (R)s.N; tr[S] = (R)s.E; tr[2 * S] = s.psi; tr[3 * S] = s.u;
         tr[4 * S] = s.v; tr[5 * S] = s.r; tr[6 * S] = s.om; tr[7 * S] = (R)s.k;
     }
@@ -1450,7 +1451,10 @@ static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, c
     }
     const ShipPtrs<R> g = ship_ptrs<R>(h, state);
     const ShipP<R>& P = HostSel<R>::ship(h);
-    const int block = 256, grid = grid_for(k.count, block);
+    // fp64: 96 registers per thread -> 2 CTAs of 256 (16 warps / SM) but 5 CTAs of 128 (20 warps / SM)
+    static const int env_block = std::getenv("SIT_FLEET_BLOCK") ? std::atoi(std::getenv("SIT_FLEET_BLOCK")) : 0;
+    const int block = (env_block >= 32 && env_block <= 256 && env_block % 32 == 0) ? env_block : (sizeof(R) == 8 ? 128 : 256);
+    const int grid = grid_for(k.count, block);
     const bool quiet = (!k.dist || k.dist_steps == 1) && !k.log27 && !k.cmd && k.store;
     const bool fast = quiet && (!k.traj || k.traj_steps == 1);
     const bool single = P.n_modes == 1;
