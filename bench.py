@@ -218,6 +218,7 @@ def run_b200(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    args.warmup = max(args.warmup, 3)                      # timing rule: at least 3 untimed warm-up steps
     S, KI = args.ships_per_gpu, args.k_inner
     rng = np.random.default_rng(SEED + 1000 * rank)       # global ship ids differ per rank: independent shards
     n_wp, wp_n, wp_e, psi0, u_sp = make_routes(S, args.max_wp, rng)
