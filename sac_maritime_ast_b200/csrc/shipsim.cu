@@ -368,11 +368,10 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         const R ect = s.e_ct;
 
         // ---- per-ship reward terms and terminal checks (sequential stop_flag gating) -------------------
-        int st = 0; bool dn_ = false; R part, part_own_nt;
-        R rp0 = (R)0, rp1 = (R)0, rp2 = (R)0;   // reward_results increments of this ship (written only when asked for)
+        int st = 0; bool dn_ = false; R part;
+        const bool stop_in = stop;               // the obstacle ship's non-terminal terms see the flag from before this step
         if (!is_obs) {
             // test_ship_non_terminal_state_reward :628-664
-            rp0 = abs_(ect) * EP.inv_e_tol; rp1 = ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
             const R ntt = abs_(ect) * EP.inv_e_tol + ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
             R rt = (R)0;
             // test_ship_terminal_state_reward :734-809
@@ -382,14 +381,11 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             if (abs_(o.rpm) > EP.rpm_max) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_MECH; }
             if (abs_(ect) > EP.e_tol) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_NAV; }
             if (o.power_me_kw > o.avail_me_kw) { if (!stop) rt += (R)1000; stop = true; dn_ = true; st |= SIT_ST_TEST_BLACKOUT; }
-            part = ntt + rt; part_own_nt = ntt;
+            part = ntt + rt;
         } else {
             // obs_ship_non_terminal_state_reward :666-710 (stop flag from before this step's checks)
             R nto = (R)0;
-            if (!stop) {
-                nto = (R)0.1 + (-(abs_(ect) * EP.inv_e_tol) * (R)0.01) + (-((R)1 - dmap * EP.inv_max_north) * (R)0.01);
-                rp0 = (R)0.1; rp1 = -(abs_(ect) * EP.inv_e_tol) * (R)0.01; rp2 = -((R)1 - dmap * EP.inv_max_north) * (R)0.01;
-            }
+            if (!stop) nto = (R)0.1 + (-(abs_(ect) * EP.inv_e_tol) * (R)0.01) + (-((R)1 - dmap * EP.inv_max_north) * (R)0.01);
             R ro_ = (R)0;
             // obs_ship_terminal_state_reward :811-881
             if (arrived) { stop = true; st |= SIT_ST_OBS_ENDPOINT; }                       // no done
@@ -402,7 +398,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             // shared_non_terminal_state_reward :712-731 (sees the stop flag after the checks above)
             R snt = (R)0;
             if (!stop) snt = ((R)1 - (R)sqrt(ship_d2) * EP.inv_max_north) * (R)0.001;
-            part = nto; part_own_nt = nto;      // assembled below as ((((ntt+rt) + nto) + ro) + snt) + rs
+            part = nto;      // assembled below as ((((ntt+rt) + nto) + ro) + snt) + rs
             // stash ro, snt in o.* free slots
             o.rud = ro_; o.thr = snt;
         }
@@ -432,10 +428,16 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
                     ob[6 * B] = pn; ob[7 * B] = pe; ob[8 * B] = s.psi; ob[9 * B] = ect;
                 }
             }
-            if (io.rew_parts) {
+            if (io.rew_parts) {   // reward_results increments, recomputed here so the default path carries nothing for them
                 R* rp = io.rew_parts + rec * SIT_N_REWARD_PARTS * B + env;
-                if (!is_obs) { rp[0] = rp0; rp[B] = rp1; rp[2 * B] = part_own_nt; }
-                else { rp[3 * B] = rp0; rp[4 * B] = rp1; rp[5 * B] = rp2; rp[6 * B] = part_own_nt; rp[7 * B] = o.thr; }
+                const R r_ect = abs_(ect) * EP.inv_e_tol, r_col = ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
+                if (!is_obs) {
+                    rp[0] = r_ect; rp[B] = r_col; rp[2 * B] = r_ect + r_col;
+                } else {
+                    const bool on = !stop_in;
+                    rp[3 * B] = on ? (R)0.1 : (R)0; rp[4 * B] = on ? -r_ect * (R)0.01 : (R)0; rp[5 * B] = on ? -r_col : (R)0;
+                    rp[6 * B] = on ? (R)0.1 + (-r_ect * (R)0.01) + (-r_col) : (R)0; rp[7 * B] = o.thr;
+                }
             }
             if (is_obs) {
                 if (io.reward) io.reward[rec * B + env] = reward;
