@@ -94,3 +94,36 @@ def test_single_env_is_call_compatible_with_the_reference():
     assert abs(r.item() - g["ep1_reward"][0]) <= 1e-9 * max(1.0, abs(g["ep1_reward"][0]))
     assert bool(d.item()) == bool(g["ep1_done"][0]) and int(st.item()) == int(g["ep1_status"][0])
     assert sit.MultiShipRLEnv.decode_status(int(st.item())).startswith(" |Test ship not in terminal state|")
+
+
+@pytest.mark.parametrize("precision", ["fp32", "fp64"])
+def test_outputs_stay_inside_their_buffers(precision):
+    """Guard bands around every output of a ragged fleet launch and a ragged env launch stay untouched (compute-sanitizer
+    is not available on the pool, so the bounds are checked with sentinels)."""
+    import gpu_helpers as G
+    real = torch.float32 if precision == "fp32" else torch.float64
+    n, K, pad = 301, 37, 4096
+    fl = G.make_fleet(sc.SHIP_SCENARIOS["short_segments"], n_ships=n, precision=precision)
+
+    def banded(shape):
+        numel = int(np.prod(shape))
+        buf = torch.full((numel + 2 * pad,), -12345.0, dtype=real, device="cuda")
+        return buf, buf[pad:pad + numel].view(shape)
+    bt, traj = banded((K, 8, n)); bl, log = banded((K, 27, n)); bc, cmd = banded((K, 2, n))
+    fl.step(K, traj=True, log27=True, cmd=True, out={"traj": traj, "log27": log, "cmd": cmd})
+    bt2, traj2 = banded((K, 8, n))
+    fl.step(K, traj=True, out={"traj": traj2})          # the specialised every-step trajectory path (running row pointer)
+    torch.cuda.synchronize()
+    for buf, view in ((bt, traj), (bl, log), (bc, cmd), (bt2, traj2)):
+        assert (buf[:pad] == -12345.0).all() and (buf[-pad:] == -12345.0).all()
+        assert (view != -12345.0).all(), "every element of the output is written"
+    B = 45
+    env = G.make_env(sc.ENV_SCENARIOS["default"], n_envs=B, precision=precision)
+    env.reset(); env.init_step()
+    bo, obs = banded((K, 10, B)); br, rew = banded((K, B)); bp, parts = banded((K, 8, B))
+    env.step_k(K, (8300.0, 8600.0), True, init=True, record_all=True, reward_parts=True,
+               out={"obs": obs, "reward": rew, "reward_parts": parts})
+    torch.cuda.synchronize()
+    for buf, view in ((bo, obs), (br, rew), (bp, parts)):
+        assert (buf[:pad] == -12345.0).all() and (buf[-pad:] == -12345.0).all()
+        assert (view != -12345.0).all()
