@@ -258,6 +258,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     bool any_done = false;
     unsigned my_cnt = 0;   // lane b < 12 counts status bit b of this warp's envs; lane 12 counts done steps
     unsigned n_live = 0;   // env-steps actually executed by this lane (ROLL: pending envs do not step)
+    unsigned n_eps = 0;    // ROLL: episodes this env ended in the launch (terminal state or num_steps_episode reached)
     MapCache mc;           // nearest-ring cache, carried across launches in the state buffer
     mc.idx = (uint32_t)g.mc_idx[i]; mc.p0n = g.mc_n[i]; mc.p0e = g.mc_e[i]; mc.b2 = g.mc_b2[i];
 
@@ -467,6 +468,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         }
         // ---- in-kernel reset() + init_step() right after a terminal step ---------------------------------
         if (episode_end) {
+            if (ROLL && active && is_obs) n_eps += 1;
             reset_ship_regs(s, g, i, io.auto_reset == 2);   // MSRL_env_ex.py:145-186 (omega, integrators, fuel kept unless hard)
             endN = g.wp_n[(int64_t)(s.n_wp - 1) * S + i]; endE = g.wp_e[(int64_t)(s.n_wp - 1) * S + i];
             stop = false; nstored = 0; fresh = true;
@@ -550,6 +552,12 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) steps += __shfl_xor_sync(FULL, steps, d);
         if (lane == 13 && steps) atomicAdd(&io.stats[13], (unsigned long long)steps);
+    }
+    if (ROLL) {
+        unsigned eps = n_eps;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) eps += __shfl_xor_sync(FULL, eps, d);
+        if (lane == 14 && eps) atomicAdd(&ro.counters[SIT_RC_EPISODES], (unsigned long long)eps);
     }
 }
 
