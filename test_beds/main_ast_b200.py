@@ -151,9 +151,21 @@ def main(argv=None):
         with open(args.log_json, "w") as f:
             json.dump(history, f)
     if world > 1:
+        # the replicas must have stayed bit-identical: compare a checksum of every rank's policy / critic parameters
+        pol = torch.cat([agent.f[k].view(torch.int32).to(torch.int64).sum()[None] for k in ("policy", "q1", "q2")])
+        allp = [torch.empty_like(pol) for _ in range(world)]
+        dist.all_gather(allp, pol)
+        same = all(torch.equal(a, allp[0]) for a in allp)
+        if rank == 0:
+            print(f"learner replicas identical over {world} ranks: {same}", flush=True)
+        if not same:
+            raise SystemExit("learner replicas diverged")
         dist.barrier()
     return history, agent, memory
 
 
 if __name__ == "__main__":
     main()
+    import torch.distributed as _dist
+    if _dist.is_available() and _dist.is_initialized():
+        _dist.destroy_process_group()
