@@ -218,7 +218,7 @@ __device__ __forceinline__ void reset_ship_regs(Ship<R>& s, const ShipPtrs<R>& g
 // ROLL: device-resident rollout (sit_rollout_step_k): envs waiting for a policy action do not step, the decision
 // step's transition is completed in the replay ring, finished episodes restart in-kernel and new decision events are
 // detected after every step.  Lanes of one env always take the same branches, so the pair exchanges use a two-lane mask.
-template <typename R, bool SAME, bool ROLL>
+template <typename R, bool SAME, bool ROLL, bool PARTS = false>
 __global__ void __launch_bounds__(128, sizeof(R) == 4 ? SIT_ENV_MINB_F32 : 2)
 env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, const EnvPtrs<R> ge, const int K,
                 const EnvIO<R> io, const RollArgs ro) {
@@ -370,7 +370,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
 
         // ---- per-ship reward terms and terminal checks (sequential stop_flag gating) -------------------
         int st = 0; bool dn_ = false; R part;
-        const bool stop_in = stop;               // the obstacle ship's non-terminal terms see the flag from before this step
+        const bool stop_in = PARTS && stop;      // the obstacle ship's non-terminal terms see the flag from before this step
         if (!is_obs) {
             // test_ship_non_terminal_state_reward :628-664
             const R ntt = abs_(ect) * EP.inv_e_tol + ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
@@ -429,7 +429,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
                     ob[6 * B] = pn; ob[7 * B] = pe; ob[8 * B] = s.psi; ob[9 * B] = ect;
                 }
             }
-            if (io.rew_parts) {   // reward_results increments, recomputed here so the default path carries nothing for them
+            if (PARTS && io.rew_parts) {   // reward_results increments: compiled into the PARTS instantiation only
                 R* rp = io.rew_parts + rec * SIT_N_REWARD_PARTS * B + env;
                 const R r_ect = abs_(ect) * EP.inv_e_tol, r_col = ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
                 if (!is_obs) {
@@ -1645,7 +1645,10 @@ static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaS
     const int block = 128, grid = grid_for(h->n_ships, block);
     RollArgs ra;
     std::memset(&ra, 0, sizeof(ra));
-    if (h->same_params) env_step_kernel<R, true, false><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
+    if (k.rew_parts) {
+        if (h->same_params) env_step_kernel<R, true, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
+        else env_step_kernel<R, false, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
+    } else if (h->same_params) env_step_kernel<R, true, false><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     else env_step_kernel<R, false, false><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
