@@ -34,17 +34,30 @@ def _worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
-def test_gather_replay_and_reduce_stats_world2():
-    world, port = 2, _free_port()
+def _run_world(world):
+    port = _free_port()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda x: x[0])
-    for p in procs:
-        p.join(timeout=60)
-        assert p.exitcode == 0
+    try:
+        res = sorted([q.get(timeout=300) for _ in range(world)], key=lambda x: x[0])
+        for p in procs:
+            p.join(timeout=120)
+        return res if all(p.exitcode == 0 for p in procs) else None
+    except Exception:
+        return None
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.terminate()
+
+
+def test_gather_replay_and_reduce_stats_world2():
+    world = 2
+    res = _run_world(world) or _run_world(world)     # one retry on a fresh port: the probe-then-bind of the port can race
+    assert res is not None, "gloo world-size-2 run failed twice"
     n_rows = [r[4] for r in res]
     for rank, allrows, tot, n_empty, _ in res:
         assert allrows.shape == (sum(n_rows), 24)
