@@ -193,3 +193,48 @@ def test_env_group_pipelining_does_not_change_any_env(monkeypatch):
         assert sorted(wa) == sorted(wb)
         for gid in wa:
             assert np.array_equal(wa[gid].view(np.int32), wb[gid].view(np.int32)), gid
+
+
+def test_full_size_rollout_properties_and_shard_invariance():
+    """BASELINE config 4 size (65 536 envs, fp32, Gaussian policy on the tensor cores): size-independent properties --
+    counters agree with the ring, every row is complete and finite, and the two half shards (env_id_offset 0 / 32 768)
+    reproduce the whole batch's transitions bit for bit, env by env."""
+    from sac_maritime_ast_b200 import rollout as ro
+    B, iters, K = 65536, 6, 32
+    pol = ro.GaussianPolicy(hidden_size=256, device="cuda:0", seed=11, tensor_cores=True)
+    pol.w0.mul_(1e-4)
+
+    def run(n, offset):
+        import gpu_helpers as G
+        env = G.make_env(sc.ENV_SCENARIOS["default"], n_envs=n, precision="fp32")
+        gen = torch.Generator(device="cuda").manual_seed(5)
+        usp = 9.5 + 2.5 * torch.rand(B, generator=gen, device="cuda")           # per GLOBAL env, so shards see the same values
+        env.ship[1].u_sp.copy_(usp[offset:offset + n])
+        env.capture_init()
+        s = ro.IntermediateWaypointSampler(env, pol, capacity=4 * n, seed=25450, env_id_offset=offset, num_steps_episode=150,
+                                           auto_reset="hard")
+        s.begin(); s.collect(iters, K)
+        torch.cuda.synchronize()
+        return s
+    whole = run(B, 0)
+    c = whole.counters.cpu().numpy()
+    n = whole.n_transitions()
+    assert B < n <= whole.capacity and c[0] == c[1] == n, "every decision opened exactly one replay row"
+    rows = whole.transitions()
+    assert torch.isfinite(rows[:, :23]).all() and (rows[:, 10].abs() <= 1).all()
+    ids = rows[:, 23].contiguous().view(torch.int32)
+    assert int(ids.min()) == 0 and int(ids.max()) == B - 1
+    assert torch.bincount(ids, minlength=B).min() >= 1, "every env took its first decision"
+    assert 0 < int(whole.env.stats[13].item()) <= B * K * iters
+    assert set(torch.unique(rows[:, 22]).tolist()) <= {0.0, 1.0}
+    # shard invariance at full size: sort rows by (env id, slot order) and compare bitwise
+    def keyed(s, lo, hi):
+        r = s.transitions()
+        i = r[:, 23].contiguous().view(torch.int32).to(torch.int64)
+        order = torch.argsort(i * (1 << 22) + torch.arange(r.shape[0], device=r.device), stable=True)
+        r, i = r[order], i[order]
+        m = (i >= lo) & (i < hi)
+        return r[m].view(torch.int32)
+    for lo in (0, B // 2):
+        part = run(B // 2, lo)
+        assert torch.equal(keyed(part, lo, lo + B // 2), keyed(whole, lo, lo + B // 2)), f"shard at {lo} differs from the whole batch"
