@@ -39,9 +39,14 @@ struct Gemm {
     int epi;
 };
 
+// The products are latency-bound (M = batch = 64, K <= 257, 16-32 CTAs): the k loop is a chain of dependent
+// global-load -> barrier -> FMA rounds, so the tile is 128 deep -- 32 independent loads per thread in flight per round, three
+// rounds for K = 257 instead of nine -- which took an H x H layer from ~20 us to a few us.  The k order of the sums is
+// unchanged (ascending), so results are bit-identical to the 32-deep version.
+constexpr int GEMM_BK = 128;
 template <bool AK, bool BN>
 __global__ void __launch_bounds__(256) gemm_kernel(const Gemm g) {
-    __shared__ float As[32][33], Bs[32][33];   // [k][m], [k][n]
+    __shared__ float As[GEMM_BK][33], Bs[GEMM_BK][33];   // [k][m], [k][n]
     const int t = threadIdx.x, z = blockIdx.z;
     const float* A = g.A + (long long)z * g.a_zs;
     const float* B = g.B + (long long)z * g.b_zs;
@@ -49,21 +54,46 @@ __global__ void __launch_bounds__(256) gemm_kernel(const Gemm g) {
     const int ty = t >> 4, tx = t & 15;
     float c00 = 0.f, c01 = 0.f, c10 = 0.f, c11 = 0.f;
     const int lo = t & 31, hi = t >> 5;        // hi: 0..7
-    for (int k0 = 0; k0 < g.K; k0 += 32) {
+    for (int k0 = 0; k0 < g.K; k0 += GEMM_BK) {
+        const int kt = min(GEMM_BK, g.K - k0);          // valid depth of this tile
+        if (AK) {      // A contiguous along k: lanes run along k, 4 k-columns x 4 m-rows per thread
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int ka = AK ? lo : hi + 8 * i, ma = AK ? hi + 8 * i : lo;
-            const int gm = m0 + ma, gk = k0 + ka;
-            As[ka][ma] = (gm < g.M && gk < g.K) ? A[(long long)gm * g.a_rs + (long long)gk * g.a_cs] : 0.f;
-            const int kb = BN ? hi + 8 * i : lo, nb = BN ? lo : hi + 8 * i;
-            const int gn = n0 + nb, gk2 = k0 + kb;
-            Bs[kb][nb] = (gn < g.N && gk2 < g.K) ? B[(long long)gk2 * g.b_rs + (long long)gn * g.b_cs] : 0.f;
+            for (int kc = 0; kc < GEMM_BK; kc += 32)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int ka = kc + lo, ma = hi + 8 * i, gm = m0 + ma;
+                    As[ka][ma] = (gm < g.M && ka < kt) ? A[(long long)gm * g.a_rs + (long long)(k0 + ka) * g.a_cs] : 0.f;
+                }
+        } else {       // A contiguous along m: lanes run along m
+#pragma unroll
+            for (int i = 0; i < GEMM_BK / 8; ++i) {
+                const int ka = hi + 8 * i, ma = lo, gm = m0 + ma;
+                As[ka][ma] = (gm < g.M && ka < kt) ? A[(long long)gm * g.a_rs + (long long)(k0 + ka) * g.a_cs] : 0.f;
+            }
+        }
+        if (BN) {      // B contiguous along n: lanes run along n
+#pragma unroll
+            for (int i = 0; i < GEMM_BK / 8; ++i) {
+                const int kb = hi + 8 * i, nb = lo, gn = n0 + nb;
+                Bs[kb][nb] = (gn < g.N && kb < kt) ? B[(long long)(k0 + kb) * g.b_rs + (long long)gn * g.b_cs] : 0.f;
+            }
+        } else {       // B contiguous along k
+#pragma unroll
+            for (int kc = 0; kc < GEMM_BK; kc += 32)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int kb = kc + lo, nb = hi + 8 * i, gn = n0 + nb;
+                    Bs[kb][nb] = (gn < g.N && kb < kt) ? B[(long long)(k0 + kb) * g.b_rs + (long long)gn * g.b_cs] : 0.f;
+                }
         }
         __syncthreads();
+        const int kend = (kt + 31) & ~31;               // rows past kt are zero-filled above
+        for (int kk0 = 0; kk0 < kend; kk0 += 32) {
 #pragma unroll
-        for (int kk = 0; kk < 32; ++kk) {
-            const float a0 = As[kk][2 * ty], a1 = As[kk][2 * ty + 1], b0 = Bs[kk][2 * tx], b1 = Bs[kk][2 * tx + 1];
-            c00 = fmaf(a0, b0, c00); c01 = fmaf(a0, b1, c01); c10 = fmaf(a1, b0, c10); c11 = fmaf(a1, b1, c11);
+            for (int kk = kk0; kk < kk0 + 32; ++kk) {
+                const float a0 = As[kk][2 * ty], a1 = As[kk][2 * ty + 1], b0 = Bs[kk][2 * tx], b1 = Bs[kk][2 * tx + 1];
+                c00 = fmaf(a0, b0, c00); c01 = fmaf(a0, b1, c01); c10 = fmaf(a1, b0, c10); c11 = fmaf(a1, b1, c11);
+            }
         }
         __syncthreads();
     }
