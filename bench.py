@@ -323,6 +323,7 @@ def run_b200(args, rank, world, local_rank):
         line["ast_env"] = ast
         ast_rec = env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", record_all=True)
         line["ast_env_recorded"] = {k: ast_rec[k] for k in ("value", "unit", "ms_per_launch", "write_gbs")}
+        line["ast_env_e2e"] = env_e2e_leg(sit, dev)
     if not args.no_extras:
         # ---- SAC-AST rollout (BASELINE config 4): policy fused into the device loop, samples/s.  Every rank rolls out its
         # own shard of envs (global env ids rank*B ..), then the replay rows of the timed segment are all-gathered and the
@@ -522,6 +523,31 @@ def env_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3, precision="fp32", rec
             "auto_reset": "hard (fresh construction; the reference's reset keeps integrators, quirk Q3)",
             "episodes_done": int(st[12]), "env_steps_counted": int(st[13]),
             "status_counts": {i: int(st[i]) for i in range(12)}}
+
+
+def env_e2e_leg(sit, dev, B=1 << 18, K=64, steps=10, warmup=3):
+    """The env-step leg through the host-buffer entry point of the drop-in (MultiShipRLEnv.step_host -> sit_env_step_host):
+    pinned host action / SAC_update in, host obs / reward / done / status of the last step out, copies inside the timed
+    region.  No auto-reset on this entry point (the reference's caller resets), so episodes run into their terminal states."""
+    import torch
+    env, g = make_bench_env(sit, dev, B, "fp32", SEED)
+    acts = [draw_waypoints(env, g, dev).t().contiguous().cpu().pin_memory() for _ in range(4)]
+    sac = torch.ones(B, dtype=torch.uint8).pin_memory()
+    out_h = dict(obs=torch.empty((10, B), dtype=torch.float32).pin_memory(), reward=torch.empty(B, dtype=torch.float32).pin_memory(),
+                 done=torch.empty(B, dtype=torch.uint8).pin_memory(), status=torch.empty(B, dtype=torch.int32).pin_memory())
+    for w in range(warmup):
+        env.step_host(K, acts[w % 4], sac, w == 0, out_h)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(steps):
+        env.step_host(K, acts[(warmup + k) % 4], sac, False, out_h)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"value": B * K / (ms * 1e-3), "unit": "env-steps/s", "envs": B, "k_per_call": K, "ms_per_call": ms,
+            "h2d_bytes_per_call": int(acts[0].numel() * 4 + B), "d2h_bytes_per_call": int(B * (10 * 4 + 4 + 1 + 4)),
+            "api": "MultiShipRLEnv.step_host -> sit_env_step_host (pinned host buffers, chunk pipeline)",
+            "obs_finite": bool(torch.isfinite(out_h["obs"]).all())}
 
 
 def long_horizon_leg(sit, dev, rank, B=65536, K=64, total_steps=10000, mode_every=512, precision="fp32"):

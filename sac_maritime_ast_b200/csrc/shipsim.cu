@@ -226,9 +226,9 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     __shared__ EdgeRec<R> s_edges[SIT_MAX_EDGES];
     stage_edges(A.M, s_edges);
     const int n_edges = A.M.n_edges;
-    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x + (ROLL ? 2 * ro.env_first : 0);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x + 2 * ro.env_first;   // env sub-range of this launch
     const int64_t S = g.n_ships, B = ge.n_envs;
-    const bool active = tid < (ROLL ? 2 * (ro.env_first + ro.env_count) : S);
+    const bool active = tid < 2 * (ro.env_first + ro.env_count);
     const int64_t i = active ? tid : (tid & 1);   // idle lanes of the last warp shadow env 0 and never store
     const int role = (int)(i & 1);
     const int64_t env = i >> 1;
@@ -1627,7 +1627,8 @@ int sit_env_init_step(SitHandle h, void* state, const uint8_t* mask, void* strea
 
 }  // extern "C"
 template <typename R>
-static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaStream_t st) {
+static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaStream_t st, int64_t env_first = 0,
+                      int64_t env_count = -1) {
     EnvIO<R> k;
     std::memset(&k, 0, sizeof(k));
     k.init = -1; k.rec_steps = 1; k.act_steps = 1;
@@ -1643,9 +1644,10 @@ static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaS
     const ShipPtrs<R> g = ship_ptrs<R>(h, state);
     const EnvPtrs<R> ge = env_ptrs<R>(h, state);
     const EnvKArgs<R>& A = HostSel<R>::env(h);
-    const int block = 128, grid = grid_for(h->n_ships, block);
     RollArgs ra;
     std::memset(&ra, 0, sizeof(ra));
+    ra.env_first = env_first; ra.env_count = env_count < 0 ? h->n_envs : env_count;
+    const int block = 128, grid = grid_for(2 * ra.env_count, block);
     if (k.rew_parts) {
         if (h->same_params) env_step_kernel<R, true, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
         else env_step_kernel<R, false, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
@@ -1978,20 +1980,55 @@ int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h,
         if (rc0) return rc0;
     }
     char* d = static_cast<char*>(h->d_scratch);
-    CUDA_TRY(cudaMemcpyAsync(d + o_act, action_h, 2 * B * rs, cudaMemcpyHostToDevice, st));
-    if (sac_update_h) CUDA_TRY(cudaMemcpyAsync(d + o_sac, sac_update_h, B, cudaMemcpyHostToDevice, st));
+    if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
     SitEnvIO io;
     std::memset(&io, 0, sizeof(io));
     io.action = d + o_act; io.sac_update = sac_update_h ? reinterpret_cast<uint8_t*>(d + o_sac) : nullptr;
     io.act_steps = 1; io.init = init; io.auto_reset = 0; io.rec_steps = 1;
     io.obs = d + o_obs; io.reward = d + o_rew; io.done = reinterpret_cast<uint8_t*>(d + o_done);
     io.status = reinterpret_cast<int32_t*>(d + o_st);
-    int rc = sit_env_step_k(h, state, K, &io, stream);
+    // envs are independent: large batches travel as chunks through the handle's internal streams, like sit_fleet_step_host
+    const int64_t min_chunk = 32768;
+    const int n_chunks = (int)std::min<int64_t>(8, (int64_t)B / min_chunk);
+    if (n_chunks < 2) {
+        CUDA_TRY(cudaMemcpyAsync(d + o_act, action_h, 2 * B * rs, cudaMemcpyHostToDevice, st));
+        if (sac_update_h) CUDA_TRY(cudaMemcpyAsync(d + o_sac, sac_update_h, B, cudaMemcpyHostToDevice, st));
+        int rc = sit_env_step_k(h, state, K, &io, stream);
+        if (rc) return rc;
+        if (obs_h) CUDA_TRY(cudaMemcpyAsync(obs_h, d + o_obs, SIT_N_OBS * B * rs, cudaMemcpyDeviceToHost, st));
+        if (reward_h) CUDA_TRY(cudaMemcpyAsync(reward_h, d + o_rew, B * rs, cudaMemcpyDeviceToHost, st));
+        if (done_h) CUDA_TRY(cudaMemcpyAsync(done_h, d + o_done, B, cudaMemcpyDeviceToHost, st));
+        if (status_h) CUDA_TRY(cudaMemcpyAsync(status_h, d + o_st, B * 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        return SIT_OK;
+    }
+    int rc = ensure_pipe(h);
     if (rc) return rc;
-    if (obs_h) CUDA_TRY(cudaMemcpyAsync(obs_h, d + o_obs, SIT_N_OBS * B * rs, cudaMemcpyDeviceToHost, st));
-    if (reward_h) CUDA_TRY(cudaMemcpyAsync(reward_h, d + o_rew, B * rs, cudaMemcpyDeviceToHost, st));
-    if (done_h) CUDA_TRY(cudaMemcpyAsync(done_h, d + o_done, B, cudaMemcpyDeviceToHost, st));
-    if (status_h) CUDA_TRY(cudaMemcpyAsync(status_h, d + o_st, B * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(h->pipe_in, st));
+    for (int j = 0; j < SIT_PIPE; ++j) CUDA_TRY(cudaStreamWaitEvent(h->pipe[j], h->pipe_in, 0));
+    const int64_t chunk = ((int64_t)B / n_chunks + 255) / 256 * 256;
+    int c = 0;
+    for (int64_t first = 0; first < (int64_t)B; first += chunk, ++c) {
+        const int64_t cnt = std::min<int64_t>(chunk, (int64_t)B - first);
+        cudaStream_t ps = h->pipe[c % SIT_PIPE];
+        CUDA_TRY(cudaMemcpy2DAsync(d + o_act + first * rs, B * rs, static_cast<const char*>(action_h) + first * rs, B * rs,
+                                   cnt * rs, 2, cudaMemcpyHostToDevice, ps));
+        if (sac_update_h) CUDA_TRY(cudaMemcpyAsync(d + o_sac + first, sac_update_h + first, cnt, cudaMemcpyHostToDevice, ps));
+        rc = h->cfg.precision == SIT_F64 ? env_step_t<double>(h, state, K, &io, ps, first, cnt)
+                                         : env_step_t<float>(h, state, K, &io, ps, first, cnt);
+        if (rc) return rc;
+        if (obs_h)
+            CUDA_TRY(cudaMemcpy2DAsync(static_cast<char*>(obs_h) + first * rs, B * rs, d + o_obs + first * rs, B * rs, cnt * rs,
+                                       SIT_N_OBS, cudaMemcpyDeviceToHost, ps));
+        if (reward_h)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(reward_h) + first * rs, d + o_rew + first * rs, cnt * rs, cudaMemcpyDeviceToHost, ps));
+        if (done_h) CUDA_TRY(cudaMemcpyAsync(done_h + first, d + o_done + first, cnt, cudaMemcpyDeviceToHost, ps));
+        if (status_h) CUDA_TRY(cudaMemcpyAsync(status_h + first, d + o_st + first * 4, cnt * 4, cudaMemcpyDeviceToHost, ps));
+    }
+    for (int j = 0; j < SIT_PIPE; ++j) {
+        CUDA_TRY(cudaEventRecord(h->pipe_done[j], h->pipe[j]));
+        CUDA_TRY(cudaStreamWaitEvent(st, h->pipe_done[j], 0));
+    }
     CUDA_TRY(cudaStreamSynchronize(st));
     return SIT_OK;
 }

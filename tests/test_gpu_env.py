@@ -163,6 +163,36 @@ def test_status_strings_and_host_step():
         env.step(None, True, True)
 
 
+@pytest.mark.parametrize("B", [70_003, 1 << 18])
+def test_host_buffer_env_step_equals_device_path(B):
+    """sit_env_step_host on a large batch (cut into chunks pipelined over internal streams, ragged tail) == sit_env_step_k on
+    device tensors: outputs and state bit-identical."""
+    import gpu_helpers as G
+    s = sc.ENV_SCENARIOS["default"]
+    env = G.make_env(s, n_envs=B, precision="fp32")
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    env.ship[1].u_sp.copy_(9.5 + 2.5 * torch.rand(B, generator=gen, device="cuda"))
+    env.capture_init(); env.reset(); env.init_step()
+    snap = env.state_dict()
+    act = torch.empty((2, B), dtype=torch.float32)
+    act[0] = 8300.0 + 50.0 * torch.rand(B, generator=torch.Generator().manual_seed(3)); act[1] = 8600.0
+    sac = (torch.arange(B) % 3 != 0).to(torch.uint8)
+    want = env.step_k(40, act.t().contiguous().cuda(), sac.cuda(), init=True, record_all=False)
+    want = {k: v.clone() for k, v in want.items()}
+    st_want = {k: env.f[k].clone() for k in ("north", "east", "psi", "flags", "eps_dist")}
+    env.load_state_dict(snap)
+    act_h, sac_h = act.pin_memory(), sac.pin_memory()
+    out_h = dict(obs=torch.empty((10, B), dtype=torch.float32).pin_memory(), reward=torch.empty(B, dtype=torch.float32).pin_memory(),
+                 done=torch.empty(B, dtype=torch.uint8).pin_memory(), status=torch.empty(B, dtype=torch.int32).pin_memory())
+    for t in out_h.values():
+        t.fill_(77)
+    env.step_host(40, act_h, sac_h, True, out_h)
+    assert torch.equal(out_h["obs"], want["obs"][0].cpu()) and torch.equal(out_h["reward"], want["reward"][0].cpu())
+    assert torch.equal(out_h["done"], want["done"][0].cpu()) and torch.equal(out_h["status"], want["status"][0].cpu())
+    for k, v in st_want.items():
+        assert torch.equal(env.f[k], v), k
+
+
 def test_map_query_matches_geometry_oracle():
     """sit_map_query (waypoint validity: obstacle.py:126-141, MSRL_env_ex.py:517-552) against the CPU restatement of
     the shapely calls, on random points plus vertices / edge points (boundary is NOT contained)."""
