@@ -332,6 +332,10 @@ def run_b200(args, rank, world, local_rank):
         rl = rollout_leg(sit, dev, B=B_roll, env_id_offset=rank * B_roll)
         smp_keep = rl.pop("sampler")
         rows = smp_keep.transitions()[:min(rl["samples"], smp_keep.capacity)]
+        if world > 1:
+            # untimed first gather of the same size: NCCL sets up its channels / protocol buffers for this message size and
+            # the caching allocator gets its blocks on the first call (in a training loop the gather recurs every segment)
+            del_me = ro_mod.gather_replay(rows); del del_me
         barrier()
         ev0.record()
         allrows = ro_mod.gather_replay(rows)
