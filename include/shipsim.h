@@ -322,7 +322,9 @@ const char* sit_last_error(void);
 const char* sit_status_string(int32_t bit_index);  /* exact reference strings, MSRL_env_ex.py:760-899 */
 int sit_abi_version(void);
 /* CUDA-core FMA peak of this device measured with a register-resident FMA chain (roofline
- * denominator for the compute-bound step kernels).  precision SIT_F32 / SIT_F64; returns TFLOP/s. */
+ * denominator for the compute-bound step kernels).  precision SIT_F32 / SIT_F64, or SIT_PEAK_F32X2 for the same
+ * chain issued as packed f32x2 FMAs (SASS FFMA2, the instruction the fp32 fleet kernel uses); returns TFLOP/s. */
+enum { SIT_PEAK_F32X2 = 2 };
 int sit_measure_fma_peak(int device, int32_t precision, double* tflops, double* ms);
 
 #ifdef __cplusplus

@@ -26,7 +26,7 @@ struct EnvP {
     R lo_n[2], hi_n[2], lo_e[2], hi_e[2];         // is_pos_outside_horizon :460-488, per role (L/2 margin)
     R inv_max_north;                              // reward normalisation :650,697,725
     R inv_e_tol, e_tol;                           // e_tolerance = 1000 :119
-    R arrive2[2];                                 // largest x with sqrt(x) <= 200 (:754,829), per precision
+    double arrive2;                               // largest double x with sqrt(x) <= 200 (:754,829): the squared distance is compared in double
     R rpm_max;                                    // 2000 :557
     double collide2;                              // 50^2 :592
     R near2;                                      // (L/2 * sqrt2 + slack)^2: beyond it all hull corners share the centre's side

@@ -1,0 +1,267 @@
+// Packed-FP32 form of the ship step: ONE THREAD OWNS TWO SHIPS and every FP32 operation of the step is issued once for
+// both as a Blackwell f32x2 instruction (SASS FFMA2 / FMUL2 / FADD2, one issue slot for two ships).  The fp32 K1 kernel
+// was bound by instruction issue (200 warp instructions per ship-step, issue slots 90 % busy, FMA pipe 60 %); packing
+// halves the FP32 instruction count per ship, uniform parameters ride as uniform-register / immediate broadcast operands
+// of the packed instructions, and the transcendental pieces are written so that their polynomials pack too:
+//   * sin / cos of the heading: Cody-Waite reduction by pi (not pi/2: no quadrant swap), sign applied by one XOR per ship,
+//     degree-9 / degree-10 minimax polynomials on [-pi/2, pi/2] (|error| < 1.3e-7 evaluated in float);
+//   * atan of the LOS term: one MUFU.RCP per ship for |x| > 1, odd degree-15 minimax polynomial on [-1, 1] (< 1.1e-7);
+//   * the machinery-mode formulas of ship_engine.py:32-76 are folded into one branch-free form (ModeX) so that ships in
+//     different modes share the packed instructions.
+// Positions stay in double per ship (waypoint switching is decided on the numbers the float64 reference sees), exactly
+// as in ship_core.cuh.  Same physics, same reference citations as ship_core.cuh::ship_step; the arithmetic differs from
+// the scalar float step only in rounding (different but equivalent operation order).
+//
+// Reference citations are relative to /root/reference/.
+#pragma once
+#include "ship_core.cuh"
+
+namespace sit {
+namespace x2 {
+
+typedef float2 V;
+
+__device__ __forceinline__ V bc(float a) { return make_float2(a, a); }
+__device__ __forceinline__ V neg(V a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ V vabs(V a) { return make_float2(fabsf(a.x), fabsf(a.y)); }
+__device__ __forceinline__ V fma(V a, V b, V c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ V fma(V a, float b, V c) { return __ffma2_rn(a, bc(b), c); }
+__device__ __forceinline__ V fma(V a, float b, float c) { return __ffma2_rn(a, bc(b), bc(c)); }
+__device__ __forceinline__ V fma(V a, V b, float c) { return __ffma2_rn(a, b, bc(c)); }
+__device__ __forceinline__ V mul(V a, V b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ V mul(V a, float b) { return __fmul2_rn(a, bc(b)); }
+__device__ __forceinline__ V add(V a, V b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ V add(V a, float b) { return __fadd2_rn(a, bc(b)); }
+__device__ __forceinline__ V sub(V a, V b) { return __fadd2_rn(a, neg(b)); }
+
+// ---- uniform parameters of the packed step (floats; ptxas keeps them as uniform-register operands) ----------------
+// One machinery mode in branch-free form.  ship_engine.py:46-76 distribute_load:
+//   MOTOR:  load_me = min(total, me_cap);            load_el = (total + hotel) - load_me
+//   other:  load_me = total + load_me_add;           load_el = load_el_const
+// both are  load_me = min(total + add, cap),  load_el = a_el * ((total + hotel) - load_me) + c_el.
+struct ModeX {
+    float avail_total, avail_me, avail_el;   // update_available_propulsion_power :32-44
+    float cap_tq_me, cap_tq_el;              // torque caps :374-375,383-384
+    float add_me, cap_me;                    // load_me = min(total + add_me, cap_me)
+    float a_el, c_el;                        // load_el = a_el * ((total + hotel) - load_me) + c_el
+    float inv_me_cap, inv_el_cap;            // 0 where the reference guards a zero capacity
+};
+
+struct ShipPX {
+    double ra2;                                            // radius_of_acceptance^2, decided in double
+    float dt, look2, sat_e, neg_ki_los, windup;            // LOS_guidance.py:105-121
+    float kp_h, kd_idt, ki_h, rud_max, rud_bias;           // controllers.py:72-100 (kd / dt folded)
+    float kp_s, ki_s, kp_w, ki_w;                          // controllers.py:138-143
+    float hotel, sfc_me[3], sfc_dg[3];                     // ship_engine.py:256-292 (/ 3.6e9 folded)
+    float sh_me, sh_hsg, sh_lin, sh_quad;                  // shaft_eq :355-361
+    float au_vr, au_vrr, au_lin, au_nl, au_wind, au_thr;   // ship_model.py:576-606, accelerations
+    float av_ur, av_urr, av_lin, av_nl, av_wind, av_rud;
+    float ar_ca, ar_lin, ar_nl, ar_wind, ar_rud;
+    ModeX mode[SIT_MAX_MODES];
+    int32_t n_modes, _pad;
+};
+
+// ---- per-thread register state: two ships --------------------------------------------------------------------------
+struct Ship2 {
+    double N[2], E[2];                      // ship_model.py:159-160
+    double pN[2], pE[2], cN[2], cE[2];      // cached route segment k-1 -> k
+    V psi, u, v, r, om;                     // :161-164, ship_engine.py:327
+    V ei_s, ei_w, ei_h, e_prev, e_ct, e_int;
+    V f_me, f_el, f_tot;
+    V u_sp, vcn, vce, wcb, wsb;
+    V alpha, sa, ca;
+    int32_t k[2], n_wp[2];
+};
+
+// per-ship mode constants as lanes of packed registers (several modes in one fleet) or as uniform scalars (one mode)
+struct ModeV { V avail_total, avail_me, avail_el, cap_tq_me, cap_tq_el, add_me, cap_me, a_el, c_el, inv_me_cap, inv_el_cap; };
+
+__device__ __forceinline__ float& lane(V& a, int l) { return l == 0 ? a.x : a.y; }
+__device__ __forceinline__ float lane(const V& a, int l) { return l == 0 ? a.x : a.y; }
+__device__ __forceinline__ float lane(const float& a, int) { return a; }
+
+__device__ __forceinline__ void load_segment2(Ship2& s, const ShipPtrs<float>& g, const int64_t i, const int l) {
+    // LOS_guidance.py:110-112: segment k-1 -> k and its angle (atan2(dE, dN))
+    const int64_t S = g.n_ships;
+    s.pN[l] = g.wp_n[(int64_t)(s.k[l] - 1) * S + i];
+    s.pE[l] = g.wp_e[(int64_t)(s.k[l] - 1) * S + i];
+    s.cN[l] = g.wp_n[(int64_t)s.k[l] * S + i];
+    s.cE[l] = g.wp_e[(int64_t)s.k[l] * S + i];
+    const float a = atan2f((float)(s.cE[l] - s.pE[l]), (float)(s.cN[l] - s.pN[l]));
+    float sa, ca;
+    sincos_(a, sa, ca);
+    lane(s.alpha, l) = a; lane(s.sa, l) = sa; lane(s.ca, l) = ca;
+}
+
+// sin and cos of two headings.  t = x / pi + 1.5 * 2^23 holds round(x / pi) in its low mantissa bits; r = x - j pi in two
+// Cody-Waite steps (pi = 3.140625 + 9.67653589793e-4: the product j * 3.140625 is exact for |j| < 2^13, i.e. |x| < 2.5e4 rad);
+// sin x = (-1)^j sin r, cos x = (-1)^j cos r: the parity bit of j moves to the sign position and is XOR-ed in.
+__device__ __forceinline__ void sincos2(const V x, V& sn, V& cs) {
+    const V t = fma(x, 0.318309886183790672f, 12582912.0f);
+    const V j = add(t, -12582912.0f);
+    V r = fma(j, -3.140625f, x);
+    r = fma(j, -9.67653589793e-4f, r);
+    const V r2 = mul(r, r);
+    V ps = fma(r2, 2.600024345156271e-06f, -0.00019806601630989462f);
+    ps = fma(ps, r2, 0.008333017118275166f);
+    ps = fma(ps, r2, -0.16666656732559204f);
+    ps = mul(ps, r2);
+    ps = fma(ps, r, r);
+    V pc = fma(r2, -2.607681608424173e-07f, 2.476187000866048e-05f);
+    pc = fma(pc, r2, -0.00138884037733078f);
+    pc = fma(pc, r2, 0.04166664183139801f);
+    pc = fma(pc, r2, -0.5f);
+    pc = fma(pc, r2, 1.0f);
+    const uint32_t fx = (uint32_t)__float_as_int(t.x) << 31, fy = (uint32_t)__float_as_int(t.y) << 31;
+    sn.x = __int_as_float(__float_as_int(ps.x) ^ fx); sn.y = __int_as_float(__float_as_int(ps.y) ^ fy);
+    cs.x = __int_as_float(__float_as_int(pc.x) ^ fx); cs.y = __int_as_float(__float_as_int(pc.y) ^ fy);
+}
+
+// atan of two arguments: z = x for |x| <= 1, 1 / x beyond (atan x = sign(x) pi/2 - atan(1 / x)); atan z = z + z^3 P(z^2)
+__device__ __forceinline__ V atan2v(const V x) {
+    const bool ix = fabsf(x.x) > 1.0f, iy = fabsf(x.y) > 1.0f;
+    V z;
+    z.x = ix ? rcp_approx(x.x) : x.x;
+    z.y = iy ? rcp_approx(x.y) : x.y;
+    const V z2 = mul(z, z);
+    V p = fma(z2, -0.004355357028543949f, 0.023039964959025383f);
+    p = fma(p, z2, -0.05777335166931152f);
+    p = fma(p, z2, 0.09794218093156815f);
+    p = fma(p, z2, -0.13976575434207916f);
+    p = fma(p, z2, 0.19962702691555023f);
+    p = fma(p, z2, -0.3333165943622589f);
+    p = mul(p, z2);
+    p = fma(p, z, z);
+    V h;   // copysign(pi / 2, x)
+    h.x = __int_as_float((__float_as_int(x.x) & 0x80000000) | 0x3fc90fdb);
+    h.y = __int_as_float((__float_as_int(x.y) & 0x80000000) | 0x3fc90fdb);
+    const V alt = sub(h, p);
+    V res;
+    res.x = ix ? alt.x : p.x;
+    res.y = iy ? alt.y : p.y;
+    return res;
+}
+
+// One step of two ships.  MP = ModeX: one machinery mode for the whole fleet (uniform operands); MP = ModeV: per-ship modes.
+template <bool AVOID, typename MP>
+__device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& s, const ShipPtrs<float>& g, const int64_t i0,
+                                           const int64_t i1) {
+    // ---- LOS_guidance.py:88-103 next_wpt: squared distance, <=, end-of-route hold (double, per ship) ----------------
+#pragma unroll
+    for (int l = 0; l < 2; ++l) {
+        const double dn = s.cN[l] - s.N[l], de = s.cE[l] - s.E[l];
+        const double d2 = __dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de));
+        if (d2 <= P.ra2 && s.n_wp[l] > s.k[l] + 1) {
+            s.k[l] += 1;
+            load_segment2(s, g, l == 0 ? i0 : i1, l);
+        }
+    }
+    // ---- LOS_guidance.py:105-121 los_guidance ---------------------------------------------------------------------
+    const V en = make_float2((float)(s.N[0] - s.pN[0]), (float)(s.N[1] - s.pN[1]));
+    const V ee = make_float2((float)(s.E[0] - s.pE[0]), (float)(s.E[1] - s.pE[1]));
+    V e = fma(ee, s.ca, neg(mul(en, s.sa)));
+    s.e_ct = e;                                             // |e| is taken where it is stored
+    const V e2 = mul(e, e);
+    if (e2.x >= P.look2) e.x = P.sat_e;                      // sign lost on purpose (0.99 * lookahead)
+    if (e2.y >= P.look2) e.y = P.sat_e;
+    const V w = fma(neg(e), e, P.look2);
+    const V q = mul(e, make_float2(rsqrt_approx(w.x), rsqrt_approx(w.y)));
+    const V ti = add(s.e_int, q);
+    if (fabsf(ti.x) <= P.windup) s.e_int.x = ti.x;
+    if (fabsf(ti.y) <= P.windup) s.e_int.y = ti.y;
+    const V href = add(s.alpha, atan2v(fma(s.e_int, P.neg_ki_los, neg(q))));
+
+    // ---- controllers.py:81-93,188-189 heading PID: no wrap, no anti-windup -------------------------------------------
+    const V err = sub(href, s.psi);
+    const V derr = sub(err, s.e_prev);
+    s.ei_h = fma(err, P.dt, s.ei_h);
+    s.e_prev = err;
+    V rud = mul(err, P.kp_h);
+    rud = fma(derr, P.kd_idt, rud);
+    rud = fma(s.ei_h, P.ki_h, rud);                          // negated in the clamp below
+    rud.x = fmaxf(-P.rud_max, fminf(-rud.x, P.rud_max));
+    rud.y = fmaxf(-P.rud_max, fminf(-rud.y, P.rud_max));
+
+    // ---- controllers.py:138-143 throttle cascade; the shaft PI is fed u (MSRL_env_ex.py:233-237) ----------------------
+    const V e1 = sub(s.u_sp, s.u);
+    s.ei_s = fma(e1, P.dt, s.ei_s);
+    const V e2s = fma(e1, P.kp_s, fma(s.ei_s, P.ki_s, neg(s.u)));
+    s.ei_w = fma(e2s, P.dt, s.ei_w);
+    V thr = fma(e2s, P.kp_w, mul(s.ei_w, P.ki_w));
+
+    // ---- MSRL_env_ex.py:240-249 collision-avoidance branch (test ship: always) ---------------------------------------
+    if (AVOID) {
+        thr.x = fminf(fmaxf(thr.x * 0.5f, 0.0f), 1.1f); thr.y = fminf(fmaxf(thr.y * 0.5f, 0.0f), 1.1f);
+        rud.x = fminf(fmaxf(rud.x + P.rud_bias, -P.rud_max), P.rud_max);
+        rud.y = fminf(fmaxf(rud.y + P.rud_bias, -P.rud_max), P.rud_max);
+    }
+
+    // ---- ship_engine.py:363-384 torques (capped), thrust from the pre-update omega ------------------------------------
+    const V om = s.om;
+    const V omp = add(om, 0.1f);
+    const V tio = mul(thr, make_float2(rcp_approx(omp.x), rcp_approx(omp.y)));
+    V tq_me = mul(tio, M.avail_me), tq_hsg = mul(tio, M.avail_el);
+    tq_me.x = fminf(tq_me.x, lane(M.cap_tq_me, 0)); tq_me.y = fminf(tq_me.y, lane(M.cap_tq_me, 1));
+    tq_hsg.x = fminf(tq_hsg.x, lane(M.cap_tq_el, 0)); tq_hsg.y = fminf(tq_hsg.y, lane(M.cap_tq_el, 1));
+    const V thrust_w = mul(om, vabs(om));
+
+    // ---- ship_model.py:645-684 store_simulation_data: load split + fuel accumulators (ship_engine.py:239-292) -----------
+    {
+        const V total = mul(thr, M.avail_total);
+        V load_me = add(total, M.add_me);
+        load_me.x = fminf(load_me.x, lane(M.cap_me, 0)); load_me.y = fminf(load_me.y, lane(M.cap_me, 1));
+        const V load_el = fma(sub(add(total, P.hotel), load_me), M.a_el, M.c_el);
+        const V pct_me = mul(load_me, M.inv_me_cap), pct_el = mul(load_el, M.inv_el_cap);
+        // rate = load * (a pct^2 + b pct + c) / 3.6e9; a zero load gives a zero rate without the reference's guards
+        const V rate_me = mul(load_me, fma(fma(pct_me, P.sfc_me[0], P.sfc_me[1]), pct_me, P.sfc_me[2]));
+        const V rate_el = mul(load_el, fma(fma(pct_el, P.sfc_dg[0], P.sfc_dg[1]), pct_el, P.sfc_dg[2]));
+        s.f_me = fma(rate_me, P.dt, s.f_me);
+        s.f_el = fma(rate_el, P.dt, s.f_el);
+        s.f_tot = fma(add(rate_me, rate_el), P.dt, s.f_tot);
+    }
+
+    // ---- ship_model.py:233-250 kinematics ---------------------------------------------------------------------------
+    V sn, c;
+    sincos2(s.psi, sn, c);
+    const V udt = mul(s.u, P.dt), vdt = mul(s.v, P.dt);
+    const V d_north = fma(c, udt, neg(mul(sn, vdt)));
+    const V d_east = fma(sn, udt, mul(c, vdt));
+
+    // ---- ship_engine.py:355-361,391-395 shaft equation ------------------------------------------------------------------
+    V d_om = mul(tq_me, P.sh_me);
+    d_om = fma(tq_hsg, P.sh_hsg, d_om);
+    d_om = fma(neg(fma(om, P.sh_quad, P.sh_lin)), om, d_om);
+
+    // ---- ship_model.py:576-622 kinetics: current in the body frame, wind, rudder -----------------------------------------
+    const V ur = fma(neg(sn), s.vce, fma(neg(c), s.vcn, s.u));      // u - (c vcn + s vce)
+    const V vr = fma(sn, s.vcn, fma(neg(c), s.vce, s.v));           // v - (c vce - s vcn)
+    const V urw = fma(s.wsb, sn, fma(s.wcb, c, neg(s.u)));          // W cos(b - psi) - u
+    const V vrw = fma(neg(s.wcb), sn, fma(s.wsb, c, neg(s.v)));     // W sin(b - psi) - v
+    const V w2 = fma(vrw, vrw, mul(urw, urw));
+    const V Vw = make_float2(sqrt_approx(w2.x), sqrt_approx(w2.y));
+    const V ru = mul(rud, ur);
+    V d_u = mul(fma(vr, -P.au_vrr, mul(s.v, P.au_vr)), s.r);
+    d_u = fma(neg(fma(s.u, P.au_nl, P.au_lin)), ur, d_u);
+    d_u = fma(mul(Vw, urw), -P.au_wind, d_u);
+    d_u = fma(thrust_w, P.au_thr, d_u);
+    V d_v = mul(fma(s.u, -P.av_ur, mul(ur, P.av_urr)), s.r);
+    d_v = fma(neg(fma(s.v, P.av_nl, P.av_lin)), vr, d_v);
+    d_v = fma(mul(Vw, vrw), -P.av_wind, d_v);
+    d_v = fma(ru, -P.av_rud, d_v);
+    V d_r = mul(neg(fma(s.r, P.ar_nl, P.ar_lin)), s.r);
+    d_r = fma(mul(ur, vr), -P.ar_ca, d_r);
+    d_r = fma(mul(urw, vrw), -P.ar_wind, d_r);
+    d_r = fma(ru, -P.ar_rud, d_r);
+
+    // ---- ship_model.py:632-643, utils.py:50-53 explicit Euler, all derivatives from the old state ---------------------------
+    s.N[0] += (double)d_north.x; s.N[1] += (double)d_north.y;
+    s.E[0] += (double)d_east.x; s.E[1] += (double)d_east.y;
+    s.psi = fma(s.r, P.dt, s.psi);
+    s.u = fma(d_u, P.dt, s.u);
+    s.v = fma(d_v, P.dt, s.v);
+    s.r = fma(d_r, P.dt, s.r);
+    s.om = fma(d_om, P.dt, om);
+}
+
+}  // namespace x2
+}  // namespace sit

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "env_core.cuh"
+#include "ship_x2.cuh"
 
 using namespace sit;
 
@@ -135,6 +136,104 @@ __global__ void __launch_bounds__(256) fleet_step_fast_kernel(const __grid_const
         tr[4 * S] = s.v; tr[5 * S] = s.r; tr[6 * S] = s.om; tr[7 * S] = (R)s.k;
     }
     store_ship(s, g, i);
+}
+
+// fp32 fast variant, packed: one thread owns the two ships (i0, i0 + 1) and runs the f32x2 step of ship_x2.cuh (SASS FFMA2 /
+// FMUL2 / FADD2: one issue slot advances both ships).  State rows are read / written as 64-bit (float2 / double2) accesses,
+// so a warp still touches whole 256-byte / 512-byte lines.  An odd tail ship is paired with a copy of itself that is
+// never stored.
+#ifndef SIT_X2_BLOCK
+#define SIT_X2_BLOCK 128
+#endif
+#ifndef SIT_X2_MINB
+#define SIT_X2_MINB 3
+#endif
+template <bool AVOID, bool SINGLE_MODE, bool TRAJ>
+__global__ void __launch_bounds__(SIT_X2_BLOCK, SIT_X2_MINB)
+fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float> g, const int K, const FleetIO<float> io) {
+    using namespace x2;
+    const int64_t li = 2 * ((int64_t)blockIdx.x * blockDim.x + threadIdx.x);
+    if (li >= io.count) return;
+    const int64_t S = g.n_ships, i0 = io.first + li;
+    const bool two = li + 1 < io.count;
+    const int64_t i1 = two ? i0 + 1 : i0;
+    // 64-bit accesses need an even element offset: state rows start 256-byte aligned (i0 is even), rows of [c][S] blocks
+    // (disturbances, trajectory) only when S is even
+    const bool vec = two && !(S & 1);
+    auto ld = [&](const float* p) -> V { return two ? *reinterpret_cast<const float2*>(p + i0) : make_float2(p[i0], p[i0]); };
+    auto st = [&](float* p, const V v) { if (two) *reinterpret_cast<float2*>(p + i0) = v; else p[i0] = v.x; };
+    auto ldr = [&](const float* p) -> V { return vec ? *reinterpret_cast<const float2*>(p + i0) : make_float2(p[i0], p[i1]); };
+    auto str = [&](float* p, const V v) {
+        if (vec) *reinterpret_cast<float2*>(p + i0) = v;
+        else { p[i0] = v.x; if (two) p[i1] = v.y; }
+    };
+    Ship2 s;
+    s.N[0] = g.north[i0]; s.N[1] = g.north[i1]; s.E[0] = g.east[i0]; s.E[1] = g.east[i1];
+    s.psi = ld(g.psi); s.u = ld(g.u); s.v = ld(g.v); s.r = ld(g.r); s.om = ld(g.omega);
+    s.ei_s = ld(g.ei_speed); s.ei_w = ld(g.ei_shaft); s.ei_h = ld(g.ei_heading); s.e_prev = ld(g.e_prev);
+    s.e_ct = ld(g.e_ct); s.e_int = ld(g.e_ct_int);
+    s.f_me = ld(g.fuel_me); s.f_el = ld(g.fuel_el); s.f_tot = ld(g.fuel);
+    s.u_sp = ld(g.u_sp);
+    V w_speed, w_dir;
+    if (io.dist) {   // disturbances held for the launch (ship_model.py:154-156: plain attributes)
+        s.vcn = ldr(io.dist); s.vce = ldr(io.dist + S); w_speed = ldr(io.dist + 2 * S); w_dir = ldr(io.dist + 3 * S);
+        st(g.vc_n, s.vcn); st(g.vc_e, s.vce); st(g.wind_speed, w_speed); st(g.wind_dir, w_dir);
+    } else {
+        s.vcn = ld(g.vc_n); s.vce = ld(g.vc_e); w_speed = ld(g.wind_speed); w_dir = ld(g.wind_dir);
+    }
+    {
+        float sb, cb;
+        sincos_(w_dir.x, sb, cb); s.wcb.x = w_speed.x * cb; s.wsb.x = w_speed.x * sb;
+        sincos_(w_dir.y, sb, cb); s.wcb.y = w_speed.y * cb; s.wsb.y = w_speed.y * sb;
+    }
+    s.k[0] = g.k[i0]; s.k[1] = g.k[i1]; s.n_wp[0] = g.n_wp[i0]; s.n_wp[1] = g.n_wp[i1];
+    load_segment2(s, g, i0, 0); load_segment2(s, g, i1, 1);
+    ModeV MV;
+    if (!SINGLE_MODE) {
+        const ModeX &a = P.mode[g.mode[i0]], &b = P.mode[g.mode[i1]];
+#define MV_(f) MV.f = make_float2(a.f, b.f)
+        MV_(avail_total); MV_(avail_me); MV_(avail_el); MV_(cap_tq_me); MV_(cap_tq_el); MV_(add_me); MV_(cap_me);
+        MV_(a_el); MV_(c_el); MV_(inv_me_cap); MV_(inv_el_cap);
+#undef MV_
+    }
+    float* tr = io.traj + i0;   // running row pointer of the every-step trajectory
+#pragma unroll 1
+    for (int t = 0; t < K; ++t) {
+        if (SINGLE_MODE) ship_step2<AVOID>(P, P.mode[0], s, g, i0, i1);
+        else ship_step2<AVOID>(P, MV, s, g, i0, i1);
+        if (TRAJ) {   // every-step trajectory [K][8][S]: coalesced 64-bit streaming stores, the only memory traffic of the loop
+            float* q = tr;
+            const V vn = make_float2((float)s.N[0], (float)s.N[1]), ve = make_float2((float)s.E[0], (float)s.E[1]);
+            const V vk = make_float2((float)s.k[0], (float)s.k[1]);
+            if (vec) {
+                __stcs(reinterpret_cast<float2*>(q), vn); q += S; __stcs(reinterpret_cast<float2*>(q), ve); q += S;
+                __stcs(reinterpret_cast<float2*>(q), s.psi); q += S; __stcs(reinterpret_cast<float2*>(q), s.u); q += S;
+                __stcs(reinterpret_cast<float2*>(q), s.v); q += S; __stcs(reinterpret_cast<float2*>(q), s.r); q += S;
+                __stcs(reinterpret_cast<float2*>(q), s.om); q += S; __stcs(reinterpret_cast<float2*>(q), vk);
+            } else {
+                const int64_t o = two ? 1 : 0;   // the odd tail ship writes its own element twice
+                __stcs(q, vn.x); __stcs(q + o, vn.y); q += S; __stcs(q, ve.x); __stcs(q + o, ve.y); q += S;
+                __stcs(q, s.psi.x); __stcs(q + o, s.psi.y); q += S; __stcs(q, s.u.x); __stcs(q + o, s.u.y); q += S;
+                __stcs(q, s.v.x); __stcs(q + o, s.v.y); q += S; __stcs(q, s.r.x); __stcs(q + o, s.r.y); q += S;
+                __stcs(q, s.om.x); __stcs(q + o, s.om.y); q += S; __stcs(q, vk.x); __stcs(q + o, vk.y);
+            }
+            tr = q + S;
+        }
+    }
+    if (!TRAJ && io.traj) {
+        float* t0 = io.traj;
+        str(t0, make_float2((float)s.N[0], (float)s.N[1])); str(t0 + S, make_float2((float)s.E[0], (float)s.E[1]));
+        str(t0 + 2 * S, s.psi); str(t0 + 3 * S, s.u); str(t0 + 4 * S, s.v); str(t0 + 5 * S, s.r); str(t0 + 6 * S, s.om);
+        str(t0 + 7 * S, make_float2((float)s.k[0], (float)s.k[1]));
+    }
+    g.north[i0] = s.N[0]; g.east[i0] = s.E[0];
+    if (two) { g.north[i1] = s.N[1]; g.east[i1] = s.E[1]; }
+    st(g.psi, s.psi); st(g.u, s.u); st(g.v, s.v); st(g.r, s.r); st(g.omega, s.om);
+    st(g.ei_speed, s.ei_s); st(g.ei_shaft, s.ei_w); st(g.ei_heading, s.ei_h); st(g.e_prev, s.e_prev);
+    st(g.e_ct, vabs(s.e_ct)); st(g.e_ct_int, s.e_int);
+    st(g.fuel_me, s.f_me); st(g.fuel_el, s.f_el); st(g.fuel, s.f_tot);
+    g.k[i0] = s.k[0]; g.n_wp[i0] = s.n_wp[0]; g.steps[i0] += K;   // utils.py:42-48 next_time, once per stored step
+    if (two) { g.k[i1] = s.k[1]; g.n_wp[i1] = s.n_wp[1]; g.steps[i1] += K; }
 }
 
 // =================================================================================================
@@ -365,7 +464,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         const R dmap = sqrt_(d2map);
         const bool outside = pn < EP.lo_n[role] || pn > EP.hi_n[role] || pe < EP.lo_e[role] || pe > EP.hi_e[role];
         const double dnE = s.N - (double)endN, deE = s.E - (double)endE;
-        const bool arrived = (R)__dadd_rn(__dmul_rn(dnE, dnE), __dmul_rn(deE, deE)) <= EP.arrive2[role];
+        const bool arrived = __dadd_rn(__dmul_rn(dnE, dnE), __dmul_rn(deE, deE)) <= EP.arrive2;   // decided in double in both precisions
         const R ect = s.e_ct;
 
         // ---- per-ship reward terms and terminal checks (sequential stop_flag gating) -------------------
@@ -1074,6 +1173,23 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(R* out, int iters, R a, R
     if (sum == (R)123456789) out[0] = sum;   // never true: keeps the chain alive
 }
 
+// the same chain as packed f32x2 FMAs (FFMA2: two FMAs per lane per instruction)
+__global__ void __launch_bounds__(256) fma_peak_x2_kernel(float* out, int iters, float a, float b) {
+    const float t = (float)threadIdx.x;
+    float2 x0 = make_float2(t, t + 8), x1 = make_float2(t + 1, t + 9), x2 = make_float2(t + 2, t + 10), x3 = make_float2(t + 3, t + 11),
+           x4 = make_float2(t + 4, t + 12), x5 = make_float2(t + 5, t + 13), x6 = make_float2(t + 6, t + 14), x7 = make_float2(t + 7, t + 15);
+    const float2 a2 = make_float2(a, a), b2 = make_float2(b, b);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            x0 = __ffma2_rn(x0, a2, b2); x1 = __ffma2_rn(x1, a2, b2); x2 = __ffma2_rn(x2, a2, b2); x3 = __ffma2_rn(x3, a2, b2);
+            x4 = __ffma2_rn(x4, a2, b2); x5 = __ffma2_rn(x5, a2, b2); x6 = __ffma2_rn(x6, a2, b2); x7 = __ffma2_rn(x7, a2, b2);
+        }
+    }
+    const float2 s = __fadd2_rn(__fadd2_rn(__fadd2_rn(x0, x1), __fadd2_rn(x2, x3)), __fadd2_rn(__fadd2_rn(x4, x5), __fadd2_rn(x6, x7)));
+    if (s.x + s.y == 123456789.0f) out[0] = s.x;   // never true: keeps the chain alive
+}
+
 // =================================================================================================
 // Host side
 // =================================================================================================
@@ -1121,6 +1237,7 @@ struct SitHandle_ {
     std::vector<SitField> fields;
     size_t state_bytes;
     ShipP<double> pd[2]; ShipP<float> pf[2];
+    x2::ShipPX px;                               // packed fp32 fleet step (fleet handles, ship[0])
     EnvKArgs<double>* kd; EnvKArgs<float>* kf;   // host copies passed by value at launch
     // scratch for the *_host entry point
     void* d_scratch; size_t scratch_bytes;
@@ -1226,6 +1343,32 @@ static void derive_ship(const SitShipParams& c, ShipP<R>& P) {
     }
 }
 
+// uniform parameters of the packed fp32 step (ship_x2.cuh) from the scalar ones: folded gains, branch-free machinery modes
+static void derive_shipx(const ShipP<float>& P, x2::ShipPX& X) {
+    std::memset(&X, 0, sizeof(X));
+    X.ra2 = P.ra2;
+    X.dt = P.dt; X.look2 = P.look2; X.sat_e = P.sat_e; X.neg_ki_los = -P.ki_los; X.windup = P.windup;
+    X.kp_h = P.kp_h; X.kd_idt = P.kd_h * P.inv_dt; X.ki_h = P.ki_h; X.rud_max = P.rud_max; X.rud_bias = P.rud_bias;
+    X.kp_s = P.kp_s; X.ki_s = P.ki_s; X.kp_w = P.kp_w; X.ki_w = P.ki_w;
+    X.hotel = P.hotel;
+    for (int j = 0; j < 3; ++j) { X.sfc_me[j] = P.sfc_me[j]; X.sfc_dg[j] = P.sfc_dg[j]; }
+    X.sh_me = P.sh_me; X.sh_hsg = P.sh_hsg; X.sh_lin = P.sh_lin; X.sh_quad = P.sh_quad;
+    X.au_vr = P.au_vr; X.au_vrr = P.au_vrr; X.au_lin = P.au_lin; X.au_nl = P.au_nl; X.au_wind = P.au_wind;
+    X.au_thr = P.au_thr;   // already carries D^4 k_t (derive_ship)
+    X.av_ur = P.av_ur; X.av_urr = P.av_urr; X.av_lin = P.av_lin; X.av_nl = P.av_nl; X.av_wind = P.av_wind; X.av_rud = P.av_rud;
+    X.ar_ca = P.ar_ca; X.ar_lin = P.ar_lin; X.ar_nl = P.ar_nl; X.ar_wind = P.ar_wind; X.ar_rud = P.ar_rud;
+    X.n_modes = P.n_modes;
+    for (int j = 0; j < P.n_modes && j < SIT_MAX_MODES; ++j) {
+        const ModeP<float>& M = P.mode[j];
+        x2::ModeX& Y = X.mode[j];
+        Y.avail_total = M.avail_total; Y.avail_me = M.avail_me; Y.avail_el = M.avail_el;
+        Y.cap_tq_me = M.cap_tq_me; Y.cap_tq_el = M.cap_tq_el;
+        Y.inv_me_cap = M.inv_me_cap; Y.inv_el_cap = M.inv_el_cap;
+        if (M.sg == SIT_SG_MOTOR) { Y.add_me = 0.0f; Y.cap_me = M.me_cap; Y.a_el = 1.0f; Y.c_el = 0.0f; }
+        else { Y.add_me = M.load_me_add; Y.cap_me = INFINITY; Y.a_el = 0.0f; Y.c_el = M.load_el_const; }
+    }
+}
+
 template <typename R>
 static void derive_env(const SitConfig& c, EnvKArgs<R>& A) {
     derive_ship(c.ship[0], A.P[0]);
@@ -1253,9 +1396,9 @@ static void derive_env(const SitConfig& c, EnvKArgs<R>& A) {
         E.lo_n[r] = (R)(mn_n + margin); E.hi_n[r] = (R)(mx_n - margin);
         E.lo_e[r] = (R)(mn_e + margin); E.hi_e[r] = (R)(mx_e - margin);
         E.half_len[r] = (R)margin;
-        E.arrive2[r] = largest_with_sqrt_le<R>(200.0);
         hl_max = std::fmax(hl_max, margin);
     }
+    E.arrive2 = largest_with_sqrt_le<double>(200.0);
     E.inv_max_north = (R)(1.0 / mx_n);
     E.e_tol = (R)1000; E.inv_e_tol = (R)(1.0 / 1000);
     E.rpm_max = (R)2000;
@@ -1398,6 +1541,7 @@ int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out)
     cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
     derive_ship(cfg->ship[0], h->pd[0]); derive_ship(cfg->ship[1].dt > 0 ? cfg->ship[1] : cfg->ship[0], h->pd[1]);
     derive_ship(cfg->ship[0], h->pf[0]); derive_ship(cfg->ship[1].dt > 0 ? cfg->ship[1] : cfg->ship[0], h->pf[1]);
+    derive_shipx(h->pf[0], h->px);
     h->kd = nullptr; h->kf = nullptr;
     if (cfg->kind == SIT_KIND_ENV) {
         if (cfg->precision == SIT_F64) { h->kd = new EnvKArgs<double>(); derive_env(*cfg, *h->kd); }
@@ -1446,6 +1590,31 @@ int sit_layout(SitHandle h, SitField* fields, int32_t capacity, int32_t* n_field
 static int grid_for(int64_t n, int block) { return (int)((n + block - 1) / block); }
 
 }  // extern "C"
+// fp32 fleets: every launch without per-step inputs / logs runs the packed kernel.  Returns false when the launch is not
+// its case (fp64, per-step disturbances, 27-channel log, command stream).
+template <typename R>
+static bool fleet_x2(SitHandle, const ShipPtrs<R>&, int, const FleetIO<R>&, bool, bool, bool, cudaStream_t) { return false; }
+template <>
+bool fleet_x2<float>(SitHandle h, const ShipPtrs<float>& g, int K, const FleetIO<float>& k, bool quiet, bool fast, bool single,
+                     cudaStream_t st) {
+    const bool traj_all = quiet && k.traj && k.traj_steps == K && K > 1;
+    if (!(traj_all || fast) || (k.first & 1)) return false;
+    static const bool off = std::getenv("SIT_NO_X2") != nullptr;   // A/B switch for profiling runs
+    if (off) return false;
+    const int block = SIT_X2_BLOCK, grid = (int)(((k.count + 1) / 2 + block - 1) / block);
+    const x2::ShipPX& P = h->px;
+#define X2_(A, M, T) fleet_step_x2_kernel<A, M, T><<<grid, block, 0, st>>>(P, g, K, k)
+    if (traj_all) {
+        if (k.avoid) { if (single) X2_(true, true, true); else X2_(true, false, true); }
+        else { if (single) X2_(false, true, true); else X2_(false, false, true); }
+    } else {
+        if (k.avoid) { if (single) X2_(true, true, false); else X2_(true, false, false); }
+        else { if (single) X2_(false, true, false); else X2_(false, false, false); }
+    }
+#undef X2_
+    return true;
+}
+
 template <typename R>
 static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, cudaStream_t st, int64_t first = 0,
                         int64_t count = -1) {
@@ -1468,7 +1637,9 @@ static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, c
     const bool quiet = (!k.dist || k.dist_steps == 1) && !k.log27 && !k.cmd && k.store;
     const bool fast = quiet && (!k.traj || k.traj_steps == 1);
     const bool single = P.n_modes == 1;
-    if (quiet && k.traj && k.traj_steps == K && K > 1) {   // every-step trajectory on the specialised compute path
+    if (fleet_x2<R>(h, g, K, k, quiet, fast, single, st)) {
+        // fp32: packed two-ships-per-thread kernel (ship_x2.cuh) launched
+    } else if (quiet && k.traj && k.traj_steps == K && K > 1) {   // every-step trajectory on the specialised compute path
         if (k.avoid) {
             if (single) fleet_step_fast_kernel<R, true, true, true><<<grid, block, 0, st>>>(P, g, K, k);
             else fleet_step_fast_kernel<R, true, false, true><<<grid, block, 0, st>>>(P, g, K, k);
@@ -2067,6 +2238,7 @@ int sit_measure_fma_peak(int device, int32_t precision, double* tflops, double* 
     for (int rep = 0; rep < 5; ++rep) {
         cudaEventRecord(e0, 0);
         if (precision == SIT_F64) fma_peak_kernel<double><<<grid, block>>>(static_cast<double*>(out), iters, 1.0000001, 1e-9);
+        else if (precision == SIT_PEAK_F32X2) fma_peak_x2_kernel<<<grid, block>>>(static_cast<float*>(out), iters, 1.0000001f, 1e-9f);
         else fma_peak_kernel<float><<<grid, block>>>(static_cast<float*>(out), iters, 1.0000001f, 1e-9f);
         cudaEventRecord(e1, 0);
         CUDA_TRY(cudaEventSynchronize(e1));
@@ -2075,7 +2247,7 @@ int sit_measure_fma_peak(int device, int32_t precision, double* tflops, double* 
         if (rep > 0 && ms < best) best = ms;
     }
     CUDA_TRY(cudaGetLastError());
-    const double flops = 2.0 * 8 * 16 * (double)iters * block * (double)grid;
+    const double flops = (precision == SIT_PEAK_F32X2 ? 2.0 : 1.0) * 2.0 * 8 * 16 * (double)iters * block * (double)grid;
     *tflops = flops / (best * 1e-3) / 1e12;
     if (ms_out) *ms_out = best;
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
