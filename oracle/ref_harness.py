@@ -1,9 +1,11 @@
 """Run the REAL reference simulator/env from /root/reference behind import shims.
 
-TEST INFRASTRUCTURE, build-container only: ``/root/reference`` does not exist on the GPU
-box, so nothing reachable from ``-m gpu`` tests, ``smoke()`` or ``bench.py`` imports this.
-It is used by ``tests/golden/make_golden.py`` to freeze reference outputs as fixtures and
-by CPU tests (skipped when the tree is absent) that pin the C / Python restatements.
+TEST / BASELINE INFRASTRUCTURE.  ``/root/reference`` does not exist on the GPU box; there the
+files staged by ``oracle/stage_ref.py`` under ``oracle/_ref/`` (git-ignored, shipped with the
+snapshot) are used instead, and only by ``bench.py``'s CPU-baseline legs (``oracle/ref_timing.py``),
+never by ``-m gpu`` tests or ``smoke()``.  In the build container it is used by
+``tests/golden/make_golden.py`` to freeze reference outputs as fixtures and by CPU tests
+(skipped when the tree is absent) that pin the C / Python restatements.
 
 Shims: empty ``matplotlib{,.pyplot,.patches}`` modules (imported at
 ship_model.py:8, LOS_guidance.py:8, obstacle.py:2,5 but only used for plotting); a
@@ -21,7 +23,17 @@ from types import SimpleNamespace
 
 import numpy as np
 
-REFERENCE_ROOT = os.environ.get("SIT_REFERENCE_ROOT", "/root/reference")
+def _reference_root() -> str:
+    """/root/reference in the build container; on the GPU box the copy staged by oracle/stage_ref.py (oracle/_ref/)."""
+    env = os.environ.get("SIT_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/simulators/ship_in_transit"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REFERENCE_ROOT = _reference_root()
 
 DEFAULT_MAP = [
     [(0, 10000), (5500, 10000), (5300, 9000), (4800, 8500), (4200, 7300), (4000, 5700), (4300, 4900),

@@ -117,6 +117,7 @@ struct ShipPtrs {
     int32_t *k, *n_wp, *mode, *n_wp0, *steps;
     R *wp_n, *wp_e, *wp0_n, *wp0_e;  // [max_wp][n_ships]
     int32_t* mc_idx; float *mc_n, *mc_e, *mc_b2;   // nearest-ring cache (env kernel)
+    float *rel_n, *rel_cn, *rel_e, *rel_ce;        // packed fp32 fleet kernel: compensated position relative to the segment start
     int64_t n_ships;
     int32_t max_wp, _pad;
 };

@@ -8,9 +8,15 @@
 //   * atan of the LOS term: one MUFU.RCP per ship for |x| > 1, odd degree-15 minimax polynomial on [-1, 1] (< 1.1e-7);
 //   * the machinery-mode formulas of ship_engine.py:32-76 are folded into one branch-free form (ModeX) so that ships in
 //     different modes share the packed instructions.
-// Positions stay in double per ship (waypoint switching is decided on the numbers the float64 reference sees), exactly
-// as in ship_core.cuh.  Same physics, same reference citations as ship_core.cuh::ship_step; the arithmetic differs from
-// the scalar float step only in rounding (different but equivalent operation order).
+//   * positions: the state in HBM stays float64 (north, east); inside the loop each ship carries its position RELATIVE TO THE
+//     START OF ITS ROUTE SEGMENT as a compensated float pair (X - CX, Kahan summation: ~48 significant bits, as good as the
+//     float64 accumulation of float increments it replaces) so that the per-step position update, the LOS cross-track error
+//     and the waypoint pre-test are packed FP32 too -- no FP64 and no F2F conversion in the steady-state step.  The
+//     waypoint switch itself is still DECIDED IN DOUBLE on the reconstructed float64 position with the reference's
+//     operation order: a packed float pre-test with a 1 % band around the acceptance circle selects the (rare) steps on
+//     which that exact test runs, for both ships of the thread in one branch.
+// Same physics, same reference citations as ship_core.cuh::ship_step; the arithmetic differs from the scalar float step
+// only in rounding (different but equivalent operation order).
 //
 // Reference citations are relative to /root/reference/.
 #pragma once
@@ -49,10 +55,12 @@ struct ModeX {
 
 struct ShipPX {
     double ra2;                                            // radius_of_acceptance^2, decided in double
+    float ra2_band;                                        // float pre-test: d2 <= 1.01 ra^2 + 16 -> run the exact test
+    float c_inv_pi, c_s3, c_c4, c_a6;                      // second constants of two-constant FMAs (uniform operands)
     float dt, look2, sat_e, neg_ki_los, windup;            // LOS_guidance.py:105-121
     float kp_h, kd_idt, ki_h, rud_max, rud_bias;           // controllers.py:72-100 (kd / dt folded)
     float kp_s, ki_s, kp_w, ki_w;                          // controllers.py:138-143
-    float hotel, sfc_me[3], sfc_dg[3];                     // ship_engine.py:256-292 (/ 3.6e9 folded)
+    float hotel, sfc_me[3], sfc_dg[3];                     // ship_engine.py:256-292 (dt / 3.6e9 folded)
     float sh_me, sh_hsg, sh_lin, sh_quad;                  // shaft_eq :355-361
     float au_vr, au_vrr, au_lin, au_nl, au_wind, au_thr;   // ship_model.py:576-606, accelerations
     float av_ur, av_urr, av_lin, av_nl, av_wind, av_rud;
@@ -63,11 +71,12 @@ struct ShipPX {
 
 // ---- per-thread register state: two ships --------------------------------------------------------------------------
 struct Ship2 {
-    double N[2], E[2];                      // ship_model.py:159-160
-    double pN[2], pE[2], cN[2], cE[2];      // cached route segment k-1 -> k
-    V psi, u, v, r, om;                     // :161-164, ship_engine.py:327
+    V X, Y, CX, CY;                         // position relative to the segment start; true value = X - CX (Kahan)
+    V SX, SY;                               // segment vector wp[k] - wp[k-1]
+    V thr2;                                 // pre-test threshold: ra2_band while a next waypoint exists, -1 at the end of the route
+    V psi, u, v, r, om;                     // ship_model.py:161-164, ship_engine.py:327
     V ei_s, ei_w, ei_h, e_prev, e_ct, e_int;
-    V f_me, f_el, f_tot;
+    V f_me, f_el;                           // fuel_cons = its value at load + the increments of both (formed at store)
     V u_sp, vcn, vce, wcb, wsb;
     V alpha, sa, ca;
     int32_t k[2], n_wp[2];
@@ -80,34 +89,71 @@ __device__ __forceinline__ float& lane(V& a, int l) { return l == 0 ? a.x : a.y;
 __device__ __forceinline__ float lane(const V& a, int l) { return l == 0 ? a.x : a.y; }
 __device__ __forceinline__ float lane(const float& a, int) { return a; }
 
-__device__ __forceinline__ void load_segment2(Ship2& s, const ShipPtrs<float>& g, const int64_t i, const int l) {
-    // LOS_guidance.py:110-112: segment k-1 -> k and its angle (atan2(dE, dN))
-    const int64_t S = g.n_ships;
-    s.pN[l] = g.wp_n[(int64_t)(s.k[l] - 1) * S + i];
-    s.pE[l] = g.wp_e[(int64_t)(s.k[l] - 1) * S + i];
-    s.cN[l] = g.wp_n[(int64_t)s.k[l] * S + i];
-    s.cE[l] = g.wp_e[(int64_t)s.k[l] * S + i];
-    const float a = atan2f((float)(s.cE[l] - s.pE[l]), (float)(s.cN[l] - s.pN[l]));
-    float sa, ca;
-    sincos_(a, sa, ca);
+// float64 position of ship l from its segment start and the compensated relative pair
+__device__ __forceinline__ double abs_pos(double p, float x, float c) { return p + ((double)x - (double)c); }
+// relative pair of a float64 offset: x = nearest float, c = -(remainder)
+__device__ __forceinline__ void split_rel(double rel, float& x, float& c) { x = (float)rel; c = -(float)(rel - (double)x); }
+
+// LOS_guidance.py:110-112: segment k-1 -> k of ship l: vector, angle (atan2(dE, dN)), threshold of the waypoint pre-test
+__device__ __forceinline__ void set_segment2(Ship2& s, const ShipPX& P, const double pN, const double pE, const double cN,
+                                             const double cE, const int l) {
+    const float sx = (float)(cN - pN), sy = (float)(cE - pE);
+    // direction cosines straight from the segment vector (one MUFU.RSQ + a Newton step) and a branch-free atan2 on the
+    // same odd polynomial as atan2v: this block runs once per waypoint switch, for one ship of the warp at a time
+    const float l2 = fmaf(sx, sx, sy * sy);
+    float il = rsqrt_approx(l2);
+    il = il * fmaf(-0.5f * l2 * il, il, 1.5f);
+    const bool degenerate = !(l2 > 0.0f);                     // zero-length segment: atan2(0, 0) = 0
+    const float sa = degenerate ? 0.0f : sy * il, ca = degenerate ? 1.0f : sx * il;
+    const float ax = fabsf(sx), ay = fabsf(sy);
+    const float z = fminf(ax, ay) * rcp_(fmaxf(fmaxf(ax, ay), 1e-30f));
+    const float z2 = z * z;
+    float pa = fmaf(z2, -0.004355357028543949f, 0.023039964959025383f);
+    pa = fmaf(pa, z2, -0.05777335166931152f); pa = fmaf(pa, z2, 0.09794218093156815f);
+    pa = fmaf(pa, z2, -0.13976575434207916f); pa = fmaf(pa, z2, 0.19962702691555023f);
+    pa = fmaf(pa, z2, -0.3333165943622589f);
+    pa = fmaf(pa * z2, z, z);
+    if (ay > ax) pa = 1.57079632679489662f - pa;
+    if (sx < 0.0f) pa = 3.14159265358979324f - pa;
+    const float a = copysignf(pa, sy);
+    lane(s.SX, l) = sx; lane(s.SY, l) = sy;
     lane(s.alpha, l) = a; lane(s.sa, l) = sa; lane(s.ca, l) = ca;
+    lane(s.thr2, l) = s.n_wp[l] > s.k[l] + 1 ? P.ra2_band : -1.0f;
+}
+
+// LOS_guidance.py:88-103 next_wpt for ship l, decided in double on the float64 position with the reference's operation order
+// (squared distance, <=, end-of-route hold).  On a switch the relative pair is re-based on the new segment start.
+__device__ __forceinline__ void next_wpt2(Ship2& s, const ShipPX& P, const ShipPtrs<float>& g, const int64_t i, const int l) {
+    const int64_t S = g.n_ships;
+    const int k = s.k[l];
+    const double pN = g.wp_n[(int64_t)(k - 1) * S + i], pE = g.wp_e[(int64_t)(k - 1) * S + i];
+    const double cN = g.wp_n[(int64_t)k * S + i], cE = g.wp_e[(int64_t)k * S + i];
+    const double N = abs_pos(pN, lane(s.X, l), lane(s.CX, l)), E = abs_pos(pE, lane(s.Y, l), lane(s.CY, l));
+    const double dn = cN - N, de = cE - E;
+    const double d2 = __dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de));
+    if (d2 <= P.ra2 && s.n_wp[l] > k + 1) {
+        s.k[l] = k + 1;
+        split_rel(N - cN, lane(s.X, l), lane(s.CX, l));
+        split_rel(E - cE, lane(s.Y, l), lane(s.CY, l));
+        set_segment2(s, P, cN, cE, g.wp_n[(int64_t)(k + 1) * S + i], g.wp_e[(int64_t)(k + 1) * S + i], l);
+    }
 }
 
 // sin and cos of two headings.  t = x / pi + 1.5 * 2^23 holds round(x / pi) in its low mantissa bits; r = x - j pi in two
 // Cody-Waite steps (pi = 3.140625 + 9.67653589793e-4: the product j * 3.140625 is exact for |j| < 2^13, i.e. |x| < 2.5e4 rad);
 // sin x = (-1)^j sin r, cos x = (-1)^j cos r: the parity bit of j moves to the sign position and is XOR-ed in.
-__device__ __forceinline__ void sincos2(const V x, V& sn, V& cs) {
-    const V t = fma(x, 0.318309886183790672f, 12582912.0f);
+__device__ __forceinline__ void sincos2(const ShipPX& P, const V x, V& sn, V& cs) {
+    const V t = fma(x, P.c_inv_pi, 12582912.0f);
     const V j = add(t, -12582912.0f);
     V r = fma(j, -3.140625f, x);
     r = fma(j, -9.67653589793e-4f, r);
     const V r2 = mul(r, r);
-    V ps = fma(r2, 2.600024345156271e-06f, -0.00019806601630989462f);
+    V ps = fma(r2, P.c_s3, -0.00019806601630989462f);
     ps = fma(ps, r2, 0.008333017118275166f);
     ps = fma(ps, r2, -0.16666656732559204f);
     ps = mul(ps, r2);
     ps = fma(ps, r, r);
-    V pc = fma(r2, -2.607681608424173e-07f, 2.476187000866048e-05f);
+    V pc = fma(r2, P.c_c4, 2.476187000866048e-05f);
     pc = fma(pc, r2, -0.00138884037733078f);
     pc = fma(pc, r2, 0.04166664183139801f);
     pc = fma(pc, r2, -0.5f);
@@ -118,13 +164,13 @@ __device__ __forceinline__ void sincos2(const V x, V& sn, V& cs) {
 }
 
 // atan of two arguments: z = x for |x| <= 1, 1 / x beyond (atan x = sign(x) pi/2 - atan(1 / x)); atan z = z + z^3 P(z^2)
-__device__ __forceinline__ V atan2v(const V x) {
+__device__ __forceinline__ V atan2v(const ShipPX& P, const V x) {
     const bool ix = fabsf(x.x) > 1.0f, iy = fabsf(x.y) > 1.0f;
     V z;
     z.x = ix ? rcp_approx(x.x) : x.x;
     z.y = iy ? rcp_approx(x.y) : x.y;
     const V z2 = mul(z, z);
-    V p = fma(z2, -0.004355357028543949f, 0.023039964959025383f);
+    V p = fma(z2, P.c_a6, 0.023039964959025383f);
     p = fma(p, z2, -0.05777335166931152f);
     p = fma(p, z2, 0.09794218093156815f);
     p = fma(p, z2, -0.13976575434207916f);
@@ -143,23 +189,21 @@ __device__ __forceinline__ V atan2v(const V x) {
 }
 
 // One step of two ships.  MP = ModeX: one machinery mode for the whole fleet (uniform operands); MP = ModeV: per-ship modes.
-template <bool AVOID, typename MP>
-__device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& s, const ShipPtrs<float>& g, const int64_t i0,
-                                           const int64_t i1) {
-    // ---- LOS_guidance.py:88-103 next_wpt: squared distance, <=, end-of-route hold (double, per ship) ----------------
-#pragma unroll
-    for (int l = 0; l < 2; ++l) {
-        const double dn = s.cN[l] - s.N[l], de = s.cE[l] - s.E[l];
-        const double d2 = __dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de));
-        if (d2 <= P.ra2 && s.n_wp[l] > s.k[l] + 1) {
-            s.k[l] += 1;
-            load_segment2(s, g, l == 0 ? i0 : i1, l);
+// i0 / i1: the two ships' indices (only read on the rare waypoint-switch path).
+template <bool AVOID, typename MP, typename IdxFn>
+__device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& s, const ShipPtrs<float>& g, const IdxFn& idx) {
+    // ---- LOS_guidance.py:88-103 next_wpt: packed float pre-test; the decision itself in double (next_wpt2) -----------------
+    {
+        const V dn = sub(s.SX, s.X), de = sub(s.SY, s.Y);
+        const V d2 = fma(de, de, mul(dn, dn));
+        const bool h0 = d2.x <= s.thr2.x, h1 = d2.y <= s.thr2.y;
+        if (h0 | h1) {
+            if (h0) next_wpt2(s, P, g, idx(0), 0);
+            if (h1) next_wpt2(s, P, g, idx(1), 1);
         }
     }
     // ---- LOS_guidance.py:105-121 los_guidance ---------------------------------------------------------------------
-    const V en = make_float2((float)(s.N[0] - s.pN[0]), (float)(s.N[1] - s.pN[1]));
-    const V ee = make_float2((float)(s.E[0] - s.pE[0]), (float)(s.E[1] - s.pE[1]));
-    V e = fma(ee, s.ca, neg(mul(en, s.sa)));
+    V e = fma(s.Y, s.ca, neg(mul(s.X, s.sa)));
     s.e_ct = e;                                             // |e| is taken where it is stored
     const V e2 = mul(e, e);
     if (e2.x >= P.look2) e.x = P.sat_e;                      // sign lost on purpose (0.99 * lookahead)
@@ -169,7 +213,7 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
     const V ti = add(s.e_int, q);
     if (fabsf(ti.x) <= P.windup) s.e_int.x = ti.x;
     if (fabsf(ti.y) <= P.windup) s.e_int.y = ti.y;
-    const V href = add(s.alpha, atan2v(fma(s.e_int, P.neg_ki_los, neg(q))));
+    const V href = add(s.alpha, atan2v(P, fma(s.e_int, P.neg_ki_los, neg(q))));
 
     // ---- controllers.py:81-93,188-189 heading PID: no wrap, no anti-windup -------------------------------------------
     const V err = sub(href, s.psi);
@@ -212,17 +256,16 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
         load_me.x = fminf(load_me.x, lane(M.cap_me, 0)); load_me.y = fminf(load_me.y, lane(M.cap_me, 1));
         const V load_el = fma(sub(add(total, P.hotel), load_me), M.a_el, M.c_el);
         const V pct_me = mul(load_me, M.inv_me_cap), pct_el = mul(load_el, M.inv_el_cap);
-        // rate = load * (a pct^2 + b pct + c) / 3.6e9; a zero load gives a zero rate without the reference's guards
-        const V rate_me = mul(load_me, fma(fma(pct_me, P.sfc_me[0], P.sfc_me[1]), pct_me, P.sfc_me[2]));
-        const V rate_el = mul(load_el, fma(fma(pct_el, P.sfc_dg[0], P.sfc_dg[1]), pct_el, P.sfc_dg[2]));
-        s.f_me = fma(rate_me, P.dt, s.f_me);
-        s.f_el = fma(rate_el, P.dt, s.f_el);
-        s.f_tot = fma(add(rate_me, rate_el), P.dt, s.f_tot);
+        // rate dt = load (a pct^2 + b pct + c) dt / 3.6e9; a zero load gives a zero rate without the reference's guards
+        const V pme = fma(fma(pct_me, P.sfc_me[0], P.sfc_me[1]), pct_me, P.sfc_me[2]);
+        const V pel = fma(fma(pct_el, P.sfc_dg[0], P.sfc_dg[1]), pct_el, P.sfc_dg[2]);
+        s.f_me = fma(load_me, pme, s.f_me);
+        s.f_el = fma(load_el, pel, s.f_el);   // fuel_cons (the sum of both, ship_engine.py:288-292) is formed where the state is stored
     }
 
     // ---- ship_model.py:233-250 kinematics ---------------------------------------------------------------------------
     V sn, c;
-    sincos2(s.psi, sn, c);
+    sincos2(P, s.psi, sn, c);
     const V udt = mul(s.u, P.dt), vdt = mul(s.v, P.dt);
     const V d_north = fma(c, udt, neg(mul(sn, vdt)));
     const V d_east = fma(sn, udt, mul(c, vdt));
@@ -254,8 +297,12 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
     d_r = fma(ru, -P.ar_rud, d_r);
 
     // ---- ship_model.py:632-643, utils.py:50-53 explicit Euler, all derivatives from the old state ---------------------------
-    s.N[0] += (double)d_north.x; s.N[1] += (double)d_north.y;
-    s.E[0] += (double)d_east.x; s.E[1] += (double)d_east.y;
+    {   // position: Kahan-compensated float accumulation of the float increments
+        const V yn = sub(d_north, s.CX), ye = sub(d_east, s.CY);
+        const V tn = add(s.X, yn), te = add(s.Y, ye);
+        s.CX = sub(sub(tn, s.X), yn); s.CY = sub(sub(te, s.Y), ye);
+        s.X = tn; s.Y = te;
+    }
     s.psi = fma(s.r, P.dt, s.psi);
     s.u = fma(d_u, P.dt, s.u);
     s.v = fma(d_v, P.dt, s.v);

@@ -148,6 +148,11 @@ __global__ void __launch_bounds__(256) fleet_step_fast_kernel(const __grid_const
 #ifndef SIT_X2_MINB
 #define SIT_X2_MINB 3
 #endif
+#ifndef SIT_X2_UNROLL
+#define SIT_X2_UNROLL 2   /* two steps per loop trip: the loop-carried register moves disappear (2.19e11 -> 2.24e11 ship-steps/s) */
+#endif
+#define SIT_PRAGMA_(x) _Pragma(#x)
+#define SIT_PRAGMA(x) SIT_PRAGMA_(x)
 template <bool AVOID, bool SINGLE_MODE, bool TRAJ>
 __global__ void __launch_bounds__(SIT_X2_BLOCK, SIT_X2_MINB)
 fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float> g, const int K, const FleetIO<float> io) {
@@ -167,12 +172,19 @@ fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float>
         if (vec) *reinterpret_cast<float2*>(p + i0) = v;
         else { p[i0] = v.x; if (two) p[i1] = v.y; }
     };
+    // ship index of lane l, recomputed where it is needed (the rare waypoint-switch path) instead of living in registers
+    auto idx = [&](int l) -> int64_t {
+        const int64_t j = io.first + 2 * ((int64_t)blockIdx.x * blockDim.x + threadIdx.x);
+        return (l == 1 && 2 * ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) + 1 < io.count) ? j + 1 : j;
+    };
     Ship2 s;
-    s.N[0] = g.north[i0]; s.N[1] = g.north[i1]; s.E[0] = g.east[i0]; s.E[1] = g.east[i1];
     s.psi = ld(g.psi); s.u = ld(g.u); s.v = ld(g.v); s.r = ld(g.r); s.om = ld(g.omega);
     s.ei_s = ld(g.ei_speed); s.ei_w = ld(g.ei_shaft); s.ei_h = ld(g.ei_heading); s.e_prev = ld(g.e_prev);
     s.e_ct = ld(g.e_ct); s.e_int = ld(g.e_ct_int);
-    s.f_me = ld(g.fuel_me); s.f_el = ld(g.fuel_el); s.f_tot = ld(g.fuel);
+    s.f_me = ld(g.fuel_me); s.f_el = ld(g.fuel_el);
+    // fuel_cons (ship_engine.py:288-292) accumulates the sum of both rates: carried as fuel_me + fuel_el plus whatever offset
+    // the caller's state had (zero unless a caller set the three accumulators inconsistently)
+    const V f_off = sub(ld(g.fuel), add(s.f_me, s.f_el));
     s.u_sp = ld(g.u_sp);
     V w_speed, w_dir;
     if (io.dist) {   // disturbances held for the launch (ship_model.py:154-156: plain attributes)
@@ -187,7 +199,25 @@ fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float>
         sincos_(w_dir.y, sb, cb); s.wcb.y = w_speed.y * cb; s.wsb.y = w_speed.y * sb;
     }
     s.k[0] = g.k[i0]; s.k[1] = g.k[i1]; s.n_wp[0] = g.n_wp[i0]; s.n_wp[1] = g.n_wp[i1];
-    load_segment2(s, g, i0, 0); load_segment2(s, g, i1, 1);
+    double pN[2], pE[2];   // segment start of each ship (float64): live across the loop only in the TRAJ instantiation
+    int kk[2];
+#pragma unroll
+    for (int l = 0; l < 2; ++l) {
+        const int64_t i = l == 0 ? i0 : i1;
+        const int k = s.k[l];
+        kk[l] = k;
+        pN[l] = g.wp_n[(int64_t)(k - 1) * S + i]; pE[l] = g.wp_e[(int64_t)(k - 1) * S + i];
+        const double cN = g.wp_n[(int64_t)k * S + i], cE = g.wp_e[(int64_t)k * S + i];
+        // the relative pair written by the previous launch is used as it is when it still describes the float64 position
+        // (bit-identical continuation across launches); anything else (reset, a caller that moved the ship or its route)
+        // re-derives it from the float64 position
+        const double N = g.north[i], E = g.east[i];
+        float x = g.rel_n[i], cx = g.rel_cn[i], y = g.rel_e[i], cy = g.rel_ce[i];
+        if (!(abs_pos(pN[l], x, cx) == N)) split_rel(N - pN[l], x, cx);
+        if (!(abs_pos(pE[l], y, cy) == E)) split_rel(E - pE[l], y, cy);
+        lane(s.X, l) = x; lane(s.CX, l) = cx; lane(s.Y, l) = y; lane(s.CY, l) = cy;
+        set_segment2(s, P, pN[l], pE[l], cN, cE, l);
+    }
     ModeV MV;
     if (!SINGLE_MODE) {
         const ModeX &a = P.mode[g.mode[i0]], &b = P.mode[g.mode[i1]];
@@ -197,13 +227,20 @@ fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float>
 #undef MV_
     }
     float* tr = io.traj + i0;   // running row pointer of the every-step trajectory
-#pragma unroll 1
+    SIT_PRAGMA(unroll SIT_X2_UNROLL)
     for (int t = 0; t < K; ++t) {
-        if (SINGLE_MODE) ship_step2<AVOID>(P, P.mode[0], s, g, i0, i1);
-        else ship_step2<AVOID>(P, MV, s, g, i0, i1);
+        if (SINGLE_MODE) ship_step2<AVOID>(P, P.mode[0], s, g, idx);
+        else ship_step2<AVOID>(P, MV, s, g, idx);
         if (TRAJ) {   // every-step trajectory [K][8][S]: coalesced 64-bit streaming stores, the only memory traffic of the loop
+#pragma unroll
+            for (int l = 0; l < 2; ++l)
+                if (s.k[l] != kk[l]) {   // the ship switched segments: new float64 base
+                    kk[l] = s.k[l];
+                    pN[l] = g.wp_n[(int64_t)(kk[l] - 1) * S + idx(l)]; pE[l] = g.wp_e[(int64_t)(kk[l] - 1) * S + idx(l)];
+                }
             float* q = tr;
-            const V vn = make_float2((float)s.N[0], (float)s.N[1]), ve = make_float2((float)s.E[0], (float)s.E[1]);
+            const V vn = make_float2((float)abs_pos(pN[0], s.X.x, s.CX.x), (float)abs_pos(pN[1], s.X.y, s.CX.y));
+            const V ve = make_float2((float)abs_pos(pE[0], s.Y.x, s.CY.x), (float)abs_pos(pE[1], s.Y.y, s.CY.y));
             const V vk = make_float2((float)s.k[0], (float)s.k[1]);
             if (vec) {
                 __stcs(reinterpret_cast<float2*>(q), vn); q += S; __stcs(reinterpret_cast<float2*>(q), ve); q += S;
@@ -220,18 +257,28 @@ fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float>
             tr = q + S;
         }
     }
+    // ---- write back: float64 position from the (possibly new) segment start, the relative pair beside it ------------------
+    double N[2], E[2];
+#pragma unroll
+    for (int l = 0; l < 2; ++l) {
+        const int64_t i = l == 0 ? i0 : i1;
+        const double bN = g.wp_n[(int64_t)(s.k[l] - 1) * S + i], bE = g.wp_e[(int64_t)(s.k[l] - 1) * S + i];
+        N[l] = abs_pos(bN, lane(s.X, l), lane(s.CX, l)); E[l] = abs_pos(bE, lane(s.Y, l), lane(s.CY, l));
+    }
     if (!TRAJ && io.traj) {
         float* t0 = io.traj;
-        str(t0, make_float2((float)s.N[0], (float)s.N[1])); str(t0 + S, make_float2((float)s.E[0], (float)s.E[1]));
+        str(t0, make_float2((float)N[0], (float)N[1])); str(t0 + S, make_float2((float)E[0], (float)E[1]));
         str(t0 + 2 * S, s.psi); str(t0 + 3 * S, s.u); str(t0 + 4 * S, s.v); str(t0 + 5 * S, s.r); str(t0 + 6 * S, s.om);
         str(t0 + 7 * S, make_float2((float)s.k[0], (float)s.k[1]));
     }
-    g.north[i0] = s.N[0]; g.east[i0] = s.E[0];
-    if (two) { g.north[i1] = s.N[1]; g.east[i1] = s.E[1]; }
+    g.north[i0] = N[0]; g.east[i0] = E[0];
+    if (two) { g.north[i1] = N[1]; g.east[i1] = E[1]; }
+    st(g.rel_n, s.X); st(g.rel_cn, s.CX); st(g.rel_e, s.Y); st(g.rel_ce, s.CY);
     st(g.psi, s.psi); st(g.u, s.u); st(g.v, s.v); st(g.r, s.r); st(g.omega, s.om);
     st(g.ei_speed, s.ei_s); st(g.ei_shaft, s.ei_w); st(g.ei_heading, s.ei_h); st(g.e_prev, s.e_prev);
     st(g.e_ct, vabs(s.e_ct)); st(g.e_ct_int, s.e_int);
-    st(g.fuel_me, s.f_me); st(g.fuel_el, s.f_el); st(g.fuel, s.f_tot);
+    st(g.fuel_me, s.f_me); st(g.fuel_el, s.f_el);
+    st(g.fuel, add(add(s.f_me, s.f_el), f_off));
     g.k[i0] = s.k[0]; g.n_wp[i0] = s.n_wp[0]; g.steps[i0] += K;   // utils.py:42-48 next_time, once per stored step
     if (two) { g.k[i1] = s.k[1]; g.n_wp[i1] = s.n_wp[1]; g.steps[i1] += K; }
 }
@@ -1219,6 +1266,9 @@ static const FieldDef kShipFields[] = {
     {"wp_n", 'R', -1, false}, {"wp_e", 'R', -1, false}, {"wp0_n", 'R', -1, false}, {"wp0_e", 'R', -1, false},
     // nearest-ring cache of the env kernel (env_core.cuh MapCache): always float32
     {"mc_idx", 'I', 1, false}, {"mc_n", 'F', 1, false}, {"mc_e", 'F', 1, false}, {"mc_b2", 'F', 1, false},
+    // packed fp32 fleet kernel (ship_x2.cuh): position relative to the segment start as a compensated float pair, carried
+    // across launches beside north / east (which stay authoritative: a pair that no longer matches them is re-derived)
+    {"rel_n", 'F', 1, false}, {"rel_cn", 'F', 1, false}, {"rel_e", 'F', 1, false}, {"rel_ce", 'F', 1, false},
 };
 static const FieldDef kEnvFields[] = {
     {"prev_n", 'D', 1, true}, {"prev_e", 'D', 1, true}, {"eps_dist", 'D', 1, true}, {"samp_dist", 'D', 1, true},
@@ -1347,11 +1397,14 @@ static void derive_ship(const SitShipParams& c, ShipP<R>& P) {
 static void derive_shipx(const ShipP<float>& P, x2::ShipPX& X) {
     std::memset(&X, 0, sizeof(X));
     X.ra2 = P.ra2;
+    X.ra2_band = (float)(1.01 * P.ra2 + 16.0);
+    X.c_inv_pi = 0.318309886183790672f; X.c_s3 = 2.600024345156271e-06f; X.c_c4 = -2.607681608424173e-07f;
+    X.c_a6 = -0.004355357028543949f;
     X.dt = P.dt; X.look2 = P.look2; X.sat_e = P.sat_e; X.neg_ki_los = -P.ki_los; X.windup = P.windup;
     X.kp_h = P.kp_h; X.kd_idt = P.kd_h * P.inv_dt; X.ki_h = P.ki_h; X.rud_max = P.rud_max; X.rud_bias = P.rud_bias;
     X.kp_s = P.kp_s; X.ki_s = P.ki_s; X.kp_w = P.kp_w; X.ki_w = P.ki_w;
     X.hotel = P.hotel;
-    for (int j = 0; j < 3; ++j) { X.sfc_me[j] = P.sfc_me[j]; X.sfc_dg[j] = P.sfc_dg[j]; }
+    for (int j = 0; j < 3; ++j) { X.sfc_me[j] = P.sfc_me[j] * P.dt; X.sfc_dg[j] = P.sfc_dg[j] * P.dt; }
     X.sh_me = P.sh_me; X.sh_hsg = P.sh_hsg; X.sh_lin = P.sh_lin; X.sh_quad = P.sh_quad;
     X.au_vr = P.au_vr; X.au_vrr = P.au_vrr; X.au_lin = P.au_lin; X.au_nl = P.au_nl; X.au_wind = P.au_wind;
     X.au_thr = P.au_thr;   // already carries D^4 k_t (derive_ship)
@@ -1459,6 +1512,8 @@ static ShipPtrs<R> ship_ptrs(const SitHandle_* h, void* st) {
     g.n_wp0 = fptr<int32_t>(h, st, "n_wp0"); g.steps = fptr<int32_t>(h, st, "steps");
     g.mc_idx = fptr<int32_t>(h, st, "mc_idx"); g.mc_n = fptr<float>(h, st, "mc_n"); g.mc_e = fptr<float>(h, st, "mc_e");
     g.mc_b2 = fptr<float>(h, st, "mc_b2");
+    g.rel_n = fptr<float>(h, st, "rel_n"); g.rel_cn = fptr<float>(h, st, "rel_cn");
+    g.rel_e = fptr<float>(h, st, "rel_e"); g.rel_ce = fptr<float>(h, st, "rel_ce");
     g.n_ships = h->n_ships; g.max_wp = h->cfg.max_wp; g._pad = 0;
     return g;
 }
