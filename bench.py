@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--ships-per-gpu", type=int, default=1 << 20)
     ap.add_argument("--k-inner", type=int, default=256)
     ap.add_argument("--max-wp", type=int, default=8)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak (default): --ships-per-gpu ships on every GPU; strong: --ships-per-gpu ships IN TOTAL, sharded")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the e2e / HBM trajectory / peak legs (profiling runs)")
     return ap.parse_args()
@@ -119,25 +121,60 @@ def calibrate_cpu_sample(k_inner, max_wp, per_step_s):
     return max(1024, min(1 << 20, (n // 1024) * 1024))
 
 
+def python_reference_rate(args, steps, warmup, ships_per_proc=4):
+    """The reference's OWN Python simulator (oracle/_ref staged by oracle/stage_ref.py, or /root/reference) on all host
+    cores: P processes x ships_per_proc independent ships of the benchmark workload.  None when the files are absent."""
+    from oracle import ref_timing as rt
+    if not rt.available():
+        return None
+    r = rt.time_reference(procs=0, ships_per_proc=ships_per_proc, k_inner=args.k_inner, steps=steps, warmup=warmup,
+                          max_wp=args.max_wp, seed=SEED)
+    r["sample"] = (f"{r['cores']} processes x {ships_per_proc} ships x {args.k_inner} steps per bench step x {steps} steps "
+                   f"(bounded sample of the {args.ships_per_gpu}-ship fleet), the reference's own Python simulator "
+                   f"(ShipModelAST + controllers, MSRL_env_ex.py:346-398 order), Python {r['python']}, numpy {r['numpy']}, "
+                   f"{r['cpu_model']}")
+    return r
+
+
 def run_reference(args, rank, world):
+    """CPU arm.  Times the reference's own Python simulator when its files are present (staged under oracle/_ref by
+    __graft_entry__.build(); kind "reference"), else the float64 C port of the same step (kind "port").  The port's rate
+    is reported beside it either way: it is ~10^3 x faster per core than the Python and is the conservative baseline."""
     if rank != 0:
         return
     wu = min(args.warmup, 2)
-    n = calibrate_cpu_sample(args.k_inner, args.max_wp, per_step_s=60.0 / (args.steps + wu))   # whole run ~1 minute
+    pr = python_reference_rate(args, args.steps, max(1, wu))
+    n = calibrate_cpu_sample(args.k_inner, args.max_wp, per_step_s=(20.0 if pr else 60.0) / (args.steps + wu))
     rate, cores, total = cpu_ship_steps_per_s(n, args.k_inner, args.steps, wu, args.max_wp, SEED)
-    sample = f"{n} ships x {args.k_inner} steps per bench step (bounded sample of the {args.ships_per_gpu}-ship fleet), float64 C port of the reference step, OpenMP"
+    port = {"value": rate, "unit": "ship-steps/s", "cores": cores, "kind": "port", "ms_per_step": 1e3 * total / args.steps,
+            "sample": f"{n} ships x {args.k_inner} steps per bench step (bounded sample of the {args.ships_per_gpu}-ship "
+                      f"fleet), float64 C port of the reference step (oracle/ship_oracle.c), OpenMP"}
+    if pr:
+        value, ms = pr["value"], 1e3 * pr["wall_s"] / args.steps
+        base = {"value": value, "unit": "ship-steps/s", "cores": pr["cores"], "kind": "reference", "sample": pr["sample"],
+                "state_finite": pr["finite"], "port": port}
+        note = ("reference arm = the reference's own Python simulator on every host core (one process per core: it has no "
+                "batching or threading of its own); `cpu_baseline.port` is the float64 C restatement of the same step on the "
+                "same cores")
+    else:
+        value, ms, base = rate, port["ms_per_step"], port
+        note = ("oracle/_ref is absent (the reference's Python files were not staged): this arm times the plain-C float64 "
+                "restatement (oracle/ship_oracle.c), ~10^3 x faster per core than the reference's own Python")
     line = {
-        "impl": "reference", "metric": METRIC, "value": rate, "unit": "ship-steps/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "ship-steps/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args),
-        "cpu_baseline": {"value": rate, "unit": "ship-steps/s", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": rate, "unit": "ship-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-        "note": "the reference is pure Python and cannot travel to the GPU box; this arm times the plain-C float64 "
-                "restatement (oracle/ship_oracle.c), which is ~10^3x faster per core than the reference's own Python",
+        "config": workload_config(args), "cpu_baseline": base,
+        "e2e": {"value": value, "unit": "ship-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "note": note,
     }
     print(json.dumps(line), flush=True)
+
+
+def shard_range(n, rank, world):
+    """Contiguous shard [lo, hi) of n units for `rank` of `world` (the partition of SURVEY 8e)."""
+    per = (n + world - 1) // world
+    return min(n, rank * per), min(n, (rank + 1) * per)
 
 
 def workload_config(args):
@@ -219,79 +256,120 @@ def run_b200(args, rank, world, local_rank):
         torch.cuda.synchronize()
 
     args.warmup = max(args.warmup, 3)                      # timing rule: at least 3 untimed warm-up steps
-    S, KI = args.ships_per_gpu, args.k_inner
-    rng = np.random.default_rng(SEED + 1000 * rank)       # global ship ids differ per rank: independent shards
-    n_wp, wp_n, wp_e, psi0, u_sp = make_routes(S, args.max_wp, rng)
-    sm, tc, ap = sit.default_ship([(0, 0), (1000, 1000)], 0.0)
-    fleet = sit.ShipFleet(sm, tc, ap, 8.0, n_ships=S, device=dev, precision="fp32", max_wp=args.max_wp)
-    fleet.set_routes(torch.from_numpy(wp_n).to(dev), torch.from_numpy(wp_e).to(dev), torch.from_numpy(n_wp).to(dev))
-    fleet.f["north"].copy_(torch.from_numpy(wp_n[0].astype(np.float64))); fleet.f["east"].copy_(torch.from_numpy(wp_e[0].astype(np.float64)))
-    fleet.f["psi"].copy_(torch.from_numpy(psi0)); fleet.f["u_sp"].copy_(torch.from_numpy(u_sp))
-    fleet.capture_init()
-    n_ring = 8                                             # 8 x 16 MB of disturbances, resident in HBM
-    ring_h = [torch.from_numpy(make_dist(S, rng)).pin_memory() for _ in range(n_ring)]
-    ring_d = [t.to(dev) for t in ring_h]
-    pose_h = torch.empty((8, S), dtype=torch.float32).pin_memory()
-    snapshot = fleet.state_dict()
+    KI = args.k_inner
+    POSE_CH = ("north", "east", "psi", "u")                # what the reference's caller reads between steps (MSRL_env_ex.py:255-278)
 
-    # ---- device-resident timed region -----------------------------------------------------------------------------
+    def fleet_leg(S, seed, e2e=True):
+        """Device-resident timed region + (optionally) the same through the host-buffer entry point for a fleet of S ships
+        on this rank.  Returns a dict with max-over-ranks times."""
+        rng = np.random.default_rng(seed)
+        n_wp, wp_n, wp_e, psi0, u_sp = make_routes(S, args.max_wp, rng)
+        sm, tc, ap = sit.default_ship([(0, 0), (1000, 1000)], 0.0)
+        fleet = sit.ShipFleet(sm, tc, ap, 8.0, n_ships=S, device=dev, precision="fp32", max_wp=args.max_wp)
+        fleet.set_routes(torch.from_numpy(wp_n).to(dev), torch.from_numpy(wp_e).to(dev), torch.from_numpy(n_wp).to(dev))
+        fleet.f["north"].copy_(torch.from_numpy(wp_n[0].astype(np.float64))); fleet.f["east"].copy_(torch.from_numpy(wp_e[0].astype(np.float64)))
+        fleet.f["psi"].copy_(torch.from_numpy(psi0)); fleet.f["u_sp"].copy_(torch.from_numpy(u_sp))
+        fleet.capture_init()
+        n_ring = 8                                         # 8 x 16 MB of disturbances, resident in HBM
+        ring_h = [torch.from_numpy(make_dist(S, rng)).pin_memory() for _ in range(n_ring)]
+        ring_d = [t.to(dev) for t in ring_h]
+        pose_h = torch.empty((len(POSE_CH), S), dtype=torch.float32).pin_memory()
+        k8_h = torch.empty(S, dtype=torch.int8).pin_memory()
+        snapshot = fleet.state_dict()
+        out = {"S": S}
+        for w in range(args.warmup):
+            fleet.step(KI, dist=ring_d[w % n_ring])
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = fleet.launches
+        t_wall0 = time.perf_counter()
+        ev0.record()
+        for k in range(args.steps):
+            fleet.step(KI, dist=ring_d[(args.warmup + k) % n_ring])
+        ev1.record()
+        barrier()
+        out["wall_s"] = time.perf_counter() - t_wall0
+        out["launches"] = fleet.launches - l0
+        tmax = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        out["ms"] = float(tmax.item())
+        out["finite"] = bool(torch.isfinite(fleet.f["north"]).all() and torch.isfinite(fleet.f["u"]).all())
+        out["stats"] = torch.stack([fleet.f["steps"].sum().double(), fleet.f["k"].double().mean(), fleet.f["u"].double().mean()])
+        if e2e:
+            # end to end through the C-ABI host-buffer entry point: pinned host disturbances in, the channels the caller
+            # reads (N, E, psi, u) + the waypoint index as int8 out, every step, copies inside the timed region
+            fleet.load_state_dict(snapshot)
+            for w in range(min(args.warmup, 3)):
+                fleet.step_host(KI, ring_h[w % n_ring], pose_h, channels=POSE_CH, k8_host=k8_h)
+            barrier()
+            ev0.record()
+            for k in range(args.steps):
+                fleet.step_host(KI, ring_h[(args.warmup + k) % n_ring], pose_h, channels=POSE_CH, k8_host=k8_h)
+            ev1.record()
+            barrier()
+            e2e_ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+            out["e2e_ms"] = float(e2e_ms.item())
+            out["h2d"] = int(ring_h[0].numel() * 4)
+            out["d2h"] = int(pose_h.numel() * 4 + k8_h.numel())
+            out["e2e_finite"] = bool(torch.isfinite(pose_h).all())
+        fleet.close()
+        return out
+
+    # ---- headline: weak scaling, ships_per_gpu ships on every rank ---------------------------------------------------
+    S = args.ships_per_gpu
+    strong_total = args.ships_per_gpu                      # BASELINE config 3: 1 048 576 ships IN TOTAL, sharded over the GPUs
+    if args.scaling == "strong":
+        lo, hi = shard_range(strong_total, rank, world)
+        S = hi - lo
     clocks = ClockSampler(local_rank)
     clocks.start()
     t_load0 = time.perf_counter()
-    for w in range(args.warmup):
-        fleet.step(KI, dist=ring_d[w % n_ring])
-    barrier()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    l0 = fleet.launches
-    t_wall0 = time.perf_counter()
-    ev0.record()
-    for k in range(args.steps):
-        fleet.step(KI, dist=ring_d[(args.warmup + k) % n_ring])
-    ev1.record()
-    barrier()
-    t_wall1 = time.perf_counter()
-    launches = fleet.launches - l0
-    ms = ev0.elapsed_time(ev1)
-    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    ms_max = float(tmax.item())
-    finite = bool(torch.isfinite(fleet.f["north"]).all() and torch.isfinite(fleet.f["u"]).all())
-    value = world * S * KI * args.steps / (ms_max * 1e-3)
-
-    line = {"metric": METRIC, "value": value, "unit": "ship-steps/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
-            "gpu_launches": launches, "state_finite": finite}
-
-    # ---- end-to-end through the C-ABI host-buffer entry point (H2D + kernel + D2H every step) -----------------------
-    if not args.no_extras:
-        fleet.load_state_dict(snapshot)
-        for w in range(min(args.warmup, 3)):
-            fleet.step_host(KI, ring_h[w % n_ring], pose_h)
-        barrier()
-        t0 = time.perf_counter()
-        ev0.record()
-        for k in range(args.steps):
-            fleet.step_host(KI, ring_h[(args.warmup + k) % n_ring], pose_h)
-        ev1.record()
-        barrier()
-        e2e_ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
-        line["e2e"] = {"value": world * S * KI * args.steps / (float(e2e_ms.item()) * 1e-3), "unit": "ship-steps/s",
-                       "h2d_bytes_per_step": int(ring_h[0].numel() * 4), "d2h_bytes_per_step": int(pose_h.numel() * 4),
-                       "api": "ShipFleet.step_host -> sit_fleet_step_host (pinned host buffers)"}
+    main = fleet_leg(S, SEED + 1000 * rank, e2e=not args.no_extras)   # global ship ids differ per rank: independent shards
     t_load1 = time.perf_counter()
     clocks.stop()
+    total_ships = strong_total if args.scaling == "strong" else world * S
+    value = total_ships * KI * args.steps / (main["ms"] * 1e-3)
+    ms_max, launches, finite = main["ms"], main["launches"], main["finite"]
+    cfg = workload_config(args)
+    if args.scaling == "strong":
+        cfg["ships_total"] = strong_total; cfg["ships_per_gpu"] = S
+    line = {"metric": METRIC, "value": value, "unit": "ship-steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": args.scaling,
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+            "gpu_launches": launches, "state_finite": finite}
+    if "e2e_ms" in main:
+        line["e2e"] = {"value": total_ships * KI * args.steps / (main["e2e_ms"] * 1e-3), "unit": "ship-steps/s",
+                       "h2d_bytes_per_step": main["h2d"], "d2h_bytes_per_step": main["d2h"],
+                       "api": "ShipFleet.step_host(channels=N,E,psi,u + int8 waypoint index) -> sit_fleet_step_host_sel "
+                              "(pinned host buffers, chunk pipeline)", "pose_finite": main["e2e_finite"]}
     # sampled over warm-up + timed region + the e2e loop (the same kernel under load throughout); the timed
     # region alone can be shorter than one nvidia-smi sampling period
     line["clocks"] = clocks.summary(t_load0, t_load1)
     line["clocks"]["window_s"] = t_load1 - t_load0
-    line["clocks"]["timed_region_s"] = t_wall1 - t_wall0
+    line["clocks"]["timed_region_s"] = main["wall_s"]
+
+    # ---- strong scaling beside it: the SAME 1 048 576-ship fleet cut into N shards (BASELINE config 3 as written) ----------
+    if not args.no_extras and args.scaling == "weak":
+        if world == 1:
+            line["strong"] = {"ships_total": S, "ships_per_gpu": S, "value": value, "ms_per_step": ms_max / args.steps,
+                              "e2e": line["e2e"]["value"], "note": "N = 1: the strong-scaling point is the headline itself"}
+        else:
+            lo, hi = shard_range(strong_total, rank, world)
+            st = fleet_leg(hi - lo, SEED + 1000 * rank + 500, e2e=True)
+            line["strong"] = {"ships_total": strong_total, "ships_per_gpu": hi - lo,
+                              "value": strong_total * KI * args.steps / (st["ms"] * 1e-3), "ms_per_step": st["ms"] / args.steps,
+                              "e2e": strong_total * KI * args.steps / (st["e2e_ms"] * 1e-3),
+                              "efficiency_vs_one_gpu_holding_the_whole_fleet": (ms_max / args.steps) / (world * st["ms"] / args.steps)
+                              if S == strong_total else None,
+                              "state_finite": st["finite"],
+                              "note": "one GPU advances the whole fleet in the headline's ms_per_step (same run, same "
+                                      "kernel); N GPUs each advance a 1/N shard in strong.ms_per_step"}
 
     # ---- rollout statistics gathered over NCCL (outside the step path) ------------------------------------------------
-    stats = torch.stack([fleet.f["steps"].sum().double(), fleet.f["k"].double().mean(), fleet.f["u"].double().mean()])
+    stats = main["stats"]
     if world > 1:
         gathered = [torch.empty_like(stats) for _ in range(world)]
         dist.all_gather(gathered, stats)
@@ -303,14 +381,19 @@ def run_b200(args, rank, world, local_rank):
         L = _lib.lib()
         tf, pms = C.c_double(), C.c_double()
         _lib.check(L.sit_measure_fma_peak(local_rank, _lib.F32, C.byref(tf), C.byref(pms)))
+        tf2 = C.c_double()
+        _lib.check(L.sit_measure_fma_peak(local_rank, 2, C.byref(tf2), None))      # the same chain as packed FFMA2
         per_gpu = value / world
         ach = per_gpu * F_SHIP / 1e12
         line["roofline"] = {"bound": "fp32", "achieved": ach, "peak": tf.value, "unit": "TFLOP/s", "frac": ach / tf.value,
+                            "peak_ffma2": tf2.value,
                             "traffic": ncu_traffic("fleet32") if (S == 1 << 20 and KI == 256) else None,
-                            "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r01_traffic.json)",
+                            "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/r02_traffic.json)",
+                            "kernel": "fleet_step_x2_kernel<AVOID=0, SINGLE_MODE=1, TRAJ=0> (packed f32x2, two ships per thread)",
                             "note": "CUDA-core FP32 pipe bound (no tensor-core or HBM roofline applies to the K-step kernel): "
                                     "achieved = ship-steps/s/GPU x 250 algorithmic FLOP; peak = FFMA chain measured live on this GPU "
-                                    "(sit_measure_fma_peak); kernel time = ms_per_step (one launch per step, CUDA events)"}
+                                    "(sit_measure_fma_peak; peak_ffma2 = the same chain as packed FFMA2: the same FLOP rate, "
+                                    "half the issue slots); kernel time = ms_per_step (one launch per step, CUDA events)"}
         # ---- trajectory write-out mode (BASELINE config 2 style, fp64): HBM-write bound ------------------------------
         line["roofline_hbm"] = traj_roofline(sit, dev)
         line["roofline_hbm_fp32"] = traj_roofline(sit, dev, "fp32")
@@ -337,19 +420,25 @@ def run_b200(args, rank, world, local_rank):
             # the caching allocator gets its blocks on the first call (in a training loop the gather recurs every segment)
             del_me = ro_mod.gather_replay(rows); del del_me
         barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         allrows = ro_mod.gather_replay(rows)
         tot_stats = ro_mod.reduce_stats(smp_keep.env.stats)
         ev1.record()
         barrier()
-        agg = torch.tensor([rl["samples"], rl["env_steps"], rows.shape[0]], dtype=torch.float64, device=dev)
+        agg = torch.tensor([rl["samples"], rl["env_steps"], rows.shape[0], rl["resamples"], rl["episodes"], rl["launches"]],
+                           dtype=torch.float64, device=dev)
         tm = torch.tensor([rl["ms_total"], ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(agg, op=dist.ReduceOp.SUM)
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         ids = allrows[:, 23].contiguous().view(torch.int32)
         rl.update({"n_gpus": world, "envs": world * B_roll, "envs_per_gpu": B_roll, "samples": int(agg[0].item()),
-                   "env_steps": int(agg[1].item()), "ms_total": float(tm[0].item()), "gather_ms": float(tm[1].item()),
+                   "env_steps": int(agg[1].item()), "resamples": int(agg[3].item()), "episodes": int(agg[4].item()),
+                   "launches": int(agg[5].item()),
+                   "lane_utilisation": float(agg[1].item()) / (world * B_roll * rl["k_per_launch"] * rl["iterations"]),
+                   "fields": "samples, env_steps, resamples, episodes, launches are sums over all ranks",
+                   "ms_total": float(tm[0].item()), "gather_ms": float(tm[1].item()),
                    "gathered_rows": int(allrows.shape[0]), "gathered_bytes": int(allrows.numel() * 4),
                    "gather_complete": bool(allrows.shape[0] == int(agg[2].item()) and int(ids.min()) >= 0
                                            and int(ids.max()) < world * B_roll and int(tot_stats[13].item()) > 0),
@@ -379,11 +468,18 @@ def run_b200(args, rank, world, local_rank):
                 "collective": "one all_reduce of 16 counters after the run" if world > 1 else "none (one rank)"}
             line["rollout"] = rl
             line["learner"] = learner_leg(sit, dev, smp_keep)
-    if rank == 0 and not args.no_cpu_baseline and not args.no_extras:
-        n = calibrate_cpu_sample(KI, args.max_wp, per_step_s=4.0)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not args.no_extras:
+        # N = 1 only: with several ranks the others would sit in a barrier on the same host cores
+        n = calibrate_cpu_sample(KI, args.max_wp, per_step_s=2.5)
         rate, cores, total = cpu_ship_steps_per_s(n, KI, 4, 1, args.max_wp, SEED)
-        line["cpu_baseline"] = {"value": rate, "unit": "ship-steps/s", "cores": cores, "kind": "port",
-                                "sample": f"{n} ships x {KI} steps x 4 (oracle/ship_oracle.c float64, OpenMP, {total:.1f} s)"}
+        port = {"value": rate, "unit": "ship-steps/s", "cores": cores, "kind": "port",
+                "sample": f"{n} ships x {KI} steps x 4 (oracle/ship_oracle.c float64, OpenMP, {total:.1f} s)"}
+        pr = python_reference_rate(args, steps=4, warmup=1)
+        if pr:
+            line["cpu_baseline"] = {"value": pr["value"], "unit": "ship-steps/s", "cores": pr["cores"], "kind": "reference",
+                                    "sample": pr["sample"], "port": port}
+        else:
+            line["cpu_baseline"] = port
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -391,11 +487,14 @@ def run_b200(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+TRAFFIC_FILE = "r02_traffic.json" if os.path.exists(os.path.join(ROOT, "profiles", "r02_traffic.json")) else "r01_traffic.json"
+
+
 def ncu_traffic(label):
     """DRAM bytes per launch of the kernel `label` from the committed `ncu --set full` capture of the same workload
     (profiles/r01_traffic.json, written by tools/ncu_traffic.py), or None."""
     try:
-        return json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))[label]["dram_bytes_per_launch"]
+        return json.load(open(os.path.join(ROOT, "profiles", TRAFFIC_FILE)))[label]["dram_bytes_per_launch"]
     except Exception:
         return None
 
@@ -431,7 +530,7 @@ def traj_roofline(sit, dev, precision="fp64"):
         pass
     return {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
             "traffic": ncu_traffic("traj64" if f64 else "traj32"), "algorithmic_bytes_per_launch": bytes_per_step * S * K,
-            "kernel": f"fleet_step_fast_kernel<{'double' if f64 else 'float'}, TRAJ> (every-step trajectory write-out)", "ships": S, "k": K,
+            "kernel": ("fleet_step_fast_kernel<double, TRAJ>" if f64 else "fleet_step_x2_kernel<TRAJ> (packed f32x2)") + " (every-step trajectory write-out)", "ships": S, "k": K,
             "ms_per_launch": ms, "ship_steps_per_s": S * K / (ms * 1e-3), "peak_source": src,
             "note": f"algorithmic bytes = {bytes_per_step} B written per ship-step (8 {precision} channels); output ~1.2 GB per launch > L2"}
 

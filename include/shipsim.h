@@ -153,6 +153,13 @@ int sit_fleet_step_k(SitHandle h, void* state, int32_t K, const SitFleetIO* io, 
  * (N, E, psi, u, v, r, omega, k) of the LAST step is copied out to pose_h [SIT_N_TRAJ][n_ships]; synchronises. */
 int sit_fleet_step_host(SitHandle h, void* state, int32_t K, const void* dist_h, int32_t avoid, void* pose_h,
                         void* stream);
+/* Same, copying out only what the caller reads: pose_h receives the channels whose bit is set in channel_mask
+ * (bit c = channel c of N, E, psi, u, v, r, omega, k), packed as [popcount(mask)][n_ships] rows in channel order;
+ * k8_h (may be NULL) receives the waypoint index as int8 [n_ships] -- one byte per ship instead of a real.  The
+ * reference's callers read the pose and speed of a ship between steps (ship_model.north / east / yaw_angle /
+ * forward_speed, MSRL_env_ex.py:255-278): mask 0x0f + k8_h is 17 bytes per fp32 ship instead of 32. */
+int sit_fleet_step_host_sel(SitHandle h, void* state, int32_t K, const void* dist_h, int32_t avoid, void* pose_h,
+                            int32_t channel_mask, int8_t* k8_h, void* stream);
 /* snapshot pose / environment / route as the values reset() restores (the deepcopy at
  * MSRL_env_ex.py:55-56 and the init_* attributes set in ship_model.py:132-157) */
 int sit_capture_init(SitHandle h, void* state, void* stream);

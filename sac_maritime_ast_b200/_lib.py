@@ -100,7 +100,7 @@ POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
 POLICY_TC_BF16 = 0x100
 RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_N = 0, 1, 2, 3, 8
 
-EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host",
+EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host", "sit_fleet_step_host_sel",
            "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_group_count", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
            "sit_sac_create", "sit_sac_destroy", "sit_sac_workspace_bytes", "sit_sac_field", "sit_sac_init", "sit_sac_policy",
            "sit_sac_update",
@@ -131,6 +131,7 @@ def lib():
     L.sit_n_ships.restype = I64
     L.sit_fleet_step_k.argtypes = [vp, vp, I32, P(SitFleetIO), vp]
     L.sit_fleet_step_host.argtypes = [vp, vp, I32, vp, I32, vp, vp]
+    L.sit_fleet_step_host_sel.argtypes = [vp, vp, I32, vp, I32, vp, I32, vp, vp]
     L.sit_capture_init.argtypes = [vp, vp, vp]
     L.sit_reset.argtypes = [vp, vp, vp, I32, vp]
     L.sit_env_init_step.argtypes = [vp, vp, vp, vp]

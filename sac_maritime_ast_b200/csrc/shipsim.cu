@@ -23,6 +23,7 @@ template <typename R>
 struct FleetIO {
     const R* dist; int32_t dist_steps; int32_t avoid; int32_t store; int32_t traj_steps;
     R* traj; R* log27; R* cmd;
+    int8_t* k8;              // optional: waypoint index of the last step as int8 [n_ships] (host-buffer path)
     int64_t first, count;    // ship sub-range [first, first + count) of this launch (the host-buffer pipeline launches chunks)
 };
 
@@ -135,6 +136,7 @@ __global__ void __launch_bounds__(256) fleet_step_fast_kernel(const __grid_const
         tr[0] = (R)s.N; tr[S] = (R)s.E; tr[2 * S] = s.psi; tr[3 * S] = s.u;
         tr[4 * S] = s.v; tr[5 * S] = s.r; tr[6 * S] = s.om; tr[7 * S] = (R)s.k;
     }
+    if (io.k8) io.k8[i] = (int8_t)s.k;
     store_ship(s, g, i);
 }
 
@@ -271,6 +273,7 @@ fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float>
         str(t0 + 2 * S, s.psi); str(t0 + 3 * S, s.u); str(t0 + 4 * S, s.v); str(t0 + 5 * S, s.r); str(t0 + 6 * S, s.om);
         str(t0 + 7 * S, make_float2((float)s.k[0], (float)s.k[1]));
     }
+    if (io.k8) { io.k8[i0] = (int8_t)s.k[0]; if (two) io.k8[i1] = (int8_t)s.k[1]; }
     g.north[i0] = N[0]; g.east[i0] = E[0];
     if (two) { g.north[i1] = N[1]; g.east[i1] = E[1]; }
     st(g.rel_n, s.X); st(g.rel_cn, s.CX); st(g.rel_e, s.Y); st(g.rel_ce, s.CY);
@@ -1656,7 +1659,21 @@ bool fleet_x2<float>(SitHandle h, const ShipPtrs<float>& g, int K, const FleetIO
     if (!(traj_all || fast) || (k.first & 1)) return false;
     static const bool off = std::getenv("SIT_NO_X2") != nullptr;   // A/B switch for profiling runs
     if (off) return false;
-    const int block = SIT_X2_BLOCK, grid = (int)(((k.count + 1) / 2 + block - 1) / block);
+    // CTA size: 128 threads (256 ships) for fleets of many waves; a shard of a strong-scaled fleet (131 072 ships on 148 SMs)
+    // is a single wave, where the SM holding one CTA more than the others sets the time -- smaller CTAs even it out
+    // (per-SM load = ceil(CTAs / SMs) x CTA size: 512 ships at 128 threads, 448 at 64 for 131 072 ships; ideal 442.8)
+    static const int env_block = std::getenv("SIT_X2_BLOCK_RT") ? std::atoi(std::getenv("SIT_X2_BLOCK_RT")) : 0;
+    int block = SIT_X2_BLOCK;
+    const int64_t pairs = (k.count + 1) / 2;
+    if (env_block == 32 || env_block == 64 || env_block == 128) block = env_block;
+    else {
+        int64_t best = -1;
+        for (int b = SIT_X2_BLOCK; b >= 32; b >>= 1) {
+            const int64_t ctas = (pairs + b - 1) / b, load = (ctas + h->sm_count - 1) / h->sm_count * b;
+            if (best < 0 || load < best) { best = load; block = b; }
+        }
+    }
+    const int grid = (int)((pairs + block - 1) / block);
     const x2::ShipPX& P = h->px;
 #define X2_(A, M, T) fleet_step_x2_kernel<A, M, T><<<grid, block, 0, st>>>(P, g, K, k)
     if (traj_all) {
@@ -1672,10 +1689,10 @@ bool fleet_x2<float>(SitHandle h, const ShipPtrs<float>& g, int K, const FleetIO
 
 template <typename R>
 static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, cudaStream_t st, int64_t first = 0,
-                        int64_t count = -1) {
+                        int64_t count = -1, int8_t* k8 = nullptr) {
     FleetIO<R> k;
     std::memset(&k, 0, sizeof(k));
-    k.store = 1;
+    k.store = 1; k.k8 = k8;
     k.first = first; k.count = count < 0 ? h->n_ships : count;
     if (io) {
         k.dist = static_cast<const R*>(io->dist); k.dist_steps = io->dist_steps; k.avoid = io->avoid; k.store = io->store; k.traj_steps = io->traj_steps;
@@ -1745,14 +1762,41 @@ static int ensure_pol_scratch(SitHandle h, size_t total) {
     return SIT_OK;
 }
 
-int sit_fleet_step_host(SitHandle h, void* state, int32_t K, const void* dist_h, int32_t avoid, void* pose_h,
-                        void* stream) {
+// rows of pose_h selected by channel_mask, copied as runs of consecutive channels (one 2-D copy per run and chunk)
+static int copy_pose_rows(char* pose_h, const char* d_pose, int mask, size_t first, size_t cnt, size_t S, size_t rs,
+                          cudaStream_t st) {
+    int out_row = 0;
+    for (int c = 0; c < SIT_N_TRAJ;) {
+        if (!((mask >> c) & 1)) { ++c; continue; }
+        int run = 1;
+        while (c + run < SIT_N_TRAJ && ((mask >> (c + run)) & 1)) ++run;
+        CUDA_TRY(cudaMemcpy2DAsync(pose_h + ((size_t)out_row * S + first) * rs, S * rs, d_pose + ((size_t)c * S + first) * rs, S * rs,
+                                   cnt * rs, run, cudaMemcpyDeviceToHost, st));
+        out_row += run; c += run;
+    }
+    return SIT_OK;
+}
+
+// join the internal pipe streams back into the caller's stream (also on the error paths: the caller's stream must never
+// run ahead of work that was forked from it)
+static void join_pipes(SitHandle h, cudaStream_t st) {
+    for (int j = 0; j < SIT_PIPE; ++j) {
+        if (cudaEventRecord(h->pipe_done[j], h->pipe[j]) == cudaSuccess) cudaStreamWaitEvent(st, h->pipe_done[j], 0);
+    }
+}
+
+int sit_fleet_step_host_sel(SitHandle h, void* state, int32_t K, const void* dist_h, int32_t avoid, void* pose_h,
+                            int32_t channel_mask, int8_t* k8_h, void* stream) {
     if (!h || !state) return fail(SIT_E_INVALID, "null argument");
     if (h->cfg.kind != SIT_KIND_FLEET) return fail(SIT_E_KIND, "sit_fleet_step_host needs a SIT_KIND_FLEET handle");
+    if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
+    if (pose_h && (channel_mask & 0xff) == 0) return fail(SIT_E_INVALID, "channel_mask selects no channel");
+    channel_mask &= 0xff;
     CUDA_TRY(cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const size_t S = (size_t)h->n_ships, rs = h->cfg.precision == SIT_F64 ? 8 : 4;
-    const size_t o_dist = 0, o_pose = align_up(4 * S * rs, 256), total = o_pose + align_up(SIT_N_TRAJ * S * rs, 256);
+    const size_t o_dist = 0, o_pose = align_up(4 * S * rs, 256), o_k8 = o_pose + align_up(SIT_N_TRAJ * S * rs, 256),
+                 total = o_k8 + align_up(S, 256);
     int rc = ensure_scratch(h, total);
     if (rc) return rc;
     char* d = static_cast<char*>(h->d_scratch);
@@ -1760,46 +1804,53 @@ int sit_fleet_step_host(SitHandle h, void* state, int32_t K, const void* dist_h,
     std::memset(&io, 0, sizeof(io));
     io.dist = dist_h ? d + o_dist : nullptr; io.dist_steps = 1; io.avoid = avoid; io.store = 1;
     io.traj = pose_h ? d + o_pose : nullptr; io.traj_steps = 1;
+    int8_t* d_k8 = k8_h ? reinterpret_cast<int8_t*>(d + o_k8) : nullptr;
     // Large fleets: the ships are cut into chunks that travel through SIT_PIPE internal streams, so the H2D copy of
     // chunk c+1 and the D2H copy of chunk c-1 run on the two copy engines while chunk c computes (ships are independent,
     // so a chunk is a complete unit of work).  Small fleets: one copy-in, one launch, one copy-out on the caller's stream.
     static const int env_chunks = std::getenv("SIT_HOST_CHUNKS") ? std::atoi(std::getenv("SIT_HOST_CHUNKS")) : 0;
     const int64_t min_chunk = env_chunks > 0 ? 16384 : 65536;
     int n_chunks = (int)std::min<int64_t>(env_chunks > 0 ? env_chunks : 16, (int64_t)S / min_chunk);   // 4 / 8 / 16 / 32 chunks at 1 M ships: 1.40 / 1.49 / 1.54 / 1.39e11 ship-steps/s
-    if (n_chunks < 2 || (!dist_h && !pose_h)) {
+    if (n_chunks < 2 || (!dist_h && !pose_h && !k8_h)) {
         if (dist_h) CUDA_TRY(cudaMemcpyAsync(d + o_dist, dist_h, 4 * S * rs, cudaMemcpyHostToDevice, st));
-        rc = sit_fleet_step_k(h, state, K, &io, stream);
+        rc = h->cfg.precision == SIT_F64 ? fleet_step_t<double>(h, state, K, &io, st, 0, -1, d_k8)
+                                         : fleet_step_t<float>(h, state, K, &io, st, 0, -1, d_k8);
         if (rc) return rc;
-        if (pose_h) CUDA_TRY(cudaMemcpyAsync(pose_h, d + o_pose, SIT_N_TRAJ * S * rs, cudaMemcpyDeviceToHost, st));
+        if (pose_h && (rc = copy_pose_rows(static_cast<char*>(pose_h), d + o_pose, channel_mask, 0, S, S, rs, st))) return rc;
+        if (k8_h) CUDA_TRY(cudaMemcpyAsync(k8_h, d_k8, S, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
         return SIT_OK;
     }
-    if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
     if ((rc = ensure_pipe(h))) return rc;
     CUDA_TRY(cudaEventRecord(h->pipe_in, st));
     for (int j = 0; j < SIT_PIPE; ++j) CUDA_TRY(cudaStreamWaitEvent(h->pipe[j], h->pipe_in, 0));
     const int64_t chunk = ((int64_t)S / n_chunks + 255) / 256 * 256;
     const size_t pitch = S * rs;
     int c = 0;
-    for (int64_t first = 0; first < (int64_t)S; first += chunk, ++c) {
+    cudaError_t ce = cudaSuccess;
+    for (int64_t first = 0; first < (int64_t)S && !rc && ce == cudaSuccess; first += chunk, ++c) {
         const int64_t cnt = std::min<int64_t>(chunk, (int64_t)S - first);
         cudaStream_t ps = h->pipe[c % SIT_PIPE];
         if (dist_h)
-            CUDA_TRY(cudaMemcpy2DAsync(d + o_dist + first * rs, pitch, static_cast<const char*>(dist_h) + first * rs, pitch,
-                                       cnt * rs, 4, cudaMemcpyHostToDevice, ps));
-        rc = h->cfg.precision == SIT_F64 ? fleet_step_t<double>(h, state, K, &io, ps, first, cnt)
-                                         : fleet_step_t<float>(h, state, K, &io, ps, first, cnt);
-        if (rc) return rc;
-        if (pose_h)
-            CUDA_TRY(cudaMemcpy2DAsync(static_cast<char*>(pose_h) + first * rs, pitch, d + o_pose + first * rs, pitch,
-                                       cnt * rs, SIT_N_TRAJ, cudaMemcpyDeviceToHost, ps));
+            ce = cudaMemcpy2DAsync(d + o_dist + first * rs, pitch, static_cast<const char*>(dist_h) + first * rs, pitch,
+                                   cnt * rs, 4, cudaMemcpyHostToDevice, ps);
+        if (ce != cudaSuccess) break;
+        rc = h->cfg.precision == SIT_F64 ? fleet_step_t<double>(h, state, K, &io, ps, first, cnt, d_k8)
+                                         : fleet_step_t<float>(h, state, K, &io, ps, first, cnt, d_k8);
+        if (rc) break;
+        if (pose_h) rc = copy_pose_rows(static_cast<char*>(pose_h), d + o_pose, channel_mask, (size_t)first, (size_t)cnt, S, rs, ps);
+        if (!rc && k8_h) ce = cudaMemcpyAsync(k8_h + first, d_k8 + first, cnt, cudaMemcpyDeviceToHost, ps);
     }
-    for (int j = 0; j < SIT_PIPE; ++j) {
-        CUDA_TRY(cudaEventRecord(h->pipe_done[j], h->pipe[j]));
-        CUDA_TRY(cudaStreamWaitEvent(st, h->pipe_done[j], 0));
-    }
+    join_pipes(h, st);   // also after an error: the forked work is joined before the call returns
+    if (rc) return rc;
+    if (ce != cudaSuccess) return fail(SIT_E_CUDA, std::string("sit_fleet_step_host: ") + cudaGetErrorString(ce));
     CUDA_TRY(cudaStreamSynchronize(st));
     return SIT_OK;
+}
+
+int sit_fleet_step_host(SitHandle h, void* state, int32_t K, const void* dist_h, int32_t avoid, void* pose_h,
+                        void* stream) {
+    return sit_fleet_step_host_sel(h, state, K, dist_h, avoid, pose_h, 0xff, nullptr, stream);
 }
 
 int sit_capture_init(SitHandle h, void* state, void* stream) {
@@ -2242,7 +2293,7 @@ int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h,
         if (sac_update_h) CUDA_TRY(cudaMemcpyAsync(d + o_sac + first, sac_update_h + first, cnt, cudaMemcpyHostToDevice, ps));
         rc = h->cfg.precision == SIT_F64 ? env_step_t<double>(h, state, K, &io, ps, first, cnt)
                                          : env_step_t<float>(h, state, K, &io, ps, first, cnt);
-        if (rc) return rc;
+        if (rc) { join_pipes(h, st); return rc; }
         if (obs_h)
             CUDA_TRY(cudaMemcpy2DAsync(static_cast<char*>(obs_h) + first * rs, B * rs, d + o_obs + first * rs, B * rs, cnt * rs,
                                        SIT_N_OBS, cudaMemcpyDeviceToHost, ps));

@@ -106,13 +106,25 @@ class ShipFleet(SimCore):
         self.launches += 1
         return res
 
+    CHANNELS = ("north", "east", "psi", "u", "v", "r", "omega", "k")
+
     def step_host(self, K: int, dist_host: Optional[torch.Tensor], pose_host: Optional[torch.Tensor],
-                  avoid: bool = False):
-        """One call through ``sit_fleet_step_host``: HOST (pinned) disturbances [4, n_ships] in, HOST post-step
-        (N, E, psi, u, v, r, omega, k) [8, n_ships] of the last step out; copies and synchronisation inside."""
+                  avoid: bool = False, channels=None, k8_host: Optional[torch.Tensor] = None):
+        """One call through ``sit_fleet_step_host[_sel]``: HOST (pinned) disturbances [4, n_ships] in, HOST post-step
+        (N, E, psi, u, v, r, omega, k) [8, n_ships] of the last step out; copies and synchronisation inside.
+        ``channels``: names (or a bit mask) of the channels the caller reads -- pose_host is then
+        [len(channels), n_ships] in channel order; ``k8_host``: int8 [n_ships] waypoint index."""
         for t in (dist_host, pose_host):
             assert t is None or (t.device.type == "cpu" and t.dtype == self.real and t.is_contiguous())
-        _lib.check(self.L.sit_fleet_step_host(self.h, self.state_ptr(), int(K), ptr(dist_host), int(avoid),
-                                              ptr(pose_host), self.stream()))
+        if channels is None and k8_host is None:
+            _lib.check(self.L.sit_fleet_step_host(self.h, self.state_ptr(), int(K), ptr(dist_host), int(avoid),
+                                                  ptr(pose_host), self.stream()))
+        else:
+            mask = 0xff if channels is None else (channels if isinstance(channels, int) else
+                                                  sum(1 << self.CHANNELS.index(c) for c in channels))
+            assert pose_host is None or pose_host.shape == (bin(mask & 0xff).count("1"), self.n_ships)
+            assert k8_host is None or (k8_host.dtype == torch.int8 and k8_host.numel() == self.n_ships and k8_host.is_contiguous())
+            _lib.check(self.L.sit_fleet_step_host_sel(self.h, self.state_ptr(), int(K), ptr(dist_host), int(avoid),
+                                                      ptr(pose_host), int(mask), ptr(k8_host), self.stream()))
         self.launches += 1
         return pose_host

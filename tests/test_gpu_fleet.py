@@ -176,3 +176,10 @@ def test_host_buffer_path_equals_device_path(n):
     assert torch.equal(a.f["vc_n"].cpu(), dist[0]) and torch.equal(a.f["wind_dir"].cpu(), dist[3])
     a.step_host(3, None, pose_h)          # no disturbance update: held values stay
     assert (a.f["steps"] == 67).all() and torch.isfinite(pose_h).all()
+    # the masked form (sit_fleet_step_host_sel): only the channels the caller reads + the waypoint index as int8
+    a.load_state_dict(snap)
+    sel_h = torch.full((4, n), float("nan"), dtype=torch.float32).pin_memory()
+    k8_h = torch.full((n,), -1, dtype=torch.int8).pin_memory()
+    a.step_host(64, dist_h, sel_h, channels=("north", "psi", "u", "omega"), k8_host=k8_h)
+    assert torch.equal(sel_h, want_pose.cpu()[[0, 2, 3, 6]]), "masked host path: rows are the selected channels in channel order"
+    assert torch.equal(k8_h.to(torch.float32), want_pose.cpu()[7]), "int8 waypoint index"
