@@ -412,41 +412,35 @@ def run_b200(args, rank, world, local_rank):
         # own shard of envs (global env ids rank*B ..), then the replay rows of the timed segment are all-gathered and the
         # episode counters all-reduced over NCCL -- the only collectives of the framework, after the segment ----------------
         B_roll = 65536
-        rl = rollout_leg(sit, dev, B=B_roll, env_id_offset=rank * B_roll)
+        rl = rollout_leg(sit, dev, B=B_roll, env_id_offset=rank * B_roll, world=world, barrier=barrier)
         smp_keep = rl.pop("sampler")
-        rows = smp_keep.transitions()[:min(rl["samples"], smp_keep.capacity)]
-        if world > 1:
-            # untimed first gather of the same size: NCCL sets up its channels / protocol buffers for this message size and
-            # the caching allocator gets its blocks on the first call (in a training loop the gather recurs every segment)
-            del_me = ro_mod.gather_replay(rows); del del_me
-        barrier()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-        allrows = ro_mod.gather_replay(rows)
+        mem_roll = rl.pop("memory")
         tot_stats = ro_mod.reduce_stats(smp_keep.env.stats)
-        ev1.record()
-        barrier()
-        agg = torch.tensor([rl["samples"], rl["env_steps"], rows.shape[0], rl["resamples"], rl["episodes"], rl["launches"]],
+        agg = torch.tensor([rl["samples"], rl["env_steps"], rl["resamples"], rl["episodes"], rl["launches"], rl["rows_left_behind"]],
                            dtype=torch.float64, device=dev)
-        tm = torch.tensor([rl["ms_total"], ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+        tm = torch.tensor([rl["ms_total"], rl["ms_rollout_only"], rl["ms_exposed_exchange"]], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(agg, op=dist.ReduceOp.SUM)
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        allrows = mem_roll.buffer[:len(mem_roll)]
         ids = allrows[:, 23].contiguous().view(torch.int32)
         rl.update({"n_gpus": world, "envs": world * B_roll, "envs_per_gpu": B_roll, "samples": int(agg[0].item()),
-                   "env_steps": int(agg[1].item()), "resamples": int(agg[3].item()), "episodes": int(agg[4].item()),
-                   "launches": int(agg[5].item()),
+                   "env_steps": int(agg[1].item()), "resamples": int(agg[2].item()), "episodes": int(agg[3].item()),
+                   "launches": int(agg[4].item()), "rows_left_behind": int(agg[5].item()),
                    "lane_utilisation": float(agg[1].item()) / (world * B_roll * rl["k_per_launch"] * rl["iterations"]),
-                   "fields": "samples, env_steps, resamples, episodes, launches are sums over all ranks",
-                   "ms_total": float(tm[0].item()), "gather_ms": float(tm[1].item()),
+                   "fields": "samples, env_steps, resamples, episodes, launches are sums over all ranks; times are max over ranks",
+                   "ms_total": float(tm[0].item()), "ms_rollout_only": float(tm[1].item()),
+                   "ms_exposed_exchange": float(tm[2].item()),
                    "gathered_rows": int(allrows.shape[0]), "gathered_bytes": int(allrows.numel() * 4),
-                   "gather_complete": bool(allrows.shape[0] == int(agg[2].item()) and int(ids.min()) >= 0
-                                           and int(ids.max()) < world * B_roll and int(tot_stats[13].item()) > 0),
-                   "value": float(agg[0].item()) / ((float(tm[0].item()) + float(tm[1].item())) * 1e-3),
-                   "value_without_gather": float(agg[0].item()) / (float(tm[0].item()) * 1e-3),
-                   "env_steps_per_s": float(agg[1].item()) / (float(tm[0].item()) * 1e-3),
-                   "collective": "NCCL all_gather of replay rows + all_reduce of 16 counters after the segment"
-                                 if world > 1 else "none (one rank)"})
+                   "gather_complete": bool(allrows.shape[0] == int(agg[0].item()) and int(agg[5].item()) == 0
+                                           and int(ids.min()) >= 0 and int(ids.max()) < world * B_roll
+                                           and int(tot_stats[13].item()) > 0),
+                   "value": float(agg[0].item()) / (float(tm[0].item()) * 1e-3),
+                   "value_without_gather": float(agg[0].item()) / (float(tm[1].item()) * 1e-3),
+                   "env_steps_per_s": float(agg[1].item()) / (float(tm[1].item()) * 1e-3),
+                   "collective": ("NCCL all_gather_into_tensor of fixed-capacity row blocks on a side stream after every segment "
+                                  "(no count exchange, no host sync; segment s+1 rolls out under the exchange of segment s) + "
+                                  "one all_reduce of 16 counters") if world > 1 else "none (one rank): blocks appended on the side stream"})
         del allrows
         # ---- long horizon (BASELINE config 5): 10 000 steps, run-time machinery-mode switching, all checks on; every rank
         # runs its own envs, the termination histogram is summed over ranks with one all-reduce after the run ---------------
@@ -685,40 +679,80 @@ def long_horizon_leg(sit, dev, rank, B=65536, K=64, total_steps=10000, mode_ever
 
 
 def rollout_leg(sit, dev, B=65536, K=32, iters=40, warm_iters=20, hidden=256, precision="fp32", mode="gaussian",
-                env_id_offset=0, tc=1):
+                env_id_offset=0, tc=1, world=1, barrier=None, segments=4):
     """BASELINE config 4: SAC-AST rollout, policy MLP 10 -> 256 -> 256 -> 2 with fixed seeded weights evaluated on the
-    decision-event subset between step launches, transitions compacted into a device replay ring.  Returns
-    samples/s (pushed transitions) and env-steps/s actually executed (pending envs do not step)."""
+    decision-event subset between step launches, transitions compacted into a device replay ring; after every segment of
+    iters / segments iterations the segment's rows go to every rank's replay memory (rollout.ReplayExchange: fixed-capacity
+    blocks, side stream).  The timed region is the whole of it: `segments` x (collect, pack, exchange) and the wait for the
+    last exchange.  Returns samples/s (pushed transitions) and env-steps/s actually executed (pending envs do not step).
+    Episodes follow the reference (`while not done`, num_steps_episode = 600 only masks the row closing at that step)."""
     import torch
     from sac_maritime_ast_b200 import rollout as ro
+    from sac_maritime_ast_b200 import sac as sac_mod
     env, g = make_bench_env(sit, dev, B, precision, SEED)
     if mode == "uniform":
         pol = ro.UniformPolicy()
     else:
-        pol = ro.GaussianPolicy(hidden_size=hidden, device=dev, seed=SEED, mode=mode, tensor_cores=bool(tc))
-        pol.w0.mul_(1e-4)      # raw observations are ~1e4 m (the reference feeds them unnormalised): keep layer 0 O(1)
+        # the network sees obs / observation_space.high (the raw observation is metres / rpm / kW up to 2e4)
+        pol = ro.GaussianPolicy(hidden_size=hidden, device=dev, seed=SEED, mode=mode, tensor_cores=bool(tc), obs_scale="space")
     smp = ro.IntermediateWaypointSampler(env, pol, capacity=max(B * 4, 1 << 16), seed=SEED, env_id_offset=env_id_offset,
                                          num_steps_episode=600, max_route_resampling=1000, auto_reset="hard")
+    per_seg = iters // segments
     smp.begin()
     smp.collect(warm_iters, K)
     torch.cuda.synchronize()
-    c0, s0, l0 = smp.counters.clone(), env.stats.clone(), smp.launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    smp.collect(iters, K)
-    e1.record()
+    # block size of the exchange: the row rate seen in the warm-up with head-room (a host-known bound; every rank uses the
+    # same number; rows that do not fit would be counted in rows_left_behind and fail gather_complete)
+    rows_per_iter = torch.tensor([float(smp.counters[1].item()) / warm_iters], dtype=torch.float64, device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(rows_per_iter, op=dist.ReduceOp.MAX)
+    block = int(min(per_seg * B, 2.0 * float(rows_per_iter.item()) * per_seg + 4096))
+    block = (block + 255) // 256 * 256
+    mem = sac_mod.ReplayMemory(world * block * (segments + 2), seed=SEED, device=dev)
+    xch = ro.ReplayExchange(smp, block)
+    xch.pack(); xch.exchange(mem); xch.wait()            # untimed: the warm-up rows, NCCL channel / allocator set-up at this size
     torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
+    mem.count.zero_()
+
+    def timed(exchange):
+        if barrier:
+            barrier()
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+        for _ in range(segments):
+            smp.collect(per_seg, K)
+            if exchange:
+                xch.pack(); xch.exchange(mem)
+        e1.record()
+        if exchange:
+            xch.wait()
+        e2.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e2), e1.elapsed_time(e2)
+    c0, s0, l0 = smp.counters.clone(), env.stats.clone(), smp.launches
+    ms, ms_tail = timed(True)
     dc, ds = (smp.counters - c0).cpu().numpy(), (env.stats - s0).cpu().numpy()
+    launches = smp.launches - l0
+    left_behind = int(xch.dropped.item())
+    c1 = smp.counters.clone()
+    ms_plain, _ = timed(False)                             # the same number of iterations without the exchange
+    dc1 = (smp.counters - c1).cpu().numpy()
     rows = smp.replay[:min(smp.n_transitions(), smp.capacity)]
-    return {"metric": "SAC-AST rollout samples/s", "value": float(dc[0]) / (ms * 1e-3), "unit": "samples/s",
+    iters = per_seg * segments
+    return {"metric": "SAC-AST rollout samples/s", "value": float(dc[4]) / (ms * 1e-3), "unit": "samples/s",
             "env_steps_per_s": float(ds[13]) / (ms * 1e-3), "envs": B, "k_per_launch": K, "iterations": iters,
-            "ms_per_iteration": ms / iters, "ms_total": ms, "policy": f"{mode} MLP 10-{hidden}-{hidden}-2" if mode != "uniform" else "uniform",
+            "segments": segments, "exchange_block_rows": block,
+            "ms_per_iteration": ms / iters, "ms_total": ms, "ms_exposed_exchange": ms_tail,
+            "ms_rollout_only": ms_plain * (float(dc[4]) / max(float(dc1[4]), 1.0)),   # scaled to the same number of samples
+            "policy": f"{mode} MLP 10-{hidden}-{hidden}-2" if mode != "uniform" else "uniform",
             "policy_hidden_layer": "tcgen05 bf16 x bf16 -> fp32 (TMEM)" if (tc and mode != "uniform") else "fp32 CUDA cores",
-            "dtype": precision, "samples": int(dc[0]), "env_steps": int(ds[13]), "resamples": int(dc[2]),
+            "policy_input": "obs / observation_space.high (SitPolicy.obs_scale)",
+            "episodes_end": "terminal states only (reference loop); num_steps_episode = 600 masks the row closing at that step",
+            "dtype": precision, "samples": int(dc[4]), "env_steps": int(ds[13]), "resamples": int(dc[2]),
             "episodes": int(ds[12]), "lane_utilisation": float(ds[13]) / (B * K * iters),
-            "launches": smp.launches - l0, "bytes_per_sample": 96,
-            "replay_finite": bool(torch.isfinite(rows[:, :23]).all()), "sampler": smp}
+            "launches": launches, "bytes_per_sample": 96, "rows_left_behind": left_behind,
+            "replay_finite": bool(torch.isfinite(rows[:, :23]).all()), "sampler": smp, "memory": mem}
 
 
 def learner_leg(sit, dev, sampler, batch=64, hidden=256, n=400, warm=50):

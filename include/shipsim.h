@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define SIT_ABI_VERSION 2
+#define SIT_ABI_VERSION 3
 #define SIT_MAX_WP 16     /* route capacity per ship: 2 + sampling_frequency (main_ast.py:47) fits */
 #define SIT_MAX_MODES 4   /* machinery modes per ship (PTO / PTI / MEC, main_ast.py:136-158) */
 #define SIT_MAX_EDGES 128 /* polygon ring segments of the map (default map: 39, main_ast.py:200-205) */
@@ -230,7 +230,9 @@ enum { SIT_POLICY_UNIFORM = 0, SIT_POLICY_GAUSSIAN = 1, SIT_POLICY_MEAN = 2 };
  * and w1 rounded to nearest-even bf16 -- fp32 accumulate in TMEM); everything else stays fp32.  Without it the whole MLP
  * is fp32 on the CUDA cores. */
 enum { SIT_POLICY_TC_BF16 = 0x100 };
-enum { SIT_RC_TRANSITIONS = 0, SIT_RC_DECISIONS = 1, SIT_RC_RESAMPLES = 2, SIT_RC_EPISODES = 3, SIT_RC_N = 8 };
+/* TRANSITIONS counts replay rows OPENED by sit_rollout_policy (state, action written); CLOSED counts rows whose reward,
+ * next_state and mask the following step has written.  Rows [0, CLOSED) (ring order) are complete: a learner reads CLOSED. */
+enum { SIT_RC_TRANSITIONS = 0, SIT_RC_DECISIONS = 1, SIT_RC_RESAMPLES = 2, SIT_RC_EPISODES = 3, SIT_RC_CLOSED = 4, SIT_RC_N = 8 };
 
 typedef struct SitPolicy {
     int32_t mode;              /* SIT_POLICY_* */
@@ -241,16 +243,22 @@ typedef struct SitPolicy {
     const float* b1;           /* [H] */
     const float* w2;           /* [H][2]:  (mu, log_sigma) = b2 + layer1 . w2, log_sigma clipped to [-20, 2] */
     const float* b2;           /* [2] */
+    const float* obs_scale;    /* [10] or NULL: the network sees obs[c] * obs_scale[c] (e.g. 1 / observation_space.high,
+                                  MSRL_env_ex.py:67-78); the replay rows keep the raw observation */
 } SitPolicy;
 
 typedef struct SitRollout {
     uint64_t seed;             /* Philox key; draws are keyed by (global env id, decision serial, resample index) */
     int64_t env_id_offset;     /* global id of env 0 of this handle: results do not depend on the sharding */
-    int32_t max_episode_steps; /* num_steps_episode cap (0 = none): reset after that many steps */
+    int32_t max_episode_steps; /* args.num_steps_episode (0 = none).  Reference semantics (main_ast.py:322,387): the row that
+                                  closes at episode_steps == num_steps_episode gets mask = 1 and the episode CONTINUES until
+                                  a terminal state (`while not done`); see truncate_episodes */
     int32_t max_route_resampling;
     float* replay;             /* [capacity][SIT_TR_FLOATS] device ring, capacity >= n_envs */
     int64_t capacity;
     unsigned long long* counters; /* [SIT_RC_N] device counters, accumulated */
+    int32_t truncate_episodes; /* opt-in extension: != 0 also ENDS the episode (reset + init_step) at num_steps_episode */
+    int32_t _pad;
 } SitRollout;
 
 /* give every pending env an action: policy forward on its current observation, sample, convert, validate, open
@@ -302,6 +310,12 @@ typedef struct SitSacConfig {
     int32_t automatic_entropy_tuning;  /* main_ast.py:59 */
     int32_t target_update_interval;    /* main_ast.py:84 */
     uint64_t seed;                     /* main_ast.py:61 */
+    float obs_scale[SIT_N_OBS];        /* per-channel input scale of all five networks (state part of s and s'); an entry of 0
+                                          means 1.  The raw observation is metres / rpm / kW (up to 2e4): unscaled it saturates
+                                          tanh(mu) and zeroes every policy gradient */
+    int32_t tensor_cores;              /* 1: H x H products of the update on tcgen05 (bf16 operands, fp32 accumulate) when
+                                          batch_size >= 1024; 0: fp32 CUDA cores everywhere */
+    int32_t _pad;
 } SitSacConfig;
 typedef struct SitSac_* SitSac;
 enum { SIT_SAC_LOSS_Q1 = 0, SIT_SAC_LOSS_Q2 = 1, SIT_SAC_LOSS_POLICY = 2, SIT_SAC_LOSS_ALPHA = 3, SIT_SAC_ALPHA = 4,
@@ -311,11 +325,12 @@ int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out);
 int sit_sac_destroy(SitSac h);
 int sit_sac_workspace_bytes(SitSac h, size_t* nbytes);
 /* named float32 / int32 region of the workspace: "policy", "q1", "q2", "q1_target", "q2_target", "log_alpha", "alpha",
- * "grad", "adam_m", "adam_v", "idx", "eps_next", "eps_cur", "losses", "updates".  offset in bytes, count in elements. */
+ * "grad", "adam_m", "adam_v", "idx", "eps_next", "eps_cur", "losses", "updates", "obs_scale".  offset in bytes, count in
+ * elements. */
 int sit_sac_field(SitSac h, const char* name, int64_t* offset, int64_t* count);
 /* Glorot-uniform weights (Philox, cfg.seed), zero biases, targets = critics, log_alpha = 0, Adam state and counter 0 */
 int sit_sac_init(SitSac h, void* workspace, void* stream);
-/* fill a SitPolicy (mode GAUSSIAN) with pointers into the workspace's policy block */
+/* fill a SitPolicy (mode GAUSSIAN) with pointers into the workspace's policy block (and its obs_scale) */
 int sit_sac_policy(SitSac h, void* workspace, SitPolicy* out);
 /* n_updates x update_parameters on batches drawn from replay[0 .. min(*n_rows, capacity)) (n_rows: device counter, e.g.
  * SitRollout.counters + SIT_RC_TRANSITIONS; NULL = all `capacity` rows are valid).  losses (device, may be NULL)

@@ -53,12 +53,13 @@ class RolloutRef:
     """One env.  mode: 'uniform' | 'gaussian' | 'mean'."""
 
     def __init__(self, p, m, e, gid, seed=25450, mode="uniform", weights=None, num_steps_episode=600,
-                 max_route_resampling=1000, sampling_frequency=7, hard_reset=False):
+                 max_route_resampling=1000, sampling_frequency=7, hard_reset=False, truncate=False):
         self.L = cport.lib()
         self.p, self.m, self.e = p, m, e
         self.gid, self.seed, self.mode, self.weights = gid, seed, mode, weights
         self.cap, self.max_resample, self.sf = num_steps_episode, max_route_resampling, sampling_frequency
         self.hard = hard_reset
+        self.truncate = truncate     # False: the reference's loop (`while not done`, main_ast.py:322): num_steps_episode only masks
         self.serial = 0
         self.transitions = []          # (state[10], a, r, next_state[10], mask)
         self.decisions = []            # (global step, a, wp_n, wp_e, tries)
@@ -119,12 +120,12 @@ class RolloutRef:
         self.ep_steps += 1
         self.steps += 1
         nxt, done = list(o10), bool(d.value)
-        timeup = self.cap > 0 and self.ep_steps + 1 >= self.cap
+        timeup = self.cap > 0 and self.ep_steps + 1 == self.cap      # episode_steps == num_steps_episode, main_ast.py:387
         if su:
             mask = 1.0 if timeup else float(not done)      # main_ast.py:387
             self.transitions.append((list(self.state), a, r.value, nxt, mask))
         out = dict(obs=nxt, reward=r.value, done=done, status=st.value)
-        if done or timeup:
+        if done or (timeup and self.truncate):
             if self.hard:
                 raise NotImplementedError("hard reset is a product extension; the oracle keeps the reference's reset")
             self._begin_episode()

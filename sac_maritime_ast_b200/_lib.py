@@ -7,7 +7,7 @@ import os
 
 MAX_WP, MAX_MODES, MAX_EDGES = 16, 4, 128
 N_OBS, N_TRAJ, N_LOG, N_STATS = 10, 8, 27, 16
-ABI_VERSION = 2
+ABI_VERSION = 3
 F64, F32 = 0, 1
 KIND_FLEET, KIND_ENV = 1, 2
 SG = {"MOTOR": 0, "GEN": 1, "OFF": 2}
@@ -80,25 +80,26 @@ class SitEnvIO(C.Structure):
 
 class SitPolicy(C.Structure):
     _fields_ = [("mode", I32), ("hidden", I32), ("w0", C.c_void_p), ("b0", C.c_void_p), ("w1", C.c_void_p),
-                ("b1", C.c_void_p), ("w2", C.c_void_p), ("b2", C.c_void_p)]
+                ("b1", C.c_void_p), ("w2", C.c_void_p), ("b2", C.c_void_p), ("obs_scale", C.c_void_p)]
 
 
 class SitRollout(C.Structure):
     _fields_ = [("seed", C.c_uint64), ("env_id_offset", I64), ("max_episode_steps", I32),
-                ("max_route_resampling", I32), ("replay", C.c_void_p), ("capacity", I64), ("counters", C.c_void_p)]
+                ("max_route_resampling", I32), ("replay", C.c_void_p), ("capacity", I64), ("counters", C.c_void_p),
+                ("truncate_episodes", I32), ("_pad", I32)]
 
 
 class SitSacConfig(C.Structure):
     _fields_ = [("hidden", I32), ("batch_size", I32), ("gamma", C.c_float), ("tau", C.c_float), ("lr", C.c_float),
                 ("alpha", C.c_float), ("automatic_entropy_tuning", I32), ("target_update_interval", I32),
-                ("seed", C.c_uint64)]
+                ("seed", C.c_uint64), ("obs_scale", C.c_float * 10), ("tensor_cores", I32), ("_pad", I32)]
 
 
 N_REWARD_PARTS = 8
 TR_FLOATS = 24
 POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
 POLICY_TC_BF16 = 0x100
-RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_N = 0, 1, 2, 3, 8
+RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_CLOSED, RC_N = 0, 1, 2, 3, 4, 8
 
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host", "sit_fleet_step_host_sel",
            "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_group_count", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",

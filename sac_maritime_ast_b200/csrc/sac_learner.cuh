@@ -125,7 +125,7 @@ struct Layout {
     long long o_xs, o_xs2, o_xsa, o_xs2a, o_xspi, o_r, o_mask;
     long long o_hp1, o_hp2, o_op, o_hq1, o_hq2, o_oq, o_oqt;
     long long o_doq, o_dhq2, o_dhq1, o_da, o_dop, o_dhp2, o_dhp1;
-    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, total;
+    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, total;
 };
 
 static void make_layout(Layout& L, int H, int B) {
@@ -152,6 +152,7 @@ static void make_layout(Layout& L, int H, int B) {
     L.o_dop = take(b * 2); L.o_dhp2 = take(b * H); L.o_dhp1 = take(b * H);
     L.o_eps_next = take(b); L.o_eps_cur = take(b); L.o_logp_next = take(b); L.o_logp_cur = take(b);
     L.o_idx = take(b); L.o_losses = take(SIT_SAC_N_LOSS); L.o_updates = take(2);   // updates: one unsigned long long
+    L.o_obs_scale = take(S);
     L.total = o;
 }
 
@@ -172,6 +173,10 @@ __global__ void init_layer_kernel(float* w, int K, int N, uint64_t seed, uint32_
     w[i] = v;
 }
 
+struct ObsScale { float v[SIT_N_OBS]; };
+__global__ void obs_scale_kernel(float* p, const ObsScale sc) {
+    if (threadIdx.x < SIT_N_OBS) p[threadIdx.x] = sc.v[threadIdx.x] != 0.0f ? sc.v[threadIdx.x] : 1.0f;
+}
 __global__ void fill_kernel(float* p, long long n, float v) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = v;
@@ -214,7 +219,8 @@ __global__ void batch_kernel(float* ws, const Layout L, const Hyper hp, const fl
     float* xspi = ws + L.o_xspi + (long long)b * (SA + 1);
 #pragma unroll
     for (int c = 0; c < S; ++c) {
-        const float s = tr[c], s2 = tr[12 + c];
+        const float sc = ws[L.o_obs_scale + c];            // SitSacConfig.obs_scale: the networks see scaled observations
+        const float s = tr[c] * sc, s2 = tr[12 + c] * sc;
         xs[c] = s; xsa[c] = s; xspi[c] = s; xs2[c] = s2; xs2a[c] = s2;
     }
     xsa[S] = tr[10];
@@ -495,7 +501,7 @@ int sit_sac_field(SitSac h, const char* name, int64_t* offset, int64_t* count) {
         {"q1_target", L.o_qt, L.P_q}, {"q2_target", L.o_qt + L.P_q, L.P_q}, {"log_alpha", L.o_log_alpha, 1},
         {"alpha", L.o_alpha, 1}, {"grad", L.o_grad, L.n_train}, {"adam_m", L.o_m, L.n_train}, {"adam_v", L.o_v, L.n_train},
         {"idx", L.o_idx, L.B}, {"eps_next", L.o_eps_next, L.B}, {"eps_cur", L.o_eps_cur, L.B},
-        {"losses", L.o_losses, SIT_SAC_N_LOSS}, {"updates", L.o_updates, 2}};
+        {"losses", L.o_losses, SIT_SAC_N_LOSS}, {"updates", L.o_updates, 2}, {"obs_scale", L.o_obs_scale, sac::S}};
     for (const auto& e : tab)
         if (std::strcmp(e.n, name) == 0) { *offset = e.o * (long long)sizeof(float); *count = e.c; return SIT_OK; }
     return fail(SIT_E_INVALID, std::string("unknown learner field: ") + name);
@@ -520,6 +526,9 @@ int sit_sac_init(SitSac h, void* workspace, void* stream) {
     }
     CUDA_TRY(cudaMemcpyAsync(ws + L.o_qt, ws + L.o_q, (size_t)(2 * L.P_q) * sizeof(float), cudaMemcpyDeviceToDevice, st));
     sac::fill_kernel<<<1, 32, 0, st>>>(ws + L.o_alpha, 1, h->hp.alpha0);
+    sac::ObsScale osc;
+    for (int c = 0; c < sac::S; ++c) osc.v[c] = h->cfg.obs_scale[c];
+    sac::obs_scale_kernel<<<1, 32, 0, st>>>(ws + L.o_obs_scale, osc);
     auto ones = [&](long long o, long long rows, int ld) { sac::ones_col_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(ws + o, rows, ld); };
     ones(L.o_xs, B, sac::S + 1); ones(L.o_xs2, B, sac::S + 1);
     ones(L.o_xsa, B, sac::SA + 1); ones(L.o_xs2a, B, sac::SA + 1); ones(L.o_xspi, B, sac::SA + 1);
@@ -536,6 +545,7 @@ int sit_sac_policy(SitSac h, void* workspace, SitPolicy* out) {
     out->w0 = p + L.pol.l0; out->b0 = out->w0 + (long long)sac::S * L.H;
     out->w1 = p + L.pol.l1; out->b1 = out->w1 + (long long)L.H * L.H;
     out->w2 = p + L.pol.l2; out->b2 = out->w2 + (long long)L.H * 2;
+    out->obs_scale = static_cast<const float*>(workspace) + L.o_obs_scale;
     return SIT_OK;
 }
 

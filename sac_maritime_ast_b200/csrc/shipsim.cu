@@ -40,7 +40,7 @@ struct EnvPtrs {
 struct RollArgs {   // device-resident rollout (include/shipsim.h SitRollout), by value
     float* replay; int64_t capacity; unsigned long long* counters;
     uint64_t seed; int64_t env_id_offset;
-    int32_t max_episode_steps, max_route_resampling, sampling_frequency, _pad;
+    int32_t max_episode_steps, max_route_resampling, sampling_frequency, truncate;
     int64_t env_first, env_count;   // env sub-range of this launch (sit_rollout_collect pipelines env groups)
 };
 
@@ -407,7 +407,8 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     bool any_done = false;
     unsigned my_cnt = 0;   // lane b < 12 counts status bit b of this warp's envs; lane 12 counts done steps
     unsigned n_live = 0;   // env-steps actually executed by this lane (ROLL: pending envs do not step)
-    unsigned n_eps = 0;    // ROLL: episodes this env ended in the launch (terminal state or num_steps_episode reached)
+    unsigned n_eps = 0;    // ROLL: episodes this env ended in the launch (terminal state; num_steps_episode when truncating)
+    unsigned n_closed = 0; // ROLL: replay rows this env completed in the launch
     MapCache mc;           // nearest-ring cache, carried across launches in the state buffer
     mc.idx = (uint32_t)g.mc_idx[i]; mc.p0n = g.mc_n[i]; mc.p0e = g.mc_e[i]; mc.b2 = g.mc_b2[i];
 
@@ -599,7 +600,9 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         if (ROLL) {
             // main_ast.py:387: mask = 1 if episode_steps == num_steps_episode else float(not done); the reference's
             // episode_steps counts init_step as 1, so it equals ep_steps + 1 here
-            const bool timeup = ro.max_episode_steps > 0 && ep_steps + 1 >= ro.max_episode_steps;
+            // (== : only the row that closes AT that step is masked; the reference's loop is `while not done`, :322, so the
+            // episode goes on unless the caller opted into truncation -- then >= and == coincide)
+            const bool timeup = ro.max_episode_steps > 0 && ep_steps + 1 == ro.max_episode_steps;
             if (tr_open) {   // close the replay row opened by sit_rollout_policy: (reward, next_state, mask), :395-396
                 if (active) {
                     float* row = ro.replay + (int64_t)ge.tr_slot[env] * SIT_TR_FLOATS;
@@ -612,8 +615,9 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
                     }
                 }
                 tr_open = false;
+                if (active && is_obs) n_closed += 1;
             }
-            episode_end = done || timeup;
+            episode_end = done || (timeup && ro.truncate);
         }
         // ---- in-kernel reset() + init_step() right after a terminal step ---------------------------------
         if (episode_end) {
@@ -707,6 +711,10 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) eps += __shfl_xor_sync(FULL, eps, d);
         if (lane == 14 && eps) atomicAdd(&ro.counters[SIT_RC_EPISODES], (unsigned long long)eps);
+        unsigned cl = n_closed;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) cl += __shfl_xor_sync(FULL, cl, d);
+        if (lane == 15 && cl) atomicAdd(&ro.counters[SIT_RC_CLOSED], (unsigned long long)cl);
     }
 }
 
@@ -746,16 +754,69 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
-struct PolicyArgs { int32_t mode, hidden; const float *w0, *b0, *w1, *b1, *w2, *b2; };
+struct PolicyArgs { int32_t mode, hidden; const float *w0, *b0, *w1, *b1, *w2, *b2, *obs_scale; };
 // scratch of one sit_rollout_policy call (device, owned by the handle): compact list of the pending envs
-struct PolScratch { unsigned int *n_pending, *n_retry; int32_t *env, *retry; float *obs, *out; unsigned char* w1p; };   // env / retry [B], obs [B][10], out [B][2]
+struct PolScratch {   // env / retry [B], obs [B][10], out [B][2]
+    unsigned int *n_pending, *n_retry, *ticket; unsigned long long* slot_base;
+    int32_t *env, *retry, *cta_cnt; float *obs, *out; unsigned char* w1p;
+};
 
-// ---- K4a: compact the pending envs, open their replay rows ---------------------------------------------------------
+// ---- K4a: compact the pending envs, open their replay rows.  DETERMINISTIC ORDER: pass 1 counts the pending envs of every
+// 256-env CTA; the last CTA to finish (ticket) turns the counts into exclusive offsets in blockIdx order and reserves the
+// replay slots [TRANSITIONS, TRANSITIONS + total); pass 2 places env e at offset[cta] + rank inside the CTA.  The compact
+// list and the ring rows are therefore in ascending env order whatever the CTA scheduling: two runs with one seed fill
+// the ring identically (the learner draws batches by row index).  With several env groups in flight (SIT_ROLLOUT_GROUPS > 1)
+// each group's block of rows is ordered, the order of the blocks is not.
 template <typename R>
-__global__ void __launch_bounds__(256) rollout_gather_kernel(const EnvPtrs<R> ge, const RollArgs ro, const PolScratch sc) {
+__global__ void __launch_bounds__(256) rollout_count_kernel(const EnvPtrs<R> ge, const RollArgs ro, const PolScratch sc) {
     __shared__ int s_warp_cnt[8];
-    __shared__ unsigned int s_base;
-    __shared__ unsigned long long s_slot0;
+    __shared__ bool s_last;
+    __shared__ unsigned int s_scan[256];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t env = ro.env_first + (int64_t)blockIdx.x * 256 + tid;
+    const int32_t fl = env < ro.env_first + ro.env_count ? ge.flags[env] : 0;
+    const bool pend = (fl & F_PENDING) && !(fl & F_HAVE_ACT);
+    const unsigned bal = __ballot_sync(0xffffffffu, pend);
+    if (lane == 0) s_warp_cnt[wid] = __popc(bal);
+    __syncthreads();
+    if (tid == 0) {
+        int total = 0;
+        for (int w = 0; w < 8; ++w) total += s_warp_cnt[w];
+        sc.cta_cnt[blockIdx.x] = total;
+        __threadfence();
+        s_last = atomicAdd(sc.ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // exclusive scan of cta_cnt[0 .. gridDim.x) in place: thread t owns a contiguous run of `per` entries
+    const int nb = (int)gridDim.x, per = (nb + 255) / 256;
+    const int lo = min(tid * per, nb), hi = min(lo + per, nb);
+    unsigned int mine = 0;
+    for (int j = lo; j < hi; ++j) mine += (unsigned int)__ldcg(&sc.cta_cnt[j]);
+    s_scan[tid] = mine;
+    __syncthreads();
+    for (int d = 1; d < 256; d <<= 1) {
+        const unsigned int v = tid >= d ? s_scan[tid - d] : 0u;
+        __syncthreads();
+        s_scan[tid] += v;
+        __syncthreads();
+    }
+    unsigned int run = s_scan[tid] - mine;
+    for (int j = lo; j < hi; ++j) { const unsigned int c = (unsigned int)__ldcg(&sc.cta_cnt[j]); sc.cta_cnt[j] = (int32_t)run; run += c; }
+    if (tid == 255) {
+        const unsigned int total = s_scan[255];
+        *sc.n_pending = total;
+        *sc.slot_base = atomicAdd(&ro.counters[SIT_RC_TRANSITIONS], (unsigned long long)total);
+        atomicAdd(&ro.counters[SIT_RC_DECISIONS], (unsigned long long)total);
+        *sc.ticket = 0u;
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256) rollout_gather_kernel(const EnvPtrs<R> ge, const RollArgs ro, const PolScratch sc,
+                                                             const float* __restrict__ obs_scale) {
+    __shared__ int s_warp_cnt[8];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int64_t B = ge.n_envs;
     const int64_t env = ro.env_first + (int64_t)blockIdx.x * 256 + tid;
@@ -764,26 +825,20 @@ __global__ void __launch_bounds__(256) rollout_gather_kernel(const EnvPtrs<R> ge
     const unsigned bal = __ballot_sync(0xffffffffu, pend);
     if (lane == 0) s_warp_cnt[wid] = __popc(bal);
     __syncthreads();
-    int off = 0, total = 0;
-    for (int w = 0; w < 8; ++w) { if (w < wid) off += s_warp_cnt[w]; total += s_warp_cnt[w]; }
-    if (tid == 0 && total) {
-        s_base = atomicAdd(sc.n_pending, (unsigned int)total);
-        s_slot0 = atomicAdd(&ro.counters[SIT_RC_TRANSITIONS], (unsigned long long)total);
-        atomicAdd(&ro.counters[SIT_RC_DECISIONS], (unsigned long long)total);
-    }
-    __syncthreads();
     if (!pend) return;
-    const unsigned int r = off + __popc(bal & ((1u << lane) - 1u));
-    const unsigned int p = s_base + r;
-    sc.env[p] = (int32_t)env;
-    const long long slot = (long long)((s_slot0 + r) % (unsigned long long)ro.capacity);
+    int off = 0;
+    for (int w = 0; w < wid; ++w) off += s_warp_cnt[w];
+    const unsigned int r = (unsigned int)sc.cta_cnt[blockIdx.x] + off + __popc(bal & ((1u << lane) - 1u));
+    sc.env[r] = (int32_t)env;
+    const long long slot = (long long)((*sc.slot_base + r) % (unsigned long long)ro.capacity);
     ge.tr_slot[env] = (int32_t)slot;
     float* row = ro.replay + slot * SIT_TR_FLOATS;
-    // held observation (MSRL_env_ex.py:424-435 layout) as float32, like the reference's policy input and replay state
+    // held observation (MSRL_env_ex.py:424-435 layout) as float32, like the reference's policy input and replay state; the
+    // policy network sees it scaled per channel (SitPolicy.obs_scale), the replay row keeps the raw values
 #pragma unroll
     for (int c = 0; c < SIT_N_OBS; ++c) {
         const float v = (float)ge.cur_obs[(int64_t)c * B + env];
-        sc.obs[(int64_t)p * SIT_N_OBS + c] = v;
+        sc.obs[(int64_t)r * SIT_N_OBS + c] = obs_scale ? v * obs_scale[c] : v;
         row[c] = v;
     }
     row[23] = __int_as_float((int32_t)(ro.env_id_offset + env));
@@ -1941,6 +1996,7 @@ static int roll_args(SitHandle h, const SitRollout* ro, RollArgs& ra) {
     ra.replay = ro->replay; ra.capacity = ro->capacity; ra.counters = ro->counters;
     ra.seed = ro->seed; ra.env_id_offset = ro->env_id_offset;
     ra.max_episode_steps = ro->max_episode_steps; ra.max_route_resampling = ro->max_route_resampling;
+    ra.truncate = ro->truncate_episodes != 0;
     ra.sampling_frequency = (int32_t)h->cfg.sampling_frequency;
     ra.env_first = 0; ra.env_count = h->n_envs;
     return SIT_OK;
@@ -1994,24 +2050,28 @@ static int policy_args(const SitPolicy* pol, PolicyArgs& pa, bool& tensor_cores)
         if (pol->hidden < 32 || pol->hidden > 256 || pol->hidden % 32) return fail(SIT_E_INVALID, "policy hidden width must be a multiple of 32 in [32, 256]");
         if (!pol->w0 || !pol->b0 || !pol->w1 || !pol->b1 || !pol->w2 || !pol->b2) return fail(SIT_E_INVALID, "policy weights missing");
         pa.w0 = pol->w0; pa.b0 = pol->b0; pa.w1 = pol->w1; pa.b1 = pol->b1; pa.w2 = pol->w2; pa.b2 = pol->b2;
+        pa.obs_scale = pol->obs_scale;
     } else {
         tensor_cores = false;
     }
     return SIT_OK;
 }
 
-// Policy scratch: counters [SIT_ROLL_GROUPS_MAX][2] | env list [B] | obs [B][10] | out [B][2] | retry list [B] | packed W1.
+// Policy scratch: per-group header [SIT_ROLL_GROUPS_MAX][8 words: n_pending, n_retry, ticket, -, slot_base (u64), -, -] | env list [B] |
+// obs [B][10] | out [B][2] | retry list [B] | packed W1 | per-CTA counts / offsets [B / 256 + groups].
 // The lists are sized for the whole handle; an env group [first, first + count) uses the slices that start at `first`,
 // so groups that run concurrently never share a row.
 static int pol_scratch(SitHandle h, int group, int64_t first, PolScratch& sc) {
     const size_t B = (size_t)h->n_envs;
     const size_t o_env = 256, o_obs = align_up(o_env + B * 4, 256), o_out = align_up(o_obs + B * SIT_N_OBS * 4, 256),
                  o_retry = align_up(o_out + B * 2 * 4, 256), o_w1p = align_up(o_retry + B * 4, 256),
-                 total = o_w1p + 256 * 256 * 2;
+                 o_cta = o_w1p + 256 * 256 * 2, total = o_cta + (B / 256 + SIT_ROLL_GROUPS_MAX + 1) * 4;
     int rc = ensure_pol_scratch(h, total);
     if (rc) return rc;
     char* d = static_cast<char*>(h->d_pol);
-    sc.n_pending = reinterpret_cast<unsigned int*>(d) + 2 * group; sc.n_retry = sc.n_pending + 1;
+    sc.n_pending = reinterpret_cast<unsigned int*>(d) + 8 * group; sc.n_retry = sc.n_pending + 1; sc.ticket = sc.n_pending + 2;
+    sc.slot_base = reinterpret_cast<unsigned long long*>(sc.n_pending + 4);
+    sc.cta_cnt = reinterpret_cast<int32_t*>(d + o_cta) + first / 256 + group;   // group starts are multiples of 256 envs
     sc.env = reinterpret_cast<int32_t*>(d + o_env) + first; sc.retry = reinterpret_cast<int32_t*>(d + o_retry) + first;
     sc.obs = reinterpret_cast<float*>(d + o_obs) + first * SIT_N_OBS; sc.out = reinterpret_cast<float*>(d + o_out) + first * 2;
     sc.w1p = reinterpret_cast<unsigned char*>(d + o_w1p);
@@ -2035,14 +2095,15 @@ static int rollout_policy_t(SitHandle h, void* state, const PolicyArgs& pa, bool
     PolScratch sc;
     int rc = pol_scratch(h, group, ra.env_first, sc);
     if (rc) return rc;
-    CUDA_TRY(cudaMemsetAsync(sc.n_pending, 0, 2 * sizeof(unsigned int), st));
+    CUDA_TRY(cudaMemsetAsync(sc.n_pending, 0, 4 * sizeof(unsigned int), st));
     const ShipPtrs<R> g = ship_ptrs<R>(h, state);
     const EnvPtrs<R> ge = env_ptrs<R>(h, state);
     const EnvKArgs<R>& A = HostSel<R>::env(h);
     const int gather_grid = grid_for(ra.env_count, 256);
     // persistent: tiles / warps stride over the pending list (a small share of the group's envs)
     const int work_grid = h->sm_count * 4;
-    rollout_gather_kernel<R><<<gather_grid, 256, 0, st>>>(ge, ra, sc);
+    rollout_count_kernel<R><<<gather_grid, 256, 0, st>>>(ge, ra, sc);
+    rollout_gather_kernel<R><<<gather_grid, 256, 0, st>>>(ge, ra, sc, pa.obs_scale);
     if (pa.mode != SIT_POLICY_UNIFORM) {
         if (tensor_cores) {
             const int H = pa.hidden;

@@ -31,6 +31,13 @@ from .env import MultiShipRLEnv
 N_OBS, TR_FLOATS = _lib.N_OBS, _lib.TR_FLOATS
 LOG_SIG_CAP_MAX, LOG_SIG_CAP_MIN = 2.0, -20.0      # distributions/normal.py:14-15
 EPS = 1e-6                                         # policies/gaussian_policy.py:16
+# observation_space.high (MSRL_env_ex.py:67-78): dividing by it brings every channel of the raw observation (metres, rpm, kW)
+# into [-1, 1]; unscaled, |mu| runs into the hundreds, tanh saturates to exactly +-1 in fp32 and every policy gradient is 0
+OBS_HIGH = (10000.0, 20000.0, float(np.pi), 3000.0, 1000.0, 2000.0, 10000.0, 20000.0, float(np.pi), 1000.0)
+
+
+def default_obs_scale():
+    return tuple(1.0 / h for h in OBS_HIGH)
 
 
 class GaussianPolicy:
@@ -40,7 +47,7 @@ class GaussianPolicy:
     (multiple of 32, <= 256: main_ast.py:67 uses 256, the class default is (100, 100) -> use 128 or 96)."""
 
     def __init__(self, hidden_size: int = 256, device=None, seed: int = 25450, mode: str = "gaussian",
-                 tensor_cores: bool = False):
+                 tensor_cores: bool = False, obs_scale=None):
         if hidden_size % 32 or not 32 <= hidden_size <= 256:
             raise ValueError("hidden_size must be a multiple of 32 in [32, 256]")
         self.hidden, self.device, self.mode = hidden_size, torch.device(device or "cuda"), mode
@@ -55,6 +62,10 @@ class GaussianPolicy:
         self.w0, self.b0 = glorot(N_OBS, H), torch.zeros(H, device=self.device)
         self.w1, self.b1 = glorot(H, H), torch.zeros(H, device=self.device)
         self.w2, self.b2 = glorot(H, 2), torch.zeros(2, device=self.device)
+        # per-channel input scale (None: the network sees the raw observation; "space": 1 / observation_space.high)
+        if isinstance(obs_scale, str):
+            obs_scale = default_obs_scale()
+        self.obs_scale = None if obs_scale is None else torch.tensor(obs_scale, dtype=torch.float32, device=self.device)
 
     def parameters(self):
         return [self.w0, self.b0, self.w1, self.b1, self.w2, self.b2]
@@ -69,11 +80,13 @@ class GaussianPolicy:
             t = getattr(self, n)
             assert t.dtype == torch.float32 and t.is_contiguous() and t.device.type == "cuda"
             setattr(p, n, t.data_ptr())
+        p.obs_scale = None if self.obs_scale is None else self.obs_scale.data_ptr()
         return p
 
     # plain torch restatement (used by the tests as the fp32 reference of the policy kernel)
     def mu_logsig(self, obs: torch.Tensor):
-        h = torch.relu(obs.float() @ self.w0 + self.b0)
+        x = obs.float() if self.obs_scale is None else obs.float() * self.obs_scale
+        h = torch.relu(x @ self.w0 + self.b0)
         if self.tensor_cores:     # the kernel rounds both operands of the hidden-layer product to bf16 (fp32 accumulate)
             h = torch.relu(h.bfloat16().float() @ self.w1.bfloat16().float() + self.b1)
         else:
@@ -101,7 +114,10 @@ class IntermediateWaypointSampler:
 
     def __init__(self, env: MultiShipRLEnv, policy, capacity: Optional[int] = None, seed: int = 25450,
                  env_id_offset: int = 0, num_steps_episode: int = 600, max_route_resampling: int = 1000,
-                 auto_reset="reference"):
+                 auto_reset="reference", truncate_episodes: bool = False):
+        """num_steps_episode follows the reference (main_ast.py:322,387): the row that closes at that episode step gets
+        mask = 1 and the episode goes on until a terminal state.  truncate_episodes=True is an extension that also ends
+        (resets) the episode there."""
         self.env, self.policy = env, policy
         self.capacity = int(capacity if capacity is not None else max(env.n_envs * 8, 1024))
         if self.capacity < env.n_envs:
@@ -112,6 +128,7 @@ class IntermediateWaypointSampler:
         self.ro.seed, self.ro.env_id_offset = int(seed), int(env_id_offset)
         self.ro.max_episode_steps, self.ro.max_route_resampling = int(num_steps_episode), int(max_route_resampling)
         self.ro.replay, self.ro.capacity, self.ro.counters = self.replay.data_ptr(), self.capacity, self.counters.data_ptr()
+        self.ro.truncate_episodes = int(bool(truncate_episodes))
         self.io = _lib.SitEnvIO()
         self.io.auto_reset = 2 if auto_reset == "hard" else 1
         self.io.rec_steps = 1
@@ -164,11 +181,16 @@ class IntermediateWaypointSampler:
         groups = C.c_int32(1)
         _lib.check(e.L.sit_rollout_group_count(e.h, C.byref(groups)))
         tc = bool(getattr(self.policy, 'tensor_cores', False))
-        per_group = 4 + (0 if isinstance(self.policy, UniformPolicy) else 1)
+        per_group = 5 + (0 if isinstance(self.policy, UniformPolicy) else 1)   # count, gather, [mlp], sample, resample, step
         self.launches += (per_group * groups.value + (1 if tc else 0)) * iterations
 
     # ---- results ----------------------------------------------------------------------------------------------
     def n_transitions(self) -> int:
+        """Completed replay rows (SIT_RC_CLOSED: reward, next_state and mask written).  Between sit_rollout_policy and the
+        next step launch the rows just opened are not counted."""
+        return int(self.counters[_lib.RC_CLOSED].item())
+
+    def n_opened(self) -> int:
         return int(self.counters[_lib.RC_TRANSITIONS].item())
 
     def transitions(self) -> torch.Tensor:
@@ -200,6 +222,69 @@ def gather_replay(rows: torch.Tensor, group=None) -> torch.Tensor:
     out = torch.empty((world * cap, rows.shape[1]), dtype=rows.dtype, device=rows.device)
     dist.all_gather_into_tensor(out, padded, group=group)
     return torch.cat([out[r * cap:r * cap + counts[r]] for r in range(world)], dim=0)
+
+
+class ReplayExchange:
+    """The post-segment exchange with NOTHING on the critical path: fixed-capacity blocks, no count exchange, no host
+    synchronisation, collective on a side stream.
+
+    A rollout segment of ``iterations`` policy calls opens at most ``iterations * n_envs`` rows per rank (one decision per env
+    and policy call), so every rank ships one block of exactly that many rows; rows past the segment's count carry env id -1
+    and are dropped on arrival by a device-side compaction (``ReplayMemory.extend_masked``).  ``pack()`` copies the segment's
+    rows out of the sampler ring on the caller's stream (so the next segment may overwrite the ring), ``exchange()`` runs the
+    all-gather and the append on a side stream and returns an event: the next ``sampler.collect`` overlaps it, and only the
+    consumer of the memory (the learner) waits.  With one rank the block is appended directly.  CPU tensors (the gloo tests)
+    take the same path without streams."""
+
+    def __init__(self, sampler: "IntermediateWaypointSampler", block_rows: int, group=None):
+        self.smp, self.block, self.group = sampler, int(block_rows), group
+        dev = sampler.replay.device
+        self.cuda = dev.type == "cuda"
+        import torch.distributed as dist
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.ar = torch.arange(self.block, device=dev, dtype=torch.int64)
+        self.seen = torch.zeros((), dtype=torch.int64, device=dev)        # SIT_RC_CLOSED at the previous pack (device)
+        self.dropped = torch.zeros((), dtype=torch.int64, device=dev)     # rows a too-small block had to leave behind
+        self.send = torch.zeros((self.block, TR_FLOATS), dtype=torch.float32, device=dev)
+        self.recv = torch.zeros((self.world * self.block, TR_FLOATS), dtype=torch.float32, device=dev) if self.world > 1 else self.send
+        self.side = torch.cuda.Stream(device=dev) if self.cuda else None
+        self.done = None
+
+    def pack(self):
+        """Copy the rows closed since the previous pack into the send block (caller's stream, no host sync)."""
+        smp = self.smp
+        if self.cuda and self.done is not None:
+            torch.cuda.current_stream(self.send.device).wait_event(self.done)     # the previous exchange has read `send`
+        n_now = smp.counters[_lib.RC_CLOSED]
+        new = n_now - self.seen
+        self.dropped += torch.clamp(new - self.block, min=0)
+        first = torch.where(new > self.block, n_now - self.block, self.seen)      # keep the newest rows if the block is too small
+        idx = (first + self.ar) % smp.capacity
+        torch.index_select(smp.replay, 0, idx, out=self.send)
+        ids = self.send[:, 23].view(torch.int32)
+        ids.masked_fill_(self.ar >= new, -1)
+        self.seen.copy_(n_now)
+
+    def exchange(self, memory) -> Optional["torch.cuda.Event"]:
+        """All-gather the packed blocks of every rank and append the valid rows to ``memory`` (rank order, row order)."""
+        import torch.distributed as dist
+        if not self.cuda:
+            if self.world > 1:
+                dist.all_gather_into_tensor(self.recv, self.send, group=self.group)
+            memory.extend_masked(self.recv)
+            return None
+        cur = torch.cuda.current_stream(self.send.device)
+        self.side.wait_stream(cur)
+        with torch.cuda.stream(self.side):
+            if self.world > 1:
+                dist.all_gather_into_tensor(self.recv, self.send, group=self.group)
+            memory.extend_masked(self.recv)
+            self.done = self.side.record_event()
+        return self.done
+
+    def wait(self):
+        if self.cuda and self.done is not None:
+            torch.cuda.current_stream(self.send.device).wait_event(self.done)
 
 
 def reduce_stats(stats: torch.Tensor, group=None) -> torch.Tensor:

@@ -36,7 +36,9 @@ class ReplayMemory:
 
     def __init__(self, capacity: int, seed: int = 25450, device="cuda"):
         self.capacity, self.seed, self.device = int(capacity), int(seed), torch.device(device)
-        self.buffer = torch.zeros((self.capacity, TR_FLOATS), dtype=torch.float32, device=self.device)
+        # one spare row past the ring: the scatter of extend_masked parks dropped rows there
+        self._store = torch.zeros((self.capacity + 1, TR_FLOATS), dtype=torch.float32, device=self.device)
+        self.buffer = self._store[:self.capacity]
         self.count = torch.zeros(1, dtype=torch.int64, device=self.device)      # rows ever pushed (device counter)
         self._gen = torch.Generator(device=self.device).manual_seed(self.seed)
 
@@ -44,7 +46,9 @@ class ReplayMemory:
     def from_sampler(cls, sampler) -> "ReplayMemory":
         m = cls.__new__(cls)
         m.capacity, m.seed, m.device = sampler.capacity, int(sampler.ro.seed), sampler.replay.device
-        m.buffer, m.count = sampler.replay, sampler.counters[_lib.RC_TRANSITIONS:_lib.RC_TRANSITIONS + 1]
+        # completed rows only (SIT_RC_CLOSED): a row opened by the policy call is not drawn before its step has closed it
+        m.buffer, m.count = sampler.replay, sampler.counters[_lib.RC_CLOSED:_lib.RC_CLOSED + 1]
+        m._store = None
         m._gen = torch.Generator(device=m.device).manual_seed(m.seed)
         return m
 
@@ -60,6 +64,22 @@ class ReplayMemory:
         pos = (start + torch.arange(n, device=self.device)) % self.capacity
         self.buffer[pos] = rows.to(self.device, torch.float32)
         self.count += n
+
+    def extend_masked(self, rows: torch.Tensor):
+        """Append the rows whose env id (column 23, int32 bits) is >= 0, in order, WITHOUT a host synchronisation: ring
+        positions come from a device prefix sum over the validity flags, dropped rows are scattered to the spare row.
+        The fixed-capacity exchange of ``rollout.ReplayExchange`` ends here."""
+        if getattr(self, "_store", None) is None:
+            raise ValueError("extend_masked needs a memory that owns its ring (not from_sampler)")
+        rows = rows.to(self.device, torch.float32)
+        valid = rows[:, 23].contiguous().view(torch.int32) >= 0
+        rank = torch.cumsum(valid.to(torch.int64), 0) - 1
+        n_valid = rank[-1] + 1 if rows.shape[0] else torch.zeros((), dtype=torch.int64, device=self.device)
+        # if more valid rows arrive than the ring holds, only the last `capacity` of them may land (no duplicate positions)
+        keep = valid & (rank >= n_valid - self.capacity)
+        pos = torch.where(keep, (self.count + rank) % self.capacity, torch.full_like(rank, self.capacity))
+        self._store.index_copy_(0, pos, rows)
+        self.count += n_valid
 
     def push(self, state, action, reward, next_state, mask):
         row = torch.zeros(TR_FLOATS, dtype=torch.float32, device=self.device)
@@ -81,7 +101,7 @@ class SAC:
     """``agent = SAC(num_inputs, action_space, args)``; ``agent.update_parameters(memory, batch_size, updates)``."""
 
     FIELDS = ("policy", "q1", "q2", "q1_target", "q2_target", "log_alpha", "alpha", "grad", "adam_m", "adam_v", "idx",
-              "eps_next", "eps_cur", "losses", "updates")
+              "eps_next", "eps_cur", "losses", "updates", "obs_scale")
 
     def __init__(self, num_inputs: int = 10, action_space=None, args=None, device="cuda", batch_size: Optional[int] = None,
                  use_graph: bool = True, **kw):
@@ -100,6 +120,14 @@ class SAC:
         cfg.automatic_entropy_tuning = int(bool(arg("automatic_entropy_tuning", True)))
         cfg.target_update_interval = int(arg("target_update_interval", 1))
         cfg.seed = int(arg("seed", 25450))
+        # input scale of all networks: default 1 / observation_space.high (MSRL_env_ex.py:67-78); None = raw observations
+        from .rollout import default_obs_scale
+        obs_scale = kw.get("obs_scale", "space")
+        if isinstance(obs_scale, str):
+            obs_scale = default_obs_scale()
+        for c in range(_lib.N_OBS):
+            cfg.obs_scale[c] = 1.0 if obs_scale is None else float(obs_scale[c])
+        cfg.tensor_cores = int(bool(arg("tensor_cores", True)))
         self.cfg, self.hidden, self.batch_size, self.use_graph = cfg, cfg.hidden, cfg.batch_size, bool(use_graph)
         self.h = C.c_void_p()
         idx = self.device.index if self.device.index is not None else torch.cuda.current_device()

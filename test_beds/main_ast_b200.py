@@ -62,6 +62,9 @@ def parse_args(argv=None):
     p.add_argument("--precision", default="fp32", choices=["fp32", "fp64"])
     p.add_argument("--tensor_cores", type=int, default=1, help="policy hidden layer on tcgen05 (bf16 operands)")
     p.add_argument("--max_updates_per_segment", type=int, default=0, help="0 = update_per_step x steps per env")
+    p.add_argument("--truncate_episodes", type=int, default=0,
+                   help="0 (reference, main_ast.py:322,387): num_steps_episode only sets mask = 1 at that step and the episode "
+                        "runs on to a terminal state; 1: also reset the episode there")
     p.add_argument("--log_json", default="")
     return p.parse_args(argv)
 
@@ -97,12 +100,18 @@ def main(argv=None):
     memory = ReplayMemory(capacity, seed=args.seed, device=dev)
     uniform, learned = ro.UniformPolicy(), agent.policy("gaussian" if args.policy == "Gaussian" else "mean",
                                                          tensor_cores=bool(args.tensor_cores))
-    smp = ro.IntermediateWaypointSampler(env, uniform, capacity=max(8 * (hi - lo), 4096), seed=args.seed, env_id_offset=lo,
-                                         num_steps_episode=args.num_steps_episode,
-                                         max_route_resampling=args.max_route_resampling)
+    # a segment opens at most collect_iterations rows per env: the sampler ring holds at least two segments, so the rows of
+    # a segment are packed long before they can be overwritten
+    block = args.collect_iterations * (hi - lo)
+    smp = ro.IntermediateWaypointSampler(env, uniform, capacity=max(2 * block, 8 * (hi - lo), 4096), seed=args.seed,
+                                         env_id_offset=lo, num_steps_episode=args.num_steps_episode,
+                                         max_route_resampling=args.max_route_resampling,
+                                         truncate_episodes=bool(args.truncate_episodes))
+    # fixed-capacity exchange (every rank has the same block size: the shards differ by at most one env)
+    xch = ro.ReplayExchange(smp, args.collect_iterations * (-(-args.n_envs // world)))
     smp.begin()
     steps_per_segment = args.k_steps * args.collect_iterations
-    total_numsteps, updates, seen, segment = 0, 0, 0, 0
+    total_numsteps, updates, segment = 0, 0, 0
     history = []
     t_start = time.time()
     while total_numsteps < args.num_steps:
@@ -111,13 +120,11 @@ def main(argv=None):
             smp.set_policy(learned if use_learned else uniform)                        # mode 0 / mode 1 of agent.select_action
         stats0, count0 = env.stats.clone(), smp.counters.clone()
         smp.collect(args.collect_iterations, args.k_steps)
-        # ---- push: the rows of this segment (ring order) -> every rank's memory ----------------------------------
-        n_now = smp.n_transitions()
-        new = min(n_now - seen, smp.capacity)
-        idx = (torch.arange(n_now - new, n_now, device=dev)) % smp.capacity
-        rows = smp.replay[idx]
-        seen = n_now
-        memory.extend(ro.gather_replay(rows))
+        # ---- push: the rows of this segment (ring order) -> every rank's memory.  Fixed-capacity blocks, all-gather and
+        # append on a side stream, no host sync: the learner below waits for it, the next segment's rollout does not -------
+        xch.pack()
+        xch.exchange(memory)
+        xch.wait()                                   # the update draws from this segment's rows too (main_ast.py:350-357)
         total_numsteps += steps_per_segment
         # ---- update_parameters: update_per_step per simulator step of an env (main_ast.py:350-362) ----------------
         losses = None
@@ -138,7 +145,10 @@ def main(argv=None):
         if losses is not None:
             ls = losses.tolist()
             rec.update(critic_1_loss=ls[0], critic_2_loss=ls[1], policy_loss=ls[2], ent_loss=ls[3], alpha=ls[4])
-        rec["mean_reward_of_new_rows"] = float(rows[:, 11].mean()) if rows.shape[0] else None
+        new_rows = xch.send[xch.send[:, 23].view(torch.int32) >= 0]
+        rec["mean_reward_of_new_rows"] = float(new_rows[:, 11].mean()) if new_rows.shape[0] else None
+        rec["share_of_unsaturated_actions"] = float((new_rows[:, 10].abs() < 0.999).float().mean()) if new_rows.shape[0] else None
+        rec["rows_left_behind"] = int(xch.dropped.item())
         history.append(rec)
         if rank == 0:
             msg = (f"segment {segment:4d}  steps/env {total_numsteps:7d}  {rec['policy']:8s} memory {rec['memory']:8d} "

@@ -29,7 +29,27 @@ def _worker(rank, world, port, q):
     stats = torch.arange(16, dtype=torch.int64) * (rank + 1)
     tot = reduce_stats(stats)
     empty = gather_replay(torch.zeros((0, 24)) if rank == 0 else rows[:2])   # ragged incl. an empty rank
-    q.put((rank, allrows.clone(), tot.clone(), empty.shape[0], n))
+    # fixed-capacity exchange (ReplayExchange): no count exchange, padding rows carry env id -1 and are dropped on arrival.
+    # A stand-in sampler: a ring, its counters, its capacity.  Two segments; rank 1's second segment is empty.
+    from types import SimpleNamespace
+    from sac_maritime_ast_b200 import _lib
+    from sac_maritime_ast_b200.rollout import ReplayExchange
+    from sac_maritime_ast_b200.sac import ReplayMemory
+    ring = torch.zeros((16, 24)); counters = torch.zeros(_lib.RC_N, dtype=torch.int64)
+    fake = SimpleNamespace(replay=ring, counters=counters, capacity=16)
+    xch = ReplayExchange(fake, block_rows=6)
+    mem = ReplayMemory(64, device="cpu")
+    sent = []
+    for seg, n_new in enumerate([(3, 5), (4, 0)]):
+        k = n_new[rank]
+        start = int(counters[_lib.RC_CLOSED])
+        for j in range(k):
+            slot = (start + j) % 16
+            ring[slot, 0], ring[slot, 1] = 100 * rank + start + j, seg
+            ring[slot, 23] = torch.tensor(rank, dtype=torch.int32).view(torch.float32)
+        counters[_lib.RC_CLOSED] += k; counters[_lib.RC_TRANSITIONS] += k
+        xch.pack(); xch.exchange(mem)
+    q.put((rank, allrows.clone(), tot.clone(), empty.shape[0], n, mem.buffer[:len(mem)].clone(), int(xch.dropped)))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -59,7 +79,11 @@ def test_gather_replay_and_reduce_stats_world2():
     res = _run_world(world) or _run_world(world)     # one retry on a fresh port: the probe-then-bind of the port can race
     assert res is not None, "gloo world-size-2 run failed twice"
     n_rows = [r[4] for r in res]
-    for rank, allrows, tot, n_empty, _ in res:
+    for rank, allrows, tot, n_empty, _, xrows, dropped in res:
+        # fixed-capacity path: segment 0 = rank 0's 3 rows then rank 1's 5, segment 1 = rank 0's 4 rows; same on every rank
+        assert dropped == 0 and xrows.shape[0] == 12 and torch.equal(xrows, res[0][5])
+        assert xrows[:, 0].tolist() == [0, 1, 2, 100, 101, 102, 103, 104, 3, 4, 5, 6]
+        assert xrows[:, 1].tolist() == [0] * 8 + [1] * 4
         assert allrows.shape == (sum(n_rows), 24)
         assert torch.equal(allrows, res[0][1])                       # same on every rank
         assert torch.equal(tot, torch.arange(16, dtype=torch.int64) * 3)

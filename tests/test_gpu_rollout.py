@@ -21,14 +21,17 @@ def _make(n_envs, precision, policy, offset=0, cap=600, scenario="default", **kw
     import gpu_helpers as G
     from sac_maritime_ast_b200 import rollout as ro
     env = G.make_env(sc.ENV_SCENARIOS[scenario], n_envs=n_envs, precision=precision)
+    # tests that shorten the episode (cap != 600) were written for truncated episodes: opt in explicitly
+    kw.setdefault("truncate_episodes", cap != 600)
     return ro.IntermediateWaypointSampler(env, policy, capacity=max(4096, n_envs), seed=25450, env_id_offset=offset,
                                           num_steps_episode=cap, **kw)
 
 
-def _oracle_rows(gid, nsteps, mode="uniform", weights=None, cap=600, scenario="default"):
+def _oracle_rows(gid, nsteps, mode="uniform", weights=None, cap=600, scenario="default", truncate=None):
     from oracle import rollout_ref as rr
     p, m, e = H.oracle_env(sc.ENV_SCENARIOS[scenario])
-    ref = rr.RolloutRef(p, m, e, gid, seed=25450, mode=mode, weights=weights, num_steps_episode=cap)
+    ref = rr.RolloutRef(p, m, e, gid, seed=25450, mode=mode, weights=weights, num_steps_episode=cap,
+                        truncate=(cap != 600) if truncate is None else truncate)
     for _ in range(nsteps):
         ref.step()
     return ref
@@ -47,13 +50,15 @@ def _check_rows(got, ref_tr, tol):
         assert H.rel_err(row[11], r, 1.0).max() <= tol, (j, "reward", row[11], r)
 
 
-@pytest.mark.parametrize("cap", [600, 150])
-def test_uniform_policy_rollout_matches_oracle_fp64(cap):
+@pytest.mark.parametrize("cap,truncate", [(600, False), (150, True), (150, False), (40, False)])
+def test_uniform_policy_rollout_matches_oracle_fp64(cap, truncate):
     """fp64 env, UniformPolicy: every env's transition sequence equals the CPU loop's (envs pause at decision events,
-    so each env is compared on its own step count)."""
+    so each env is compared on its own step count).  truncate False is the reference's loop (main_ast.py:322,387): the row
+    closing at episode step num_steps_episode gets mask 1 and the episode runs on to a terminal state; True also resets
+    the episode there (opt-in extension)."""
     from sac_maritime_ast_b200 import rollout as ro
     B = 6
-    smp = _make(B, "fp64", ro.UniformPolicy(), offset=100, cap=cap)
+    smp = _make(B, "fp64", ro.UniformPolicy(), offset=100, cap=cap, truncate_episodes=truncate)
     smp.begin()
     smp.collect(iterations=60, K=32)
     torch.cuda.synchronize()
@@ -62,7 +67,7 @@ def test_uniform_policy_rollout_matches_oracle_fp64(cap):
     per_env = _by_env(rows)
     assert sorted(per_env) == list(range(100, 100 + B))
     for gid, got in per_env.items():
-        ref = _oracle_rows(gid, 60 * 32, cap=cap)
+        ref = _oracle_rows(gid, 60 * 32, cap=cap, truncate=truncate)
         # replay rows of one env are in order of their slots within a launch sequence; sort by nothing: slots grow in time
         _check_rows(got, ref.transitions, 2e-7)
     assert len({len(v) for v in per_env.values()}) >= 1
@@ -212,7 +217,7 @@ def test_full_size_rollout_properties_and_shard_invariance():
         env.ship[1].u_sp.copy_(usp[offset:offset + n])
         env.capture_init()
         s = ro.IntermediateWaypointSampler(env, pol, capacity=4 * n, seed=25450, env_id_offset=offset, num_steps_episode=150,
-                                           auto_reset="hard")
+                                           auto_reset="hard", truncate_episodes=True)
         s.begin(); s.collect(iters, K)
         torch.cuda.synchronize()
         return s
@@ -238,3 +243,55 @@ def test_full_size_rollout_properties_and_shard_invariance():
     for lo in (0, B // 2):
         part = run(B // 2, lo)
         assert torch.equal(keyed(part, lo, lo + B // 2), keyed(whole, lo, lo + B // 2)), f"shard at {lo} differs from the whole batch"
+
+
+def test_replay_ring_order_is_deterministic_and_closed_rows_are_counted():
+    """Two runs with one seed fill the replay ring IDENTICALLY (row for row, not only as a set): the compaction orders
+    the pending envs by env index whatever the CTA scheduling.  SIT_RC_CLOSED trails SIT_RC_TRANSITIONS between a policy
+    call and the step launch that closes the rows it opened, and catches up after it."""
+    from sac_maritime_ast_b200 import _lib, rollout as ro
+    pol = ro.GaussianPolicy(hidden_size=64, device="cuda:0", seed=3, obs_scale="space")
+    rings = []
+    for _ in range(2):
+        smp = _make(5000, "fp32", pol, cap=200, auto_reset="hard")
+        smp.begin()
+        smp.collect(12, 16, graph=True)
+        torch.cuda.synchronize()
+        c = smp.counters.cpu().numpy()
+        assert c[_lib.RC_CLOSED] == c[_lib.RC_TRANSITIONS] == c[_lib.RC_DECISIONS] > 5000
+        rings.append((smp.replay.clone(), c.copy()))
+        ids = smp.replay[:5000, 23].contiguous().view(torch.int32)
+        assert torch.equal(ids, torch.arange(5000, dtype=torch.int32, device=ids.device)), "first decisions are in env order"
+        # a policy call opens rows that only the next step launch completes
+        smp.policy_step()
+        torch.cuda.synchronize()
+        c2 = smp.counters.cpu().numpy()
+        opened = int(c2[_lib.RC_TRANSITIONS] - c[_lib.RC_TRANSITIONS])
+        assert opened > 0 and c2[_lib.RC_CLOSED] == c[_lib.RC_CLOSED] and smp.n_transitions() == int(c[_lib.RC_CLOSED])
+        smp.env_steps(1)
+        torch.cuda.synchronize()
+        c3 = smp.counters.cpu().numpy()
+        assert c3[_lib.RC_CLOSED] == c3[_lib.RC_TRANSITIONS]
+    assert np.array_equal(rings[0][1], rings[1][1])
+    assert torch.equal(rings[0][0].view(torch.int32), rings[1][0].view(torch.int32)), "ring contents differ between two runs"
+
+
+def test_policy_input_scale_reaches_both_mlp_kernels():
+    """SitPolicy.obs_scale: the network sees obs * scale; the replay row keeps the raw observation.  A policy with scale s and
+    layer-0 weights w must act exactly like a policy without scale and weights diag(s) w (fp32 CUDA-core MLP, same sums up to
+    one rounding), on both MLP kernels."""
+    from sac_maritime_ast_b200 import rollout as ro
+    for tc in (False, True):
+        a = ro.GaussianPolicy(hidden_size=64, device="cuda:0", seed=9, mode="mean", tensor_cores=tc, obs_scale="space")
+        b = ro.GaussianPolicy(hidden_size=64, device="cuda:0", seed=9, mode="mean", tensor_cores=tc)
+        b.w0.mul_(a.obs_scale[:, None])
+        outs = []
+        for pol in (a, b):
+            smp = _make(512, "fp32", pol)
+            smp.begin(); smp.policy_step(); smp.env_steps(1)
+            torch.cuda.synchronize()
+            rows = smp.transitions()
+            assert rows.shape[0] == 512 and float(rows[:, 0].min()) >= 400.0, "replay state is the raw observation"
+            outs.append(rows[:, 10].clone())
+        assert float((outs[0] - outs[1]).abs().max()) <= (2e-3 if tc else 2e-5)
+        assert float(outs[0].abs().max()) < 0.999, "scaled inputs keep tanh(mu) off saturation"

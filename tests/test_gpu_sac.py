@@ -31,6 +31,7 @@ class TorchSAC:
 
     def __init__(self, agent):
         self.cfg = agent.cfg
+        self.obs_scale = agent.f["obs_scale"].clone()       # SitSacConfig.obs_scale: every network sees s * obs_scale
         self.nets = {}
         for net in ("policy", "q1", "q2", "q1_target", "q2_target"):
             self.nets[net] = [(w.clone().requires_grad_(not net.endswith("target")), b.clone().requires_grad_(not net.endswith("target")))
@@ -63,7 +64,7 @@ class TorchSAC:
 
     def update(self, rows, eps_next, eps_cur):
         c = self.cfg
-        s, a, r, s2, m = rows[:, 0:10], rows[:, 10], rows[:, 11], rows[:, 12:22], rows[:, 22]
+        s, a, r, s2, m = rows[:, 0:10] * self.obs_scale, rows[:, 10], rows[:, 11], rows[:, 12:22] * self.obs_scale, rows[:, 22]
         with torch.no_grad():
             a2, lp2 = self.pi(s2, eps_next)
             qt = torch.min(self.q("q1_target", s2, a2), self.q("q2_target", s2, a2)) - self.alpha * lp2
@@ -97,7 +98,10 @@ def test_update_matches_torch_autograd(hidden, batch, graph):
     from sac_maritime_ast_b200 import sac
     mem = sac.ReplayMemory(4096, device=DEV)
     mem.extend(_fake_replay(1000).to(DEV))
-    agent = sac.SAC(10, None, None, device=DEV, hidden_size=hidden, batch_size=batch, use_graph=graph, seed=11)
+    # the fake replay holds unit-scale observations: no input scale, except one case with a non-trivial per-channel scale
+    scale = tuple(0.5 + 0.1 * c for c in range(10)) if batch == 300 else None
+    agent = sac.SAC(10, None, None, device=DEV, hidden_size=hidden, batch_size=batch, use_graph=graph, seed=11, obs_scale=scale)
+    assert torch.allclose(agent.f["obs_scale"], torch.tensor(scale if scale else [1.0] * 10, device=DEV))
     ref = TorchSAC(agent)
     assert len(mem) == 1000
     for u in range(5):
@@ -125,9 +129,9 @@ def test_initialisation_and_determinism():
     from sac_maritime_ast_b200 import sac
     mem = sac.ReplayMemory(2048, device=DEV)
     mem.extend(_fake_replay(2048, seed=3).to(DEV))
-    a = sac.SAC(10, None, None, device=DEV, hidden_size=128, batch_size=64, seed=5)
-    b = sac.SAC(10, None, None, device=DEV, hidden_size=128, batch_size=64, seed=5)
-    c = sac.SAC(10, None, None, device=DEV, hidden_size=128, batch_size=64, seed=6)
+    a = sac.SAC(10, None, None, device=DEV, hidden_size=128, batch_size=64, seed=5, obs_scale=None)
+    b = sac.SAC(10, None, None, device=DEV, hidden_size=128, batch_size=64, seed=5, obs_scale=None)
+    c = sac.SAC(10, None, None, device=DEV, hidden_size=128, batch_size=64, seed=6, obs_scale=None)
     for net, kin, nout in (("policy", 10, 2), ("q1", 11, 1), ("q2", 11, 1)):
         for (w, bias), (K, N) in zip(a.layers(net), ((kin, 128), (128, 128), (128, nout))):
             lim = math.sqrt(6.0 / (K + N))
@@ -153,9 +157,10 @@ def test_learner_policy_drives_the_rollout():
     from sac_maritime_ast_b200 import rollout as ro, sac
     env = G.make_env(sc.ENV_SCENARIOS["default"], n_envs=256, precision="fp32")
     agent = sac.SAC(10, None, None, device=DEV, hidden_size=64, batch_size=64, seed=1)
-    w0, _ = agent.layers("policy")[0]
-    w0.mul_(1e-4)                                    # raw observations are ~1e4 m
-    smp = ro.IntermediateWaypointSampler(env, agent.policy(), capacity=4096, num_steps_episode=200, auto_reset="hard")
+    # raw observations are ~1e4 m: the learner's default obs_scale (1 / observation_space.high) brings them into [-1, 1]
+    assert float(agent.f["obs_scale"][0]) == pytest.approx(1e-4)
+    smp = ro.IntermediateWaypointSampler(env, agent.policy(), capacity=4096, num_steps_episode=200, auto_reset="hard",
+                                         truncate_episodes=True)
     mem = sac.ReplayMemory.from_sampler(smp)
     smp.begin()
     smp.collect(30, 16)
@@ -170,3 +175,6 @@ def test_learner_policy_drives_the_rollout():
     assert not torch.equal(before, agent.f["policy"])
     rows = smp.transitions()
     assert torch.isfinite(rows[:, :23]).all() and float(rows[:, 10].abs().max()) <= 1.0
+    # the policy is not saturated: a non-trivial share of the actions lies strictly inside (-1, 1) (with raw
+    # observations tanh(mu) is exactly +-1 and every policy gradient is 0)
+    assert float((rows[:, 10].abs() < 0.999).float().mean()) > 0.5

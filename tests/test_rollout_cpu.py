@@ -21,7 +21,7 @@ def test_rollout_ref_loop_contract():
     step only, at most sampling_frequency decisions per episode, mask rule of :387."""
     from oracle import rollout_ref as rr
     p, m, e = H.oracle_env(sc.ENV_SCENARIOS["default"])
-    ref = rr.RolloutRef(p, m, e, gid=3, mode="uniform", num_steps_episode=250)
+    ref = rr.RolloutRef(p, m, e, gid=3, mode="uniform", num_steps_episode=250, truncate=True)
     eps_decisions, n_in_ep = [], 0
     for t in range(1500):
         before = len(ref.transitions)
