@@ -734,7 +734,7 @@ def rollout_leg(sit, dev, B=65536, K=32, iters=40, warm_iters=20, hidden=256, pr
     ms, ms_tail = timed(True)
     dc, ds = (smp.counters - c0).cpu().numpy(), (env.stats - s0).cpu().numpy()
     launches = smp.launches - l0
-    left_behind = int(xch.dropped.item())
+    left_behind = int(xch.dropped[0].item())
     c1 = smp.counters.clone()
     ms_plain, _ = timed(False)                             # the same number of iterations without the exchange
     dc1 = (smp.counters - c1).cpu().numpy()

@@ -7,10 +7,16 @@
  *   - extern "C", plain pointers and sizes, no torch / C++ types in any signature;
  *   - returns 0 on success or a negative SitError; never throws; sit_last_error() gives the
  *     thread-local message of the last failure;
- *   - a handle owns no simulation memory: the caller allocates ONE device buffer of
+ *   - a handle owns no SIMULATION memory: the caller allocates ONE device buffer of
  *     sit_state_bytes() bytes and passes it to every call (layout: sit_layout());
  *   - device entry points only enqueue work on the caller's CUDA stream (a cudaStream_t passed
  *     as void*; NULL = legacy default stream) and never synchronise;
+ *   - what a handle does own is SCRATCH, allocated lazily and kept until sit_destroy: the staging
+ *     buffers + 4 internal streams of the *_host entry points (first *_host call), and the policy
+ *     scratch of sit_rollout_policy / sit_rollout_collect (compact env list, MLP inputs / outputs,
+ *     the packed bf16 W1 image: ~60 B per env + 128 KiB, first rollout call; cudaMalloc is a
+ *     device-wide synchronisation, so that FIRST call is not "enqueue only").  sit_rollout_collect
+ *     runs one eager iteration before it captures its CUDA graph for exactly this reason;
  *   - the *_host entry points take HOST buffers, copy in, run, copy out and synchronise;
  *   - there is no CPU fallback: without a CUDA device every compute entry point fails.
  */
@@ -280,6 +286,19 @@ int sit_rollout_begin(SitHandle h, void* state, void* stream);
  * independent and every random draw is keyed by (global env id, decision serial, try), so no env's trajectory depends on
  * it.  Chosen from n_envs; the environment variable SIT_ROLLOUT_GROUPS overrides. */
 int sit_rollout_group_count(SitHandle h, int32_t* groups);
+
+/* ---- replay exchange after a rollout segment (the only multi-GPU exchange of the loop: main_ast.py:396 memory.push, batched).
+ * A block is [1 + block_rows][SIT_TR_FLOATS] floats: row 0 is a header whose first 8 bytes hold the int64 count of valid rows,
+ * rows 1 .. count are transitions.  block_rows is a HOST constant (e.g. policy calls per segment x n_envs), so every rank
+ * ships the same number of bytes and no counts are exchanged; nothing here synchronises with the host.
+ *   sit_replay_pack:   rows closed since *seen (device int64, SIT_RC_CLOSED at the previous pack; updated) -> block; rows
+ *                      that do not fit are counted in *dropped (device int64, may be NULL) and the newest are kept;
+ *   sit_replay_append: n_blocks blocks laid out back to back (the output of an all-gather of every rank's block) are
+ *                      appended to the ring dst [dst_capacity][SIT_TR_FLOATS] in block order, row order; *dst_count
+ *                      (device, rows ever appended) advances by the number of valid rows. */
+int sit_replay_pack(const SitRollout* ro, int64_t* seen, int64_t* dropped, float* block, int64_t block_rows, void* stream);
+int sit_replay_append(float* dst, int64_t dst_capacity, unsigned long long* dst_count, const float* blocks, int32_t n_blocks,
+                      int64_t block_rows, void* stream);
 
 /* Map predicates for n candidate waypoints (device arrays of reals): flags[i] bit 0 = inside an obstacle polygon
  * (is_route_inside_obstacles MSRL_env_ex.py:544-552 -> obstacle.py:131-136), bit 1 = outside the map AABB

@@ -104,7 +104,7 @@ RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_CLOSED, RC_N = 0, 1,
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host", "sit_fleet_step_host_sel",
            "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_group_count", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
            "sit_sac_create", "sit_sac_destroy", "sit_sac_workspace_bytes", "sit_sac_field", "sit_sac_init", "sit_sac_policy",
-           "sit_sac_update",
+           "sit_sac_update", "sit_replay_pack", "sit_replay_append",
            "sit_last_error", "sit_status_string", "sit_abi_version", "sit_measure_fma_peak")
 
 _lib = None
@@ -151,6 +151,8 @@ def lib():
     L.sit_sac_init.argtypes = [vp, vp, vp]
     L.sit_sac_policy.argtypes = [vp, vp, P(SitPolicy)]
     L.sit_sac_update.argtypes = [vp, vp, vp, I64, vp, I32, vp, I32, vp]
+    L.sit_replay_pack.argtypes = [P(SitRollout), vp, vp, vp, I64, vp]
+    L.sit_replay_append.argtypes = [vp, I64, vp, vp, I32, I64, vp]
     L.sit_last_error.restype = C.c_char_p
     L.sit_status_string.argtypes = [I32]
     L.sit_status_string.restype = C.c_char_p

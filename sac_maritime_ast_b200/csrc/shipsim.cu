@@ -2291,6 +2291,102 @@ int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K,
 }
 
 }  // extern "C"
+// =================================================================================================
+// Replay exchange: the rows of a rollout segment leave the sampler ring as ONE fixed-capacity block per rank (header row +
+// block_rows rows) and are appended, rank block after rank block, to a replay memory.  Sizes are host constants, counts
+// live in the block headers, so neither side synchronises with the host or exchanges counts.
+// =================================================================================================
+__global__ void __launch_bounds__(256) replay_pack_kernel(const float4* __restrict__ ring, const int64_t capacity,
+                                                          const unsigned long long* __restrict__ closed,
+                                                          const long long* __restrict__ seen, float4* __restrict__ block,
+                                                          const int64_t block_rows) {
+    const long long n_now = (long long)*closed, fresh = n_now - *seen;
+    const long long n = fresh < block_rows ? fresh : block_rows;          // a too-small block keeps the newest rows
+    const long long first = n_now - n;
+    const int64_t items = n * (SIT_TR_FLOATS / 4);
+    for (int64_t it = (int64_t)blockIdx.x * 256 + threadIdx.x; it < items; it += (int64_t)gridDim.x * 256) {
+        const int64_t j = it / (SIT_TR_FLOATS / 4), q = it % (SIT_TR_FLOATS / 4);
+        block[(1 + j) * (SIT_TR_FLOATS / 4) + q] = ring[((first + j) % capacity) * (SIT_TR_FLOATS / 4) + q];
+    }
+}
+__global__ void replay_pack_finish_kernel(const unsigned long long* closed, long long* seen, long long* dropped, float* block,
+                                          const int64_t block_rows) {
+    const long long n_now = (long long)*closed, fresh = n_now - *seen;
+    const long long n = fresh < block_rows ? fresh : block_rows;
+    reinterpret_cast<long long*>(block)[0] = n;                           // header row: valid rows of this block
+    if (fresh > block_rows && dropped) *dropped += fresh - block_rows;
+    *seen = n_now;
+}
+// blocks: [n_blocks][1 + block_rows][24].  Row j of block r lands at ring position (count + sum of the earlier blocks' counts
+// + j) mod capacity: rank order, row order, deterministic.  If more rows arrive than the ring holds only the newest land.
+__global__ void __launch_bounds__(256) replay_append_kernel(float4* __restrict__ dst, const int64_t capacity,
+                                                            const unsigned long long* __restrict__ count,
+                                                            const float4* __restrict__ blocks, const int n_blocks,
+                                                            const int64_t block_rows) {
+    __shared__ long long s_pre[65];
+    if (threadIdx.x == 0) {
+        long long run = 0;
+        for (int r = 0; r < n_blocks; ++r) {
+            s_pre[r] = run;
+            long long c = reinterpret_cast<const long long*>(blocks + (int64_t)r * (1 + block_rows) * (SIT_TR_FLOATS / 4))[0];
+            run += c < 0 ? 0 : (c > block_rows ? block_rows : c);
+        }
+        s_pre[n_blocks] = run;
+    }
+    __syncthreads();
+    const long long total = s_pre[n_blocks], skip = total > capacity ? total - capacity : 0;
+    const long long base = (long long)*count;
+    const int64_t items = total * (SIT_TR_FLOATS / 4);
+    for (int64_t it = (int64_t)blockIdx.x * 256 + threadIdx.x; it < items; it += (int64_t)gridDim.x * 256) {
+        const long long g = it / (SIT_TR_FLOATS / 4);
+        const int q = (int)(it % (SIT_TR_FLOATS / 4));
+        if (g < skip) continue;
+        int r = 0;
+        while (r + 1 < n_blocks && s_pre[r + 1] <= g) ++r;
+        const long long j = g - s_pre[r];
+        dst[((base + g) % capacity) * (SIT_TR_FLOATS / 4) + q] =
+            blocks[((int64_t)r * (1 + block_rows) + 1 + j) * (SIT_TR_FLOATS / 4) + q];
+    }
+}
+__global__ void replay_append_finish_kernel(unsigned long long* count, const float* blocks, const int n_blocks, const int64_t block_rows) {
+    long long run = 0;
+    for (int r = 0; r < n_blocks; ++r) {
+        long long c = reinterpret_cast<const long long*>(blocks + (int64_t)r * (1 + block_rows) * SIT_TR_FLOATS)[0];
+        run += c < 0 ? 0 : (c > block_rows ? block_rows : c);
+    }
+    *count += (unsigned long long)run;
+}
+
+extern "C" {
+
+int sit_replay_pack(const SitRollout* ro, int64_t* seen, int64_t* dropped, float* block, int64_t block_rows, void* stream) {
+    if (!ro || !ro->replay || !ro->counters || !seen || !block) return fail(SIT_E_INVALID, "null argument");
+    if (block_rows < 1 || ro->capacity < 1) return fail(SIT_E_INVALID, "block_rows and capacity must be >= 1");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int grid = (int)std::min<int64_t>((block_rows * (SIT_TR_FLOATS / 4) + 255) / 256, 148 * 8);
+    replay_pack_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(ro->replay), ro->capacity, ro->counters + SIT_RC_CLOSED,
+                                             reinterpret_cast<const long long*>(seen), reinterpret_cast<float4*>(block), block_rows);
+    replay_pack_finish_kernel<<<1, 1, 0, st>>>(ro->counters + SIT_RC_CLOSED, reinterpret_cast<long long*>(seen),
+                                               reinterpret_cast<long long*>(dropped), block, block_rows);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+int sit_replay_append(float* dst, int64_t dst_capacity, unsigned long long* dst_count, const float* blocks, int32_t n_blocks,
+                      int64_t block_rows, void* stream) {
+    if (!dst || !dst_count || !blocks) return fail(SIT_E_INVALID, "null argument");
+    if (n_blocks < 1 || n_blocks > 64 || block_rows < 1 || dst_capacity < 1) return fail(SIT_E_INVALID, "bad block geometry (1..64 blocks)");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int grid = (int)std::min<int64_t>(((int64_t)n_blocks * block_rows * (SIT_TR_FLOATS / 4) + 255) / 256, 148 * 8);
+    replay_append_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<float4*>(dst), dst_capacity, dst_count,
+                                               reinterpret_cast<const float4*>(blocks), n_blocks, block_rows);
+    replay_append_finish_kernel<<<1, 1, 0, st>>>(dst_count, blocks, n_blocks, block_rows);
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+}  // extern "C"
+
 extern "C" {
 
 int sit_env_step_k(SitHandle h, void* state, int32_t K, const SitEnvIO* io, void* stream) {
@@ -2346,27 +2442,27 @@ int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h,
     for (int j = 0; j < SIT_PIPE; ++j) CUDA_TRY(cudaStreamWaitEvent(h->pipe[j], h->pipe_in, 0));
     const int64_t chunk = ((int64_t)B / n_chunks + 255) / 256 * 256;
     int c = 0;
-    for (int64_t first = 0; first < (int64_t)B; first += chunk, ++c) {
+    cudaError_t ce = cudaSuccess;
+    auto ok = [&](cudaError_t e) { if (ce == cudaSuccess) ce = e; return e == cudaSuccess; };
+    for (int64_t first = 0; first < (int64_t)B && !rc && ce == cudaSuccess; first += chunk, ++c) {
         const int64_t cnt = std::min<int64_t>(chunk, (int64_t)B - first);
         cudaStream_t ps = h->pipe[c % SIT_PIPE];
-        CUDA_TRY(cudaMemcpy2DAsync(d + o_act + first * rs, B * rs, static_cast<const char*>(action_h) + first * rs, B * rs,
-                                   cnt * rs, 2, cudaMemcpyHostToDevice, ps));
-        if (sac_update_h) CUDA_TRY(cudaMemcpyAsync(d + o_sac + first, sac_update_h + first, cnt, cudaMemcpyHostToDevice, ps));
+        if (!ok(cudaMemcpy2DAsync(d + o_act + first * rs, B * rs, static_cast<const char*>(action_h) + first * rs, B * rs,
+                                  cnt * rs, 2, cudaMemcpyHostToDevice, ps))) break;
+        if (sac_update_h && !ok(cudaMemcpyAsync(d + o_sac + first, sac_update_h + first, cnt, cudaMemcpyHostToDevice, ps))) break;
         rc = h->cfg.precision == SIT_F64 ? env_step_t<double>(h, state, K, &io, ps, first, cnt)
                                          : env_step_t<float>(h, state, K, &io, ps, first, cnt);
-        if (rc) { join_pipes(h, st); return rc; }
-        if (obs_h)
-            CUDA_TRY(cudaMemcpy2DAsync(static_cast<char*>(obs_h) + first * rs, B * rs, d + o_obs + first * rs, B * rs, cnt * rs,
-                                       SIT_N_OBS, cudaMemcpyDeviceToHost, ps));
-        if (reward_h)
-            CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(reward_h) + first * rs, d + o_rew + first * rs, cnt * rs, cudaMemcpyDeviceToHost, ps));
-        if (done_h) CUDA_TRY(cudaMemcpyAsync(done_h + first, d + o_done + first, cnt, cudaMemcpyDeviceToHost, ps));
-        if (status_h) CUDA_TRY(cudaMemcpyAsync(status_h + first, d + o_st + first * 4, cnt * 4, cudaMemcpyDeviceToHost, ps));
+        if (rc) break;
+        if (obs_h && !ok(cudaMemcpy2DAsync(static_cast<char*>(obs_h) + first * rs, B * rs, d + o_obs + first * rs, B * rs, cnt * rs,
+                                           SIT_N_OBS, cudaMemcpyDeviceToHost, ps))) break;
+        if (reward_h && !ok(cudaMemcpyAsync(static_cast<char*>(reward_h) + first * rs, d + o_rew + first * rs, cnt * rs,
+                                            cudaMemcpyDeviceToHost, ps))) break;
+        if (done_h && !ok(cudaMemcpyAsync(done_h + first, d + o_done + first, cnt, cudaMemcpyDeviceToHost, ps))) break;
+        if (status_h && !ok(cudaMemcpyAsync(status_h + first, d + o_st + first * 4, cnt * 4, cudaMemcpyDeviceToHost, ps))) break;
     }
-    for (int j = 0; j < SIT_PIPE; ++j) {
-        CUDA_TRY(cudaEventRecord(h->pipe_done[j], h->pipe[j]));
-        CUDA_TRY(cudaStreamWaitEvent(st, h->pipe_done[j], 0));
-    }
+    join_pipes(h, st);   // also after an error: the forked work is joined before the call returns
+    if (rc) return rc;
+    if (ce != cudaSuccess) return fail(SIT_E_CUDA, std::string("sit_env_step_host: ") + cudaGetErrorString(ce));
     CUDA_TRY(cudaStreamSynchronize(st));
     return SIT_OK;
 }

@@ -229,12 +229,12 @@ class ReplayExchange:
     synchronisation, collective on a side stream.
 
     A rollout segment of ``iterations`` policy calls opens at most ``iterations * n_envs`` rows per rank (one decision per env
-    and policy call), so every rank ships one block of exactly that many rows; rows past the segment's count carry env id -1
-    and are dropped on arrival by a device-side compaction (``ReplayMemory.extend_masked``).  ``pack()`` copies the segment's
-    rows out of the sampler ring on the caller's stream (so the next segment may overwrite the ring), ``exchange()`` runs the
-    all-gather and the append on a side stream and returns an event: the next ``sampler.collect`` overlaps it, and only the
-    consumer of the memory (the learner) waits.  With one rank the block is appended directly.  CPU tensors (the gloo tests)
-    take the same path without streams."""
+    and policy call), so every rank ships one block of exactly ``1 + block_rows`` rows (header row with the count, then the
+    rows; layout in include/shipsim.h next to sit_replay_pack).  ``pack()`` copies the segment's rows out of the sampler ring
+    on the caller's stream (sit_replay_pack: the next segment may then overwrite the ring); ``exchange()`` runs the all-gather
+    and the append (sit_replay_append: block order = rank order, row order) on a side stream and returns an event: the next
+    ``sampler.collect`` overlaps it and only the consumer of the memory (the learner) waits.  With one rank the block is
+    appended directly.  CPU tensors (the world-size-2 gloo tests of the host logic) take the same steps with torch ops."""
 
     def __init__(self, sampler: "IntermediateWaypointSampler", block_rows: int, group=None):
         self.smp, self.block, self.group = sampler, int(block_rows), group
@@ -242,28 +242,33 @@ class ReplayExchange:
         self.cuda = dev.type == "cuda"
         import torch.distributed as dist
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
-        self.ar = torch.arange(self.block, device=dev, dtype=torch.int64)
-        self.seen = torch.zeros((), dtype=torch.int64, device=dev)        # SIT_RC_CLOSED at the previous pack (device)
-        self.dropped = torch.zeros((), dtype=torch.int64, device=dev)     # rows a too-small block had to leave behind
-        self.send = torch.zeros((self.block, TR_FLOATS), dtype=torch.float32, device=dev)
-        self.recv = torch.zeros((self.world * self.block, TR_FLOATS), dtype=torch.float32, device=dev) if self.world > 1 else self.send
+        self.seen = torch.zeros(1, dtype=torch.int64, device=dev)        # SIT_RC_CLOSED at the previous pack (device)
+        self.dropped = torch.zeros(1, dtype=torch.int64, device=dev)     # rows a too-small block had to leave behind
+        self.send = torch.zeros((1 + self.block, TR_FLOATS), dtype=torch.float32, device=dev)
+        self.recv = (torch.zeros((self.world * (1 + self.block), TR_FLOATS), dtype=torch.float32, device=dev)
+                     if self.world > 1 else self.send)
         self.side = torch.cuda.Stream(device=dev) if self.cuda else None
         self.done = None
+        self.L = _lib.lib() if self.cuda else None
 
     def pack(self):
         """Copy the rows closed since the previous pack into the send block (caller's stream, no host sync)."""
         smp = self.smp
-        if self.cuda and self.done is not None:
-            torch.cuda.current_stream(self.send.device).wait_event(self.done)     # the previous exchange has read `send`
-        n_now = smp.counters[_lib.RC_CLOSED]
-        new = n_now - self.seen
-        self.dropped += torch.clamp(new - self.block, min=0)
-        first = torch.where(new > self.block, n_now - self.block, self.seen)      # keep the newest rows if the block is too small
-        idx = (first + self.ar) % smp.capacity
-        torch.index_select(smp.replay, 0, idx, out=self.send)
-        ids = self.send[:, 23].view(torch.int32)
-        ids.masked_fill_(self.ar >= new, -1)
-        self.seen.copy_(n_now)
+        if self.cuda:
+            cur = torch.cuda.current_stream(self.send.device)
+            if self.done is not None:
+                cur.wait_event(self.done)                                   # the previous exchange has read `send`
+            _lib.check(self.L.sit_replay_pack(C.byref(smp.ro), self.seen.data_ptr(), self.dropped.data_ptr(),
+                                              self.send.data_ptr(), self.block, cur.cuda_stream))
+            return
+        n_now = int(smp.counters[_lib.RC_CLOSED])
+        fresh = n_now - int(self.seen)
+        n = min(fresh, self.block)
+        idx = (torch.arange(n_now - n, n_now)) % smp.capacity
+        self.send[1:1 + n] = smp.replay[idx]
+        self.send[0].view(torch.int64)[0] = n
+        self.dropped += max(fresh - self.block, 0)
+        self.seen.fill_(n_now)
 
     def exchange(self, memory) -> Optional["torch.cuda.Event"]:
         """All-gather the packed blocks of every rank and append the valid rows to ``memory`` (rank order, row order)."""
@@ -271,20 +276,24 @@ class ReplayExchange:
         if not self.cuda:
             if self.world > 1:
                 dist.all_gather_into_tensor(self.recv, self.send, group=self.group)
-            memory.extend_masked(self.recv)
+            memory.append_blocks(self.recv, self.world, self.block)
             return None
         cur = torch.cuda.current_stream(self.send.device)
         self.side.wait_stream(cur)
         with torch.cuda.stream(self.side):
             if self.world > 1:
                 dist.all_gather_into_tensor(self.recv, self.send, group=self.group)
-            memory.extend_masked(self.recv)
+            memory.append_blocks(self.recv, self.world, self.block)
             self.done = self.side.record_event()
         return self.done
 
     def wait(self):
         if self.cuda and self.done is not None:
             torch.cuda.current_stream(self.send.device).wait_event(self.done)
+
+    def rows(self) -> torch.Tensor:
+        """The valid rows of this rank's last packed block (host sync: for logging only)."""
+        return self.send[1:1 + int(self.send[0].view(torch.int64)[0].item())]
 
 
 def reduce_stats(stats: torch.Tensor, group=None) -> torch.Tensor:

@@ -36,9 +36,7 @@ class ReplayMemory:
 
     def __init__(self, capacity: int, seed: int = 25450, device="cuda"):
         self.capacity, self.seed, self.device = int(capacity), int(seed), torch.device(device)
-        # one spare row past the ring: the scatter of extend_masked parks dropped rows there
-        self._store = torch.zeros((self.capacity + 1, TR_FLOATS), dtype=torch.float32, device=self.device)
-        self.buffer = self._store[:self.capacity]
+        self.buffer = torch.zeros((self.capacity, TR_FLOATS), dtype=torch.float32, device=self.device)
         self.count = torch.zeros(1, dtype=torch.int64, device=self.device)      # rows ever pushed (device counter)
         self._gen = torch.Generator(device=self.device).manual_seed(self.seed)
 
@@ -48,7 +46,6 @@ class ReplayMemory:
         m.capacity, m.seed, m.device = sampler.capacity, int(sampler.ro.seed), sampler.replay.device
         # completed rows only (SIT_RC_CLOSED): a row opened by the policy call is not drawn before its step has closed it
         m.buffer, m.count = sampler.replay, sampler.counters[_lib.RC_CLOSED:_lib.RC_CLOSED + 1]
-        m._store = None
         m._gen = torch.Generator(device=m.device).manual_seed(m.seed)
         return m
 
@@ -65,21 +62,19 @@ class ReplayMemory:
         self.buffer[pos] = rows.to(self.device, torch.float32)
         self.count += n
 
-    def extend_masked(self, rows: torch.Tensor):
-        """Append the rows whose env id (column 23, int32 bits) is >= 0, in order, WITHOUT a host synchronisation: ring
-        positions come from a device prefix sum over the validity flags, dropped rows are scattered to the spare row.
-        The fixed-capacity exchange of ``rollout.ReplayExchange`` ends here."""
-        if getattr(self, "_store", None) is None:
-            raise ValueError("extend_masked needs a memory that owns its ring (not from_sampler)")
-        rows = rows.to(self.device, torch.float32)
-        valid = rows[:, 23].contiguous().view(torch.int32) >= 0
-        rank = torch.cumsum(valid.to(torch.int64), 0) - 1
-        n_valid = rank[-1] + 1 if rows.shape[0] else torch.zeros((), dtype=torch.int64, device=self.device)
-        # if more valid rows arrive than the ring holds, only the last `capacity` of them may land (no duplicate positions)
-        keep = valid & (rank >= n_valid - self.capacity)
-        pos = torch.where(keep, (self.count + rank) % self.capacity, torch.full_like(rank, self.capacity))
-        self._store.index_copy_(0, pos, rows)
-        self.count += n_valid
+    def append_blocks(self, blocks: torch.Tensor, n_blocks: int, block_rows: int):
+        """Append the valid rows of ``n_blocks`` exchange blocks ([1 + block_rows][24] each: header row with the int64 count,
+        then the rows; include/shipsim.h sit_replay_append) in block order, row order, WITHOUT a host synchronisation on the
+        device path.  The fixed-capacity exchange of ``rollout.ReplayExchange`` ends here."""
+        if self.device.type == "cuda":
+            _lib.check(_lib.lib().sit_replay_append(self.buffer.data_ptr(), self.capacity, self.count.data_ptr(),
+                                                    blocks.data_ptr(), int(n_blocks), int(block_rows),
+                                                    torch.cuda.current_stream(self.device).cuda_stream))
+            return
+        b = blocks.view(n_blocks, 1 + block_rows, TR_FLOATS)           # host logic of the gloo tests
+        for r in range(n_blocks):
+            n = max(0, min(int(b[r, 0].view(torch.int64)[0]), block_rows))
+            self.extend(b[r, 1:1 + n])
 
     def push(self, state, action, reward, next_state, mask):
         row = torch.zeros(TR_FLOATS, dtype=torch.float32, device=self.device)

@@ -145,7 +145,7 @@ def main(argv=None):
         if losses is not None:
             ls = losses.tolist()
             rec.update(critic_1_loss=ls[0], critic_2_loss=ls[1], policy_loss=ls[2], ent_loss=ls[3], alpha=ls[4])
-        new_rows = xch.send[xch.send[:, 23].view(torch.int32) >= 0]
+        new_rows = xch.rows()
         rec["mean_reward_of_new_rows"] = float(new_rows[:, 11].mean()) if new_rows.shape[0] else None
         rec["share_of_unsaturated_actions"] = float((new_rows[:, 10].abs() < 0.999).float().mean()) if new_rows.shape[0] else None
         rec["rows_left_behind"] = int(xch.dropped.item())

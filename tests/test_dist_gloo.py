@@ -29,7 +29,7 @@ def _worker(rank, world, port, q):
     stats = torch.arange(16, dtype=torch.int64) * (rank + 1)
     tot = reduce_stats(stats)
     empty = gather_replay(torch.zeros((0, 24)) if rank == 0 else rows[:2])   # ragged incl. an empty rank
-    # fixed-capacity exchange (ReplayExchange): no count exchange, padding rows carry env id -1 and are dropped on arrival.
+    # fixed-capacity exchange (ReplayExchange): no count exchange, every block carries its own count in a header row.
     # A stand-in sampler: a ring, its counters, its capacity.  Two segments; rank 1's second segment is empty.
     from types import SimpleNamespace
     from sac_maritime_ast_b200 import _lib
@@ -49,7 +49,7 @@ def _worker(rank, world, port, q):
             ring[slot, 23] = torch.tensor(rank, dtype=torch.int32).view(torch.float32)
         counters[_lib.RC_CLOSED] += k; counters[_lib.RC_TRANSITIONS] += k
         xch.pack(); xch.exchange(mem)
-    q.put((rank, allrows.clone(), tot.clone(), empty.shape[0], n, mem.buffer[:len(mem)].clone(), int(xch.dropped)))
+    q.put((rank, allrows.clone(), tot.clone(), empty.shape[0], n, mem.buffer[:len(mem)].clone(), int(xch.dropped[0])))
     dist.barrier()
     dist.destroy_process_group()
 

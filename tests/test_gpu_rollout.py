@@ -94,7 +94,7 @@ def test_gaussian_policy_actions_match_torch_reference(tc, hidden):
     obs = co.t().contiguous().float()
     smp.policy_step()
     torch.cuda.synchronize()
-    rows = _by_env(smp.transitions())
+    rows = _by_env(smp.replay[:smp.n_opened()])          # opened rows: state + action are written, the step closes them
     mu, logsig = pol.mu_logsig(obs)
     mu, sig = mu.cpu().numpy(), torch.exp(logsig).cpu().numpy()
     e_ab = smp.env.f["ab_seg"].cpu().numpy(), smp.env.f["ab_alpha"].cpu().numpy()
@@ -255,18 +255,24 @@ def test_replay_ring_order_is_deterministic_and_closed_rows_are_counted():
     for _ in range(2):
         smp = _make(5000, "fp32", pol, cap=200, auto_reset="hard")
         smp.begin()
-        smp.collect(12, 16, graph=True)
+        smp.collect(20, 32, graph=True)
         torch.cuda.synchronize()
         c = smp.counters.cpu().numpy()
         assert c[_lib.RC_CLOSED] == c[_lib.RC_TRANSITIONS] == c[_lib.RC_DECISIONS] > 5000
         rings.append((smp.replay.clone(), c.copy()))
         ids = smp.replay[:5000, 23].contiguous().view(torch.int32)
         assert torch.equal(ids, torch.arange(5000, dtype=torch.int32, device=ids.device)), "first decisions are in env order"
-        # a policy call opens rows that only the next step launch completes
-        smp.policy_step()
-        torch.cuda.synchronize()
-        c2 = smp.counters.cpu().numpy()
-        opened = int(c2[_lib.RC_TRANSITIONS] - c[_lib.RC_TRANSITIONS])
+        # a policy call opens rows that only the next step launch completes (step on until some env reaches a decision)
+        opened = 0
+        for _ in range(200):
+            c = smp.counters.cpu().numpy()
+            smp.policy_step()
+            torch.cuda.synchronize()
+            c2 = smp.counters.cpu().numpy()
+            opened = int(c2[_lib.RC_TRANSITIONS] - c[_lib.RC_TRANSITIONS])
+            if opened:
+                break
+            smp.env_steps(8)
         assert opened > 0 and c2[_lib.RC_CLOSED] == c[_lib.RC_CLOSED] and smp.n_transitions() == int(c[_lib.RC_CLOSED])
         smp.env_steps(1)
         torch.cuda.synchronize()
