@@ -52,6 +52,12 @@ enum { SIT_F64 = 0, SIT_F32 = 1 };            /* arithmetic of the step kernels 
 enum { SIT_KIND_FLEET = 1, SIT_KIND_ENV = 2 };/* bare ships | two-ship AST envs */
 enum { SIT_SG_MOTOR = 0, SIT_SG_GEN = 1, SIT_SG_OFF = 2 }; /* ship_engine.py:32-44 */
 enum { SIT_ROLE_TEST = 0, SIT_ROLE_OBS = 1 };
+/* machinery model of a ship: ShipMachineryModel (ship_engine.py:298-395: shaft-speed state, torque caps) or
+ * SimplifiedMachineryModel (ship_engine.py:398-433: thrust force as a first-order lag of the commanded power, driven by
+ * ThrottleFromSpeedSetPointSimplifiedPropulsion controllers.py:154-172).  The simplified model is a FLEET-only variant: the
+ * reference's MultiShipRLEnv calls throttle(speed_set_point, measured_speed, measured_shaft_speed) and reads the shaft
+ * rpm, which only the full model has. */
+enum { SIT_MACH_FULL = 0, SIT_MACH_SIMPLIFIED = 1 };
 
 /* status bits; strings at MSRL_env_ex.py:760-899 (sit_status_string) */
 enum {
@@ -77,7 +83,7 @@ typedef struct SitShipParams {
            mass_over_linear_friction_coefficient_in_yaw;
     double nonlinear_friction_coefficient__in_surge, nonlinear_friction_coefficient__in_sway,
            nonlinear_friction_coefficient__in_yaw;
-    int32_t n_modes, _pad0;
+    int32_t n_modes, machinery_kind;   /* SIT_MACH_* */
     double mode_main_engine_capacity[SIT_MAX_MODES], mode_electrical_capacity[SIT_MAX_MODES];
     int32_t mode_shaft_generator_state[SIT_MAX_MODES];
     double hotel_load;
@@ -90,6 +96,10 @@ typedef struct SitShipParams {
     double kp_ship_speed, ki_ship_speed, kp_shaft_speed, ki_shaft_speed;
     double kp_heading, kd_heading, ki_heading;
     double radius_of_acceptance, lookahead_distance, los_integral_gain, los_integrator_windup_limit;
+    /* SIT_MACH_SIMPLIFIED only: SimplifiedPropulsionMachinerySystemConfiguration.thrust_force_dynamic_time_constant
+     * (ship_engine.py:148-157) and the kp, ki of ThrottleFromSpeedSetPointSimplifiedPropulsion (controllers.py:160-168).
+     * The thrust force [N] is the machinery state: it lives in the state field "omega" (initial_thrust_force at reset). */
+    double thrust_force_dynamic_time_constant, kp_simplified, ki_simplified;
 } SitShipParams;
 
 /* PolygonObstacle (obstacle.py:92-148): ring segments in (x, y) = (east, north), one poly id per
@@ -199,6 +209,11 @@ typedef struct SitEnvIO {
                                 reward_function :924-964): test_ship reward_e_ct, reward_near_col, total_non_terminal;
                                 obs_ship reward_base, reward_e_ct, reward_near_col, total_non_terminal; shared
                                 total_non_terminal */
+    uint8_t* snap;           /* [rec_steps][n_envs], may be NULL; needs rec_steps == K.  1 where the reference would have called
+                                ship_snap_shot() on both ships in that step (`ship_draw`, MSRL_env_ex.py:416-421: timer > 30 s ->
+                                snapshot, timer = 0; then timer += dt).  The timer is the env state field "draw_t" (seconds, f64;
+                                the constructor argument time_since_last_ship_drawing, never reset by reset()).  The outline
+                                rows are sit_ship_outline of that step's obs pose (obs 0,1,2 / 6,7,8). */
 } SitEnvIO;
 
 /* MultiShipRLEnv.reset (MSRL_env_ex.py:145-186): same as sit_reset on an env handle */
@@ -304,6 +319,17 @@ int sit_replay_append(float* dst, int64_t dst_capacity, unsigned long long* dst_
  * (is_route_inside_obstacles MSRL_env_ex.py:544-552 -> obstacle.py:131-136), bit 1 = outside the map AABB
  * (is_route_outside_horizon :517-542); dist[i] = obstacles_distance (obstacle.py:138-141).  flags / dist may be NULL. */
 int sit_map_query(SitHandle h, int64_t n, const void* north, const void* east, uint8_t* flags, void* dist, void* stream);
+
+/* ---- model variants and snapshot data ------------------------------------------------------------------
+ * StaticObstacle (obstacle.py:8-90): n_circles rows (north, east, radius) of HOST doubles; for n points (device reals of
+ * `precision`): flags[i] = 1 if inside or on any circle (if_ship_inside_obstacles / if_route_inside_obstacles :69-85),
+ * dist[i] = obstacles_distance :55-67 (negative inside).  flags / dist may be NULL.  Needs no handle: circles are not part
+ * of MultiShipRLEnv (it requires PolygonObstacle.map_boundaries). */
+int sit_circle_query(int32_t precision, int32_t n_circles, const double* circles, int64_t n, const void* north, const void* east,
+                     uint8_t* flags, void* dist, void* stream);
+/* ship_snap_shot (ship_model.py:326-338, ShipDraw utils.py:56-101) for n poses (device reals): x_ned, y_ned [n][6], the
+ * closed outline of the 80 m x 20 m hull rotated by psi and translated to (north, east).  Legacy default stream. */
+int sit_ship_outline(int32_t precision, int64_t n, const void* north, const void* east, const void* psi, void* x_ned, void* y_ned);
 
 /* ---- SAC learner (the step after the path: the empty ast_core/algorithms/sac.py; call contract
  * `critic_1_loss, critic_2_loss, policy_loss, ent_loss, alpha = agent.update_parameters(memory, batch_size, updates)`

@@ -42,6 +42,8 @@ class OrcParams(C.Structure):
         ("mass", D), ("i_z", D), ("x_du", D), ("y_dv", D), ("n_dr", D), ("proj_area_f", D), ("proj_area_l", D),
         ("rho_a", D), ("cx", D), ("cy", D), ("cn", D), ("rudder_max", D),
         ("avail_total", D * MAX_MODES), ("avail_me", D * MAX_MODES), ("avail_el", D * MAX_MODES),
+        ("mach_kind", C.c_int), ("_pad_mach", C.c_int),
+        ("thrust_time_constant", D), ("kp_simplified", D), ("ki_simplified", D),
     ]
 
 

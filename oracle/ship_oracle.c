@@ -144,10 +144,18 @@ void orc_ship_step(const OrcParams* p, OrcShip* s, int avoid, int store, double*
      *     MSRL_env_ex.py:233-237,358-362) --- */
     double e1 = s->u_sp - u;
     s->ei_speed = s->ei_speed + e1 * dt;
-    double omega_des = e1 * p->kp_speed + s->ei_speed * p->ki_speed;
-    double e2 = omega_des - u;
-    s->ei_shaft = s->ei_shaft + e2 * dt;
-    double thr = e2 * p->kp_shaft + s->ei_shaft * p->ki_shaft;
+    double thr;
+    if (p->mach_kind == 1) {
+        /* controllers.py:170-172 ThrottleFromSpeedSetPointSimplifiedPropulsion.throttle: pi_ctrl (:51-61) then
+         * sat(val, 0, 1.1) = max(low, min(val, hi)) (:63-69) */
+        thr = e1 * p->kp_simplified + s->ei_speed * p->ki_simplified;
+        thr = sat(thr, 0.0, 1.1);
+    } else {
+        double omega_des = e1 * p->kp_speed + s->ei_speed * p->ki_speed;
+        double e2 = omega_des - u;
+        s->ei_shaft = s->ei_shaft + e2 * dt;
+        thr = e2 * p->kp_shaft + s->ei_shaft * p->ki_shaft;
+    }
 
     /* --- MSRL_env_ex.py:240-249 collision-avoidance branch (always taken for the test ship, Q2) --- */
     if (avoid) {
@@ -181,7 +189,7 @@ void orc_ship_step(const OrcParams* p, OrcShip* s, int avoid, int store, double*
             log27[5] = u;
             log27[6] = s->v;
             log27[7] = s->r * 180 / M_PI;
-            log27[8] = omega * 30 / M_PI;
+            log27[8] = p->mach_kind == 1 ? 0.0 : omega * 30 / M_PI;   /* the simplified model has no shaft */
             log27[9] = pct_me;
             log27[10] = pct_el;
             log27[11] = load_me / 1000;
@@ -196,8 +204,8 @@ void orc_ship_step(const OrcParams* p, OrcShip* s, int avoid, int store, double*
             log27[20] = s->fuel_me;
             log27[21] = s->fuel_el;
             log27[22] = s->fuel;
-            log27[23] = torque_limited(thr, p->avail_me[mode], omega);
-            log27[24] = pow(p->dp, 4) * p->kt * omega * fabs(omega) / 1000;
+            log27[23] = p->mach_kind == 1 ? 0.0 : torque_limited(thr, p->avail_me[mode], omega);
+            log27[24] = p->mach_kind == 1 ? omega / 1000 : pow(p->dp, 4) * p->kt * omega * fabs(omega) / 1000;
             log27[25] = s->e_ct;
             log27[26] = fabs(s->heading_mea - s->heading_ref);  /* radians, despite the key (Q12) */
         }
@@ -210,14 +218,23 @@ void orc_ship_step(const OrcParams* p, OrcShip* s, int avoid, int store, double*
     double d_yaw = s->r;
 
     /* --- ship_engine.py:391-395,355-361 shaft equation --- */
-    double t_me = torque_limited(thr, p->avail_me[mode], omega);
-    double t_hsg = torque_limited(thr, p->avail_el[mode], omega);
-    double eq_me = (t_me - p->d_me * omega) / p->r_me;
-    double eq_hsg = (t_hsg - p->d_hsg * omega) / p->r_hsg;
-    double d_omega = (eq_me + eq_hsg - p->kp_torque * (omega * omega)) / p->jp;
-
-    /* --- ship_engine.py:363-366 thrust (pre-update omega) --- */
-    double thrust = pow(p->dp, 4) * p->kt * omega * fabs(omega);
+    double d_omega, thrust;
+    if (p->mach_kind == 1) {
+        /* ship_engine.py:423-428 update_thrust_force: power = load_perc * (P_me + P_el);
+         * d_thrust = (-k_thrust * thrust + power) / T, k_thrust = 2160 / 790 (:420); the kinetics get the PRE-update thrust
+         * (the order of ShipModel.update_differentials, ship_model.py:484-490) */
+        double power = thr * (p->avail_me[mode] + p->avail_el[mode]);
+        d_omega = (-(2160.0 / 790.0) * omega + power) / p->thrust_time_constant;
+        thrust = omega;
+    } else {
+        double t_me = torque_limited(thr, p->avail_me[mode], omega);
+        double t_hsg = torque_limited(thr, p->avail_el[mode], omega);
+        double eq_me = (t_me - p->d_me * omega) / p->r_me;
+        double eq_hsg = (t_hsg - p->d_hsg * omega) / p->r_hsg;
+        d_omega = (eq_me + eq_hsg - p->kp_torque * (omega * omega)) / p->jp;
+        /* --- ship_engine.py:363-366 thrust (pre-update omega) --- */
+        thrust = pow(p->dp, 4) * p->kt * omega * fabs(omega);
+    }
 
     /* --- ship_model.py:576-622 kinetics --- */
     /* current to body frame: inv(R) * v_c */

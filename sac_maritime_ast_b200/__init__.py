@@ -9,9 +9,11 @@ from .config import (  # noqa: F401
     DEFAULT_MAP, EngineThrottleFromSpeedSetPoint, EnvironmentConfiguration, FuelConsumptionCoefficients,
     HeadingByRouteController, HeadingBySampledRouteController, HeadingControllerGains, LosParameters,
     MachineryMode, MachineryModeParams, MachineryModes, MachinerySystemConfiguration, PolygonObstacle,
-    ShipConfiguration, ShipModel, ShipModelAST, SimulationConfiguration,
+    ShipConfiguration, ShipDraw, ShipModel, ShipModelAST, ShipModelSimplifiedPropulsion, SimplifiedMachineryModel,
+    SimplifiedPropulsionMachinerySystemConfiguration, SimulationConfiguration, StaticObstacle,
+    ThrottleFromSpeedSetPointSimplifiedPropulsion,
     SpecificFuelConsumptionBaudouin6M26Dot3, SpecificFuelConsumptionWartila6L26, ThrottleControllerGains,
-    default_ship, ship_params)
+    default_ship, ship_params, simplified_ship)
 from .env import MultiShipRLEnv, ShipAssets  # noqa: F401
 from .fleet import ShipFleet  # noqa: F401
 from .results import LOG_KEYS, REWARD_KEYS, RewardResults, SimulationResults  # noqa: F401

@@ -30,7 +30,7 @@ class SitShipParams(C.Structure):
         ("mass_over_linear_friction_coefficient_in_yaw", D),
         ("nonlinear_friction_coefficient__in_surge", D), ("nonlinear_friction_coefficient__in_sway", D),
         ("nonlinear_friction_coefficient__in_yaw", D),
-        ("n_modes", I32), ("_pad0", I32),
+        ("n_modes", I32), ("machinery_kind", I32),
         ("mode_main_engine_capacity", D * MAX_MODES), ("mode_electrical_capacity", D * MAX_MODES),
         ("mode_shaft_generator_state", I32 * MAX_MODES),
         ("hotel_load", D),
@@ -46,6 +46,7 @@ class SitShipParams(C.Structure):
         ("kp_heading", D), ("kd_heading", D), ("ki_heading", D),
         ("radius_of_acceptance", D), ("lookahead_distance", D), ("los_integral_gain", D),
         ("los_integrator_windup_limit", D),
+        ("thrust_force_dynamic_time_constant", D), ("kp_simplified", D), ("ki_simplified", D),
     ]
 
 
@@ -75,7 +76,7 @@ class SitEnvIO(C.Structure):
                 ("auto_reset", I32), ("rec_steps", I32),
                 ("obs", C.c_void_p), ("reward", C.c_void_p), ("done", C.c_void_p), ("status", C.c_void_p),
                 ("reward_sum", C.c_void_p), ("done_any", C.c_void_p), ("stats", C.c_void_p),
-                ("reward_parts", C.c_void_p)]
+                ("reward_parts", C.c_void_p), ("snap", C.c_void_p)]
 
 
 class SitPolicy(C.Structure):
@@ -97,6 +98,8 @@ class SitSacConfig(C.Structure):
 
 N_REWARD_PARTS = 8
 TR_FLOATS = 24
+MACH_FULL, MACH_SIMPLIFIED = 0, 1
+MAX_CIRCLES = 64
 POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
 POLICY_TC_BF16 = 0x100
 RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_CLOSED, RC_N = 0, 1, 2, 3, 4, 8
@@ -104,7 +107,7 @@ RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_CLOSED, RC_N = 0, 1,
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host", "sit_fleet_step_host_sel",
            "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_group_count", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
            "sit_sac_create", "sit_sac_destroy", "sit_sac_workspace_bytes", "sit_sac_field", "sit_sac_init", "sit_sac_policy",
-           "sit_sac_update", "sit_replay_pack", "sit_replay_append",
+           "sit_sac_update", "sit_replay_pack", "sit_replay_append", "sit_circle_query", "sit_ship_outline",
            "sit_last_error", "sit_status_string", "sit_abi_version", "sit_measure_fma_peak")
 
 _lib = None
@@ -153,6 +156,8 @@ def lib():
     L.sit_sac_update.argtypes = [vp, vp, vp, I64, vp, I32, vp, I32, vp]
     L.sit_replay_pack.argtypes = [P(SitRollout), vp, vp, vp, I64, vp]
     L.sit_replay_append.argtypes = [vp, I64, vp, vp, I32, I64, vp]
+    L.sit_circle_query.argtypes = [I32, I32, vp, I64, vp, vp, vp, vp, vp]
+    L.sit_ship_outline.argtypes = [I32, I64, vp, vp, vp, vp, vp]
     L.sit_last_error.restype = C.c_char_p
     L.sit_status_string.argtypes = [I32]
     L.sit_status_string.restype = C.c_char_p

@@ -115,6 +115,19 @@ class MachinerySystemConfiguration(NamedTuple):
     specific_fuel_consumption_coefficients_dg: FuelConsumptionCoefficients
 
 
+class SimplifiedPropulsionMachinerySystemConfiguration(NamedTuple):
+    """ship_engine.py:148-157."""
+    hotel_load: float
+    machinery_modes: MachineryModes
+    machinery_operating_mode: int
+    specific_fuel_consumption_coefficients_me: FuelConsumptionCoefficients
+    specific_fuel_consumption_coefficients_dg: FuelConsumptionCoefficients
+    thrust_force_dynamic_time_constant: float
+    rudder_angle_to_sway_force_coefficient: float
+    rudder_angle_to_yaw_force_coefficient: float
+    max_rudder_angle_degrees: float
+
+
 # ---- controllers.py:16-38, LOS_guidance.py:15-19 ---------------------------------------------------
 class ThrottleControllerGains(NamedTuple):
     kp_ship_speed: float
@@ -165,6 +178,41 @@ class ShipModelAST:
 ShipModel = ShipModelAST  # ship_model.py:406-542: identical on the step path
 
 
+class SimplifiedMachineryModel:
+    """ship_engine.py:398-433 -- configuration holder: thrust force as a first-order lag of the commanded power,
+    ``d_thrust = (-k_thrust thrust + load_perc (P_me + P_el)) / T`` with ``k_thrust = 2160 / 790``."""
+
+    def __init__(self, machinery_config: SimplifiedPropulsionMachinerySystemConfiguration, time_step: float,
+                 initial_thrust_force: float):
+        self.machinery_config, self.time_step = machinery_config, float(time_step)
+        self.thrust = float(initial_thrust_force)
+        self.k_thrust = 2160 / 790
+        self.thrust_time_constant = machinery_config.thrust_force_dynamic_time_constant
+
+
+class ShipModelSimplifiedPropulsion:
+    """A hull (``BaseShipModel`` kinematics / ``three_dof_kinetics(thrust_force=..., rudder_angle=...)``,
+    ship_model.py:233-250,436-466) propelled by a ``SimplifiedMachineryModel``.  The reference ships the machinery and the
+    throttle controller classes (ship_engine.py:398-433, controllers.py:154-172) but no ship class that joins them; this
+    holder is that join, in the order of ``ShipModel.update_differentials`` (ship_model.py:484-490): kinematics,
+    ``update_thrust_force(throttle)``, kinetics with the pre-update thrust, Euler step of hull and thrust.
+    Runs as SIT_MACH_SIMPLIFIED in a ``ShipFleet`` (the state field ``omega`` then holds the thrust force [N])."""
+
+    def __init__(self, ship_config: ShipConfiguration, simulation_config: SimulationConfiguration,
+                 environment_config: EnvironmentConfiguration,
+                 machinery_config: SimplifiedPropulsionMachinerySystemConfiguration, initial_thrust_force: float):
+        self.ship_config, self.simulation_config = ship_config, simulation_config
+        self.environment_config, self.machinery_config = environment_config, machinery_config
+        self.ship_machinery_model = SimplifiedMachineryModel(machinery_config, simulation_config.integration_step,
+                                                             initial_thrust_force)
+        # ShipFleet.init_from_config writes this into the machinery state slot
+        self.initial_propeller_shaft_speed_rad_per_s = float(initial_thrust_force)
+        self.north = float(simulation_config.initial_north_position_m)
+        self.east = float(simulation_config.initial_east_position_m)
+        self.yaw_angle = float(simulation_config.initial_yaw_angle_rad)
+        self.l_ship = ship_config.length_of_ship
+
+
 class EngineThrottleFromSpeedSetPoint:
     """controllers.py:108-136."""
 
@@ -174,6 +222,14 @@ class EngineThrottleFromSpeedSetPoint:
         self.max_shaft_speed = max_shaft_speed
         self.time_step = time_step
         self.initial_shaft_speed_integral_error = float(initial_shaft_speed_integral_error)
+
+
+class ThrottleFromSpeedSetPointSimplifiedPropulsion:
+    """controllers.py:154-172: ``sat(PI(speed set point, speed), 0, 1.1)``."""
+
+    def __init__(self, kp: float, ki: float, time_step: float):
+        self.kp, self.ki, self.time_step = float(kp), float(ki), float(time_step)
+        self.initial_shaft_speed_integral_error = 0.0      # no shaft loop: the slot stays 0
 
 
 class HeadingBySampledRouteController:
@@ -231,6 +287,11 @@ def ship_params(ship_model: ShipModelAST, throttle_controller: EngineThrottleFro
     """Flatten one ship's configuration objects into the C ABI's SitShipParams."""
     sc, mc = ship_model.ship_config, ship_model.machinery_config
     p = _lib.SitShipParams()
+    simplified = isinstance(mc, SimplifiedPropulsionMachinerySystemConfiguration)
+    if simplified != isinstance(throttle_controller, ThrottleFromSpeedSetPointSimplifiedPropulsion):
+        raise TypeError("SimplifiedMachineryModel goes with ThrottleFromSpeedSetPointSimplifiedPropulsion (no shaft speed to "
+                        "feed back), ShipMachineryModel with EngineThrottleFromSpeedSetPoint")
+    p.machinery_kind = _lib.MACH_SIMPLIFIED if simplified else _lib.MACH_FULL
     p.dt = float(ship_model.simulation_config.integration_step)
     for name in ShipConfiguration._fields:
         setattr(p, name, float(getattr(sc, name)))
@@ -242,24 +303,110 @@ def ship_params(ship_model: ShipModelAST, throttle_controller: EngineThrottleFro
         p.mode_main_engine_capacity[i] = float(m.main_engine_capacity)
         p.mode_electrical_capacity[i] = float(m.electrical_capacity)
         p.mode_shaft_generator_state[i] = _lib.SG[m.shaft_generator_state]
-    for name in ("hotel_load", "linear_friction_main_engine", "linear_friction_hybrid_shaft_generator",
-                 "gear_ratio_between_main_engine_and_propeller",
-                 "gear_ratio_between_hybrid_shaft_generator_and_propeller", "propeller_inertia",
-                 "propeller_speed_to_torque_coefficient", "propeller_diameter",
-                 "propeller_speed_to_thrust_force_coefficient", "rudder_angle_to_sway_force_coefficient",
-                 "rudder_angle_to_yaw_force_coefficient", "max_rudder_angle_degrees"):
+    names = ("hotel_load", "rudder_angle_to_sway_force_coefficient", "rudder_angle_to_yaw_force_coefficient",
+             "max_rudder_angle_degrees")
+    if simplified:
+        p.thrust_force_dynamic_time_constant = float(mc.thrust_force_dynamic_time_constant)
+        p.kp_simplified, p.ki_simplified = throttle_controller.kp, throttle_controller.ki
+    else:
+        names += ("linear_friction_main_engine", "linear_friction_hybrid_shaft_generator",
+                  "gear_ratio_between_main_engine_and_propeller",
+                  "gear_ratio_between_hybrid_shaft_generator_and_propeller", "propeller_inertia",
+                  "propeller_speed_to_torque_coefficient", "propeller_diameter",
+                  "propeller_speed_to_thrust_force_coefficient")
+    for name in names:
         setattr(p, name, float(getattr(mc, name)))
     for i in range(3):
         p.sfc_me[i] = float(mc.specific_fuel_consumption_coefficients_me[i])
         p.sfc_dg[i] = float(mc.specific_fuel_consumption_coefficients_dg[i])
-    g = throttle_controller.gains
-    p.kp_ship_speed, p.ki_ship_speed = float(g.kp_ship_speed), float(g.ki_ship_speed)
-    p.kp_shaft_speed, p.ki_shaft_speed = float(g.kp_shaft_speed), float(g.ki_shaft_speed)
+    if not simplified:
+        g = throttle_controller.gains
+        p.kp_ship_speed, p.ki_ship_speed = float(g.kp_ship_speed), float(g.ki_ship_speed)
+        p.kp_shaft_speed, p.ki_shaft_speed = float(g.kp_shaft_speed), float(g.ki_shaft_speed)
     h, l = auto_pilot.heading_controller_gains, auto_pilot.los_parameters
     p.kp_heading, p.kd_heading, p.ki_heading = float(h.kp), float(h.kd), float(h.ki)
     p.radius_of_acceptance, p.lookahead_distance = float(l.radius_of_acceptance), float(l.lookahead_distance)
     p.los_integral_gain, p.los_integrator_windup_limit = float(l.integral_gain), float(l.integrator_windup_limit)
     return p
+
+
+class StaticObstacle:
+    """obstacle.py:8-90: circular obstacles, rows (north, east, radius) of an array or a text file.  The three queries keep
+    the reference's names and run batched on the device (``sit_circle_query``): scalars or equal-shaped tensors / arrays of
+    positions in, a tensor per query out.  ``if_ship_inside_obstacles`` / ``if_route_inside_obstacles``: d^2 <= r^2 for any
+    circle (boundary counts as inside, :69-85); ``obstacles_distance``: min over circles of sqrt(|d^2|) - r (:55-67)."""
+
+    def __init__(self, obstacle_data, print_init_msg=False, device="cuda", precision="fp64"):
+        data = np.loadtxt(obstacle_data) if isinstance(obstacle_data, (str, bytes)) else np.asarray(obstacle_data, dtype=np.float64)
+        if data.ndim == 1 and data.shape[0] == 3:
+            data = data.reshape(1, 3)
+        if data.ndim != 2 or data.shape[1] != 3 or not 1 <= data.shape[0] <= _lib.MAX_CIRCLES:
+            raise ValueError(f"obstacle_data must be [1..{_lib.MAX_CIRCLES}, 3] rows of (north, east, radius)")
+        self.data = np.ascontiguousarray(data)
+        self.num_obstacles = data.shape[0]
+        self.n_obs, self.e_obs, self.r_obs = data[:, 0].tolist(), data[:, 1].tolist(), data[:, 2].tolist()
+        self.device, self.precision = device, precision
+
+    def _query(self, n_pos, e_pos, want_dist):
+        import ctypes as C
+        import torch
+        real = torch.float64 if self.precision == "fp64" else torch.float32
+        dev = torch.device(self.device)
+        if dev.type != "cuda":
+            raise _lib.ShipSimError("StaticObstacle queries run on a CUDA device only (no CPU fallback)")
+        n = torch.as_tensor(n_pos, dtype=real, device=dev).contiguous()
+        e = torch.as_tensor(e_pos, dtype=real, device=dev).contiguous()
+        if n.shape != e.shape:
+            raise ValueError("north and east must have the same shape")
+        flags = torch.empty(n.shape, dtype=torch.uint8, device=dev)
+        dist = torch.empty(n.shape, dtype=real, device=dev) if want_dist else None
+        _lib.check(_lib.lib().sit_circle_query(_lib.F64 if self.precision == "fp64" else _lib.F32, self.num_obstacles,
+                                               self.data.ctypes.data_as(C.c_void_p), n.numel(), n.data_ptr(), e.data_ptr(),
+                                               flags.data_ptr(), dist.data_ptr() if want_dist else None,
+                                               torch.cuda.current_stream(dev).cuda_stream))
+        return flags, dist
+
+    def obstacles_distance(self, n_ship, e_ship):
+        return self._query(n_ship, e_ship, True)[1]
+
+    def if_ship_inside_obstacles(self, n_ship, e_ship):
+        return self._query(n_ship, e_ship, False)[0].bool()
+
+    def if_route_inside_obstacles(self, n_route, e_route):
+        return self._query(n_route, e_route, False)[0].bool()
+
+
+class ShipDraw:
+    """utils.py:56-101: the six outline points (closed pentagon) of an 80 m x 20 m ship seen from above.
+    ``ship_snap_shot`` data (ship_model.py:326-338) for a batch of poses: ``outline(north, east, psi)`` ->
+    (x_ned [n, 6], y_ned [n, 6]), the rows the reference appends to ``ship_drawings[0]`` / ``[1]``; device kernel
+    ``sit_ship_outline``."""
+
+    def __init__(self):
+        self.l, self.b = 80.0, 20.0
+
+    def local_coords(self):
+        l, b = self.l, self.b
+        x = np.array([-l / 2, l / 4, l / 2, l / 4, -l / 2, -l / 2])
+        y = np.array([-b / 2, -b / 2, 0.0, b / 2, b / 2, -b / 2])
+        return x, y
+
+    def outline(self, north, east, psi):
+        import torch
+        n = torch.as_tensor(north)
+        if n.device.type != "cuda":
+            raise _lib.ShipSimError("ShipDraw.outline runs on a CUDA device only (no CPU fallback)")
+        real = n.dtype
+        if real not in (torch.float32, torch.float64):
+            raise TypeError("poses must be float32 or float64 tensors")
+        n = n.contiguous()
+        e = torch.as_tensor(east, dtype=real, device=n.device).contiguous()
+        p = torch.as_tensor(psi, dtype=real, device=n.device).contiguous()
+        x = torch.empty((n.numel(), 6), dtype=real, device=n.device)
+        y = torch.empty_like(x)
+        _lib.check(_lib.lib().sit_ship_outline(_lib.F64 if real == torch.float64 else _lib.F32, n.numel(), n.data_ptr(),
+                                               e.data_ptr(), p.data_ptr(), x.data_ptr(), y.data_ptr()))
+        return x, y
 
 
 # ---- the default parameter set, test_beds/main_ast.py:106-237 --------------------------------------
@@ -318,3 +465,23 @@ def default_ship(route, psi0: float, mode_names: Sequence[str] = ("PTI",), mode_
                                      integrator_windup_limit=4000),
         time_step=dt, max_rudder_angle=30 * np.pi / 180, num_of_samplings=2)
     return ship_model, throttle_controller, auto_pilot
+
+
+def simplified_ship(route, psi0: float, thrust_force_dynamic_time_constant: float, kp: float, ki: float,
+                    initial_thrust_force: float, mode_names: Sequence[str] = ("MEC",), mode_index: int = 0, **kw):
+    """(ship_model, throttle_controller, auto_pilot) of the default hull propelled by a SimplifiedMachineryModel
+    (ship_engine.py:398-433) under ThrottleFromSpeedSetPointSimplifiedPropulsion (controllers.py:154-172)."""
+    full, _, auto_pilot = default_ship(route, psi0, mode_names=mode_names, mode_index=mode_index, **kw)
+    mc = full.machinery_config
+    machinery_config = SimplifiedPropulsionMachinerySystemConfiguration(
+        hotel_load=mc.hotel_load, machinery_modes=mc.machinery_modes, machinery_operating_mode=mode_index,
+        specific_fuel_consumption_coefficients_me=mc.specific_fuel_consumption_coefficients_me,
+        specific_fuel_consumption_coefficients_dg=mc.specific_fuel_consumption_coefficients_dg,
+        thrust_force_dynamic_time_constant=thrust_force_dynamic_time_constant,
+        rudder_angle_to_sway_force_coefficient=mc.rudder_angle_to_sway_force_coefficient,
+        rudder_angle_to_yaw_force_coefficient=mc.rudder_angle_to_yaw_force_coefficient,
+        max_rudder_angle_degrees=mc.max_rudder_angle_degrees)
+    ship_model = ShipModelSimplifiedPropulsion(full.ship_config, full.simulation_config, full.environment_config,
+                                               machinery_config, initial_thrust_force)
+    dt = full.simulation_config.integration_step
+    return ship_model, ThrottleFromSpeedSetPointSimplifiedPropulsion(kp=kp, ki=ki, time_step=dt), auto_pilot

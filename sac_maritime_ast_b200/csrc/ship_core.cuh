@@ -102,6 +102,9 @@ struct ShipP {
     R av_ur, av_urr, av_lin, av_nl, av_wind, av_rud;
     R ar_ca, ar_lin, ar_nl, ar_wind, ar_rud;
     R half_len;                                   // L / 2, MSRL_env_ex.py:476,498
+    // SimplifiedMachineryModel (ship_engine.py:398-433) + ThrottleFromSpeedSetPointSimplifiedPropulsion (controllers.py:154-172)
+    R k_thrust, inv_thrust_T, kp_sp, ki_sp, inv_m11;
+    int32_t mach, _pad_m;
     ModeP<R> mode[SIT_MAX_MODES];
     int32_t n_modes, _pad;
 };
@@ -187,7 +190,9 @@ struct StepOut {
 
 // One ship-step.  avoid: MSRL_env_ex.py:240-249.  store: store_simulation_data + next_time
 // (false reproduces init_step, MSRL_env_ex.py:188-215).  lg: 27 logged channels or nullptr.
-template <typename R, bool LOG, bool SINGLE_MODE = false>
+// MACH = SIT_MACH_SIMPLIFIED: the machinery state s.om is the THRUST FORCE (first-order lag of the commanded power) and the
+// throttle is the saturated speed PI; guidance, heading PID, load split, fuel and the hull are the same code.
+template <typename R, bool LOG, bool SINGLE_MODE = false, int MACH = SIT_MACH_FULL>
 __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const ShipPtrs<R>& g, int64_t i,
                                           bool avoid, bool store, StepOut<R>& o, R* lg) {
     // ---- LOS_guidance.py:88-103 next_wpt: squared distance, <=, end-of-route hold --------------
@@ -219,9 +224,15 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
     // ---- controllers.py:138-143 throttle cascade; the shaft PI is fed u (MSRL_env_ex.py:233-237) -
     const R e1 = s.u_sp - s.u;
     s.ei_s += e1 * P.dt;
-    const R e2 = (e1 * P.kp_s + s.ei_s * P.ki_s) - s.u;
-    s.ei_w += e2 * P.dt;
-    R thr = e2 * P.kp_w + s.ei_w * P.ki_w;
+    R thr;
+    if (MACH == SIT_MACH_SIMPLIFIED) {
+        // controllers.py:170-172: sat(pi_ctrl(set point, speed), 0, 1.1) with sat = max(low, min(val, hi)) (:63-69)
+        thr = max_((R)0, min_(e1 * P.kp_sp + s.ei_s * P.ki_sp, (R)1.1));
+    } else {
+        const R e2 = (e1 * P.kp_s + s.ei_s * P.ki_s) - s.u;
+        s.ei_w += e2 * P.dt;
+        thr = e2 * P.kp_w + s.ei_w * P.ki_w;
+    }
 
     // ---- MSRL_env_ex.py:240-249 collision-avoidance branch (test ship: always) -------------------
     if (avoid) {
@@ -234,10 +245,13 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
     // uniform operands; with several modes the per-ship index makes them per-lane constant loads
     const ModeP<R>& M = SINGLE_MODE ? P.mode[0] : P.mode[s.mode];
     const R om = s.om;
-    const R inv_om = rcp_(om + (R)0.1);
-    const R tq_me = min_(thr * M.avail_me * inv_om, M.cap_tq_me);   // ship_engine.py:368-375
-    const R tq_hsg = min_(thr * M.avail_el * inv_om, M.cap_tq_el);  // :377-384
-    const R thrust_w = om * abs_(om);                               // :363-366 (pre-update omega)
+    R tq_me = (R)0, tq_hsg = (R)0, thrust_w = (R)0;
+    if (MACH == SIT_MACH_FULL) {
+        const R inv_om = rcp_(om + (R)0.1);
+        tq_me = min_(thr * M.avail_me * inv_om, M.cap_tq_me);       // ship_engine.py:368-375
+        tq_hsg = min_(thr * M.avail_el * inv_om, M.cap_tq_el);      // :377-384
+        thrust_w = om * abs_(om);                                   // :363-366 (pre-update omega)
+    }
 
     // ---- ship_model.py:645-684 store_simulation_data: observables + fuel accumulators ------------
     if (store) {
@@ -257,7 +271,7 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
         s.f_me += rate_me * P.dt;
         s.f_el += rate_el * P.dt;
         s.f_tot += (rate_me + rate_el) * P.dt;
-        o.rpm = om * P.rpm_per_rads;
+        o.rpm = MACH == SIT_MACH_FULL ? om * P.rpm_per_rads : (R)0;   // the simplified model has no shaft
         o.power_me_kw = kilo_(load_me);
         o.avail_me_kw = M.me_cap_kw;
         if (LOG && lg) {
@@ -269,7 +283,7 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
             lg[15] = kilo_(load_el + load_me);                                  lg[16] = kilo_(total);
             lg[17] = rate_me;                   lg[18] = rate_el;               lg[19] = rate_me + rate_el;
             lg[20] = s.f_me;                    lg[21] = s.f_el;                lg[22] = s.f_tot;
-            lg[23] = tq_me;                     lg[24] = kilo_(P.thrust_coef * thrust_w);
+            lg[23] = tq_me;                     lg[24] = MACH == SIT_MACH_FULL ? kilo_(P.thrust_coef * thrust_w) : kilo_(om);
             lg[25] = s.e_ct;                    lg[26] = abs_(s.psi - href);    // radians (controllers.py:327-328)
         }
         s.steps += 1;                                               // utils.py:42-48 next_time
@@ -282,7 +296,9 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
     const R d_east = sn * s.u + c * s.v;
 
     // ---- ship_engine.py:355-361,391-395 shaft equation --------------------------------------------
-    const R d_om = tq_me * P.sh_me + tq_hsg * P.sh_hsg - (P.sh_lin + P.sh_quad * om) * om;
+    // simplified: ship_engine.py:423-428 update_thrust_force, d_thrust = (-k_thrust thrust + load_perc (P_me + P_el)) / T
+    const R d_om = MACH == SIT_MACH_FULL ? tq_me * P.sh_me + tq_hsg * P.sh_hsg - (P.sh_lin + P.sh_quad * om) * om
+                                         : (thr * (M.avail_me + M.avail_el) - P.k_thrust * om) * P.inv_thrust_T;
 
     // ---- ship_model.py:576-622 kinetics ------------------------------------------------------------
     const R uc = c * s.vcn + sn * s.vce, vc = c * s.vce - sn * s.vcn;   // inv(R(psi)) * v_current
@@ -292,7 +308,7 @@ __device__ __forceinline__ void ship_step(const ShipP<R>& P, Ship<R>& s, const S
     const R vrw = (s.wsb * c - s.wcb * sn) - s.v;
     const R Vw = sqrt_(urw * urw + vrw * vrw);
     const R d_u = P.au_vr * s.v * s.r - P.au_vrr * vr * s.r - (P.au_lin + P.au_nl * s.u) * ur -
-                  P.au_wind * Vw * urw + P.au_thr * thrust_w;
+                  P.au_wind * Vw * urw + (MACH == SIT_MACH_FULL ? P.au_thr * thrust_w : P.inv_m11 * om);
     const R d_v = P.av_urr * ur * s.r - P.av_ur * s.u * s.r - (P.av_lin + P.av_nl * s.v) * vr -
                   P.av_wind * Vw * vrw - P.av_rud * rud * ur;
     const R d_r = -P.ar_ca * ur * vr - (P.ar_lin + P.ar_nl * s.r) * s.r - P.ar_wind * urw * vrw -

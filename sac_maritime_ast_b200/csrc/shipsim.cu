@@ -34,6 +34,7 @@ struct EnvPtrs {
     R *ab_alpha, *cur_obs;                       // rollout: AB heading (MSRL_env_ex.py:125), observation held for the policy [10][B]
     int32_t *flags, *ep_steps;
     int32_t *n_dec, *dec_serial, *tr_slot;       // rollout: decisions this episode / ever, open replay row
+    double* draw_t;                              // time_since_last_ship_drawing (MSRL_env_ex.py:60,416-421)
     int64_t n_envs;
 };
 
@@ -50,6 +51,8 @@ struct EnvIO {
     R* obs; R* reward; uint8_t* done; int32_t* status; R* reward_sum; uint8_t* done_any; unsigned long long* stats;
     const uint8_t* mask;   // init_step only
     R* rew_parts;          // [rec][SIT_N_REWARD_PARTS][B] per-step increments of reward_results (MSRL_env_ex.py:924-964)
+    uint8_t* snap;         // [rec][B]: ship_snap_shot() taken in this step (MSRL_env_ex.py:416-421)
+    double draw_dt;        // ship_model.int.dt as the reference adds it to the timer (double)
 };
 
 template <typename R>
@@ -62,7 +65,7 @@ struct EnvKArgs {
 // =================================================================================================
 // K1: fleet of bare ships, K steps per launch, state in registers
 // =================================================================================================
-template <typename R, bool LOG>
+template <typename R, bool LOG, int MACH = SIT_MACH_FULL>
 __global__ void __launch_bounds__(256) fleet_step_kernel(const __grid_constant__ ShipP<R> P, const ShipPtrs<R> g,
                                                          const int K, const FleetIO<R> io) {
     const int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -81,7 +84,7 @@ __global__ void __launch_bounds__(256) fleet_step_kernel(const __grid_constant__
         }
         StepOut<R> o;
         R lg[SIT_N_LOG];
-        ship_step<R, LOG>(P, s, g, i, io.avoid != 0, io.store != 0, o, (LOG && io.log27) ? lg : nullptr);
+        ship_step<R, LOG, false, MACH>(P, s, g, i, io.avoid != 0, io.store != 0, o, (LOG && io.log27) ? lg : nullptr);
         if (io.traj && (io.traj_steps != 1 || t == K - 1)) {
             R* tr = io.traj + (int64_t)(io.traj_steps != 1 ? t : 0) * SIT_N_TRAJ * S + i;
             // streaming stores (st.global.cs): the trajectory is written once and never read back by the kernel
@@ -409,6 +412,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     unsigned n_live = 0;   // env-steps actually executed by this lane (ROLL: pending envs do not step)
     unsigned n_eps = 0;    // ROLL: episodes this env ended in the launch (terminal state; num_steps_episode when truncating)
     unsigned n_closed = 0; // ROLL: replay rows this env completed in the launch
+    double draw_t = (PARTS && io.snap) ? ge.draw_t[env] : 0.0;   // ship_draw timer: compiled into the PARTS instantiation only
     MapCache mc;           // nearest-ring cache, carried across launches in the state buffer
     mc.idx = (uint32_t)g.mc_idx[i]; mc.p0n = g.mc_n[i]; mc.p0e = g.mc_e[i]; mc.b2 = g.mc_b2[i];
 
@@ -567,6 +571,13 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         rsum += reward; ep_return += reward; ep_steps += 1;
         any_done |= done;
         fresh = false;
+        // MSRL_env_ex.py:416-421: `if time_since_last_ship_drawing > 30: snap both ships; timer = 0`, then `timer += dt`
+        // (after both ship steps, before the observation is assembled: the outline is drawn on this step's obs pose)
+        bool snapped = false;
+        if (PARTS && io.snap) {
+            if (draw_t > 30.0) { snapped = true; draw_t = 0.0; }
+            draw_t += io.draw_dt;
+        }
 
         // ---- outputs: coalesced SoA rows [step][channel][env] -------------------------------------------
         if (active && (io.rec_steps > 1 || t == K - 1)) {
@@ -594,6 +605,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
                 if (io.reward) io.reward[rec * B + env] = reward;
                 if (io.done) io.done[rec * B + env] = done ? 1 : 0;
                 if (io.status) io.status[rec * B + env] = status;
+                if (PARTS && io.snap) io.snap[rec * B + env] = snapped ? 1 : 0;
             }
         }
         bool episode_end = done && io.auto_reset != 0;
@@ -695,6 +707,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             ge.act_n[env] = act_n; ge.act_e[env] = act_e;
             ge.ep_return[env] = ep_return; ge.ep_steps[env] = ep_steps;
             if (ROLL) ge.n_dec[env] = n_dec;
+            if (PARTS && io.snap) ge.draw_t[env] = draw_t;
             if (io.reward_sum) io.reward_sum[env] = rsum;
             if (io.done_any) io.done_any[env] = any_done ? 1 : 0;
         }
@@ -1261,6 +1274,57 @@ __global__ void __launch_bounds__(256) map_query_kernel(const __grid_constant__ 
     }
 }
 
+// StaticObstacle (obstacle.py:8-90): circular obstacles.  obstacles_distance :55-67 = min_i (sqrt(|d_i^2|) - r_i);
+// if_ship_inside_obstacles / if_route_inside_obstacles :69-85 = any_i (d_i^2 <= r_i^2) with r_i^2 formed by the same product.
+// The reference's operation order (squares summed north first, no FMA contraction) is kept so the fp64 result is the
+// reference's bit for bit.
+#define SIT_MAX_CIRCLES 64
+template <typename R> struct CircleSet { int32_t n, _pad; R cn[SIT_MAX_CIRCLES], ce[SIT_MAX_CIRCLES], cr[SIT_MAX_CIRCLES]; };
+__device__ __forceinline__ double mul_rn_(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn_(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double add_rn_(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float add_rn_(float a, float b) { return __fadd_rn(a, b); }
+template <typename R>
+__global__ void __launch_bounds__(256) circle_query_kernel(const __grid_constant__ CircleSet<R> cs, const int64_t n,
+                                                           const R* __restrict__ north, const R* __restrict__ east,
+                                                           uint8_t* __restrict__ flags, R* __restrict__ dist) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const R pn = north[i], pe = east[i];
+    bool inside = false;
+    R dmin = (R)0;
+    for (int c = 0; c < cs.n; ++c) {
+        const R dn = pn - cs.cn[c], de = pe - cs.ce[c];
+        const R d2 = add_rn_(mul_rn_(dn, dn), mul_rn_(de, de));
+        inside |= d2 <= mul_rn_(cs.cr[c], cs.cr[c]);
+        const R d = sizeof(R) == 8 ? (R)sqrt((double)abs_(d2)) - cs.cr[c] : (R)sqrtf((float)abs_(d2)) - cs.cr[c];
+        dmin = c == 0 ? d : min_(dmin, d);
+    }
+    if (flags) flags[i] = inside ? 1 : 0;
+    if (dist) dist[i] = dmin;
+}
+
+// ship_snap_shot (ship_model.py:326-338) for n poses: ShipDraw.local_coords -> rotate_coords(psi) -> translate_coords
+// (utils.py:67-101); six outline points per pose, x_ned / y_ned [n][6].
+template <typename R>
+__global__ void __launch_bounds__(256) ship_outline_kernel(const int64_t n, const R* __restrict__ north, const R* __restrict__ east,
+                                                           const R* __restrict__ psi, R* __restrict__ x_out, R* __restrict__ y_out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const R l = (R)80, b = (R)20;
+    const R lx[6] = {-l / 2, l / 4, l / 2, l / 4, -l / 2, -l / 2};
+    const R ly[6] = {-b / 2, -b / 2, (R)0, b / 2, b / 2, -b / 2};
+    R sn, cs;
+    if (sizeof(R) == 8) { double s_, c_; sincos((double)psi[i], &s_, &c_); sn = (R)s_; cs = (R)c_; }
+    else { float s_, c_; sincosf((float)psi[i], &s_, &c_); sn = (R)s_; cs = (R)c_; }
+    const R pn = north[i], pe = east[i];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        x_out[i * 6 + j] = add_rn_(add_rn_(mul_rn_(cs, lx[j]), -mul_rn_(sn, ly[j])), pn);   // cos x - sin y + north
+        y_out[i * 6 + j] = add_rn_(add_rn_(mul_rn_(sn, lx[j]), mul_rn_(cs, ly[j])), pe);    // sin x + cos y + east
+    }
+}
+
 // =================================================================================================
 // FMA-peak microbenchmark (roofline denominator for the compute-bound step kernels)
 // =================================================================================================
@@ -1334,6 +1398,7 @@ static const FieldDef kEnvFields[] = {
     {"flags", 'I', 1, true}, {"ep_steps", 'I', 1, true},
     {"ab_alpha", 'R', 1, true}, {"cur_obs", 'R', SIT_N_OBS, true},
     {"n_dec", 'I', 1, true}, {"dec_serial", 'I', 1, true}, {"tr_slot", 'I', 1, true},
+    {"draw_t", 'D', 1, true},
 };
 
 #define SIT_PIPE 4
@@ -1431,6 +1496,11 @@ static void derive_ship(const SitShipParams& c, ShipP<R>& P) {
     P.ar_nl = (R)(c.nonlinear_friction_coefficient__in_yaw / m33);
     P.ar_wind = (R)(2.0 * 0.5 * rho * cn * a_l * L / m33); P.ar_rud = (R)(c.rudder_angle_to_yaw_force_coefficient / m33);
     P.half_len = (R)(L / 2);
+    P.mach = c.machinery_kind;
+    P.k_thrust = (R)(2160.0 / 790.0);                                  // ship_engine.py:420
+    P.inv_thrust_T = (R)(c.machinery_kind == SIT_MACH_SIMPLIFIED ? 1.0 / c.thrust_force_dynamic_time_constant : 0.0);
+    P.kp_sp = (R)c.kp_simplified; P.ki_sp = (R)c.ki_simplified;
+    P.inv_m11 = (R)(1.0 / m11);
     P.n_modes = c.n_modes;
     for (int j = 0; j < c.n_modes && j < SIT_MAX_MODES; ++j) {
         ModeP<R>& M = P.mode[j];
@@ -1590,6 +1660,7 @@ static EnvPtrs<R> env_ptrs(const SitHandle_* h, void* st) {
     e.ab_alpha = fptr<R>(h, st, "ab_alpha"); e.cur_obs = fptr<R>(h, st, "cur_obs");
     e.n_dec = fptr<int32_t>(h, st, "n_dec"); e.dec_serial = fptr<int32_t>(h, st, "dec_serial");
     e.tr_slot = fptr<int32_t>(h, st, "tr_slot");
+    e.draw_t = fptr<double>(h, st, "draw_t");
     return e;
 }
 
@@ -1599,6 +1670,14 @@ static int check_params(const SitShipParams& p, const char* who) {
     for (int j = 0; j < p.n_modes; ++j)
         if (p.mode_shaft_generator_state[j] < 0 || p.mode_shaft_generator_state[j] > 2)
             return fail(SIT_E_INVALID, std::string(who) + ": bad shaft generator state");
+    if (p.machinery_kind != SIT_MACH_FULL && p.machinery_kind != SIT_MACH_SIMPLIFIED)
+        return fail(SIT_E_INVALID, std::string(who) + ": machinery_kind must be SIT_MACH_FULL or SIT_MACH_SIMPLIFIED");
+    if (p.machinery_kind == SIT_MACH_SIMPLIFIED) {
+        if (!(p.thrust_force_dynamic_time_constant > 0))
+            return fail(SIT_E_INVALID, std::string(who) + ": thrust_force_dynamic_time_constant must be > 0");
+        if (!(p.lookahead_distance > 0)) return fail(SIT_E_INVALID, std::string(who) + ": bad parameter");
+        return SIT_OK;                                   // no shaft: propeller parameters are not read
+    }
     if (!(p.lookahead_distance > 0) || !(p.propeller_inertia > 0)) return fail(SIT_E_INVALID, std::string(who) + ": bad parameter");
     return SIT_OK;
 }
@@ -1629,6 +1708,9 @@ int sit_create(const SitConfig* cfg, int64_t n_envs, int device, SitHandle* out)
     if (cfg->kind == SIT_KIND_ENV) {
         rc = check_params(cfg->ship[1], "ship[1]");
         if (rc) return rc;
+        if (cfg->ship[0].machinery_kind != SIT_MACH_FULL || cfg->ship[1].machinery_kind != SIT_MACH_FULL)
+            return fail(SIT_E_INVALID, "SimplifiedMachineryModel is a fleet-only variant: MultiShipRLEnv passes the shaft speed to "
+                                       "the throttle controller and reads the rpm (MSRL_env_ex.py:233-237,554-558)");
         if (cfg->map.n_edges < 0 || cfg->map.n_edges > SIT_MAX_EDGES) return fail(SIT_E_INVALID, "map.n_edges out of range");
         if (!(cfg->sampling_frequency > 0)) return fail(SIT_E_INVALID, "sampling_frequency must be > 0");
         int np_ = 0;
@@ -1764,7 +1846,10 @@ static int fleet_step_t(SitHandle h, void* state, int K, const SitFleetIO* io, c
     const bool quiet = (!k.dist || k.dist_steps == 1) && !k.log27 && !k.cmd && k.store;
     const bool fast = quiet && (!k.traj || k.traj_steps == 1);
     const bool single = P.n_modes == 1;
-    if (fleet_x2<R>(h, g, K, k, quiet, fast, single, st)) {
+    if (P.mach == SIT_MACH_SIMPLIFIED) {   // SimplifiedMachineryModel: the general kernel only (a model variant, not a bench path)
+        if (k.log27) fleet_step_kernel<R, true, SIT_MACH_SIMPLIFIED><<<grid, block, 0, st>>>(P, g, K, k);
+        else fleet_step_kernel<R, false, SIT_MACH_SIMPLIFIED><<<grid, block, 0, st>>>(P, g, K, k);
+    } else if (fleet_x2<R>(h, g, K, k, quiet, fast, single, st)) {
         // fp32: packed two-ships-per-thread kernel (ship_x2.cuh) launched
     } else if (quiet && k.traj && k.traj_steps == K && K > 1) {   // every-step trajectory on the specialised compute path
         if (k.avoid) {
@@ -1970,6 +2055,8 @@ static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaS
         k.obs = static_cast<R*>(io->obs); k.reward = static_cast<R*>(io->reward); k.done = io->done; k.status = io->status;
         k.reward_sum = static_cast<R*>(io->reward_sum); k.done_any = io->done_any; k.stats = io->stats;
         k.rew_parts = static_cast<R*>(io->reward_parts);
+        k.snap = io->snap; k.draw_dt = h->cfg.ship[0].dt;
+        if (k.snap && io->rec_steps != K) return fail(SIT_E_INVALID, "snap needs rec_steps == K (a snapshot is tied to its step's pose)");
         if (!(k.act_steps == 1 || k.act_steps == K)) return fail(SIT_E_INVALID, "act_steps must be 1 or K");
         if (!(k.rec_steps == 1 || k.rec_steps == K)) return fail(SIT_E_INVALID, "rec_steps must be 1 or K");
     }
@@ -1980,7 +2067,7 @@ static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaS
     std::memset(&ra, 0, sizeof(ra));
     ra.env_first = env_first; ra.env_count = env_count < 0 ? h->n_envs : env_count;
     const int block = 128, grid = grid_for(2 * ra.env_count, block);
-    if (k.rew_parts) {
+    if (k.rew_parts || k.snap) {
         if (h->same_params) env_step_kernel<R, true, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
         else env_step_kernel<R, false, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     } else if (h->same_params) env_step_kernel<R, true, false><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
@@ -2481,6 +2568,50 @@ int sit_map_query(SitHandle h, int64_t n, const void* north, const void* east, u
     else
         map_query_kernel<float><<<grid, block, 0, st>>>(*h->kf, n, static_cast<const float*>(north), static_cast<const float*>(east),
                                                         flags, static_cast<float*>(dist));
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+int sit_circle_query(int32_t precision, int32_t n_circles, const double* circles, int64_t n, const void* north, const void* east,
+                     uint8_t* flags, void* dist, void* stream) {
+    if (!circles || !north || !east) return fail(SIT_E_INVALID, "null argument");
+    if (n_circles < 1 || n_circles > SIT_MAX_CIRCLES) return fail(SIT_E_INVALID, "n_circles must be in [1, 64]");
+    if (precision != SIT_F64 && precision != SIT_F32) return fail(SIT_E_INVALID, "bad precision");
+    if (n < 0) return fail(SIT_E_INVALID, "n must be >= 0");
+    if (n == 0) return SIT_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(SIT_E_NODEVICE, "no CUDA device: there is no CPU fallback"); }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int grid = grid_for(n, 256);
+    if (precision == SIT_F64) {
+        CircleSet<double> cs; std::memset(&cs, 0, sizeof(cs)); cs.n = n_circles;
+        for (int c = 0; c < n_circles; ++c) { cs.cn[c] = circles[3 * c]; cs.ce[c] = circles[3 * c + 1]; cs.cr[c] = circles[3 * c + 2]; }
+        circle_query_kernel<double><<<grid, 256, 0, st>>>(cs, n, static_cast<const double*>(north), static_cast<const double*>(east),
+                                                          flags, static_cast<double*>(dist));
+    } else {
+        CircleSet<float> cs; std::memset(&cs, 0, sizeof(cs)); cs.n = n_circles;
+        for (int c = 0; c < n_circles; ++c) { cs.cn[c] = (float)circles[3 * c]; cs.ce[c] = (float)circles[3 * c + 1]; cs.cr[c] = (float)circles[3 * c + 2]; }
+        circle_query_kernel<float><<<grid, 256, 0, st>>>(cs, n, static_cast<const float*>(north), static_cast<const float*>(east),
+                                                         flags, static_cast<float*>(dist));
+    }
+    CUDA_TRY(cudaGetLastError());
+    return SIT_OK;
+}
+
+int sit_ship_outline(int32_t precision, int64_t n, const void* north, const void* east, const void* psi, void* x_ned, void* y_ned) {
+    if (!north || !east || !psi || !x_ned || !y_ned) return fail(SIT_E_INVALID, "null argument");
+    if (precision != SIT_F64 && precision != SIT_F32) return fail(SIT_E_INVALID, "bad precision");
+    if (n < 0) return fail(SIT_E_INVALID, "n must be >= 0");
+    if (n == 0) return SIT_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(SIT_E_NODEVICE, "no CUDA device: there is no CPU fallback"); }
+    const int grid = grid_for(n, 256);
+    if (precision == SIT_F64)
+        ship_outline_kernel<double><<<grid, 256>>>(n, static_cast<const double*>(north), static_cast<const double*>(east),
+                                                   static_cast<const double*>(psi), static_cast<double*>(x_ned), static_cast<double*>(y_ned));
+    else
+        ship_outline_kernel<float><<<grid, 256>>>(n, static_cast<const float*>(north), static_cast<const float*>(east),
+                                                  static_cast<const float*>(psi), static_cast<float*>(x_ned), static_cast<float*>(y_ned));
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
 }

@@ -112,6 +112,12 @@ class MultiShipRLEnv(SimCore):
             v.n_wp[:] = n
         for name in ("prev_n", "prev_e", "eps_dist", "samp_dist", "act_n", "act_e", "ep_return", "flags", "ep_steps"):
             self.f[name].zero_()
+        # MSRL_env_ex.py:59-60: the snapshot timer starts at the constructor argument and is never reset by reset()
+        self.f["draw_t"].fill_(float(self.time_since_last_ship_drawing))
+        # ship_drawings[0] / [1] of each ship (ship_model.py:120,181,337-338) for the batch: one entry per snapshot step,
+        # (step index, env ids [m], x_ned [m, 6], y_ned [m, 6]); cleared by reset() like ShipModelAST.reset (:390)
+        self.ship_drawings = {"test": [], "obs": []}
+        self._draw_step = 0
         self.capture_init()   # also derives AB_segment_length (MSRL_env_ex.py:122-127)
 
     # ---- reference attributes read by callers ----------------------------------------------------------------
@@ -152,6 +158,8 @@ class MultiShipRLEnv(SimCore):
         SimCore.reset(self, mask=mask, hard=False)
         for a in self.assets:
             a.stop_flag = False
+        if mask is None:
+            self.ship_drawings = {"test": [], "obs": []}
         return self.initial_state()
 
     def init_step(self, mask: Optional[torch.Tensor] = None):
@@ -216,6 +224,10 @@ class MultiShipRLEnv(SimCore):
                 ("done", (rec, B), torch.uint8), ("status", (rec, B), torch.int32))
         if reward_parts:
             spec += (("reward_parts", (rec, _lib.N_REWARD_PARTS, B), self.real),)
+        if self.ship_draw:
+            if not (record_all or K == 1):
+                raise ValueError("ship_draw needs every step recorded (record_all=True): a snapshot is tied to its step's pose")
+            spec += (("snap", (rec, B), torch.uint8),)
         for name, shape, dt in spec:
             t = res.get(name)
             if t is None or tuple(t.shape) != shape:
@@ -233,7 +245,23 @@ class MultiShipRLEnv(SimCore):
         _lib.check(self.L.sit_env_step_k(self.h, self.state_ptr(), int(K), C.byref(io), self.stream()))
         self.launches += 1
         self._keep = (act, sac)   # keep inputs alive until the stream has consumed them
+        if self.ship_draw:
+            self._collect_snapshots(res, rec)
         return res
+
+    def _collect_snapshots(self, res, rec):
+        """ship_snap_shot of both ships for the steps the kernel flagged (MSRL_env_ex.py:416-421): outline rows from that
+        step's observation pose (post-step north, east, yaw), appended to ``ship_drawings`` (data only, no plotting)."""
+        snap = res["snap"]
+        for t in range(rec):
+            ids = torch.nonzero(snap[t], as_tuple=False).flatten()
+            if ids.numel():
+                ob = res["obs"][t]
+                draw = config.ShipDraw()
+                for name, c0 in (("test", 0), ("obs", 6)):
+                    x, y = draw.outline(ob[c0, ids], ob[c0 + 1, ids], ob[c0 + 2, ids])
+                    self.ship_drawings[name].append((self._draw_step + t, ids, x, y))
+        self._draw_step += rec
 
     def step_host(self, K, action_host: torch.Tensor, sac_update_host: torch.Tensor, init, out_host: dict):
         """One call through ``sit_env_step_host``: HOST (pinned) action [2, n_envs] / sac_update [n_envs] in,
