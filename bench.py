@@ -757,13 +757,16 @@ def rollout_leg(sit, dev, B=65536, K=32, iters=40, warm_iters=20, hidden=256, pr
 
 def learner_leg(sit, dev, sampler, batch=64, hidden=256, n=400, warm=50):
     """SAC update_parameters/s (main_ast.py:354) on the replay ring the rollout leg filled: twin-Q SAC, policy and critics
-    10/11 -> 256 -> 256, batch 64 (main_ast.py:63-67), one CUDA-graph replay (35 kernels) per update."""
+    10/11 -> 256 -> 256, one CUDA-graph replay per update.  Batch 64 (main_ast.py:63-67): fp32 CUDA-core products (latency-bound
+    chain of ~35 small kernels).  Batch 4096: hidden-layer products and every contraction over the batch on tcgen05 (bf16
+    operands, fp32 accumulate in TMEM), split-k partials reduced in a fixed order; the fp32-only path is timed beside it."""
     import torch
     from sac_maritime_ast_b200 import sac
     mem = sac.ReplayMemory.from_sampler(sampler)
     out = {}
-    for b in (batch, 4096):
-        agent = sac.SAC(10, None, None, device=dev, hidden_size=hidden, batch_size=b, seed=SEED)
+
+    def run(b, tc):
+        agent = sac.SAC(10, None, None, device=dev, hidden_size=hidden, batch_size=b, seed=SEED, tensor_cores=tc)
         agent.update(mem, warm)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -773,12 +776,18 @@ def learner_leg(sit, dev, sampler, batch=64, hidden=256, n=400, warm=50):
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
         flop = 3 * 2 * b * (2 * (11 * hidden + hidden * hidden + 2 * hidden) + 4 * (12 * hidden + hidden * hidden + hidden))
-        out[f"batch_{b}"] = {"updates_per_s": n / (ms * 1e-3), "us_per_update": ms * 1e3 / n, "samples_per_s": n * b / (ms * 1e-3),
-                             "approx_tflops": flop * n / (ms * 1e-3) / 1e12, "kernels_per_update": 35,
-                             "losses_finite": bool(torch.isfinite(ls).all()), "alpha": float(ls[4])}
+        res = {"updates_per_s": n / (ms * 1e-3), "us_per_update": ms * 1e3 / n, "samples_per_s": n * b / (ms * 1e-3),
+               "approx_tflops": flop * n / (ms * 1e-3) / 1e12, "kernels_per_update": agent.kernels_per_update,
+               "products": "tcgen05 bf16 x bf16 -> fp32 (TMEM) for k >= 128, fp32 CUDA cores for the thin ones"
+                           if (tc and b >= 1024) else "fp32 CUDA cores",
+               "losses_finite": bool(torch.isfinite(ls).all()), "alpha": float(ls[4])}
         agent.close()
+        return res
+    out[f"batch_{batch}"] = run(batch, True)
+    out["batch_4096"] = run(4096, True)
+    out["batch_4096_fp32_only"] = run(4096, False)
     out["replay_rows"] = len(mem)
-    out["metric"] = "SAC update_parameters/s (twin-Q, auto-alpha, Adam, soft target update), fp32, CUDA graph"
+    out["metric"] = "SAC update_parameters/s (twin-Q, auto-alpha, Adam, soft target update), CUDA graph"
     return out
 
 

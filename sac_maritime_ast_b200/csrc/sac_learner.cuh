@@ -114,6 +114,319 @@ __global__ void __launch_bounds__(256) gemm_kernel(const Gemm g) {
         }
 }
 
+// ---- two degenerate shapes of the large-batch update, kept off the tiled kernels -------------------------------------
+// k <= 16 (layer 0 forward: k = 11 / 12 inputs; input gradient through the 1- / 2-wide output layer): a CTA owns 8 output
+// rows (their A values in shared memory), a thread one column n of all 8 (its B column in registers), lanes along n.  The
+// sum runs over ascending k from zero with fmaf, exactly like gemm_kernel: bit-identical results.
+__global__ void __launch_bounds__(256) gemm_thin_k_kernel(const Gemm g) {
+    __shared__ float sa[8][16];                       // the CTA's 8 rows of A (k <= 16)
+    const int z = blockIdx.z, tid = threadIdx.x, m0 = blockIdx.x * 8;
+    const float* A = g.A + (long long)z * g.a_zs;
+    const float* B = g.B + (long long)z * g.b_zs;
+    float* C = g.C + (long long)z * g.c_zs;
+    const float* Hm = g.epi == EPI_MASK ? g.Hm + (long long)z * g.h_zs : nullptr;
+    if (tid < 128) {
+        const int r = tid >> 4, k = tid & 15;
+        sa[r][k] = (m0 + r < g.M && k < g.K) ? A[(long long)(m0 + r) * g.a_rs + (long long)k * g.a_cs] : 0.f;
+    }
+    __syncthreads();
+    for (int n = tid; n < g.N; n += 256) {
+        float b[16], hm[8];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) b[k] = k < g.K ? B[(long long)k * g.b_rs + (long long)n * g.b_cs] : 0.f;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) hm[r] = (Hm && m0 + r < g.M) ? Hm[(long long)(m0 + r) * g.ldh + n] : 1.f;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (m0 + r >= g.M) break;
+            float acc = 0.f;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) if (k < g.K) acc = fmaf(sa[r][k], b[k], acc);
+            if (g.epi == EPI_RELU) acc = fmaxf(acc, 0.f);
+            else if (g.epi == EPI_MASK) acc = hm[r] > 0.f ? acc : 0.f;
+            C[(long long)(m0 + r) * g.ldc + n] = acc;
+        }
+    }
+}
+// n <= 4 with A contiguous along k (the 1- / 2-wide output layer forward, d loss / d action): one warp per output row, lanes
+// along k (coalesced), fixed shuffle tree -> deterministic; fp32 throughout.
+__global__ void __launch_bounds__(256) gemm_skinny_n_kernel(const Gemm g) {
+    const int z = blockIdx.z, lane = threadIdx.x & 31;
+    const int m = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (m >= g.M) return;
+    const float* A = g.A + (long long)z * g.a_zs + (long long)m * g.a_rs;
+    const float* B = g.B + (long long)z * g.b_zs;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int k = lane; k < g.K; k += 32) {
+        const float a = A[k];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) if (j < g.N) acc[j] = fmaf(a, B[(long long)k * g.b_rs + (long long)j * g.b_cs], acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], d);
+    if (lane < g.N) {
+        float v = lane == 0 ? acc[0] : (lane == 1 ? acc[1] : (lane == 2 ? acc[2] : acc[3]));
+        if (g.epi == EPI_RELU) v = fmaxf(v, 0.f);
+        else if (g.epi == EPI_MASK) v = (g.Hm + (long long)z * g.h_zs)[(long long)m * g.ldh + lane] > 0.f ? v : 0.f;
+        (g.C + (long long)z * g.c_zs)[(long long)m * g.ldc + lane] = v;
+    }
+}
+
+// ---- the same GEMM on the tensor cores (tcgen05) for the large-batch learner -----------------------------------------
+// C[z](m, n) = epi( sum_k A[z](m, k) * B[z](k, n) ) with bf16 operands and fp32 accumulation in TMEM.  Operands stay fp32 in
+// global memory (master weights, activations, gradients): a CTA converts its tiles to bf16 on the way into shared memory and
+// writes them in the UMMA canonical K-major layout (8-row x 16-byte core matrices, no swizzle), transposing where the source
+// is contiguous along m / n instead of k -- so forward (X . W), input gradient (dY . W^T) and weight gradient (X^T . dY, the
+// contraction over the batch) all run through this one kernel.  One CTA = one 128 x BN output tile (BN = 16 .. 128); the k
+// range is cut into 64-deep chunks, double buffered: while tcgen05.mma (issued by one thread, completion signalled on an
+// mbarrier by tcgen05.commit) consumes chunk c, all 256 threads stage chunk c + 1.  Products whose k is the batch are also
+// split over `splits` CTAs along k: every CTA writes its fp32 partial tile and splitk_reduce_kernel sums the partials IN SPLIT
+// ORDER and applies the epilogue -- a fixed summation order, so two runs give bit-identical results.
+constexpr int TCG_M = 128, TCG_KC = 64, TCG_MAX_SPLITS = 32, TCG_MAX_STAGES = 5;
+struct GemmTC { Gemm g; int bn, splits, tmem_cols, stages; float* partial; };
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile("{\n\t.reg .pred P1;\n\tLAB_WAIT_TCG:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t@P1 bra DONE_TCG;\n\t"
+                 "bra LAB_WAIT_TCG;\n\tDONE_TCG:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+
+__global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const GemmTC t) {
+    extern __shared__ __align__(128) unsigned char tcg_smem[];
+    __shared__ uint64_t s_bar[TCG_MAX_STAGES];
+    __shared__ uint32_t s_tmem;
+    const Gemm& g = t.g;
+    const int BN = t.bn, bn_shift = 31 - __clz(BN);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int z = blockIdx.z / t.splits, sp = blockIdx.z % t.splits;
+    const int m0 = blockIdx.y * TCG_M, n0 = blockIdx.x * BN;
+    const int n_chunks = (g.K + TCG_KC - 1) / TCG_KC, per = (n_chunks + t.splits - 1) / t.splits;
+    const int c_lo = sp * per, c_hi = min(n_chunks, c_lo + per);
+    const float* A = g.A + (long long)z * g.a_zs;
+    const float* B = g.B + (long long)z * g.b_zs;
+    const uint32_t a_bytes = TCG_M * TCG_KC * 2, stage_bytes = a_bytes + (uint32_t)BN * TCG_KC * 2;
+    float* s_c = reinterpret_cast<float*>(tcg_smem);              // epilogue tile [128][BN + 1], aliases the staging buffers
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(t.tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    if (tid == 32) {
+        for (int i = 0; i < TCG_MAX_STAGES; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[i])));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+    const uint32_t tmem_base = s_tmem;
+    // kind::f16 instruction descriptor: fp32 accumulate, bf16 A and B, both K-major, N = BN, M = 128
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TCG_M >> 4) << 24);
+    const uint32_t lbo = 128u, sbo = 8u * 128u;                   // next 16-byte k chunk | next 8-row group (64-deep chunk)
+
+    // One 64-deep chunk of an operand tile (`rows` = 128 for A, BN for B) goes global -> registers -> canonical K-major bf16
+    // image in two phases, so that ALL of a chunk's loads are in flight together and the loads of chunk c + 1 are issued
+    // before the CTA waits for the tensor core to release chunk c - 1's buffer.  Element (r, k) = P[(r0 + r) rs + (k0 + k) cs].
+    //   mode 1 (source contiguous along k, 16-byte aligned rows): a thread owns (r, 8 consecutive k): two 128-bit loads;
+    //   mode 2 (source contiguous along r, 16-byte aligned):      a thread owns (4 consecutive r, 8 k): eight 128-bit loads,
+    //                                                             transposed in registers into four core-matrix rows;
+    //   mode 0 (anything else, and the k tail of mode 1):         a thread owns (r, 8 k): eight predicated scalar loads.
+    struct Regs { float v[32]; };
+    auto pick_mode = [&](const float* P, const long long rs, const long long cs) {
+        const bool al = (reinterpret_cast<uintptr_t>(P) & 15) == 0;
+        if (cs == 1 && al && (rs & 3) == 0) return 1;
+        if (rs == 1 && al && (cs & 3) == 0) return 2;
+        return 0;
+    };
+    auto load_tile = [&](Regs& R, int mode, const float* P, const int r_total, const long long rs, const long long cs, const int r0,
+                         const int rows_shift, const int k0) {
+        const int rows = 1 << rows_shift;
+        if (mode == 1 && k0 + TCG_KC > g.K) mode = 0;
+        if (mode == 2) {
+            const int q_shift = rows_shift - 2;                       // row quads per tile
+            const int r4 = (tid & ((1 << q_shift) - 1)) * 4, ko = tid >> q_shift, gr = r0 + r4;
+            const bool ok = tid < (8 << q_shift);
+            const float* p = P + gr + (long long)(k0 + ko * 8) * cs;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ok && gr < r_total && k0 + ko * 8 + j < g.K) q = *reinterpret_cast<const float4*>(p + (long long)j * cs);
+                R.v[j * 4 + 0] = q.x;
+                R.v[j * 4 + 1] = gr + 1 < r_total ? q.y : 0.f;
+                R.v[j * 4 + 2] = gr + 2 < r_total ? q.z : 0.f;
+                R.v[j * 4 + 3] = gr + 3 < r_total ? q.w : 0.f;
+            }
+            return;
+        }
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int item = tid + it * 256;
+            const int r = item & (rows - 1), ko = item >> rows_shift, gr = r0 + r, kb = k0 + ko * 8;
+            const bool ok = item < 8 * rows && gr < r_total;
+            const float* p = P + (long long)gr * rs + (long long)kb * cs;
+            if (mode == 1) {
+                float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+                if (ok) { a = *reinterpret_cast<const float4*>(p); b = *reinterpret_cast<const float4*>(p + 4); }
+                R.v[it * 8 + 0] = a.x; R.v[it * 8 + 1] = a.y; R.v[it * 8 + 2] = a.z; R.v[it * 8 + 3] = a.w;
+                R.v[it * 8 + 4] = b.x; R.v[it * 8 + 5] = b.y; R.v[it * 8 + 6] = b.z; R.v[it * 8 + 7] = b.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) R.v[it * 8 + j] = (ok && kb + j < g.K) ? p[(long long)j * cs] : 0.f;
+            }
+        }
+    };
+    auto store_tile = [&](const Regs& R, const int mode, const int rows_shift, unsigned char* dst) {
+        const int rows = 1 << rows_shift;
+        if (mode == 2) {
+            const int q_shift = rows_shift - 2;
+            const int r4 = (tid & ((1 << q_shift) - 1)) * 4, ko = tid >> q_shift;
+            if (tid < (8 << q_shift)) {
+#pragma unroll
+                for (int rr = 0; rr < 4; ++rr) {
+                    const int r = r4 + rr;
+                    uint4 w;
+                    w.x = pack_bf16x2(R.v[0 * 4 + rr], R.v[1 * 4 + rr]); w.y = pack_bf16x2(R.v[2 * 4 + rr], R.v[3 * 4 + rr]);
+                    w.z = pack_bf16x2(R.v[4 * 4 + rr], R.v[5 * 4 + rr]); w.w = pack_bf16x2(R.v[6 * 4 + rr], R.v[7 * 4 + rr]);
+                    *reinterpret_cast<uint4*>(dst + (size_t)(r >> 3) * sbo + (size_t)ko * lbo + (r & 7) * 16) = w;
+                }
+            }
+            return;
+        }
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int item = tid + it * 256;
+            if (item < 8 * rows) {
+                const int r = item & (rows - 1), ko = item >> rows_shift;
+                const float* v = &R.v[it * 8];
+                uint4 w;
+                w.x = pack_bf16x2(v[0], v[1]); w.y = pack_bf16x2(v[2], v[3]); w.z = pack_bf16x2(v[4], v[5]); w.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(dst + (size_t)(r >> 3) * sbo + (size_t)ko * lbo + (r & 7) * 16) = w;
+            }
+        }
+    };
+    const int mode_a = pick_mode(A, g.a_rs, g.a_cs), mode_b = pick_mode(B, g.b_cs, g.b_rs);
+
+    // `stages` buffers (2 .. 5): a CTA whose k range fits them never waits for the tensor core inside the loop -- the issue ->
+    // completion latency of a tcgen05.mma batch is far longer than its math at these tile sizes
+    uint32_t phase[TCG_MAX_STAGES] = {0u, 0u, 0u, 0u, 0u};
+    bool used[TCG_MAX_STAGES] = {false, false, false, false, false};
+    int last_b = 0;
+    Regs ra, rb;
+    if (c_lo < c_hi) {
+        load_tile(ra, mode_a, A, g.M, g.a_rs, g.a_cs, m0, 7, c_lo * TCG_KC);
+        load_tile(rb, mode_b, B, g.N, g.b_cs, g.b_rs, n0, bn_shift, c_lo * TCG_KC);
+    }
+    for (int c = c_lo; c < c_hi; ++c) {
+        const int b = (c - c_lo) % t.stages;
+        unsigned char* sA = tcg_smem + (size_t)b * stage_bytes;
+        unsigned char* sB = sA + a_bytes;
+        if (used[b]) { mbar_wait(smem_u32(&s_bar[b]), phase[b]); phase[b] ^= 1u; }     // the MMAs that read this buffer are done
+        store_tile(ra, mode_a, 7, sA);
+        store_tile(rb, mode_b, bn_shift, sB);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::);
+            const uint64_t da = umma_desc_kmajor_noswizzle(smem_u32(sA), lbo, sbo), db = umma_desc_kmajor_noswizzle(smem_u32(sB), lbo, sbo);
+#pragma unroll
+            for (int ks = 0; ks < TCG_KC / 16; ++ks) {
+                const uint64_t adv = (uint64_t)((ks * 2 * lbo) >> 4);
+                const uint32_t acc = (c > c_lo || ks > 0) ? 1u : 0u;
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                             "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                             ::"r"(tmem_base), "l"(da + adv), "l"(db + adv), "r"(idesc), "r"(acc) : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_bar[b])) : "memory");
+        }
+        used[b] = true; last_b = b;
+        if (c + 1 < c_hi) {          // next chunk's loads fly while the tensor core works on this one
+            load_tile(ra, mode_a, A, g.M, g.a_rs, g.a_cs, m0, 7, (c + 1) * TCG_KC);
+            load_tile(rb, mode_b, B, g.N, g.b_cs, g.b_rs, n0, bn_shift, (c + 1) * TCG_KC);
+        }
+    }
+    const bool any = c_hi > c_lo;
+    if (any) mbar_wait(smem_u32(&s_bar[last_b]), phase[last_b]);   // commits complete in order: every MMA of this CTA is done
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+
+    // accumulator -> shared tile (thread = TMEM lane = output row; the two thread halves take the two column halves)
+    {
+        const int row = tid & (TCG_M - 1), half = tid >> 7, ch = BN >> 1;
+        const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+        for (int c0 = half * ch; c0 < (half + 1) * ch; c0 += 8) {
+            uint32_t r[8];
+            if (any) {
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                             : "r"(taddr + (uint32_t)c0));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) r[j] = 0u;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s_c[row * (BN + 1) + c0 + j] = __uint_as_float(r[j]);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+
+    if (t.splits == 1) {
+        float* C = g.C + (long long)z * g.c_zs;
+        const float* Hm = g.epi == EPI_MASK ? g.Hm + (long long)z * g.h_zs : nullptr;
+        // coalesced stores, eight outputs per thread and trip so that the mask loads of a trip are in flight together
+        for (int i0 = tid; i0 < TCG_M * BN; i0 += 256 * 8) {
+            float hm[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int idx = i0 + u * 256, r = idx >> bn_shift, cc = idx & (BN - 1), m = m0 + r, n = n0 + cc;
+                hm[u] = (g.epi == EPI_MASK && idx < TCG_M * BN && m < g.M && n < g.N) ? Hm[(long long)m * g.ldh + n] : 1.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int idx = i0 + u * 256, r = idx >> bn_shift, cc = idx & (BN - 1), m = m0 + r, n = n0 + cc;
+                if (idx < TCG_M * BN && m < g.M && n < g.N) {
+                    float v = s_c[r * (BN + 1) + cc];
+                    if (g.epi == EPI_RELU) v = fmaxf(v, 0.f);
+                    else if (g.epi == EPI_MASK) v = hm[u] > 0.f ? v : 0.f;
+                    C[(long long)m * g.ldc + n] = v;
+                }
+            }
+        }
+    } else {
+        // split-k: this CTA's partial tile -> [z][split][M][N]; splitk_reduce_kernel sums the splits in order
+        float* P = t.partial + ((long long)(z * t.splits + sp) * g.M) * g.N;
+        for (int idx = tid; idx < TCG_M * BN; idx += 256) {
+            const int r = idx >> bn_shift, cc = idx & (BN - 1), m = m0 + r, n = n0 + cc;
+            if (m < g.M && n < g.N) P[(long long)m * g.N + n] = s_c[r * (BN + 1) + cc];
+        }
+    }
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(t.tmem_cols));
+}
+
+// C[z](m, n) = epi( sum over splits, IN SPLIT ORDER, of the partial tiles of gemm_tc_kernel ): one thread per output, all of
+// its loads in flight together; a fixed summation order, so two runs give bit-identical results.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const GemmTC t) {
+    const Gemm& g = t.g;
+    const long long mn = (long long)g.M * g.N;
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    const int z = blockIdx.y;
+    if (i >= mn) return;
+    const float* pp = t.partial + (long long)z * t.splits * mn + i;
+    float acc = 0.f;
+    for (int q0 = 0; q0 < t.splits; q0 += 8) {
+        float x[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) x[q] = q0 + q < t.splits ? pp[(q0 + q) * mn] : 0.f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc += x[q];
+    }
+    const int m = (int)(i / g.N), n = (int)(i % g.N);
+    if (g.epi == EPI_RELU) acc = fmaxf(acc, 0.f);
+    else if (g.epi == EPI_MASK) acc = (g.Hm + (long long)z * g.h_zs)[(long long)m * g.ldh + n] > 0.f ? acc : 0.f;
+    (g.C + (long long)z * g.c_zs)[(long long)m * g.ldc + n] = acc;
+}
+
 // ---- workspace ------------------------------------------------------------------------------------------------------
 struct Net { long long l0, l1, l2; };   // float offsets of the three augmented layer blocks inside a network block
 struct Layout {
@@ -125,11 +438,15 @@ struct Layout {
     long long o_xs, o_xs2, o_xsa, o_xs2a, o_xspi, o_r, o_mask;
     long long o_hp1, o_hp2, o_op, o_hq1, o_hq2, o_oq, o_oqt;
     long long o_doq, o_dhq2, o_dhq1, o_da, o_dop, o_dhp2, o_dhp1;
-    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, total;
+    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, total;
+    int tc;                             // large-batch products on tcgen05 (gemm_tc_kernel)
+    int ldh;                            // leading dimension of the hidden activations [B][ldh]: H weights' inputs + the ones
+                                        // column (H + 1), padded to a multiple of 4 floats on the tensor-core path so that
+                                        // every row starts 16-byte aligned (128-bit operand loads)
 };
 
-static void make_layout(Layout& L, int H, int B) {
-    L.H = H; L.B = B;
+static void make_layout(Layout& L, int H, int B, int tc) {
+    L.H = H; L.B = B; L.tc = tc; L.ldh = tc ? H + 4 : H + 1;
     L.pol.l0 = 0; L.pol.l1 = (long long)(S + 1) * H; L.pol.l2 = L.pol.l1 + (long long)(H + 1) * H;
     L.P_pol = L.pol.l2 + (long long)(H + 1) * 2;
     L.q.l0 = 0; L.q.l1 = (long long)(SA + 1) * H; L.q.l2 = L.q.l1 + (long long)(H + 1) * H;
@@ -146,13 +463,14 @@ static void make_layout(Layout& L, int H, int B) {
     L.o_xs = take(b * (S + 1)); L.o_xs2 = take(b * (S + 1));
     L.o_xsa = take(b * (SA + 1)); L.o_xs2a = take(b * (SA + 1)); L.o_xspi = take(b * (SA + 1));
     L.o_r = take(b); L.o_mask = take(b);
-    L.o_hp1 = take(b * (H + 1)); L.o_hp2 = take(b * (H + 1)); L.o_op = take(b * 2);
-    L.o_hq1 = take(2 * b * (H + 1)); L.o_hq2 = take(2 * b * (H + 1)); L.o_oq = take(2 * b); L.o_oqt = take(2 * b);
+    L.o_hp1 = take(b * L.ldh); L.o_hp2 = take(b * L.ldh); L.o_op = take(b * 2);
+    L.o_hq1 = take(2 * b * L.ldh); L.o_hq2 = take(2 * b * L.ldh); L.o_oq = take(2 * b); L.o_oqt = take(2 * b);
     L.o_doq = take(2 * b); L.o_dhq2 = take(2 * b * H); L.o_dhq1 = take(2 * b * H); L.o_da = take(2 * b);
     L.o_dop = take(b * 2); L.o_dhp2 = take(b * H); L.o_dhp1 = take(b * H);
     L.o_eps_next = take(b); L.o_eps_cur = take(b); L.o_logp_next = take(b); L.o_logp_cur = take(b);
     L.o_idx = take(b); L.o_losses = take(SIT_SAC_N_LOSS); L.o_updates = take(2);   // updates: one unsigned long long
     L.o_obs_scale = take(S);
+    L.o_part = take(tc ? 2LL * TCG_MAX_SPLITS * (H + 1) * H : 0);   // split-k partial tiles [z][split][M][N]
     L.total = o;
 }
 
@@ -182,9 +500,9 @@ __global__ void fill_kernel(float* p, long long n, float v) {
     if (i < n) p[i] = v;
 }
 // ones column of an activation buffer [rows][ld] (written once: no kernel ever touches that column again)
-__global__ void ones_col_kernel(float* p, long long rows, int ld) {
+__global__ void ones_col_kernel(float* p, long long rows, int ld, int col) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < rows) p[i * ld + (ld - 1)] = 1.0f;
+    if (i < rows) p[i * ld + col] = 1.0f;
 }
 
 // draw the batch: uniform row indices over the valid part of the replay ring (memory.sample, main_ast.py:354), gather
@@ -387,6 +705,38 @@ struct Launcher {
         g.A = ws + oA; g.B = ws + oB; g.C = ws + oC; g.Hm = ws + oH;
         g.M = M; g.N = N; g.K = K; g.a_rs = a_rs; g.a_cs = a_cs; g.b_rs = b_rs; g.b_cs = b_cs; g.ldc = ldc; g.ldh = ldh;
         g.a_zs = a_zs; g.b_zs = b_zs; g.c_zs = c_zs; g.h_zs = h_zs; g.epi = epi;
+        if (L.tc && K <= 16) {
+            gemm_thin_k_kernel<<<dim3((M + 7) / 8, 1, Z), 256, 0, st>>>(g);
+            return;
+        }
+        if (L.tc && N <= 4 && a_cs == 1 && K >= 128) {
+            gemm_skinny_n_kernel<<<dim3((M + 7) / 8, 1, Z), 256, 0, st>>>(g);
+            return;
+        }
+        if (L.tc && K >= 128) {      // hidden-layer products and every contraction over the batch: tensor cores
+            GemmTC t;
+            t.g = g;
+            t.bn = N > 64 ? 128 : (N > 32 ? 64 : (N > 16 ? 32 : 16));
+            t.tmem_cols = t.bn < 32 ? 32 : t.bn;
+            const int n_chunks = (K + TCG_KC - 1) / TCG_KC;
+            int splits = K >= 1024 ? std::min(TCG_MAX_SPLITS, std::max(1, n_chunks / 4)) : 1;
+            const int per = (n_chunks + splits - 1) / splits;
+            splits = (n_chunks + per - 1) / per;                       // no empty split
+            if ((long long)Z * splits * M * N > 2LL * TCG_MAX_SPLITS * (L.H + 1) * L.H) splits = 1;
+            // 64-wide tiles when 128-wide ones would leave most of the 148 SMs without a CTA
+            // (two CTAs fit one SM: 115 registers, <= 66 KB shared memory)
+            if (t.bn == 128 && (long long)((N + 127) / 128) * ((M + TCG_M - 1) / TCG_M) * Z * splits < 296) t.bn = 64;
+            t.tmem_cols = t.bn < 32 ? 32 : t.bn;
+            t.splits = splits;
+            t.partial = ws + L.o_part;
+            const size_t stage = (size_t)TCG_M * TCG_KC * 2 + (size_t)t.bn * TCG_KC * 2;
+            t.stages = std::max(2, std::min(t.bn <= 64 ? 4 : 3, (n_chunks + splits - 1) / splits));    // <= 96 KB: two CTAs per SM
+            const size_t smem = std::max((size_t)t.stages * stage, (size_t)TCG_M * (t.bn + 1) * 4);
+            const dim3 tgrid((N + t.bn - 1) / t.bn, (M + TCG_M - 1) / TCG_M, Z * splits);
+            gemm_tc_kernel<<<tgrid, 256, smem, st>>>(t);
+            if (splits > 1) splitk_reduce_kernel<<<dim3((unsigned)(((long long)M * N + 255) / 256), Z), 256, 0, st>>>(t);
+            return;
+        }
         const dim3 grid((N + 31) / 32, (M + 31) / 32, Z);
         const bool ak = a_cs == 1, bn = b_cs == 1;
         if (ak && bn) gemm_kernel<true, true><<<grid, 256, 0, st>>>(g);
@@ -398,10 +748,11 @@ struct Launcher {
     void forward(long long oX, int kin, long long oW, long long w_zs, const Net& n, int nout, long long oH1, long long oH2,
                  long long oOut, int Z) const {
         const int B = L.B, H = L.H;
-        const long long hz = (long long)B * (H + 1);
-        gemm(oX, kin + 1, 1, 0, oW + n.l0, H, 1, w_zs, oH1, H + 1, hz, B, H, kin + 1, Z, EPI_RELU);
-        gemm(oH1, H + 1, 1, hz, oW + n.l1, H, 1, w_zs, oH2, H + 1, hz, B, H, H + 1, Z, EPI_RELU);
-        gemm(oH2, H + 1, 1, hz, oW + n.l2, nout, 1, w_zs, oOut, nout, (long long)B * nout, B, nout, H + 1, Z, EPI_STORE);
+        const int ld = L.ldh;
+        const long long hz = (long long)B * ld;
+        gemm(oX, kin + 1, 1, 0, oW + n.l0, H, 1, w_zs, oH1, ld, hz, B, H, kin + 1, Z, EPI_RELU);
+        gemm(oH1, ld, 1, hz, oW + n.l1, H, 1, w_zs, oH2, ld, hz, B, H, H + 1, Z, EPI_RELU);
+        gemm(oH2, ld, 1, hz, oW + n.l2, nout, 1, w_zs, oOut, nout, (long long)B * nout, B, nout, H + 1, Z, EPI_STORE);
     }
     // backward: dOut [Z][B][nout] -> (optionally) weight gradients into the grad block, and d/dX of the first `dx_cols`
     // input columns starting at column dx_first (0 columns: stop at layer 0's weight gradient)
@@ -409,13 +760,14 @@ struct Launcher {
                   long long oDOut, long long oDH2, long long oDH1, int Z, bool want_dw, long long oG, long long oDX, int dx_first,
                   int dx_cols) const {
         const int B = L.B, H = L.H;
-        const long long hz = (long long)B * (H + 1), dz = (long long)B * H, oz = (long long)B * nout;
+        const int ld = L.ldh;
+        const long long hz = (long long)B * ld, dz = (long long)B * H, oz = (long long)B * nout;
         // layer 2
-        if (want_dw) gemm(oH2, 1, H + 1, hz, oDOut, nout, 1, oz, oG + n.l2, nout, w_zs, H + 1, nout, B, Z, EPI_STORE);
-        gemm(oDOut, nout, 1, oz, oW + n.l2, 1, nout, w_zs, oDH2, H, dz, B, H, nout, Z, EPI_MASK, oH2, H + 1, hz);
+        if (want_dw) gemm(oH2, 1, ld, hz, oDOut, nout, 1, oz, oG + n.l2, nout, w_zs, H + 1, nout, B, Z, EPI_STORE);
+        gemm(oDOut, nout, 1, oz, oW + n.l2, 1, nout, w_zs, oDH2, H, dz, B, H, nout, Z, EPI_MASK, oH2, ld, hz);
         // layer 1
-        if (want_dw) gemm(oH1, 1, H + 1, hz, oDH2, H, 1, dz, oG + n.l1, H, w_zs, H + 1, H, B, Z, EPI_STORE);
-        gemm(oDH2, H, 1, dz, oW + n.l1, 1, H, w_zs, oDH1, H, dz, B, H, H, Z, EPI_MASK, oH1, H + 1, hz);
+        if (want_dw) gemm(oH1, 1, ld, hz, oDH2, H, 1, dz, oG + n.l1, H, w_zs, H + 1, H, B, Z, EPI_STORE);
+        gemm(oDH2, H, 1, dz, oW + n.l1, 1, H, w_zs, oDH1, H, dz, B, H, H, Z, EPI_MASK, oH1, ld, hz);
         // layer 0
         if (want_dw) gemm(oX, 1, kin + 1, 0, oDH1, H, 1, dz, oG + n.l0, H, w_zs, kin + 1, H, B, Z, EPI_STORE);
         if (dx_cols > 0)
@@ -472,7 +824,15 @@ int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out) {
     SitSac_* h = new (std::nothrow) SitSac_();
     if (!h) return fail(SIT_E_INVALID, "out of memory");
     h->cfg = *cfg; h->device = device; h->graph = nullptr;
-    sac::make_layout(h->L, cfg->hidden, cfg->batch_size);
+    // tensor cores from batch 1024 on: below that an update is ~35 dependent few-microsecond launches and latency, not math,
+    // is the cost (the SIMT products run at batch 64 in 220 us per update)
+    const int tc = (cfg->tensor_cores && cfg->batch_size >= 1024 && cfg->hidden >= 128) ? 1 : 0;
+    sac::make_layout(h->L, cfg->hidden, cfg->batch_size, tc);
+    if (tc) {
+        cudaError_t ce = cudaSetDevice(device);
+        if (ce == cudaSuccess) ce = cudaFuncSetAttribute(sac::gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (ce != cudaSuccess) { delete h; return fail(SIT_E_CUDA, std::string("gemm_tc_kernel shared memory: ") + cudaGetErrorString(ce)); }
+    }
     h->hp.gamma = cfg->gamma; h->hp.tau = cfg->tau; h->hp.lr = cfg->lr; h->hp.alpha0 = cfg->alpha;
     h->hp.auto_alpha = cfg->automatic_entropy_tuning ? 1 : 0; h->hp.target_interval = cfg->target_update_interval;
     h->hp.seed = cfg->seed;
@@ -529,10 +889,12 @@ int sit_sac_init(SitSac h, void* workspace, void* stream) {
     sac::ObsScale osc;
     for (int c = 0; c < sac::S; ++c) osc.v[c] = h->cfg.obs_scale[c];
     sac::obs_scale_kernel<<<1, 32, 0, st>>>(ws + L.o_obs_scale, osc);
-    auto ones = [&](long long o, long long rows, int ld) { sac::ones_col_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(ws + o, rows, ld); };
+    auto ones = [&](long long o, long long rows, int ld, int col = -1) {
+        sac::ones_col_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(ws + o, rows, ld, col < 0 ? ld - 1 : col);
+    };
     ones(L.o_xs, B, sac::S + 1); ones(L.o_xs2, B, sac::S + 1);
     ones(L.o_xsa, B, sac::SA + 1); ones(L.o_xs2a, B, sac::SA + 1); ones(L.o_xspi, B, sac::SA + 1);
-    ones(L.o_hp1, B, H + 1); ones(L.o_hp2, B, H + 1); ones(L.o_hq1, 2LL * B, H + 1); ones(L.o_hq2, 2LL * B, H + 1);
+    ones(L.o_hp1, B, L.ldh, H); ones(L.o_hp2, B, L.ldh, H); ones(L.o_hq1, 2LL * B, L.ldh, H); ones(L.o_hq2, 2LL * B, L.ldh, H);
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
 }

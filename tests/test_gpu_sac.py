@@ -178,3 +178,61 @@ def test_learner_policy_drives_the_rollout():
     # the policy is not saturated: a non-trivial share of the actions lies strictly inside (-1, 1) (with raw
     # observations tanh(mu) is exactly +-1 and every policy gradient is 0)
     assert float((rows[:, 10].abs() < 0.999).float().mean()) > 0.5
+
+
+def _grad_blocks(agent):
+    """name -> gradient tensor of every layer block (weights + bias row) as the last update left them."""
+    H, out, o = agent.hidden, {}, 0
+    g = agent.f["grad"]
+    for net, kin, nout in (("policy", 10, 2), ("q1", 11, 1), ("q2", 11, 1)):
+        for li, (K, N) in enumerate(((kin, H), (H, H), (H, nout))):
+            out[f"{net}.l{li}"] = g[o:o + (K + 1) * N].view(K + 1, N)
+            o += (K + 1) * N
+    return out
+
+
+@pytest.mark.parametrize("hidden,batch", [(256, 1024), (128, 4096), (256, 1500)])
+def test_tensor_core_update_matches_fp32_update(hidden, batch):
+    """Large-batch learner: the hidden-layer products and every contraction over the batch run on tcgen05 (bf16 operands,
+    fp32 accumulate in TMEM, split-k partials summed in a fixed order).  Against the fp32 CUDA-core update with the same
+    seed, batch indices and normal draws: every layer's gradient within 4e-2 relative (L2), losses within 1e-2 -- the
+    bf16 tolerance (operands carry 8 significant bits = 0.4 % per element, sums over >= 128 terms average the rounding
+    out; the layer-0 gradient sits behind three bf16 products in a row and shows the largest error, 2.4e-2); the same
+    update twice is bit-identical."""
+    from sac_maritime_ast_b200 import sac
+    mem = sac.ReplayMemory(8192, device=DEV)
+    mem.extend(_fake_replay(8192, seed=2).to(DEV))
+    kw = dict(device=DEV, hidden_size=hidden, batch_size=batch, seed=21, obs_scale=None)
+    tc, tc2, ref = (sac.SAC(10, None, None, tensor_cores=True, **kw), sac.SAC(10, None, None, tensor_cores=True, **kw),
+                    sac.SAC(10, None, None, tensor_cores=False, **kw))
+    assert torch.equal(tc.f["policy"], ref.f["policy"]) and torch.equal(tc.f["q1"], ref.f["q1"])
+    outs = [a.update_parameters(mem, batch, 0) for a in (tc, tc2, ref)]
+    torch.cuda.synchronize()
+    assert torch.equal(tc.f["idx"], ref.f["idx"]) and torch.equal(tc.f["eps_cur"], ref.f["eps_cur"])
+    for k in range(3):
+        assert abs(outs[0][k] - outs[2][k]) <= 1e-2 * max(1.0, abs(outs[2][k])), (k, outs[0], outs[2])
+    gt, gr = _grad_blocks(tc), _grad_blocks(ref)
+    for name in gr:
+        rel = float((gt[name] - gr[name]).norm() / (gr[name].norm() + 1e-12))
+        assert rel <= 4e-2, (name, rel)
+        assert float(gr[name].norm()) > 0
+    for a in (tc, tc2, ref):
+        a.update(mem, 6)
+    torch.cuda.synchronize()
+    for k in ("policy", "q1", "q2", "q1_target", "q2_target", "adam_m", "adam_v", "log_alpha"):
+        assert torch.equal(tc.f[k], tc2.f[k]), f"{k}: two tensor-core learners with one seed diverged"
+        assert torch.isfinite(tc.f[k]).all()
+    # seven Adam steps of 3e-4: parameters of the two arithmetic paths stay within a few steps of each other
+    assert float((tc.f["policy"] - ref.f["policy"]).abs().max()) <= 7 * 2 * 3e-4 + 1e-6
+    assert tc.updates == ref.updates == 7
+
+
+def test_tensor_core_learner_below_the_batch_threshold_is_the_fp32_path():
+    from sac_maritime_ast_b200 import sac
+    mem = sac.ReplayMemory(2048, device=DEV)
+    mem.extend(_fake_replay(2048, seed=4).to(DEV))
+    a = sac.SAC(10, None, None, device=DEV, hidden_size=128, batch_size=512, seed=3, tensor_cores=True, obs_scale=None)
+    b = sac.SAC(10, None, None, device=DEV, hidden_size=128, batch_size=512, seed=3, tensor_cores=False, obs_scale=None)
+    a.update(mem, 3); b.update(mem, 3)
+    torch.cuda.synchronize()
+    assert torch.equal(a.f["policy"], b.f["policy"]) and torch.equal(a.f["q1"], b.f["q1"])
