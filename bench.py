@@ -758,7 +758,7 @@ def rollout_leg(sit, dev, B=65536, K=32, iters=40, warm_iters=20, hidden=256, pr
 def learner_leg(sit, dev, sampler, batch=64, hidden=256, n=400, warm=50):
     """SAC update_parameters/s (main_ast.py:354) on the replay ring the rollout leg filled: twin-Q SAC, policy and critics
     10/11 -> 256 -> 256, one CUDA-graph replay per update.  Batch 64 (main_ast.py:63-67): fp32 CUDA-core products (latency-bound
-    chain of ~35 small kernels).  Batch 4096: hidden-layer products and every contraction over the batch on tcgen05 (bf16
+    chain of 37 small kernels).  Batch 4096: hidden-layer products and every contraction over the batch on tcgen05 (bf16
     operands, fp32 accumulate in TMEM), split-k partials reduced in a fixed order; the fp32-only path is timed beside it."""
     import torch
     from sac_maritime_ast_b200 import sac

@@ -346,7 +346,7 @@ int sit_ship_outline(int32_t precision, int64_t n, const void* north, const void
  *   target_update_interval updates.
  * Networks: policy 10 -> H -> H -> (mu, log sigma), Q(s, a) 11 -> H -> H -> 1, ReLU, Glorot-uniform weights, zero biases.
  * The policy block has the SitPolicy layout, so the rollout kernels read the weights the learner is updating.
- * All device memory is ONE caller-owned workspace (sit_sac_workspace_bytes, sit_sac_field); an update is ~35 small
+ * All device memory is ONE caller-owned workspace (sit_sac_workspace_bytes, sit_sac_field); an update is 37 small
  * kernels captured once into a CUDA graph and replayed; every random draw is Philox keyed by (seed, update index). */
 typedef struct SitSacConfig {
     int32_t hidden;                    /* H: multiple of 32 in [32, 256] (main_ast.py:67: 256) */

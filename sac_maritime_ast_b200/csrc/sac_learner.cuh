@@ -12,7 +12,7 @@
 //     backward  dWaug = Xaug^T . dY              (weight and bias gradients in one product)
 //               dX    = (dY . W^T) * (X > 0)     (first K rows of Waug only)
 // are all instances of one strided, z-batched (twin critics side by side) GEMM kernel with a fused epilogue.
-// An update is 28 such products + 7 element-wise kernels; sizes are tiny (B = 64, H = 256: 0.16 GFLOP), so the cost is
+// An update is 28 such products + 9 element-wise kernels; sizes are tiny (B = 64, H = 256: 0.16 GFLOP), so the cost is
 // launch latency: the whole update is captured once into a CUDA graph and replayed.  All reductions have a fixed order:
 // two runs with the same seed give bit-identical parameters.
 #pragma once
@@ -776,7 +776,7 @@ struct Launcher {
     }
 };
 
-// one update_parameters (main_ast.py:354): ~35 kernels on `st`
+// one update_parameters (main_ast.py:354): 37 kernels on `st` (43 on the tensor-core path: 6 split-k reduces)
 static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long capacity, const unsigned long long* n_rows,
                            float* losses, cudaStream_t st) {
     const Layout& L = h->L;
@@ -824,7 +824,7 @@ int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out) {
     SitSac_* h = new (std::nothrow) SitSac_();
     if (!h) return fail(SIT_E_INVALID, "out of memory");
     h->cfg = *cfg; h->device = device; h->graph = nullptr;
-    // tensor cores from batch 1024 on: below that an update is ~35 dependent few-microsecond launches and latency, not math,
+    // tensor cores from batch 1024 on: below that an update is 37 dependent few-microsecond launches and latency, not math,
     // is the cost (the SIMT products run at batch 64 in 220 us per update)
     const int tc = (cfg->tensor_cores && cfg->batch_size >= 1024 && cfg->hidden >= 128) ? 1 : 0;
     sac::make_layout(h->L, cfg->hidden, cfg->batch_size, tc);

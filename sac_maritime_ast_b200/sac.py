@@ -138,10 +138,10 @@ class SAC:
         self.f["idx"] = self.f["idx"].view(torch.int32)
         self.f["updates"] = self.f["updates"].view(torch.int64)
         self.losses = torch.zeros(8, dtype=torch.float32, device=self.device)
-        # kernels one update enqueues: 28 products + 7 element-wise; on the tensor-core path (batch >= 1024, hidden >= 128)
+        # kernels one update enqueues: 28 products + 9 element-wise; on the tensor-core path (batch >= 1024, hidden >= 128)
         # the 6 split-k products (weight gradients: contraction over the batch) are followed by a reduce kernel each
         self.tensor_cores = bool(cfg.tensor_cores) and cfg.batch_size >= 1024 and cfg.hidden >= 128
-        self.kernels_per_update = 35 + (6 if self.tensor_cores else 0)
+        self.kernels_per_update = 37 + (6 if self.tensor_cores else 0)
         self._side = None
         self.launches = 0
         _lib.check(self.L.sit_sac_init(self.h, self.ws.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream))
