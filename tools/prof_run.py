@@ -19,7 +19,7 @@ elif which.startswith("roll"):
     for a in sys.argv[2:]:
         k, v = a.split("=")
         kw[k] = v if k in ("precision", "mode") else int(v)
-    r = bench.rollout_leg(sit, dev, **kw); smp = r.pop("sampler"); print(r)
+    r = bench.rollout_leg(sit, dev, **kw); smp = r.pop("sampler"); r.pop("memory", None); print(r)
     if which == "roll_learn":
         print(bench.learner_leg(sit, dev, smp))
 elif which.startswith("env"):
