@@ -216,3 +216,59 @@ def test_map_query_matches_geometry_oracle():
         assert bool(flags[j] & 2) == outside, (j, n, e)
         d = min(p.exterior.distance(pt) for p in polys)
         assert abs(dist[j] - d) <= 1e-9 * max(1.0, d), (j, n, e, dist[j], d)
+
+
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_map_query_matches_exact_evaluator(precision):
+    """sit_map_query against the INDEPENDENT exact evaluator (tests/exact_geometry.py: winding number and point-segment
+    distance in integer / rational arithmetic), not against the restatement it was derived with: 10^5 grid points (a quarter
+    of them hugging the rings) plus every vertex, edge point, collinear extension and ray-through-vertex point of the
+    default map.  fp64: containment exact everywhere (boundary = not contained), distance <= 1e-12 relative.  fp32: the
+    query points are float32-representable here, so the only rounding is inside the kernel; mismatches are COUNTED and must
+    all lie within one float32 ulp (of the coordinate magnitude, 1e4 m -> 1e-3 m) of a ring."""
+    import exact_geometry as X
+    import gpu_helpers as G
+    env = G.make_env(sc.ENV_SCENARIOS["default"], n_envs=1, precision=precision)
+    rng = np.random.default_rng(11)
+    n = 100_000
+    ix = rng.integers(-500 * X.GRID, 10500 * X.GRID, n); iy = rng.integers(-500 * X.GRID, 10500 * X.GRID, n)
+    from oracle import geometry
+    edges = geometry.flatten_edges(sc.DEFAULT_MAP)
+    for j in range(0, n, 4):
+        x1, y1, x2, y2, _ = edges[j % len(edges)]
+        t = rng.random()
+        ix[j] = int(round((x1 + t * (x2 - x1)) * X.GRID)) + rng.integers(-300, 301)
+        iy[j] = int(round((y1 + t * (y2 - y1)) * X.GRID)) + rng.integers(-300, 301)
+    if precision == "fp32":                      # keep the points float32-representable: multiples of 1/64 m below 16384 m
+        ix, iy = (ix // 16) * 16, (iy // 16) * 16
+    inside, bnd = X.locate_int(sc.DEFAULT_MAP, ix, iy)
+    x, y = ix / X.GRID, iy / X.GRID
+    flags, dist = env.map_query(torch.from_numpy(y.copy()), torch.from_numpy(x.copy()), want_dist=True)
+    got = (flags.cpu().numpy() & 1).astype(bool)
+    dist = dist.double().cpu().numpy()
+    bad = np.nonzero(got != inside)[0]
+    if precision == "fp64":
+        assert len(bad) == 0, f"containment differs from the exact locator at {bad[:5]}"
+    else:
+        d_bad = [X.sqrt_fraction(X.dist2_exact(sc.DEFAULT_MAP, float(x[j]), float(y[j]))) for j in bad]
+        print(f"\n[map query fp32] {len(bad)} of {n} containment verdicts differ from the exact locator; farthest from a ring: "
+              f"{max(d_bad) if d_bad else 0.0:.2e} m")
+        assert all(d <= 1.5e-3 for d in d_bad), "an fp32 mismatch farther than a float32 ulp from every ring"
+        assert len(bad) <= 0.001 * n
+    sample = rng.choice(n, 1500, replace=False)
+    tol = 1e-12 if precision == "fp64" else 2e-6
+    for j in sample:
+        d = X.sqrt_fraction(X.dist2_exact(sc.DEFAULT_MAP, float(x[j]), float(y[j])))
+        assert abs(dist[j] - d) <= tol * max(1.0, d) + (0.0 if precision == "fp64" else 2e-3), (j, dist[j], d)
+    # special points: vertices / edge points are boundary, hence not contained -- exactly, in both precisions (the map's
+    # coordinates and these points are float32-representable)
+    pts = X.special_points(sc.DEFAULT_MAP)
+    sx = np.array([float(p[0]) for p in pts]); sy = np.array([float(p[1]) for p in pts])
+    f2 = (env.map_query(torch.from_numpy(sy), torch.from_numpy(sx)).cpu().numpy() & 1).astype(bool)
+    n_bnd = 0
+    for (px, py, tag), g in zip(pts, f2):
+        ins, b = X.locate_exact(sc.DEFAULT_MAP, px, py)
+        n_bnd += b
+        if precision == "fp64" or float(np.float32(px)) == float(px) and float(np.float32(py)) == float(py):
+            assert bool(g) == ins, (tag, px, py)
+    assert n_bnd >= 3 * 39
