@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 SRC = os.path.join(HERE, "shipsim.cu")
-DEPS = [SRC, os.path.join(HERE, "ship_core.cuh"), os.path.join(HERE, "ship_x2.cuh"), os.path.join(HERE, "env_core.cuh"), os.path.join(HERE, "sac_learner.cuh"),
+DEPS = [SRC, os.path.join(HERE, "ship_core.cuh"), os.path.join(HERE, "ship_x2.cuh"), os.path.join(HERE, "env_x2.cuh"), os.path.join(HERE, "env_core.cuh"), os.path.join(HERE, "sac_learner.cuh"),
         os.path.join(ROOT, "include", "shipsim.h")]
 OUT = os.path.join(PKG, "libshipsim.so")
 

@@ -51,6 +51,7 @@ struct ModeX {
     float add_me, cap_me;                    // load_me = min(total + add_me, cap_me)
     float a_el, c_el;                        // load_el = a_el * ((total + hotel) - load_me) + c_el
     float inv_me_cap, inv_el_cap;            // 0 where the reference guards a zero capacity
+    float me_cap_kw, _pad;                   // main_engine_capacity / 1000: 'available power me [kw]' (ship_model.py:662-664)
 };
 
 struct ShipPX {
@@ -83,7 +84,12 @@ struct Ship2 {
 };
 
 // per-ship mode constants as lanes of packed registers (several modes in one fleet) or as uniform scalars (one mode)
-struct ModeV { V avail_total, avail_me, avail_el, cap_tq_me, cap_tq_el, add_me, cap_me, a_el, c_el, inv_me_cap, inv_el_cap; };
+struct ModeV { V avail_total, avail_me, avail_el, cap_tq_me, cap_tq_el, add_me, cap_me, a_el, c_el, inv_me_cap, inv_el_cap, me_cap_kw; };
+
+// the stored (pre-step) observables the env reads back (MSRL_env_ex.py:267-269,298-300): shaft speed [rad/s] before the
+// step and the load on the main engine [W]
+struct StepOut2 { V om_pre, load_me; };
+enum { AVOID_NONE = 0, AVOID_BOTH = 1, AVOID_LANE0 = 2 };
 
 __device__ __forceinline__ float& lane(V& a, int l) { return l == 0 ? a.x : a.y; }
 __device__ __forceinline__ float lane(const V& a, int l) { return l == 0 ? a.x : a.y; }
@@ -189,9 +195,12 @@ __device__ __forceinline__ V atan2v(const ShipPX& P, const V x) {
 }
 
 // One step of two ships.  MP = ModeX: one machinery mode for the whole fleet (uniform operands); MP = ModeV: per-ship modes.
-// i0 / i1: the two ships' indices (only read on the rare waypoint-switch path).
-template <bool AVOID, typename MP, typename IdxFn>
-__device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& s, const ShipPtrs<float>& g, const IdxFn& idx) {
+// idx(l): the ship index of lane l (only read on the rare waypoint-switch path).  AVOID: the collision-avoidance branch on
+// no ship, both, or lane 0 only (the two-ship env: lane 0 = test ship, MSRL_env_ex.py:240-249).  STORE = false reproduces
+// init_step (MSRL_env_ex.py:188-215): no store_simulation_data, i.e. no fuel accumulation.
+template <int AVOID, bool STORE, typename MP, typename IdxFn>
+__device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& s, const ShipPtrs<float>& g, const IdxFn& idx,
+                                           StepOut2& o) {
     // ---- LOS_guidance.py:88-103 next_wpt: packed float pre-test; the decision itself in double (next_wpt2) -----------------
     {
         const V dn = sub(s.SX, s.X), de = sub(s.SY, s.Y);
@@ -234,9 +243,12 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
     V thr = fma(e2s, P.kp_w, mul(s.ei_w, P.ki_w));
 
     // ---- MSRL_env_ex.py:240-249 collision-avoidance branch (test ship: always) ---------------------------------------
-    if (AVOID) {
-        thr.x = fminf(fmaxf(thr.x * 0.5f, 0.0f), 1.1f); thr.y = fminf(fmaxf(thr.y * 0.5f, 0.0f), 1.1f);
+    if (AVOID != AVOID_NONE) {
+        thr.x = fminf(fmaxf(thr.x * 0.5f, 0.0f), 1.1f);
         rud.x = fminf(fmaxf(rud.x + P.rud_bias, -P.rud_max), P.rud_max);
+    }
+    if (AVOID == AVOID_BOTH) {
+        thr.y = fminf(fmaxf(thr.y * 0.5f, 0.0f), 1.1f);
         rud.y = fminf(fmaxf(rud.y + P.rud_bias, -P.rud_max), P.rud_max);
     }
 
@@ -250,7 +262,8 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
     const V thrust_w = mul(om, vabs(om));
 
     // ---- ship_model.py:645-684 store_simulation_data: load split + fuel accumulators (ship_engine.py:239-292) -----------
-    {
+    o.om_pre = om;
+    if (STORE) {
         const V total = mul(thr, M.avail_total);
         V load_me = add(total, M.add_me);
         load_me.x = fminf(load_me.x, lane(M.cap_me, 0)); load_me.y = fminf(load_me.y, lane(M.cap_me, 1));
@@ -259,6 +272,7 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
         // rate dt = load (a pct^2 + b pct + c) dt / 3.6e9; a zero load gives a zero rate without the reference's guards
         const V pme = fma(fma(pct_me, P.sfc_me[0], P.sfc_me[1]), pct_me, P.sfc_me[2]);
         const V pel = fma(fma(pct_el, P.sfc_dg[0], P.sfc_dg[1]), pct_el, P.sfc_dg[2]);
+        o.load_me = load_me;
         s.f_me = fma(load_me, pme, s.f_me);
         s.f_el = fma(load_el, pel, s.f_el);   // fuel_cons (the sum of both, ship_engine.py:288-292) is formed where the state is stored
     }

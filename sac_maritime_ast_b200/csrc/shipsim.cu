@@ -228,14 +228,15 @@ fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float>
         const ModeX &a = P.mode[g.mode[i0]], &b = P.mode[g.mode[i1]];
 #define MV_(f) MV.f = make_float2(a.f, b.f)
         MV_(avail_total); MV_(avail_me); MV_(avail_el); MV_(cap_tq_me); MV_(cap_tq_el); MV_(add_me); MV_(cap_me);
-        MV_(a_el); MV_(c_el); MV_(inv_me_cap); MV_(inv_el_cap);
+        MV_(a_el); MV_(c_el); MV_(inv_me_cap); MV_(inv_el_cap); MV_(me_cap_kw);
 #undef MV_
     }
     float* tr = io.traj + i0;   // running row pointer of the every-step trajectory
     SIT_PRAGMA(unroll SIT_X2_UNROLL)
     for (int t = 0; t < K; ++t) {
-        if (SINGLE_MODE) ship_step2<AVOID>(P, P.mode[0], s, g, idx);
-        else ship_step2<AVOID>(P, MV, s, g, idx);
+        StepOut2 so;
+        if (SINGLE_MODE) ship_step2<AVOID ? AVOID_BOTH : AVOID_NONE, true>(P, P.mode[0], s, g, idx, so);
+        else ship_step2<AVOID ? AVOID_BOTH : AVOID_NONE, true>(P, MV, s, g, idx, so);
         if (TRAJ) {   // every-step trajectory [K][8][S]: coalesced 64-bit streaming stores, the only memory traffic of the loop
 #pragma unroll
             for (int l = 0; l < 2; ++l)
@@ -747,6 +748,8 @@ __global__ void __launch_bounds__(256) env_init_step_kernel(const __grid_constan
     ship_step<R, false>(P, s, g, i, false, false, o, nullptr);
     store_ship(s, g, i);
 }
+
+#include "env_x2.cuh"
 
 // =================================================================================================
 // K4: rollout policy -- for every pending env: tanh-Gaussian / uniform policy on its held observation, scoping
@@ -1544,7 +1547,7 @@ static void derive_shipx(const ShipP<float>& P, x2::ShipPX& X) {
         x2::ModeX& Y = X.mode[j];
         Y.avail_total = M.avail_total; Y.avail_me = M.avail_me; Y.avail_el = M.avail_el;
         Y.cap_tq_me = M.cap_tq_me; Y.cap_tq_el = M.cap_tq_el;
-        Y.inv_me_cap = M.inv_me_cap; Y.inv_el_cap = M.inv_el_cap;
+        Y.inv_me_cap = M.inv_me_cap; Y.inv_el_cap = M.inv_el_cap; Y.me_cap_kw = M.me_cap_kw;
         if (M.sg == SIT_SG_MOTOR) { Y.add_me = 0.0f; Y.cap_me = M.me_cap; Y.a_el = 1.0f; Y.c_el = 0.0f; }
         else { Y.add_me = M.load_me_add; Y.cap_me = INFINITY; Y.a_el = 0.0f; Y.c_el = M.load_el_const; }
     }
@@ -2043,6 +2046,36 @@ int sit_env_init_step(SitHandle h, void* state, const uint8_t* mask, void* strea
 }
 
 }  // extern "C"
+// fp32 envs whose two roles share one parameter set CAN run the packed one-thread-per-env kernel (env_x2.cuh) unless the
+// reward_parts / snapshot outputs are asked for: SIT_ENV_X2=1 (or -DSIT_ENV_X2_DEFAULT=1) switches it on.  Off by default:
+// it wins while episodes are young (1.39e10 -> 1.67e10 env-steps/s) and loses once resets, rescans and hull checks are
+// frequent (bench env leg 1.27e10 -> 1.08e10, 10 000-step horizon 1.06e10 -> 0.86e10), see env_x2.cuh
+#ifndef SIT_ENV_X2_DEFAULT
+#define SIT_ENV_X2_DEFAULT 0
+#endif
+template <typename R, bool ROLL>
+static bool env_x2(SitHandle, const ShipPtrs<R>&, const EnvPtrs<R>&, int, const EnvIO<R>&, const RollArgs&, cudaStream_t) { return false; }
+template <bool ROLL>
+static bool env_x2_f(SitHandle h, const ShipPtrs<float>& g, const EnvPtrs<float>& ge, int K, const EnvIO<float>& k, const RollArgs& ra,
+                     cudaStream_t st) {
+    const char* sw = std::getenv("SIT_ENV_X2");      // read per call: tests switch it inside one process
+    const bool on = sw ? std::atoi(sw) != 0 : SIT_ENV_X2_DEFAULT != 0;
+    if (!on || !h->same_params || k.rew_parts || k.snap || h->cfg.ship[0].machinery_kind != SIT_MACH_FULL) return false;
+    static const int env_block = std::getenv("SIT_ENVX2_BLOCK") ? std::atoi(std::getenv("SIT_ENVX2_BLOCK")) : 0;
+    const int block = (env_block == 32 || env_block == 64 || env_block == 128) ? env_block : 128, grid = grid_for(ra.env_count, block);
+    if (h->pf[0].n_modes > 1) env_step_x2_kernel<ROLL, true><<<grid, block, 0, st>>>(*h->kf, h->px, g, ge, K, k, ra);
+    else env_step_x2_kernel<ROLL, false><<<grid, block, 0, st>>>(*h->kf, h->px, g, ge, K, k, ra);
+    return true;
+}
+template <>
+bool env_x2<float, false>(SitHandle h, const ShipPtrs<float>& g, const EnvPtrs<float>& ge, int K, const EnvIO<float>& k,
+                          const RollArgs& ra, cudaStream_t st) { return env_x2_f<false>(h, g, ge, K, k, ra, st); }
+#ifdef SIT_ROLL_X2   // the rollout variant of the packed kernel: parity-green, slower at rollout sizes (see env_x2.cuh)
+template <>
+bool env_x2<float, true>(SitHandle h, const ShipPtrs<float>& g, const EnvPtrs<float>& ge, int K, const EnvIO<float>& k,
+                         const RollArgs& ra, cudaStream_t st) { return env_x2_f<true>(h, g, ge, K, k, ra, st); }
+#endif
+
 template <typename R>
 static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaStream_t st, int64_t env_first = 0,
                       int64_t env_count = -1) {
@@ -2067,7 +2100,9 @@ static int env_step_t(SitHandle h, void* state, int K, const SitEnvIO* io, cudaS
     std::memset(&ra, 0, sizeof(ra));
     ra.env_first = env_first; ra.env_count = env_count < 0 ? h->n_envs : env_count;
     const int block = 128, grid = grid_for(2 * ra.env_count, block);
-    if (k.rew_parts || k.snap) {
+    if (env_x2<R, false>(h, g, ge, K, k, ra, st)) {
+        // packed kernel launched
+    } else if (k.rew_parts || k.snap) {
         if (h->same_params) env_step_kernel<R, true, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
         else env_step_kernel<R, false, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     } else if (h->same_params) env_step_kernel<R, true, false><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
@@ -2104,7 +2139,9 @@ static int rollout_step_t(SitHandle h, void* state, int K, const RollArgs& ra, c
     const EnvPtrs<R> ge = env_ptrs<R>(h, state);
     const EnvKArgs<R>& A = HostSel<R>::env(h);
     const int block = 128, grid = grid_for(2 * ra.env_count, block);
-    if (h->same_params) env_step_kernel<R, true, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
+    if (env_x2<R, true>(h, g, ge, K, k, ra, st)) {
+        // packed kernel launched
+    } else if (h->same_params) env_step_kernel<R, true, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     else env_step_kernel<R, false, true><<<grid, block, 0, st>>>(A, g, ge, K, k, ra);
     CUDA_TRY(cudaGetLastError());
     return SIT_OK;
