@@ -11,22 +11,31 @@
 // Used for fp32 env handles whose two roles share one parameter set (the reference's default, main_ast.py:207-237) when no
 // reward_parts / snapshot output is asked for; every other case runs env_step_kernel.  Same state buffer, same outputs.
 //
-// Measured (B200): 1.39e10 -> 1.67e10 env-steps/s on the bench's env leg (38 % fewer warp instructions per env-step).  The
-// ROLLOUT variant (ROLL = true) is written and parity-green but NOT used by default: at 65 536 envs the kernel is one to two
-// waves of 8 .. 16 warps per SM, its issue rate drops to 29 % (instruction-fetch stalls 1.8 per issue against 0.46 for the
-// lane-pair kernel, which keeps twice the warps in flight) and the rollout runs 6 % slower than with env_step_kernel
-// (2.32e7 against 2.46e7 samples/s); compile with -DSIT_ROLL_X2 to try it.
-// Reference citations are relative to /root/reference/.
+// MEASURED (B200, 262 144 envs x 64 steps per launch; rollout = 65 536 envs, K = 32), against env_step_kernel:
+//   * warp instructions per env-step: 38 % fewer (73 M against 117 M per rollout launch);
+//   * first version (two inlined step instances, every rare path inlined per ship; 4 700 SASS instructions): 1.39e10 -> 1.67e10
+//     env-steps/s while episodes are young, but 1.27e10 -> 1.08e10 once resets, rescans and hull checks are frequent (the
+//     bench's env leg) and 1.06e10 -> 0.86e10 over the 10 000-step horizon: issue slots 33 % busy with 5.3 instruction-fetch
+//     stalls per issue (0.34 for the lane-pair kernel) -- half the warps, diverging into a 75 KB instruction footprint;
+//   * this version (ONE step instance that also serves init_step through per-thread step counters, the per-ship rare paths
+//     as two-trip loops around one copy, segment geometry as a real call; 3 400 instructions): young 1.49e10, bench leg
+//     1.20e10 (lane-pair: 1.26e10), rollout 2.44e7 samples/s (lane-pair: 2.45e7) at (128, 2); (128, 3) and (128, 4) spill
+//     and are slower in the rollout.
+// The warp-cooperative rare paths (one warp rescans / hull-checks for one ship at a time) cost the same per event in both
+// kernels, and with 64 ships per warp and half the resident warps there is less left to overlap them with.  The kernel
+// is therefore OPT-IN (SIT_ENV_X2=1; the rollout variant additionally needs -DSIT_ROLL_X2 at build time), parity-tested on
+// all ten env goldens (tests/test_gpu_env.py) -- a measured experiment, not the default path.
 #pragma once
 
 namespace sit {
 
+// element l of a register pair (a run-time l compiles to selects: no local-memory array)
+template <typename T>
+__device__ __forceinline__ T& pick(T& a, T& b, const int l) { return l == 0 ? a : b; }
+
 // MULTI: per-ship machinery modes (run-time mode switching); otherwise the single mode's constants are uniform operands.
-// 128 registers / 4 CTAs per SM (16 warps): the step loop spills ~300 B but the doubled occupancy wins (measured on B200,
-// 262 144 envs x 64 steps: 1.60e10 env-steps/s at (128, 2) = 211 registers, 1.58e10 at (128, 3), 1.67e10 at (128, 4);
-// 64-thread CTAs are 1 % slower at every setting)
 #ifndef SIT_ENVX2_MINB
-#define SIT_ENVX2_MINB 4
+#define SIT_ENVX2_MINB 2   /* 243 registers, no spills; (128, 3) = 168 and (128, 4) = 128 registers spill 200 .. 570 B */
 #endif
 template <bool ROLL, bool MULTI>
 __global__ void __launch_bounds__(128, SIT_ENVX2_MINB)
@@ -63,25 +72,28 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
         sincos_(w_dir.y, sb, cb); s.wcb.y = w_speed.y * cb; s.wsb.y = w_speed.y * sb;
     };
     set_wind2(ld2(g.wind_speed), ld2(g.wind_dir));
-    int32_t steps[2], kk[2];
-    double pN[2], pE[2], aN[2], aE[2];                 // segment start and absolute position of each ship (float64)
-    float endN[2], endE[2];                            // route end point (constant: insertions go before it, controllers.py:298-303)
-#pragma unroll
+    // per ship (0 = test, 1 = obstacle), as register pairs: step counter, segment index the float64 base belongs to, segment
+    // start and absolute position (float64), route end point (constant: insertions go before it, controllers.py:298-303)
+    int32_t steps0, steps1, kk0, kk1;
+    double pN0, pN1, pE0, pE1, aN0, aN1, aE0, aE1;
+    float endN0, endN1, endE0, endE1;
+#pragma unroll 1
     for (int l = 0; l < 2; ++l) {
         const int64_t i = i0 + l;
-        s.k[l] = g.k[i]; s.n_wp[l] = g.n_wp[i]; steps[l] = g.steps[i];
-        const int k = s.k[l];
-        kk[l] = k;
-        pN[l] = g.wp_n[(int64_t)(k - 1) * S + i]; pE[l] = g.wp_e[(int64_t)(k - 1) * S + i];
+        const int k = g.k[i], nw = g.n_wp[i];
+        pick(s.k[0], s.k[1], l) = k; pick(s.n_wp[0], s.n_wp[1], l) = nw; pick(steps0, steps1, l) = g.steps[i];
+        pick(kk0, kk1, l) = k;
+        const double pN = g.wp_n[(int64_t)(k - 1) * S + i], pE = g.wp_e[(int64_t)(k - 1) * S + i];
         const double cN = g.wp_n[(int64_t)k * S + i], cE = g.wp_e[(int64_t)k * S + i];
-        aN[l] = g.north[i]; aE[l] = g.east[i];
+        const double N = g.north[i], E = g.east[i];
         // the relative pair written by the previous launch is kept while it still describes the float64 position
         float x = g.rel_n[i], cx = g.rel_cn[i], y = g.rel_e[i], cy = g.rel_ce[i];
-        if (!(abs_pos(pN[l], x, cx) == aN[l])) split_rel(aN[l] - pN[l], x, cx);
-        if (!(abs_pos(pE[l], y, cy) == aE[l])) split_rel(aE[l] - pE[l], y, cy);
+        if (!(abs_pos(pN, x, cx) == N)) split_rel(N - pN, x, cx);
+        if (!(abs_pos(pE, y, cy) == E)) split_rel(E - pE, y, cy);
         lane(s.X, l) = x; lane(s.CX, l) = cx; lane(s.Y, l) = y; lane(s.CY, l) = cy;
-        set_segment2(s, P, pN[l], pE[l], cN, cE, l);
-        endN[l] = g.wp_n[(int64_t)(s.n_wp[l] - 1) * S + i]; endE[l] = g.wp_e[(int64_t)(s.n_wp[l] - 1) * S + i];
+        pick(pN0, pN1, l) = pN; pick(pE0, pE1, l) = pE; pick(aN0, aN1, l) = N; pick(aE0, aE1, l) = E;
+        set_segment2<true>(s, P, pN, pE, cN, cE, l);
+        pick(endN0, endN1, l) = g.wp_n[(int64_t)(nw - 1) * S + i]; pick(endE0, endE1, l) = g.wp_e[(int64_t)(nw - 1) * S + i];
     }
     ModeV MV;
     auto load_modes = [&]() {
@@ -110,35 +122,44 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
     R rsum = (R)0;
     bool any_done = false;
     unsigned my_cnt = 0, n_live = 0, n_eps = 0, n_closed = 0;
-    MapCache mc[2];
-#pragma unroll
-    for (int l = 0; l < 2; ++l) {
-        mc[l].idx = (uint32_t)g.mc_idx[i0 + l]; mc[l].p0n = g.mc_n[i0 + l]; mc[l].p0e = g.mc_e[i0 + l]; mc[l].b2 = g.mc_b2[i0 + l];
-    }
+    MapCache mc0, mc1;
+    mc0.idx = (uint32_t)g.mc_idx[i0]; mc0.p0n = g.mc_n[i0]; mc0.p0e = g.mc_e[i0]; mc0.b2 = g.mc_b2[i0];
+    mc1.idx = (uint32_t)g.mc_idx[i0 + 1]; mc1.p0n = g.mc_n[i0 + 1]; mc1.p0e = g.mc_e[i0 + 1]; mc1.b2 = g.mc_b2[i0 + 1];
     const R rpm_per_rads = A.P[0].rpm_per_rads;
 
     // absolute float64 positions from the (possibly new) segment starts
     auto refresh_abs = [&]() {
-#pragma unroll
-        for (int l = 0; l < 2; ++l) {
-            if (s.k[l] != kk[l]) {     // the ship switched segments inside the step: new float64 base
-                kk[l] = s.k[l];
-                pN[l] = g.wp_n[(int64_t)(kk[l] - 1) * S + idx(l)]; pE[l] = g.wp_e[(int64_t)(kk[l] - 1) * S + idx(l)];
+        if (s.k[0] != kk0 || s.k[1] != kk1) {     // a ship switched segments inside the step: new float64 base
+#pragma unroll 1
+            for (int l = 0; l < 2; ++l) {
+                const int k = pick(s.k[0], s.k[1], l);
+                pick(kk0, kk1, l) = k;
+                pick(pN0, pN1, l) = g.wp_n[(int64_t)(k - 1) * S + idx(l)]; pick(pE0, pE1, l) = g.wp_e[(int64_t)(k - 1) * S + idx(l)];
             }
-            aN[l] = abs_pos(pN[l], lane(s.X, l), lane(s.CX, l)); aE[l] = abs_pos(pE[l], lane(s.Y, l), lane(s.CY, l));
         }
+        aN0 = abs_pos(pN0, s.X.x, s.CX.x); aE0 = abs_pos(pE0, s.Y.x, s.CY.x);
+        aN1 = abs_pos(pN1, s.X.y, s.CX.y); aE1 = abs_pos(pE1, s.Y.y, s.CY.y);
     };
 
-    for (int t = 0; t < K; ++t) {
+    // One trip of the loop = ONE packed ship step.  A thread whose episode ended reloads the initial state and spends its next
+    // trip on init_step (MSRL_env_ex.py:188-215: no avoidance, nothing stored, no rewards) WITHOUT advancing its step counter
+    // t, so the kernel holds a single instance of the step code; the other threads of the warp take an ordinary step in that
+    // trip.  t is therefore per thread, and the loop runs until every thread of the warp has done its K steps.
+    int t = 0;
+    bool init_mode = false;
+    while (true) {
+        const bool todo = t < K || init_mode, was_init = init_mode;
+        if (!__any_sync(FULL, todo)) break;
         // ---- inputs: converted_action and SAC_update (MSRL_env_ex.py:402-405) -----------------------------------------
-        bool su = false, live = true;
+        bool su = false, live = todo;
+        const bool step_mode = live && !init_mode;
         if (ROLL) {
-            if (pending) {
+            if (step_mode && pending) {
                 if (have_act) { su = true; pending = false; have_act = false; tr_open = true; }   // action from sit_rollout_policy
                 else live = false;
             }
             if (!__any_sync(FULL, live && active)) break;
-        } else if (io.action) {
+        } else if (step_mode && io.action) {
             const int64_t ta = io.act_steps > 1 ? t : 0;
             const R a_n = io.action[(ta * 2 + 0) * B + env], a_e = io.action[(ta * 2 + 1) * B + env];
             if (!iw_valid || a_n != act_n || a_e != act_e) {
@@ -155,22 +176,23 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
         StepOut2 so;
         so.om_pre = bc(0.0f); so.load_me = bc(0.0f);
         double ship_d2 = 0.0;
+        const bool stepping = live && !init_mode;   // an ordinary env step in this trip (false: idle, pending, or init_step)
         if (live) {   // ---- phase A: the two ship steps ------------------------------------------------------------------
-            n_live += 1;
+            if (stepping) n_live += 1;
             const bool init = (ROLL || io.init < 0) ? fresh : (t == 0 && io.init != 0);
-            const bool frozen = stop_o;                                  // obs_step :285-310: a stopped obstacle ship is not advanced
-            const double pre_n = aN[1], pre_e = aE[1];
-            if (!frozen && su) {
+            const bool frozen = stepping && stop_o;                      // obs_step :285-310: a stopped obstacle ship is not advanced
+            const double pre_n = aN1, pre_e = aE1;
+            if (stepping && !frozen && su) {
                 // obs_step :324-338 -> update_route controllers.py:298-303: list.insert(-1, wp)
                 const int64_t i = i0 + 1;
                 const int nw = s.n_wp[1];
                 if (nw < g.max_wp) {
                     if (active) {
-                        g.wp_n[(int64_t)nw * S + i] = endN[1]; g.wp_e[(int64_t)nw * S + i] = endE[1];
+                        g.wp_n[(int64_t)nw * S + i] = endN1; g.wp_e[(int64_t)nw * S + i] = endE1;
                         g.wp_n[(int64_t)(nw - 1) * S + i] = act_n; g.wp_e[(int64_t)(nw - 1) * S + i] = act_e;
                     }
                     s.n_wp[1] = nw + 1;
-                    if (s.k[1] == nw - 1) set_segment2(s, P, pN[1], pE[1], (double)act_n, (double)act_e, 1);   // the segment in use ended at the old last point
+                    if (s.k[1] == nw - 1) set_segment2<true>(s, P, pN1, pE1, (double)act_n, (double)act_e, 1);   // the segment in use ended at the old last point
                 }
                 samp_dist = 0.0;
             }
@@ -185,10 +207,10 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
 #undef KP_
                 kpk = s.k[1]; kpn = s.n_wp[1];
             }
-            // test_step :217-283 (avoidance branch always taken) | obs_step :346-373
-            if (MULTI) ship_step2<AVOID_LANE0, true>(P, MV, s, g, idx, so);
-            else ship_step2<AVOID_LANE0, true>(P, P.mode[0], s, g, idx, so);
-            steps[0] += 1;
+            // test_step :217-283 (avoidance branch always taken) | obs_step :346-373 | init_step :188-215 (init_mode)
+            if (MULTI) ship_step2<AVOID_LANE0_RT, true, true>(P, MV, s, g, idx, so, stepping, stepping);
+            else ship_step2<AVOID_LANE0_RT, true, true>(P, P.mode[0], s, g, idx, so, stepping, stepping);
+            if (stepping) steps0 += 1;
             if (frozen) {
 #define KP_(j, f) s.f.y = kp[j]
                 KP_(0, X); KP_(1, Y); KP_(2, CX); KP_(3, CY); KP_(4, SX); KP_(5, SY); KP_(6, thr2); KP_(7, psi); KP_(8, u); KP_(9, v);
@@ -196,14 +218,14 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                 KP_(18, f_me); KP_(19, f_el); KP_(20, alpha); KP_(21, sa); KP_(22, ca);
 #undef KP_
                 s.k[1] = kpk; s.n_wp[1] = kpn;
-                steps[1] += 2;                                           // frozen ship: next_time twice, :294,307
-            } else {
-                steps[1] += 1;
+                steps1 += 2;                                             // frozen ship: next_time twice, :294,307
+            } else if (stepping) {
+                steps1 += 1;
             }
             refresh_abs();
             if (frozen) {
                 if (nstored >= 1) nstored = 2;                           // store_last_simulation_data repeats the last row :292
-            } else {
+            } else if (stepping) {
                 if (!init && nstored >= 1) {                             // :391-395, last two *stored* (pre-step) positions
                     const double dn = pre_n - prev_n, de = pre_e - prev_e;
                     const double d = sqrt(__dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de)));
@@ -212,58 +234,63 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                 prev_n = pre_n; prev_e = pre_e;
                 nstored = nstored < 2 ? nstored + 1 : 2;
             }
-            const double ddn = aN[0] - aN[1], dde = aE[0] - aE[1];
+            const double ddn = aN0 - aN1, dde = aE0 - aE1;
             ship_d2 = __dadd_rn(__dmul_rn(ddn, ddn), __dmul_rn(dde, dde));
         }
 
-        // ---- phase B (whole warp): distance to the nearest ring + hull containment, nearest-ring cache, once per ship -------
-        R pn[2], pe[2], d2map[2];
-        bool inside[2];
-#pragma unroll
-        for (int l = 0; l < 2; ++l) {
-            pn[l] = (R)aN[l]; pe[l] = (R)aE[l];
-            d2map[l] = (R)3.0e38; inside[l] = false;
-            if (n_edges > 0) {
-                const float ddn_ = pn[l] - mc[l].p0n, dde_ = pe[l] - mc[l].p0e;
-                unsigned nb = __ballot_sync(FULL, live && !(ddn_ * ddn_ + dde_ * dde_ < fabsf(mc[l].b2)));
+        // ---- phase B (whole warp): distance to the nearest ring + hull containment, nearest-ring cache, once per ship, as a
+        //      two-trip loop around ONE copy of the cooperative scans (instruction footprint) --------------------------------
+        const R pn0 = (R)aN0, pe0 = (R)aE0, pn1 = (R)aN1, pe1 = (R)aE1;
+        R d2map0 = (R)3.0e38, d2map1 = (R)3.0e38;
+        bool inside0 = false, inside1 = false;
+        if (n_edges > 0) {
+#pragma unroll 1
+            for (int l = 0; l < 2; ++l) {
+                const R pnl = l == 0 ? pn0 : pn1, pel = l == 0 ? pe0 : pe1;
+                MapCache m = l == 0 ? mc0 : mc1;
+                const float ddn_ = pnl - m.p0n, dde_ = pel - m.p0e;
+                unsigned nb = __ballot_sync(FULL, stepping && !(ddn_ * ddn_ + dde_ * dde_ < fabsf(m.b2)));
                 while (nb) {   // budget spent: the whole warp rescans that lane's position
                     const int L = __ffs(nb) - 1;
                     nb &= nb - 1;
-                    const MapCache c = coop_scan(s_edges, n_edges, __shfl_sync(FULL, pn[l], L), __shfl_sync(FULL, pe[l], L), wl);
-                    if (wl == L) mc[l] = c;
+                    const MapCache c = coop_scan(s_edges, n_edges, __shfl_sync(FULL, pnl, L), __shfl_sync(FULL, pel, L), wl);
+                    if (wl == L) m = c;
                 }
-                d2map[l] = cached_dist2(s_edges, mc[l].idx, pn[l], pe[l]);
-                inside[l] = (__float_as_uint(mc[l].b2) >> 31) != 0u;   // far from every ring all four corners share the centre's side
-                unsigned hb = __ballot_sync(FULL, live && d2map[l] <= EP.near2);
+                const R d2 = cached_dist2(s_edges, m.idx, pnl, pel);
+                bool ins = (__float_as_uint(m.b2) >> 31) != 0u;   // far from every ring all four corners share the centre's side
+                unsigned hb = __ballot_sync(FULL, stepping && d2 <= EP.near2);
                 while (hb) {   // is_pos_inside_obstacles, MSRL_env_ex.py:490-515: the four corners of the +-L/2 square
                     const int L = __ffs(hb) - 1;
                     hb &= hb - 1;
-                    const bool in = coop_hull_inside(s_edges, n_edges, __shfl_sync(FULL, pn[l], L), __shfl_sync(FULL, pe[l], L),
-                                                     EP.half_len[l], wl);
-                    if (wl == L) inside[l] = in;
+                    const bool in = coop_hull_inside(s_edges, n_edges, __shfl_sync(FULL, pnl, L), __shfl_sync(FULL, pel, L),
+                                                     l == 0 ? EP.half_len[0] : EP.half_len[1], wl);
+                    if (wl == L) ins = in;
                 }
+                if (l == 0) { mc0 = m; d2map0 = d2; inside0 = ins; } else { mc1 = m; d2map1 = d2; inside1 = ins; }
             }
         }
 
-        if (live) {   // ---- phase C: rewards, terminal checks, outputs, episode restart ---------------------------------------
+        if (live && init_mode) {
+            init_mode = false;                       // init_step done: the new episode starts with the next trip
+        } else if (stepping) {   // ---- phase C: rewards, terminal checks, outputs, episode restart --------------------------------
             const R rpm_t = so.om_pre.x * rpm_per_rads;                  // stored (pre-step) observables of the test ship
             const R power_me_kw = so.load_me.x * 0.001f;
             const R avail_me_kw = MULTI ? MV.me_cap_kw.x : P.mode[0].me_cap_kw;
             const R ect_t = fabsf(s.e_ct.x), ect_o = fabsf(s.e_ct.y);
-            const R dmap_t = sqrt_(d2map[0]), dmap_o = sqrt_(d2map[1]);
+            const R dmap_t = sqrt_(d2map0), dmap_o = sqrt_(d2map1);
             bool dn_t = false, dn_o = false;
             int st = 0;
             // ---- test ship: test_ship_non_terminal_state_reward :628-664, test_ship_terminal_state_reward :734-809 --------
             R part_t;
             {
-                const bool outside = pn[0] < EP.lo_n[0] || pn[0] > EP.hi_n[0] || pe[0] < EP.lo_e[0] || pe[0] > EP.hi_e[0];
-                const double dnE = aN[0] - (double)endN[0], deE = aE[0] - (double)endE[0];
+                const bool outside = pn0 < EP.lo_n[0] || pn0 > EP.hi_n[0] || pe0 < EP.lo_e[0] || pe0 > EP.hi_e[0];
+                const double dnE = aN0 - (double)endN0, deE = aE0 - (double)endE0;
                 const bool arrived = __dadd_rn(__dmul_rn(dnE, dnE), __dmul_rn(deE, deE)) <= EP.arrive2;
                 const R ntt = ect_t * EP.inv_e_tol + ((R)1 - dmap_t * EP.inv_max_north) * (R)0.01;
                 R rt = (R)0;
                 if (arrived) { stop_t = true; dn_t = true; st |= SIT_ST_TEST_ENDPOINT; }
                 if (outside) { stop_t = true; dn_t = true; st |= SIT_ST_TEST_HORIZON; }
-                if (inside[0]) { if (!stop_t) rt += (R)1000; stop_t = true; dn_t = true; st |= SIT_ST_TEST_TERRAIN; }
+                if (inside0) { if (!stop_t) rt += (R)1000; stop_t = true; dn_t = true; st |= SIT_ST_TEST_TERRAIN; }
                 if (fabsf(rpm_t) > EP.rpm_max) { if (!stop_t) rt += (R)1000; stop_t = true; dn_t = true; st |= SIT_ST_TEST_MECH; }
                 if (ect_t > EP.e_tol) { if (!stop_t) rt += (R)1000; stop_t = true; dn_t = true; st |= SIT_ST_TEST_NAV; }
                 if (power_me_kw > avail_me_kw) { if (!stop_t) rt += (R)1000; stop_t = true; dn_t = true; st |= SIT_ST_TEST_BLACKOUT; }
@@ -273,13 +300,13 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
             //      obs_ship_terminal_state_reward :811-881, shared_non_terminal_state_reward :712-731 (flag after them) ------
             R nto = (R)0, ro_ = (R)0, snt = (R)0;
             {
-                const bool outside = pn[1] < EP.lo_n[1] || pn[1] > EP.hi_n[1] || pe[1] < EP.lo_e[1] || pe[1] > EP.hi_e[1];
-                const double dnE = aN[1] - (double)endN[1], deE = aE[1] - (double)endE[1];
+                const bool outside = pn1 < EP.lo_n[1] || pn1 > EP.hi_n[1] || pe1 < EP.lo_e[1] || pe1 > EP.hi_e[1];
+                const double dnE = aN1 - (double)endN1, deE = aE1 - (double)endE1;
                 const bool arrived = __dadd_rn(__dmul_rn(dnE, dnE), __dmul_rn(deE, deE)) <= EP.arrive2;
                 if (!stop_o) nto = (R)0.1 + (-(ect_o * EP.inv_e_tol) * (R)0.01) + (-((R)1 - dmap_o * EP.inv_max_north) * (R)0.01);
                 if (arrived) { stop_o = true; st |= SIT_ST_OBS_ENDPOINT; }                       // no done
                 if (outside) { stop_o = true; dn_o = true; st |= SIT_ST_OBS_HORIZON; }
-                if (inside[1]) { if (!stop_o) ro_ -= (R)1000; dn_o = true; st |= SIT_ST_OBS_TERRAIN; }   // no stop flag
+                if (inside1) { if (!stop_o) ro_ -= (R)1000; dn_o = true; st |= SIT_ST_OBS_TERRAIN; }   // no stop flag
                 if (iw_bad) { if (!stop_o) ro_ -= (R)1000; stop_o = true; dn_o = true; st |= SIT_ST_OBS_IW; }
                 if (ect_o > EP.e_tol || samp_dist > (double)ab_seg * EP.theta) {
                     if (!stop_o) ro_ -= (R)1000; stop_o = true; dn_o = true; st |= SIT_ST_OBS_NAV;
@@ -301,8 +328,8 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                 const int64_t rec = io.rec_steps > 1 ? t : 0;
                 if (io.obs) {   // :424-435: post-step pose, pre-step stored rpm / e_ct / power
                     R* ob = io.obs + rec * SIT_N_OBS * B + env;
-                    ob[0] = pn[0]; ob[B] = pe[0]; ob[2 * B] = s.psi.x; ob[3 * B] = rpm_t; ob[4 * B] = ect_t; ob[5 * B] = power_me_kw;
-                    ob[6 * B] = pn[1]; ob[7 * B] = pe[1]; ob[8 * B] = s.psi.y; ob[9 * B] = ect_o;
+                    ob[0] = pn0; ob[B] = pe0; ob[2 * B] = s.psi.x; ob[3 * B] = rpm_t; ob[4 * B] = ect_t; ob[5 * B] = power_me_kw;
+                    ob[6 * B] = pn1; ob[7 * B] = pe1; ob[8 * B] = s.psi.y; ob[9 * B] = ect_o;
                 }
                 if (io.reward) io.reward[rec * B + env] = reward;
                 if (io.done) io.done[rec * B + env] = done ? 1 : 0;
@@ -316,8 +343,8 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                 if (tr_open) {   // close the replay row opened by sit_rollout_policy: (reward, next_state, mask), :395-396
                     if (active) {
                         float* row = ro.replay + (int64_t)ge.tr_slot[env] * SIT_TR_FLOATS;
-                        row[12] = pn[0]; row[13] = pe[0]; row[14] = s.psi.x; row[15] = rpm_t; row[16] = ect_t; row[17] = power_me_kw;
-                        row[18] = pn[1]; row[19] = pe[1]; row[20] = s.psi.y; row[21] = ect_o;
+                        row[12] = pn0; row[13] = pe0; row[14] = s.psi.x; row[15] = rpm_t; row[16] = ect_t; row[17] = power_me_kw;
+                        row[18] = pn1; row[19] = pe1; row[20] = s.psi.y; row[21] = ect_o;
                         row[11] = reward; row[22] = timeup ? 1.0f : (done ? 0.0f : 1.0f);
                         n_closed += 1;
                     }
@@ -325,36 +352,33 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                 }
                 episode_end = done || (timeup && ro.truncate);
             }
-            // ---- in-kernel reset() + init_step() right after a terminal step ---------------------------------------------
+            // ---- in-kernel reset() right after a terminal step; init_step() is this thread's next trip ----------------------
             if (episode_end) {
                 if (ROLL && active) n_eps += 1;
                 const bool hard = io.auto_reset == 2;   // MSRL_env_ex.py:145-186 keeps omega, integrators, fuel unless hard
                 V w_speed, w_dir;
-#pragma unroll
+#pragma unroll 1
                 for (int l = 0; l < 2; ++l) {
                     const int64_t i = i0 + l;
-                    aN[l] = g.init_north[i]; aE[l] = g.init_east[i];
+                    const double N = g.init_north[i], E = g.init_east[i];
                     lane(s.psi, l) = g.init_psi[i]; lane(s.u, l) = g.init_u[i]; lane(s.v, l) = g.init_v[i]; lane(s.r, l) = g.init_r[i];
-                    lane(s.vcn, l) = g.init_vc_n[i]; lane(s.vce, l) = g.init_vc_e[i];
-                    lane(w_speed, l) = g.init_wind_speed[i]; lane(w_dir, l) = g.init_wind_dir[i];
-                    lane(s.u_sp, l) = g.init_u_sp[i];
-                    if (active) {
-                        g.vc_n[i] = lane(s.vcn, l); g.vc_e[i] = lane(s.vce, l);
-                        g.wind_speed[i] = lane(w_speed, l); g.wind_dir[i] = lane(w_dir, l); g.u_sp[i] = lane(s.u_sp, l);
-                    }
-                    steps[l] = 0; s.k[l] = 1; kk[l] = 1;
+                    const R vcn = g.init_vc_n[i], vce = g.init_vc_e[i], ws = g.init_wind_speed[i], wd = g.init_wind_dir[i], usp = g.init_u_sp[i];
+                    lane(s.vcn, l) = vcn; lane(s.vce, l) = vce; lane(w_speed, l) = ws; lane(w_dir, l) = wd; lane(s.u_sp, l) = usp;
+                    if (active) { g.vc_n[i] = vcn; g.vc_e[i] = vce; g.wind_speed[i] = ws; g.wind_dir[i] = wd; g.u_sp[i] = usp; }
+                    pick(steps0, steps1, l) = 0; pick(s.k[0], s.k[1], l) = 1; pick(kk0, kk1, l) = 1;
                     lane(s.e_ct, l) = 0.0f; lane(s.e_int, l) = 0.0f;
-                    s.n_wp[l] = g.n_wp0[i];
-                    for (int j = 0; j < g.max_wp; ++j) {
-                        const R wn = g.wp0_n[(int64_t)j * S + i], we = g.wp0_e[(int64_t)j * S + i];
-                        if (active) { g.wp_n[(int64_t)j * S + i] = wn; g.wp_e[(int64_t)j * S + i] = we; }
-                    }
-                    pN[l] = g.wp0_n[i]; pE[l] = g.wp0_e[i];
-                    const double cN = g.wp0_n[S + i], cE = g.wp0_e[S + i];
-                    split_rel(aN[l] - pN[l], lane(s.X, l), lane(s.CX, l));
-                    split_rel(aE[l] - pE[l], lane(s.Y, l), lane(s.CY, l));
-                    set_segment2(s, P, pN[l], pE[l], cN, cE, l);
-                    endN[l] = g.wp0_n[(int64_t)(s.n_wp[l] - 1) * S + i]; endE[l] = g.wp0_e[(int64_t)(s.n_wp[l] - 1) * S + i];
+                    const int nw = g.n_wp0[i];
+                    pick(s.n_wp[0], s.n_wp[1], l) = nw;
+                    if (active)
+                        for (int j = 0; j < g.max_wp; ++j) {
+                            g.wp_n[(int64_t)j * S + i] = g.wp0_n[(int64_t)j * S + i]; g.wp_e[(int64_t)j * S + i] = g.wp0_e[(int64_t)j * S + i];
+                        }
+                    const double pN = g.wp0_n[i], pE = g.wp0_e[i], cN = g.wp0_n[S + i], cE = g.wp0_e[S + i];
+                    pick(pN0, pN1, l) = pN; pick(pE0, pE1, l) = pE; pick(aN0, aN1, l) = N; pick(aE0, aE1, l) = E;
+                    split_rel(N - pN, lane(s.X, l), lane(s.CX, l));
+                    split_rel(E - pE, lane(s.Y, l), lane(s.CY, l));
+                    set_segment2<true>(s, P, pN, pE, cN, cE, l);
+                    pick(endN0, endN1, l) = g.wp0_n[(int64_t)(nw - 1) * S + i]; pick(endE0, endE1, l) = g.wp0_e[(int64_t)(nw - 1) * S + i];
                     if (hard) {   // what the reference's reset() leaves alone (quirk Q3): a fresh construction
                         lane(s.om, l) = g.init_omega[i];
                         lane(s.ei_s, l) = 0.0f; lane(s.ei_w, l) = g.init_ei_shaft[i]; lane(s.ei_h, l) = 0.0f; lane(s.e_prev, l) = 0.0f;
@@ -365,10 +389,7 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                 stop_t = false; stop_o = false; nstored = 0; fresh = true;
                 eps_dist = 0.0; samp_dist = 0.0; prev_n = 0.0; prev_e = 0.0;
                 ep_return = (R)0; ep_steps = 0;
-                StepOut2 o2;
-                if (MULTI) ship_step2<AVOID_NONE, false>(P, MV, s, g, idx, o2);      // init_step :188-215
-                else ship_step2<AVOID_NONE, false>(P, P.mode[0], s, g, idx, o2);
-                refresh_abs();
+                init_mode = true;                    // init_step :188-215 = the next trip of this thread
                 if (ROLL) {
                     // the new episode's first decision acts on reset()'s float32 initial state (MSRL_env_ex.py:86-90,186)
                     pending = true; n_dec = 0;
@@ -388,7 +409,7 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                     const float dnf = s.SX.y - s.X.y, def_ = s.SY.y - s.Y.y;
                     if (dnf * dnf + def_ * def_ <= P.ra2_band) {          // float pre-test, exact test in double
                         const int64_t i = i0 + 1;
-                        const double dn = (double)g.wp_n[(int64_t)s.k[1] * S + i] - aN[1], de = (double)g.wp_e[(int64_t)s.k[1] * S + i] - aE[1];
+                        const double dn = (double)g.wp_n[(int64_t)s.k[1] * S + i] - aN1, de = (double)g.wp_e[(int64_t)s.k[1] * S + i] - aE1;
                         dec = __dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de)) <= P.ra2;
                     }
                 }
@@ -396,15 +417,15 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                     pending = true;
                     if (active) {
                         R* co = ge.cur_obs + env;
-                        co[0] = pn[0]; co[B] = pe[0]; co[2 * B] = s.psi.x; co[3 * B] = rpm_t; co[4 * B] = ect_t; co[5 * B] = power_me_kw;
-                        co[6 * B] = pn[1]; co[7 * B] = pe[1]; co[8 * B] = s.psi.y; co[9 * B] = ect_o;
+                        co[0] = pn0; co[B] = pe0; co[2 * B] = s.psi.x; co[3 * B] = rpm_t; co[4 * B] = ect_t; co[5 * B] = power_me_kw;
+                        co[6 * B] = pn1; co[7 * B] = pe1; co[8 * B] = s.psi.y; co[9 * B] = ect_o;
                     }
                 }
             }
-        }   // live
+        }   // stepping
         // ---- warp-level reduction of termination / collision flags ---------------------------------------------------------
         if (io.stats) {
-            const bool cnt_lane = active && live;
+            const bool cnt_lane = active && stepping;
             if (__any_sync(FULL, cnt_lane && status != 0)) {
 #pragma unroll
                 for (int b = 0; b < 12; ++b) {
@@ -415,6 +436,7 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
                 if (wl == 12) my_cnt += __popc(bal);
             }
         }
+        if (todo && !was_init) t += 1;   // a step slot is used whether the env stepped or waited for an action; init_step is free
     }
 
     // ---- write back ------------------------------------------------------------------------------------------------------
@@ -424,13 +446,11 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
         st2(g.e_ct, vabs(s.e_ct)); st2(g.e_ct_int, s.e_int);
         st2(g.fuel_me, s.f_me); st2(g.fuel_el, s.f_el); st2(g.fuel, add(add(s.f_me, s.f_el), f_off));
         st2(g.rel_n, s.X); st2(g.rel_cn, s.CX); st2(g.rel_e, s.Y); st2(g.rel_ce, s.CY);
-#pragma unroll
-        for (int l = 0; l < 2; ++l) {
-            const int64_t i = i0 + l;
-            g.north[i] = aN[l]; g.east[i] = aE[l];
-            g.k[i] = s.k[l]; g.n_wp[i] = s.n_wp[l]; g.steps[i] = steps[l];
-            g.mc_idx[i] = (int32_t)mc[l].idx; g.mc_n[i] = mc[l].p0n; g.mc_e[i] = mc[l].p0e; g.mc_b2[i] = mc[l].b2;
-        }
+        g.north[i0] = aN0; g.east[i0] = aE0; g.north[i0 + 1] = aN1; g.east[i0 + 1] = aE1;
+        g.k[i0] = s.k[0]; g.n_wp[i0] = s.n_wp[0]; g.steps[i0] = steps0;
+        g.k[i0 + 1] = s.k[1]; g.n_wp[i0 + 1] = s.n_wp[1]; g.steps[i0 + 1] = steps1;
+        g.mc_idx[i0] = (int32_t)mc0.idx; g.mc_n[i0] = mc0.p0n; g.mc_e[i0] = mc0.p0e; g.mc_b2[i0] = mc0.b2;
+        g.mc_idx[i0 + 1] = (int32_t)mc1.idx; g.mc_n[i0 + 1] = mc1.p0n; g.mc_e[i0 + 1] = mc1.p0e; g.mc_b2[i0 + 1] = mc1.b2;
         const int32_t f = (stop_t ? F_STOP_TEST : 0) | (stop_o ? F_STOP_OBS : 0) | (nstored << F_NSTORED_SHIFT) |
                           (iw_bad ? F_IW_BAD : 0) | (iw_valid ? F_IW_VALID : 0) | (fresh ? F_FRESH : 0) |
                           (pending ? F_PENDING : 0) | (have_act ? F_HAVE_ACT : 0);

@@ -89,7 +89,7 @@ struct ModeV { V avail_total, avail_me, avail_el, cap_tq_me, cap_tq_el, add_me, 
 // the stored (pre-step) observables the env reads back (MSRL_env_ex.py:267-269,298-300): shaft speed [rad/s] before the
 // step and the load on the main engine [W]
 struct StepOut2 { V om_pre, load_me; };
-enum { AVOID_NONE = 0, AVOID_BOTH = 1, AVOID_LANE0 = 2 };
+enum { AVOID_NONE = 0, AVOID_BOTH = 1, AVOID_LANE0 = 2, AVOID_LANE0_RT = 3 };
 
 __device__ __forceinline__ float& lane(V& a, int l) { return l == 0 ? a.x : a.y; }
 __device__ __forceinline__ float lane(const V& a, int l) { return l == 0 ? a.x : a.y; }
@@ -100,17 +100,16 @@ __device__ __forceinline__ double abs_pos(double p, float x, float c) { return p
 // relative pair of a float64 offset: x = nearest float, c = -(remainder)
 __device__ __forceinline__ void split_rel(double rel, float& x, float& c) { x = (float)rel; c = -(float)(rel - (double)x); }
 
-// LOS_guidance.py:110-112: segment k-1 -> k of ship l: vector, angle (atan2(dE, dN)), threshold of the waypoint pre-test
-__device__ __forceinline__ void set_segment2(Ship2& s, const ShipPX& P, const double pN, const double pE, const double cN,
-                                             const double cE, const int l) {
-    const float sx = (float)(cN - pN), sy = (float)(cE - pE);
-    // direction cosines straight from the segment vector (one MUFU.RSQ + a Newton step) and a branch-free atan2 on the
-    // same odd polynomial as atan2v: this block runs once per waypoint switch, for one ship of the warp at a time
+// direction cosines and angle atan2(sy, sx) of a segment vector: one MUFU.RSQ + a Newton step, and a branch-free atan2 on
+// the same odd polynomial as atan2v.  Runs once per waypoint switch, for one ship of the warp at a time.
+struct SegGeo { float alpha, sa, ca; };
+__device__ __forceinline__ SegGeo seg_geometry(const float sx, const float sy) {
     const float l2 = fmaf(sx, sx, sy * sy);
     float il = rsqrt_approx(l2);
     il = il * fmaf(-0.5f * l2 * il, il, 1.5f);
     const bool degenerate = !(l2 > 0.0f);                     // zero-length segment: atan2(0, 0) = 0
-    const float sa = degenerate ? 0.0f : sy * il, ca = degenerate ? 1.0f : sx * il;
+    SegGeo q;
+    q.sa = degenerate ? 0.0f : sy * il; q.ca = degenerate ? 1.0f : sx * il;
     const float ax = fabsf(sx), ay = fabsf(sy);
     const float z = fminf(ax, ay) * rcp_(fmaxf(fmaxf(ax, ay), 1e-30f));
     const float z2 = z * z;
@@ -121,27 +120,40 @@ __device__ __forceinline__ void set_segment2(Ship2& s, const ShipPX& P, const do
     pa = fmaf(pa * z2, z, z);
     if (ay > ax) pa = 1.57079632679489662f - pa;
     if (sx < 0.0f) pa = 3.14159265358979324f - pa;
-    const float a = copysignf(pa, sy);
+    q.alpha = copysignf(pa, sy);
+    return q;
+}
+// the same as a real call: the env kernel reaches this from nine places, and a compact instruction footprint matters more there
+// than the call overhead on a path taken once per waypoint switch
+__device__ __noinline__ SegGeo seg_geometry_call(const float sx, const float sy) { return seg_geometry(sx, sy); }
+
+// LOS_guidance.py:110-112: segment k-1 -> k of ship l: vector, angle (atan2(dE, dN)), threshold of the waypoint pre-test
+template <bool COMPACT = false>
+__device__ __forceinline__ void set_segment2(Ship2& s, const ShipPX& P, const double pN, const double pE, const double cN,
+                                             const double cE, const int l) {
+    const float sx = (float)(cN - pN), sy = (float)(cE - pE);
+    const SegGeo q = COMPACT ? seg_geometry_call(sx, sy) : seg_geometry(sx, sy);
     lane(s.SX, l) = sx; lane(s.SY, l) = sy;
-    lane(s.alpha, l) = a; lane(s.sa, l) = sa; lane(s.ca, l) = ca;
-    lane(s.thr2, l) = s.n_wp[l] > s.k[l] + 1 ? P.ra2_band : -1.0f;
+    lane(s.alpha, l) = q.alpha; lane(s.sa, l) = q.sa; lane(s.ca, l) = q.ca;
+    lane(s.thr2, l) = (l == 0 ? s.n_wp[0] > s.k[0] + 1 : s.n_wp[1] > s.k[1] + 1) ? P.ra2_band : -1.0f;
 }
 
 // LOS_guidance.py:88-103 next_wpt for ship l, decided in double on the float64 position with the reference's operation order
 // (squared distance, <=, end-of-route hold).  On a switch the relative pair is re-based on the new segment start.
+template <bool COMPACT = false>
 __device__ __forceinline__ void next_wpt2(Ship2& s, const ShipPX& P, const ShipPtrs<float>& g, const int64_t i, const int l) {
     const int64_t S = g.n_ships;
-    const int k = s.k[l];
+    const int k = l == 0 ? s.k[0] : s.k[1], nw = l == 0 ? s.n_wp[0] : s.n_wp[1];
     const double pN = g.wp_n[(int64_t)(k - 1) * S + i], pE = g.wp_e[(int64_t)(k - 1) * S + i];
     const double cN = g.wp_n[(int64_t)k * S + i], cE = g.wp_e[(int64_t)k * S + i];
     const double N = abs_pos(pN, lane(s.X, l), lane(s.CX, l)), E = abs_pos(pE, lane(s.Y, l), lane(s.CY, l));
     const double dn = cN - N, de = cE - E;
     const double d2 = __dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de));
-    if (d2 <= P.ra2 && s.n_wp[l] > k + 1) {
-        s.k[l] = k + 1;
+    if (d2 <= P.ra2 && nw > k + 1) {
+        if (l == 0) s.k[0] = k + 1; else s.k[1] = k + 1;
         split_rel(N - cN, lane(s.X, l), lane(s.CX, l));
         split_rel(E - cE, lane(s.Y, l), lane(s.CY, l));
-        set_segment2(s, P, cN, cE, g.wp_n[(int64_t)(k + 1) * S + i], g.wp_e[(int64_t)(k + 1) * S + i], l);
+        set_segment2<COMPACT>(s, P, cN, cE, g.wp_n[(int64_t)(k + 1) * S + i], g.wp_e[(int64_t)(k + 1) * S + i], l);
     }
 }
 
@@ -198,17 +210,26 @@ __device__ __forceinline__ V atan2v(const ShipPX& P, const V x) {
 // idx(l): the ship index of lane l (only read on the rare waypoint-switch path).  AVOID: the collision-avoidance branch on
 // no ship, both, or lane 0 only (the two-ship env: lane 0 = test ship, MSRL_env_ex.py:240-249).  STORE = false reproduces
 // init_step (MSRL_env_ex.py:188-215): no store_simulation_data, i.e. no fuel accumulation.
-template <int AVOID, bool STORE, typename MP, typename IdxFn>
+// AVOID_LANE0_RT: lane-0 avoidance and the store are switched by the run-time flags avoid0_rt / store_rt, so that ONE instance
+// of the step serves both the normal step and init_step (the env kernel's instruction footprint); COMPACT: the rare
+// waypoint-switch path as a two-trip loop around real calls instead of two inlined copies.
+template <int AVOID, bool STORE, bool COMPACT = false, typename MP, typename IdxFn>
 __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& s, const ShipPtrs<float>& g, const IdxFn& idx,
-                                           StepOut2& o) {
+                                           StepOut2& o, const bool avoid0_rt = true, const bool store_rt = true) {
     // ---- LOS_guidance.py:88-103 next_wpt: packed float pre-test; the decision itself in double (next_wpt2) -----------------
     {
         const V dn = sub(s.SX, s.X), de = sub(s.SY, s.Y);
         const V d2 = fma(de, de, mul(dn, dn));
         const bool h0 = d2.x <= s.thr2.x, h1 = d2.y <= s.thr2.y;
         if (h0 | h1) {
-            if (h0) next_wpt2(s, P, g, idx(0), 0);
-            if (h1) next_wpt2(s, P, g, idx(1), 1);
+            if (COMPACT) {
+#pragma unroll 1
+                for (int l = 0; l < 2; ++l)
+                    if (l == 0 ? h0 : h1) next_wpt2<true>(s, P, g, idx(l), l);
+            } else {
+                if (h0) next_wpt2(s, P, g, idx(0), 0);
+                if (h1) next_wpt2(s, P, g, idx(1), 1);
+            }
         }
     }
     // ---- LOS_guidance.py:105-121 los_guidance ---------------------------------------------------------------------
@@ -243,7 +264,7 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
     V thr = fma(e2s, P.kp_w, mul(s.ei_w, P.ki_w));
 
     // ---- MSRL_env_ex.py:240-249 collision-avoidance branch (test ship: always) ---------------------------------------
-    if (AVOID != AVOID_NONE) {
+    if (AVOID != AVOID_NONE && (AVOID != AVOID_LANE0_RT || avoid0_rt)) {
         thr.x = fminf(fmaxf(thr.x * 0.5f, 0.0f), 1.1f);
         rud.x = fminf(fmaxf(rud.x + P.rud_bias, -P.rud_max), P.rud_max);
     }
@@ -263,7 +284,8 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
 
     // ---- ship_model.py:645-684 store_simulation_data: load split + fuel accumulators (ship_engine.py:239-292) -----------
     o.om_pre = om;
-    if (STORE) {
+    o.load_me = bc(0.0f);
+    if (STORE && (AVOID != AVOID_LANE0_RT || store_rt)) {
         const V total = mul(thr, M.avail_total);
         V load_me = add(total, M.add_me);
         load_me.x = fminf(load_me.x, lane(M.cap_me, 0)); load_me.y = fminf(load_me.y, lane(M.cap_me, 1));

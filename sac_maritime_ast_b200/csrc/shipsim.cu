@@ -2048,8 +2048,7 @@ int sit_env_init_step(SitHandle h, void* state, const uint8_t* mask, void* strea
 }  // extern "C"
 // fp32 envs whose two roles share one parameter set CAN run the packed one-thread-per-env kernel (env_x2.cuh) unless the
 // reward_parts / snapshot outputs are asked for: SIT_ENV_X2=1 (or -DSIT_ENV_X2_DEFAULT=1) switches it on.  Off by default:
-// it wins while episodes are young (1.39e10 -> 1.67e10 env-steps/s) and loses once resets, rescans and hull checks are
-// frequent (bench env leg 1.27e10 -> 1.08e10, 10 000-step horizon 1.06e10 -> 0.86e10), see env_x2.cuh
+// 38 % fewer instructions but no faster than the lane-pair kernel on the bench legs (measurements in env_x2.cuh)
 #ifndef SIT_ENV_X2_DEFAULT
 #define SIT_ENV_X2_DEFAULT 0
 #endif

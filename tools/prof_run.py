@@ -24,7 +24,8 @@ elif which.startswith("roll"):
         print(bench.learner_leg(sit, dev, smp))
 elif which.startswith("env"):
     prec = "fp64" if "64" in which else "fp32"
-    print(bench.env_leg(sit, dev, B=1 << 18 if prec == "fp32" else 1 << 16, K=64, steps=3, warmup=3, precision=prec,
+    steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    print(bench.env_leg(sit, dev, B=1 << 18 if prec == "fp32" else 1 << 16, K=64, steps=steps, warmup=3, precision=prec,
                         record_all=which.endswith("rec")))
 else:
     raise SystemExit("fleet32 is `python bench.py --steps 3 --warmup 3 --no-extras`")
