@@ -102,6 +102,7 @@ env_step_x2_kernel(const __grid_constant__ EnvKArgs<float> A, const __grid_const
 #define MV_(f) MV.f = make_float2(a.f, b.f)
             MV_(avail_total); MV_(avail_me); MV_(avail_el); MV_(cap_tq_me); MV_(cap_tq_el); MV_(add_me); MV_(cap_me);
             MV_(a_el); MV_(c_el); MV_(inv_me_cap); MV_(inv_el_cap); MV_(me_cap_kw);
+            MV_(fme_a); MV_(fme_b); MV_(fel_a); MV_(fel_b);
 #undef MV_
         }
     };

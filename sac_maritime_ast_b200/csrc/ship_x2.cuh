@@ -52,6 +52,9 @@ struct ModeX {
     float a_el, c_el;                        // load_el = a_el * ((total + hotel) - load_me) + c_el
     float inv_me_cap, inv_el_cap;            // 0 where the reference guards a zero capacity
     float me_cap_kw, _pad;                   // main_engine_capacity / 1000: 'available power me [kw]' (ship_model.py:662-664)
+    // specific fuel consumption as a polynomial in the LOAD instead of the load fraction (ship_engine.py:256-292 with
+    // pct = load / capacity folded in, dt / 3.6e9 too): rate dt = load ((a load + b) load + c)
+    float fme_a, fme_b, fel_a, fel_b;
 };
 
 struct ShipPX {
@@ -60,6 +63,7 @@ struct ShipPX {
     float c_inv_pi, c_s3, c_c4, c_a6;                      // second constants of two-constant FMAs (uniform operands)
     float dt, look2, sat_e, neg_ki_los, windup;            // LOS_guidance.py:105-121
     float kp_h, kd_idt, ki_h, rud_max, rud_bias;           // controllers.py:72-100 (kd / dt folded)
+    float kp_kd;                                           // kp + kd / dt: the PID on (err, e_prev) instead of (err, err - e_prev)
     float kp_s, ki_s, kp_w, ki_w;                          // controllers.py:138-143
     float hotel, sfc_me[3], sfc_dg[3];                     // ship_engine.py:256-292 (dt / 3.6e9 folded)
     float sh_me, sh_hsg, sh_lin, sh_quad;                  // shaft_eq :355-361
@@ -84,7 +88,8 @@ struct Ship2 {
 };
 
 // per-ship mode constants as lanes of packed registers (several modes in one fleet) or as uniform scalars (one mode)
-struct ModeV { V avail_total, avail_me, avail_el, cap_tq_me, cap_tq_el, add_me, cap_me, a_el, c_el, inv_me_cap, inv_el_cap, me_cap_kw; };
+struct ModeV { V avail_total, avail_me, avail_el, cap_tq_me, cap_tq_el, add_me, cap_me, a_el, c_el, inv_me_cap, inv_el_cap, me_cap_kw,
+                   fme_a, fme_b, fel_a, fel_b; };
 
 // the stored (pre-step) observables the env reads back (MSRL_env_ex.py:267-269,298-300): shaft speed [rad/s] before the
 // step and the load on the main engine [W]
@@ -247,11 +252,10 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
 
     // ---- controllers.py:81-93,188-189 heading PID: no wrap, no anti-windup -------------------------------------------
     const V err = sub(href, s.psi);
-    const V derr = sub(err, s.e_prev);
     s.ei_h = fma(err, P.dt, s.ei_h);
+    // kp err + kd (err - e_prev) / dt + ki ei  =  (kp + kd / dt) err - (kd / dt) e_prev + ki ei: one packed op fewer
+    V rud = fma(s.e_prev, -P.kd_idt, mul(err, P.kp_kd));
     s.e_prev = err;
-    V rud = mul(err, P.kp_h);
-    rud = fma(derr, P.kd_idt, rud);
     rud = fma(s.ei_h, P.ki_h, rud);                          // negated in the clamp below
     rud.x = fmaxf(-P.rud_max, fminf(-rud.x, P.rud_max));
     rud.y = fmaxf(-P.rud_max, fminf(-rud.y, P.rud_max));
@@ -286,14 +290,14 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
     o.om_pre = om;
     o.load_me = bc(0.0f);
     if (STORE && (AVOID != AVOID_LANE0_RT || store_rt)) {
-        const V total = mul(thr, M.avail_total);
-        V load_me = add(total, M.add_me);
+        // total = thr * available power is never needed on its own: it enters the two loads through fused multiply-adds
+        V load_me = fma(thr, M.avail_total, M.add_me);
         load_me.x = fminf(load_me.x, lane(M.cap_me, 0)); load_me.y = fminf(load_me.y, lane(M.cap_me, 1));
-        const V load_el = fma(sub(add(total, P.hotel), load_me), M.a_el, M.c_el);
-        const V pct_me = mul(load_me, M.inv_me_cap), pct_el = mul(load_el, M.inv_el_cap);
-        // rate dt = load (a pct^2 + b pct + c) dt / 3.6e9; a zero load gives a zero rate without the reference's guards
-        const V pme = fma(fma(pct_me, P.sfc_me[0], P.sfc_me[1]), pct_me, P.sfc_me[2]);
-        const V pel = fma(fma(pct_el, P.sfc_dg[0], P.sfc_dg[1]), pct_el, P.sfc_dg[2]);
+        const V load_el = fma(sub(fma(thr, M.avail_total, P.hotel), load_me), M.a_el, M.c_el);
+        // rate dt = load (a pct^2 + b pct + c) dt / 3.6e9 with pct = load / capacity folded into the coefficients (ModeX); a zero
+        // load gives a zero rate without the reference's guards
+        const V pme = fma(fma(load_me, M.fme_a, M.fme_b), load_me, P.sfc_me[2]);
+        const V pel = fma(fma(load_el, M.fel_a, M.fel_b), load_el, P.sfc_dg[2]);
         o.load_me = load_me;
         s.f_me = fma(load_me, pme, s.f_me);
         s.f_el = fma(load_el, pel, s.f_el);   // fuel_cons (the sum of both, ship_engine.py:288-292) is formed where the state is stored
@@ -302,9 +306,8 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
     // ---- ship_model.py:233-250 kinematics ---------------------------------------------------------------------------
     V sn, c;
     sincos2(P, s.psi, sn, c);
-    const V udt = mul(s.u, P.dt), vdt = mul(s.v, P.dt);
-    const V d_north = fma(c, udt, neg(mul(sn, vdt)));
-    const V d_east = fma(sn, udt, mul(c, vdt));
+    const V d_north = fma(c, s.u, neg(mul(sn, s.v)));      // [m/s]; the dt factor rides the Kahan update below
+    const V d_east = fma(sn, s.u, mul(c, s.v));
 
     // ---- ship_engine.py:355-361,391-395 shaft equation ------------------------------------------------------------------
     V d_om = mul(tq_me, P.sh_me);
@@ -334,7 +337,7 @@ __device__ __forceinline__ void ship_step2(const ShipPX& P, const MP& M, Ship2& 
 
     // ---- ship_model.py:632-643, utils.py:50-53 explicit Euler, all derivatives from the old state ---------------------------
     {   // position: Kahan-compensated float accumulation of the float increments
-        const V yn = sub(d_north, s.CX), ye = sub(d_east, s.CY);
+        const V yn = fma(d_north, P.dt, neg(s.CX)), ye = fma(d_east, P.dt, neg(s.CY));
         const V tn = add(s.X, yn), te = add(s.Y, ye);
         s.CX = sub(sub(tn, s.X), yn); s.CY = sub(sub(te, s.Y), ye);
         s.X = tn; s.Y = te;

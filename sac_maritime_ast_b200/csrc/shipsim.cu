@@ -229,6 +229,7 @@ fleet_step_x2_kernel(const __grid_constant__ x2::ShipPX P, const ShipPtrs<float>
 #define MV_(f) MV.f = make_float2(a.f, b.f)
         MV_(avail_total); MV_(avail_me); MV_(avail_el); MV_(cap_tq_me); MV_(cap_tq_el); MV_(add_me); MV_(cap_me);
         MV_(a_el); MV_(c_el); MV_(inv_me_cap); MV_(inv_el_cap); MV_(me_cap_kw);
+        MV_(fme_a); MV_(fme_b); MV_(fel_a); MV_(fel_b);
 #undef MV_
     }
     float* tr = io.traj + i0;   // running row pointer of the every-step trajectory
@@ -1533,6 +1534,7 @@ static void derive_shipx(const ShipP<float>& P, x2::ShipPX& X) {
     X.c_a6 = -0.004355357028543949f;
     X.dt = P.dt; X.look2 = P.look2; X.sat_e = P.sat_e; X.neg_ki_los = -P.ki_los; X.windup = P.windup;
     X.kp_h = P.kp_h; X.kd_idt = P.kd_h * P.inv_dt; X.ki_h = P.ki_h; X.rud_max = P.rud_max; X.rud_bias = P.rud_bias;
+    X.kp_kd = P.kp_h + P.kd_h * P.inv_dt;
     X.kp_s = P.kp_s; X.ki_s = P.ki_s; X.kp_w = P.kp_w; X.ki_w = P.ki_w;
     X.hotel = P.hotel;
     for (int j = 0; j < 3; ++j) { X.sfc_me[j] = P.sfc_me[j] * P.dt; X.sfc_dg[j] = P.sfc_dg[j] * P.dt; }
@@ -1548,6 +1550,8 @@ static void derive_shipx(const ShipP<float>& P, x2::ShipPX& X) {
         Y.avail_total = M.avail_total; Y.avail_me = M.avail_me; Y.avail_el = M.avail_el;
         Y.cap_tq_me = M.cap_tq_me; Y.cap_tq_el = M.cap_tq_el;
         Y.inv_me_cap = M.inv_me_cap; Y.inv_el_cap = M.inv_el_cap; Y.me_cap_kw = M.me_cap_kw;
+        Y.fme_a = (float)((double)X.sfc_me[0] * M.inv_me_cap * M.inv_me_cap); Y.fme_b = (float)((double)X.sfc_me[1] * M.inv_me_cap);
+        Y.fel_a = (float)((double)X.sfc_dg[0] * M.inv_el_cap * M.inv_el_cap); Y.fel_b = (float)((double)X.sfc_dg[1] * M.inv_el_cap);
         if (M.sg == SIT_SG_MOTOR) { Y.add_me = 0.0f; Y.cap_me = M.me_cap; Y.a_el = 1.0f; Y.c_el = 0.0f; }
         else { Y.add_me = M.load_me_add; Y.cap_me = INFINITY; Y.a_el = 0.0f; Y.c_el = M.load_el_const; }
     }
