@@ -29,6 +29,32 @@ def ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else None
 
 
+# ---- tracing: NVTX ranges around the entry points of the wrapper -------------------------------------
+# SIT_NVTX=1 brackets every launch-enqueueing call (ShipFleet.step / step_host, MultiShipRLEnv.step_k / step_host,
+# IntermediateWaypointSampler.collect, ReplayExchange.pack / exchange, SAC.update) in an NVTX range, so a timeline (nsys, or
+# ncu --nvtx --nvtx-include) shows which call a kernel belongs to.  Off by default: a range costs ~1 us of host time.
+import functools
+import os
+
+NVTX = os.environ.get("SIT_NVTX", "0") not in ("", "0")
+
+
+def nvtx_range(name):
+    def deco(fn):
+        if not NVTX:
+            return fn
+
+        @functools.wraps(fn)
+        def wrapped(*a, **kw):
+            torch.cuda.nvtx.range_push(name)
+            try:
+                return fn(*a, **kw)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        return wrapped
+    return deco
+
+
 class SimCore:
     """One libshipsim handle and its state buffer on one CUDA device."""
 

@@ -19,7 +19,7 @@ import numpy as np
 import torch
 
 from . import _lib, config
-from .core import SimCore, _precision_code, ptr
+from .core import SimCore, _precision_code, nvtx_range, ptr
 
 
 @dataclass
@@ -199,6 +199,7 @@ class MultiShipRLEnv(SimCore):
         out = self.step_k(1, converted_action, SAC_update, init=init, record_all=False)
         return out["obs"][0].t(), out["reward"][0], out["done"][0].bool(), out["status"][0]
 
+    @nvtx_range("sit.env.step_k")
     def step_k(self, K, converted_action, SAC_update=False, init=None, auto_reset=False, record_all=True,
                want_sums=False, out: Optional[dict] = None, reward_parts=False):
         """K env steps in ONE launch.  converted_action [n_envs, 2] (held for the launch; SAC_update applies to
@@ -263,6 +264,7 @@ class MultiShipRLEnv(SimCore):
                     self.ship_drawings[name].append((self._draw_step + t, ids, x, y))
         self._draw_step += rec
 
+    @nvtx_range("sit.env.step_host")
     def step_host(self, K, action_host: torch.Tensor, sac_update_host: torch.Tensor, init, out_host: dict):
         """One call through ``sit_env_step_host``: HOST (pinned) action [2, n_envs] / sac_update [n_envs] in,
         HOST obs [10, n_envs] / reward / done / status out; copies and synchronisation inside."""

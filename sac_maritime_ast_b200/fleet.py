@@ -15,7 +15,7 @@ import numpy as np
 import torch
 
 from . import _lib, config
-from .core import SimCore, _precision_code, ptr
+from .core import SimCore, _precision_code, nvtx_range, ptr
 
 
 class ShipFleet(SimCore):
@@ -77,6 +77,7 @@ class ShipFleet(SimCore):
         self.f["n_wp"].copy_(n_wp)
 
     # ---- stepping -------------------------------------------------------------------------------------
+    @nvtx_range("sit.fleet.step")
     def step(self, K: int = 1, dist: Optional[torch.Tensor] = None, avoid: bool = False, store: bool = True,
              traj: bool = False, log27: bool = False, cmd: bool = False, out: Optional[dict] = None):
         """Advance every ship K steps in one launch.
@@ -108,6 +109,7 @@ class ShipFleet(SimCore):
 
     CHANNELS = ("north", "east", "psi", "u", "v", "r", "omega", "k")
 
+    @nvtx_range("sit.fleet.step_host")
     def step_host(self, K: int, dist_host: Optional[torch.Tensor], pose_host: Optional[torch.Tensor],
                   avoid: bool = False, channels=None, k8_host: Optional[torch.Tensor] = None):
         """One call through ``sit_fleet_step_host[_sel]``: HOST (pinned) disturbances [4, n_ships] in, HOST post-step

@@ -25,7 +25,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .core import ptr
+from .core import nvtx_range, ptr
 from .env import MultiShipRLEnv
 
 N_OBS, TR_FLOATS = _lib.N_OBS, _lib.TR_FLOATS
@@ -158,6 +158,7 @@ class IntermediateWaypointSampler:
         _lib.check(e.L.sit_rollout_step_k(e.h, e.state_ptr(), int(K), C.byref(self.ro), C.byref(self.io), e.stream()))
         self.launches += 1
 
+    @nvtx_range("sit.rollout.collect")
     def collect(self, iterations: int, K: int = 16, graph: bool = True):
         """`iterations` x (policy on the pending envs, then K env steps).  Enqueues only.  With ``graph`` the loop runs
         inside libshipsim (sit_rollout_collect): one iteration is captured into a CUDA graph on a side stream (the
@@ -251,6 +252,7 @@ class ReplayExchange:
         self.done = None
         self.L = _lib.lib() if self.cuda else None
 
+    @nvtx_range("sit.replay.pack")
     def pack(self):
         """Copy the rows closed since the previous pack into the send block (caller's stream, no host sync)."""
         smp = self.smp
@@ -270,6 +272,7 @@ class ReplayExchange:
         self.dropped += max(fresh - self.block, 0)
         self.seen.fill_(n_now)
 
+    @nvtx_range("sit.replay.exchange")
     def exchange(self, memory) -> Optional["torch.cuda.Event"]:
         """All-gather the packed blocks of every rank and append the valid rows to ``memory`` (rank order, row order)."""
         import torch.distributed as dist

@@ -24,7 +24,7 @@ from typing import Dict, Optional
 import torch
 
 from . import _lib
-from .core import ptr
+from .core import nvtx_range, ptr
 
 TR_FLOATS = _lib.TR_FLOATS
 
@@ -187,6 +187,7 @@ class SAC:
         return int(self.f["updates"][0].item())
 
     # ---- the update ------------------------------------------------------------------------------------------------
+    @nvtx_range("sit.sac.update")
     def update(self, memory: ReplayMemory, n_updates: int = 1):
         """Enqueue ``n_updates`` x update_parameters; returns the device tensor that will hold the losses of the last one."""
         if n_updates <= 0:

@@ -127,3 +127,23 @@ def test_outputs_stay_inside_their_buffers(precision):
     for buf, view in ((bo, obs), (br, rew), (bp, parts)):
         assert (buf[:pad] == -12345.0).all() and (buf[-pad:] == -12345.0).all()
         assert (view != -12345.0).all()
+
+
+def test_nvtx_ranges_do_not_change_results():
+    """SIT_NVTX=1 wraps the wrapper's entry points in NVTX ranges (tracing): a fresh process with the
+    ranges on gives the same fleet state as this process without them."""
+    import os
+    import subprocess
+    import sys
+    import gpu_helpers as G
+    import scenarios as sc
+    code = ("import sys; sys.path[:0] = [%r, %r]\n"
+            "import gpu_helpers as G, scenarios as sc, sac_maritime_ast_b200.core as c\n"
+            "assert c.NVTX\n"
+            "f = G.make_fleet(sc.SHIP_SCENARIOS['default'], n_ships=8, precision='fp64'); f.step(50)\n"
+            "print(repr(float(f.f['north'][3])), repr(float(f.f['psi'][3])))\n") % (
+                os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, SIT_NVTX="1"), capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-800:]
+    f = G.make_fleet(sc.SHIP_SCENARIOS["default"], n_ships=8, precision="fp64"); f.step(50)
+    assert out.stdout.split() == [repr(float(f.f["north"][3])), repr(float(f.f["psi"][3]))]
