@@ -716,8 +716,9 @@ def rollout_leg(sit, dev, B=65536, K=32, iters=40, warm_iters=20, hidden=256, pr
     if world > 1:
         import torch.distributed as dist
         dist.all_reduce(rows_per_iter, op=dist.ReduceOp.MAX)
-    # (the warm-up rate already overstates the steady rate by ~1.5x: its first iteration opens a row for EVERY env)
-    block = int(min(per_seg * B, 1.25 * float(rows_per_iter.item()) * per_seg + 4096))
+    # (factor 2: with 1.25 the first timed segment left 60 248 rows behind -- decisions come in bursts as the obstacle ships
+    # of a synchronised batch reach their waypoints together)
+    block = int(min(per_seg * B, 2.0 * float(rows_per_iter.item()) * per_seg + 4096))
     block = (block + 255) // 256 * 256
     mem = sac_mod.ReplayMemory(world * block * (segments + 2), seed=SEED, device=dev)
     xch = ro.ReplayExchange(smp, block)
