@@ -427,7 +427,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
                 else live = false;
             }
             if (!__any_sync(FULL, live && active)) break;
-        } else if (io.action) {
+        } else if (io.action && (t == 0 || io.act_steps > 1)) {   // an action held for the launch is read (and validated) once
             const int64_t ta = io.act_steps > 1 ? t : 0;
             const R a_n = io.action[(ta * 2 + 0) * B + env], a_e = io.action[(ta * 2 + 1) * B + env];
             if (!iw_valid || a_n != act_n || a_e != act_e) {
@@ -554,7 +554,8 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             }
             // shared_non_terminal_state_reward :712-731 (sees the stop flag after the checks above)
             R snt = (R)0;
-            if (!stop) snt = ((R)1 - (R)sqrt(ship_d2) * EP.inv_max_north) * (R)0.001;
+            // (the distance itself in the arithmetic type: only the collision DECISION below needs the float64 square)
+            if (!stop) snt = ((R)1 - sqrt_((R)ship_d2) * EP.inv_max_north) * (R)0.001;
             part = nto;      // assembled below as ((((ntt+rt) + nto) + ro) + snt) + rs
             // stash ro, snt in o.* free slots
             o.rud = ro_; o.thr = snt;
