@@ -229,6 +229,21 @@ int sit_env_step_k(SitHandle h, void* state, int32_t K, const SitEnvIO* io, void
 int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h, const uint8_t* sac_update_h,
                       int32_t init, void* obs_h, void* reward_h, uint8_t* done_h, int32_t* status_h, void* stream);
 
+/* sit_env_step_host without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same results as sit_env_step_host; the device staging (action, sac_update, obs,
+ * reward, done, status) lives in a fixed 2 MiB `static __device__` array inside the library instead of the handle's
+ * lazily allocated scratch, so the call performs no cudaMalloc / cudaFree (it does cudaMemsetAsync, cudaMemcpyAsync,
+ * one kernel launch and a stream synchronise).  Limits and rules:
+ *   - handles with more than SIT_NOALLOC_MAX_ENVS envs are rejected with SIT_E_INVALID (use sit_env_step_host);
+ *   - every GPU that loads the library holds the 2 MiB array until the process exits;
+ *   - ALL calls on a device share the array (it keeps the previous call's contents; outputs are cleared at the
+ *     start of each call): two calls that overlap on the GPU -- different handles or streams -- race.  The call
+ *     synchronises its stream before returning, so calls issued one after another from one thread are safe. */
+#define SIT_NOALLOC_MAX_ENVS 16384
+int sit_env_step_host_noalloc(SitHandle h, void* state, int32_t K, const void* action_h, const uint8_t* sac_update_h,
+                              int32_t init, void* obs_h, void* reward_h, uint8_t* done_h, int32_t* status_h, void* stream);
+
 /* ---- device-resident rollout (the role of the empty ast_core/samplers/intermediate_waypoint_sampler.py; loop
  * contract of test_beds/main_ast.py:310-412).  The agent-side pieces the reference imports from the absent `ast_sac`
  * package (select_action, convert_action_to_simu_input) are DEFINED here -- parity unpinned, see DESIGN.md:

@@ -100,12 +100,13 @@ N_REWARD_PARTS = 8
 TR_FLOATS = 24
 MACH_FULL, MACH_SIMPLIFIED = 0, 1
 MAX_CIRCLES = 64
+NOALLOC_MAX_ENVS = 16384
 POLICY_UNIFORM, POLICY_GAUSSIAN, POLICY_MEAN = 0, 1, 2
 POLICY_TC_BF16 = 0x100
 RC_TRANSITIONS, RC_DECISIONS, RC_RESAMPLES, RC_EPISODES, RC_CLOSED, RC_N = 0, 1, 2, 3, 4, 8
 
 EXPORTS = ("sit_create", "sit_destroy", "sit_state_bytes", "sit_layout", "sit_n_ships", "sit_fleet_step_k", "sit_fleet_step_host", "sit_fleet_step_host_sel",
-           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_map_query", "sit_rollout_begin", "sit_rollout_group_count", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
+           "sit_capture_init", "sit_reset", "sit_env_init_step", "sit_env_step_k", "sit_env_step_host", "sit_env_step_host_noalloc", "sit_map_query", "sit_rollout_begin", "sit_rollout_group_count", "sit_rollout_policy", "sit_rollout_step_k", "sit_rollout_collect",
            "sit_sac_create", "sit_sac_destroy", "sit_sac_workspace_bytes", "sit_sac_field", "sit_sac_init", "sit_sac_policy",
            "sit_sac_update", "sit_replay_pack", "sit_replay_append", "sit_circle_query", "sit_ship_outline",
            "sit_last_error", "sit_status_string", "sit_abi_version", "sit_measure_fma_peak")
@@ -141,6 +142,7 @@ def lib():
     L.sit_env_init_step.argtypes = [vp, vp, vp, vp]
     L.sit_env_step_k.argtypes = [vp, vp, I32, P(SitEnvIO), vp]
     L.sit_env_step_host.argtypes = [vp, vp, I32, vp, vp, I32, vp, vp, vp, vp, vp]
+    L.sit_env_step_host_noalloc.argtypes = [vp, vp, I32, vp, vp, I32, vp, vp, vp, vp, vp]
     L.sit_rollout_begin.argtypes = [vp, vp, vp]
     L.sit_rollout_group_count.argtypes = [vp, C.POINTER(C.c_int32)]
     L.sit_rollout_policy.argtypes = [vp, vp, P(SitPolicy), P(SitRollout), vp]

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -2591,6 +2592,79 @@ int sit_env_step_host(SitHandle h, void* state, int32_t K, const void* action_h,
     join_pipes(h, st);   // also after an error: the forked work is joined before the call returns
     if (rc) return rc;
     if (ce != cudaSuccess) return fail(SIT_E_CUDA, std::string("sit_env_step_host: ") + cudaGetErrorString(ce));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return SIT_OK;
+}
+
+}  // extern "C"
+
+// ---- sit_env_step_host_noalloc: the staging buffers of sit_env_step_host in a fixed device array ----------------------------
+// No counterpart in the reference; added for callers that may not allocate (CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The array below is part of the module image: every
+// GPU that loads the library holds SIT_NOALLOC_SCRATCH_BYTES of it until the process exits.  In HOST code the name
+// `g_noalloc_scratch` is only a stand-in for the symbol -- its device address comes from cudaGetSymbolAddress, once per device,
+// with that device current (noalloc_scratch_ptr below); kernels are handed that address, never the name.
+#define SIT_NOALLOC_SCRATCH_BYTES (2u << 20)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[SIT_NOALLOC_SCRATCH_BYTES];
+#define SIT_NOALLOC_MAX_DEVICES 64
+static void* g_noalloc_ptr[SIT_NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch_ptr(int device, char** out) {   // the caller has made `device` current
+    if (device < 0 || device >= SIT_NOALLOC_MAX_DEVICES) return fail(SIT_E_INVALID, "device index beyond the no-alloc table (64)");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(SIT_E_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+        }
+        g_noalloc_ptr[device] = p;
+    }
+    *out = static_cast<char*>(g_noalloc_ptr[device]);
+    return SIT_OK;
+}
+
+extern "C" {
+
+int sit_env_step_host_noalloc(SitHandle h, void* state, int32_t K, const void* action_h, const uint8_t* sac_update_h,
+                              int32_t init, void* obs_h, void* reward_h, uint8_t* done_h, int32_t* status_h, void* stream) {
+    if (!h || !state || !action_h) return fail(SIT_E_INVALID, "null argument");
+    if (h->cfg.kind != SIT_KIND_ENV) return fail(SIT_E_KIND, "sit_env_step_host_noalloc needs a SIT_KIND_ENV handle");
+    if (K < 1) return fail(SIT_E_INVALID, "K must be >= 1");
+    if (h->n_envs > SIT_NOALLOC_MAX_ENVS)
+        return fail(SIT_E_INVALID, "sit_env_step_host_noalloc: n_envs = " + std::to_string((long long)h->n_envs) + " exceeds the fixed scratch (SIT_NOALLOC_MAX_ENVS = " +
+                                       std::to_string(SIT_NOALLOC_MAX_ENVS) + "); use sit_env_step_host");
+    CUDA_TRY(cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t B = (size_t)h->n_envs, rs = h->cfg.precision == SIT_F64 ? 8 : 4;
+    // same staging layout as sit_env_step_host: action [2][B] | obs [10][B] | reward [B] | status [B] i32 | sac [B] u8 | done [B] u8
+    const size_t o_act = 0, o_obs = align_up(o_act + 2 * B * rs, 256), o_rew = align_up(o_obs + SIT_N_OBS * B * rs, 256),
+                 o_st = align_up(o_rew + B * rs, 256), o_sac = align_up(o_st + B * 4, 256), o_done = align_up(o_sac + B, 256),
+                 total = align_up(o_done + B, 256);
+    if (total > SIT_NOALLOC_SCRATCH_BYTES) return fail(SIT_E_INVALID, "sit_env_step_host_noalloc: staging exceeds the fixed scratch");
+    char* d = nullptr;
+    {
+        int rc0 = noalloc_scratch_ptr(h->device, &d);
+        if (rc0) return rc0;
+    }
+    // the array keeps the previous call's contents: outputs start from zero, inputs are overwritten in full below
+    CUDA_TRY(cudaMemsetAsync(d + o_obs, 0, total - o_obs, st));
+    SitEnvIO io;
+    std::memset(&io, 0, sizeof(io));
+    io.action = d + o_act; io.sac_update = sac_update_h ? reinterpret_cast<uint8_t*>(d + o_sac) : nullptr;
+    io.act_steps = 1; io.init = init; io.auto_reset = 0; io.rec_steps = 1;
+    io.obs = d + o_obs; io.reward = d + o_rew; io.done = reinterpret_cast<uint8_t*>(d + o_done);
+    io.status = reinterpret_cast<int32_t*>(d + o_st);
+    CUDA_TRY(cudaMemcpyAsync(d + o_act, action_h, 2 * B * rs, cudaMemcpyHostToDevice, st));
+    if (sac_update_h) CUDA_TRY(cudaMemcpyAsync(d + o_sac, sac_update_h, B, cudaMemcpyHostToDevice, st));
+    int rc = h->cfg.precision == SIT_F64 ? env_step_t<double>(h, state, K, &io, st) : env_step_t<float>(h, state, K, &io, st);
+    if (rc) return rc;
+    if (obs_h) CUDA_TRY(cudaMemcpyAsync(obs_h, d + o_obs, SIT_N_OBS * B * rs, cudaMemcpyDeviceToHost, st));
+    if (reward_h) CUDA_TRY(cudaMemcpyAsync(reward_h, d + o_rew, B * rs, cudaMemcpyDeviceToHost, st));
+    if (done_h) CUDA_TRY(cudaMemcpyAsync(done_h, d + o_done, B, cudaMemcpyDeviceToHost, st));
+    if (status_h) CUDA_TRY(cudaMemcpyAsync(status_h, d + o_st, B * 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     return SIT_OK;
 }

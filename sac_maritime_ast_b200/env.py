@@ -276,6 +276,18 @@ class MultiShipRLEnv(SimCore):
         self.launches += 1
         return out_host
 
+    def step_host_noalloc(self, K, action_host: torch.Tensor, sac_update_host: torch.Tensor, init, out_host: dict):
+        """``step_host`` through ``sit_env_step_host_noalloc``: same arguments and results, the device staging in the
+        library's fixed 2 MiB array (no cudaMalloc in the call; at most ``_lib.NOALLOC_MAX_ENVS`` envs; calls on one
+        device share the array, so they must not overlap on the GPU).  No counterpart in the reference."""
+        assert action_host.device.type == "cpu" and action_host.dtype == self.real
+        _lib.check(self.L.sit_env_step_host_noalloc(
+            self.h, self.state_ptr(), int(K), ptr(action_host), ptr(sac_update_host), int(bool(init)),
+            ptr(out_host["obs"]), ptr(out_host["reward"]), ptr(out_host["done"]), ptr(out_host["status"]),
+            self.stream()))
+        self.launches += 1
+        return out_host
+
     def map_query(self, north: torch.Tensor, east: torch.Tensor, want_dist: bool = False):
         """Waypoint validity for n points: flags uint8 (bit 0 = inside an obstacle, MSRL_env_ex.py:544-552; bit 1 =
         outside the map, :517-542) and optionally the distance to the nearest obstacle ring (obstacle.py:138-141)."""
