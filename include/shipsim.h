@@ -305,16 +305,20 @@ int sit_rollout_policy(SitHandle h, void* state, const SitPolicy* pol, const Sit
  * io may carry the usual outputs (rec_steps must be 1) and stats; io->action / sac_update / init are ignored. */
 int sit_rollout_step_k(SitHandle h, void* state, int32_t K, const SitRollout* ro, const SitEnvIO* io, void* stream);
 /* `iterations` x (sit_rollout_policy, sit_rollout_step_k(K)): the inner loop of main_ast.py:320-412 between two learner
- * updates.  use_graph != 0 (and a non-default stream): one iteration is captured into a CUDA graph once and replayed, so
- * the host pays one graph launch per iteration; the graph is re-captured when any argument changes.  Enqueues only. */
+ * updates.  use_graph != 0 (and a non-default stream): replayed from a CUDA graph -- with one env group a graph of one
+ * iteration, launched `iterations` times; with several groups (sit_rollout_group_count) ONE graph of the whole call, the
+ * groups as independent chains that are joined at the end of the call only (captured on the second call with the same
+ * arguments; the first runs as plain launches).  The graph is re-captured when any argument changes.  Enqueues only. */
 int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K, const SitPolicy* pol, const SitRollout* ro,
                         const SitEnvIO* io, int32_t use_graph, void* stream);
 /* mark every env pending at the start of a rollout (after sit_reset + sit_env_init_step) */
 int sit_rollout_begin(SitHandle h, void* state, void* stream);
-/* number of env groups sit_rollout_collect pipelines one iteration over (1 = a single chain on the caller's stream; more:
- * the groups' chains run on internal streams forked from and joined to the caller's, inside the same CUDA graph).  Envs are
- * independent and every random draw is keyed by (global env id, decision serial, try), so no env's trajectory depends on
- * it.  Chosen from n_envs; the environment variable SIT_ROLLOUT_GROUPS overrides. */
+/* number of env groups of sit_rollout_collect (1 = a single chain on the caller's stream; more: every group runs its own
+ * chain policy -> K steps -> policy -> ... on an internal stream forked from the caller's at the start of the call and
+ * joined at its end, so one group's policy kernels run beside another group's step kernel).  Envs are independent and every
+ * random draw is keyed by (global env id, decision serial, try), so no env's trajectory depends on it; replay rows are
+ * reserved group after group (ascending env ranges) inside an iteration and iteration after iteration, so the ring is
+ * filled row for row as with one group.  Chosen from n_envs (1 below 32 768 envs, 2, 3 from 49 152); the environment variable SIT_ROLLOUT_GROUPS overrides. */
 int sit_rollout_group_count(SitHandle h, int32_t* groups);
 
 /* ---- replay exchange after a rollout segment (the only multi-GPU exchange of the loop: main_ast.py:396 memory.push, batched).

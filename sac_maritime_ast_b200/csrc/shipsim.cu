@@ -961,7 +961,12 @@ __global__ void __launch_bounds__(256) rollout_pack_w1_kernel(const PolicyArgs p
     }
 }
 
-__global__ void __launch_bounds__(256, 1) rollout_mlp_tc_kernel(const PolicyArgs pol, const PolScratch sc, const int tmem_cols) {
+// <= 64 registers per thread (one 256-thread CTA beside three resident env-step CTAs of 128 x 128 registers): in a chained
+// collect (rollout_chains) the policy chain of one env group runs while another group's step kernel fills the SMs
+#ifndef SIT_POL_TC_MINB
+#define SIT_POL_TC_MINB 4
+#endif
+__global__ void __launch_bounds__(256, SIT_POL_TC_MINB) rollout_mlp_tc_kernel(const PolicyArgs pol, const PolScratch sc, const int tmem_cols) {
     extern __shared__ __align__(128) unsigned char tc_smem[];
     const int H = pol.hidden;
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -1424,6 +1429,8 @@ struct SitHandle_ {
     void* h_pinned; size_t pinned_bytes;
     // sit_rollout_collect: instantiated CUDA graph of one (policy + K steps) iteration and the arguments it was captured for
     cudaGraphExec_t roll_graph; std::string roll_key;
+    std::string roll_key_seen;                   // chained collect: arguments of the last eager run (captured on their second use)
+    cudaEvent_t cnt_ev[SIT_PIPE + 1];            // chained collect: row-slot reservation order between the env groups
     size_t tc_smem_set;                          // dynamic shared memory opted in for rollout_mlp_tc_kernel
     // sit_fleet_step_host: chunk pipeline over internal streams
     bool pipe_ready; cudaStream_t pipe[SIT_PIPE]; cudaEvent_t pipe_done[SIT_PIPE], pipe_in;
@@ -1767,6 +1774,7 @@ int sit_destroy(SitHandle h) {
     if (h->roll_graph) cudaGraphExecDestroy(h->roll_graph);
     if (h->pipe_ready) {
         for (int j = 0; j < SIT_PIPE; ++j) { cudaStreamDestroy(h->pipe[j]); cudaEventDestroy(h->pipe_done[j]); }
+        for (int j = 0; j <= SIT_PIPE; ++j) cudaEventDestroy(h->cnt_ev[j]);
         cudaEventDestroy(h->pipe_in);
     }
     delete h->kd; delete h->kf;
@@ -2220,7 +2228,7 @@ static int pack_w1(SitHandle h, const PolicyArgs& pa, cudaStream_t st) {
 // gather -> MLP -> sample -> resample for the env range of `ra`; the packed W1 image must already be in the scratch
 template <typename R>
 static int rollout_policy_t(SitHandle h, void* state, const PolicyArgs& pa, bool tensor_cores, const RollArgs& ra, int group,
-                            cudaStream_t st) {
+                            cudaStream_t st, cudaEvent_t count_after = nullptr, cudaEvent_t count_done = nullptr) {
     PolScratch sc;
     int rc = pol_scratch(h, group, ra.env_first, sc);
     if (rc) return rc;
@@ -2231,7 +2239,10 @@ static int rollout_policy_t(SitHandle h, void* state, const PolicyArgs& pa, bool
     const int gather_grid = grid_for(ra.env_count, 256);
     // persistent: tiles / warps stride over the pending list (a small share of the group's envs)
     const int work_grid = h->sm_count * 4;
+    // chained collect: this group's rows are reserved after the previous group's (count_after) and before the next one's
+    if (count_after) CUDA_TRY(cudaStreamWaitEvent(st, count_after, 0));
     rollout_count_kernel<R><<<gather_grid, 256, 0, st>>>(ge, ra, sc);
+    if (count_done) CUDA_TRY(cudaEventRecord(count_done, st));
     rollout_gather_kernel<R><<<gather_grid, 256, 0, st>>>(ge, ra, sc, pa.obs_scale);
     if (pa.mode != SIT_POLICY_UNIFORM) {
         if (tensor_cores) {
@@ -2299,54 +2310,85 @@ static int ensure_pipe(SitHandle h) {
         CUDA_TRY(cudaEventCreateWithFlags(&h->pipe_done[j], cudaEventDisableTiming));
     }
     CUDA_TRY(cudaEventCreateWithFlags(&h->pipe_in, cudaEventDisableTiming));
+    for (int j = 0; j <= SIT_PIPE; ++j) CUDA_TRY(cudaEventCreateWithFlags(&h->cnt_ev[j], cudaEventDisableTiming));
     h->pipe_ready = true;
     return SIT_OK;
 }
 
+#ifndef SIT_ROLLOUT_GROUPS_DEFAULT
+#define SIT_ROLLOUT_GROUPS_DEFAULT 0   /* 0: by size (below) */
+#endif
 // Number of env groups one rollout iteration is cut into (SIT_ROLLOUT_GROUPS overrides).  The policy chain of a group
 // (gather -> MLP -> sample -> resample) is short, dependent and touches only the few envs at a decision event, so on its
 // own it leaves the GPU almost idle; with several groups in flight the chain of one group runs under the env-step kernel of
 // the others.  Envs are independent and every draw is keyed by (global env id, decision serial, try), so the grouping
 // does not change any env's trajectory.
 static int rollout_groups(SitHandle h) {
-    int g = 1;   // measured on B200, 65 536 envs: 2..3 groups within 1 % of one group once the re-draw chain was made cheap
+    // measured on B200, 65 536 envs, K = 32 (chained collect, tools/exp_groups.sh): 1 group 287 us per iteration, 2: 267,
+    // 3: 261, 4: 263, 5: 267; a per-kernel launch priority for the policy kernels changed nothing
+    int g = SIT_ROLLOUT_GROUPS_DEFAULT > 0 ? SIT_ROLLOUT_GROUPS_DEFAULT : (h->n_envs >= 49152 ? 3 : (h->n_envs >= 32768 ? 2 : 1));
     if (const char* e = std::getenv("SIT_ROLLOUT_GROUPS")) g = std::atoi(e);
     g = std::max(1, std::min(g, std::min(SIT_ROLL_GROUPS_MAX, SIT_PIPE + 1)));
     while (g > 1 && h->n_envs / g < 256) --g;
     return g;
 }
 
-// one iteration = policy + K steps for every env, as `groups` independent chains: group 0 on the caller's stream, the others
-// forked onto the handle's internal streams and joined back (works eagerly and under stream capture alike)
-static int rollout_iteration(SitHandle h, void* state, int K, const PolicyArgs& pa, bool tensor_cores, const RollArgs& ra0,
-                             const SitEnvIO* io, int groups, cudaStream_t st) {
+// one iteration = policy + K steps for every env as ONE group on the caller's stream (several groups: rollout_chains)
+static int rollout_iteration(SitHandle h, void* state, int K, const PolicyArgs& pa, bool tensor_cores, const RollArgs& ra,
+                             const SitEnvIO* io, cudaStream_t st) {
     int rc = SIT_OK;
     if (tensor_cores && (rc = pack_w1(h, pa, st))) return rc;
+    if (h->cfg.precision == SIT_F64) {
+        rc = rollout_policy_t<double>(h, state, pa, tensor_cores, ra, 0, st);
+        if (!rc) rc = rollout_step_t<double>(h, state, K, ra, io, st);
+    } else {
+        rc = rollout_policy_t<float>(h, state, pa, tensor_cores, ra, 0, st);
+        if (!rc) rc = rollout_step_t<float>(h, state, K, ra, io, st);
+    }
+    return rc;
+}
+
+// `iterations` x (policy + K steps) as `groups` INDEPENDENT CHAINS, joined only at the end of the call.  Inside one iteration
+// the groups cannot overlap much -- every group runs its short policy chain at the same time, then every group wants the
+// whole GPU for its env-step kernel -- so joining after each iteration (rollout_iteration) gains nothing.  Left to run
+// freely the chains fall out of phase after the first iteration: while one group's env-step kernel fills the SMs, the
+// other group's policy chain (few small CTAs: <= 64 registers each, they fit beside three resident env-step CTAs) runs in
+// the slots that are left, and the partial last wave of one step kernel is filled by the next one.  Per env the
+// sequence policy, K steps, policy, ... is unchanged.  Replay rows: the slot reservations (rollout_count_kernel) are
+// ordered group 0, 1, .., G-1, group 0 of the next iteration, ... by events, so the ring is filled in one fixed order.
+static int rollout_chains(SitHandle h, void* state, int iterations, int K, const PolicyArgs& pa, bool tensor_cores,
+                          const RollArgs& ra0, const SitEnvIO* io, int groups, cudaStream_t st) {
+    int rc = SIT_OK;
+    if (tensor_cores && (rc = pack_w1(h, pa, st))) return rc;      // the weights do not change inside one call
     const int64_t B = h->n_envs, per = ((B + groups - 1) / groups + 255) / 256 * 256;
-    if (groups > 1) {
-        CUDA_TRY(cudaEventRecord(h->pipe_in, st));
-        for (int gi = 1; gi < groups; ++gi) CUDA_TRY(cudaStreamWaitEvent(h->pipe[gi - 1], h->pipe_in, 0));
-    }
-    for (int gi = 0; gi < groups; ++gi) {
-        RollArgs ra = ra0;
-        ra.env_first = std::min<int64_t>(B, gi * per);
-        ra.env_count = std::min<int64_t>(B, (gi + 1) * per) - ra.env_first;
-        if (ra.env_count <= 0) continue;
-        cudaStream_t gs = gi == 0 ? st : h->pipe[gi - 1];
-        if (h->cfg.precision == SIT_F64) {
-            rc = rollout_policy_t<double>(h, state, pa, tensor_cores, ra, gi, gs);
-            if (!rc) rc = rollout_step_t<double>(h, state, K, ra, io, gs);
-        } else {
-            rc = rollout_policy_t<float>(h, state, pa, tensor_cores, ra, gi, gs);
-            if (!rc) rc = rollout_step_t<float>(h, state, K, ra, io, gs);
+    CUDA_TRY(cudaEventRecord(h->pipe_in, st));
+    for (int gi = 1; gi < groups; ++gi) CUDA_TRY(cudaStreamWaitEvent(h->pipe[gi - 1], h->pipe_in, 0));
+    cudaEvent_t prev = nullptr;
+    for (int it = 0; it < iterations; ++it) {
+        for (int gi = 0; gi < groups; ++gi) {
+            RollArgs ra = ra0;
+            ra.env_first = std::min<int64_t>(B, gi * per);
+            ra.env_count = std::min<int64_t>(B, (gi + 1) * per) - ra.env_first;
+            if (ra.env_count <= 0) continue;
+            cudaStream_t gs = gi == 0 ? st : h->pipe[gi - 1];
+            if (h->cfg.precision == SIT_F64) {
+                rc = rollout_policy_t<double>(h, state, pa, tensor_cores, ra, gi, gs, prev, h->cnt_ev[gi]);
+                if (!rc) rc = rollout_step_t<double>(h, state, K, ra, io, gs);
+            } else {
+                rc = rollout_policy_t<float>(h, state, pa, tensor_cores, ra, gi, gs, prev, h->cnt_ev[gi]);
+                if (!rc) rc = rollout_step_t<float>(h, state, K, ra, io, gs);
+            }
+            if (rc) break;
+            prev = h->cnt_ev[gi];
         }
-        if (rc) return rc;
+        if (rc) break;
     }
-    for (int gi = 1; gi < groups; ++gi) {
-        CUDA_TRY(cudaEventRecord(h->pipe_done[gi - 1], h->pipe[gi - 1]));
-        CUDA_TRY(cudaStreamWaitEvent(st, h->pipe_done[gi - 1], 0));
+    for (int gi = 1; gi < groups; ++gi) {   // also after an error: forked work is joined before the call returns
+        cudaError_t e1 = cudaEventRecord(h->pipe_done[gi - 1], h->pipe[gi - 1]);
+        cudaError_t e2 = e1 == cudaSuccess ? cudaStreamWaitEvent(st, h->pipe_done[gi - 1], 0) : e1;
+        if (e2 != cudaSuccess && !rc) rc = fail(SIT_E_CUDA, std::string("rollout_chains join: ") + cudaGetErrorString(e2));
     }
-    return SIT_OK;
+    return rc;
 }
 
 extern "C" {
@@ -2358,10 +2400,11 @@ int sit_rollout_group_count(SitHandle h, int32_t* groups) {
     return SIT_OK;
 }
 
-// `iterations` x (sit_rollout_policy, sit_rollout_step_k(K)), each iteration cut into env groups whose chains overlap
-// (rollout_groups above).  One iteration is captured once into a CUDA graph and replayed, so the loop costs one graph launch
-// per iteration instead of ~7 launches per group through the caller's language binding; the graph is re-captured when any
-// argument changes.  use_graph == 0: plain launches.
+// `iterations` x (sit_rollout_policy, sit_rollout_step_k(K)).  One env group (rollout_groups above): one iteration is captured
+// once into a CUDA graph and replayed, one graph launch per iteration instead of ~7 launches through the caller's language
+// binding.  Several groups: the whole call is one graph of independent per-group chains (rollout_chains), captured on the
+// second use of a set of arguments (the first use runs as plain launches and sizes the scratch).  Either graph is
+// re-captured when any argument changes.  use_graph == 0: plain launches.
 int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K, const SitPolicy* pol, const SitRollout* ro,
                         const SitEnvIO* io, int32_t use_graph, void* stream) {
     if (!h || !state || !pol || !ro) return fail(SIT_E_INVALID, "null argument");
@@ -2383,11 +2426,14 @@ int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K,
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (st != nullptr) CUDA_TRY(cudaStreamIsCapturing(st, &cs));
     if (!use_graph || st == nullptr || cs != cudaStreamCaptureStatusNone) {   // legacy stream cannot be captured
+        if (groups > 1) return rollout_chains(h, state, iterations, K, pa, tensor_cores, ra, io, groups, st);
         for (int it = 0; it < iterations; ++it)
-            if ((rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, groups, st))) return rc;
+            if ((rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, st))) return rc;
         return SIT_OK;
     }
     std::string key;
+    const int32_t chain_iters = groups > 1 ? iterations : 0;   // a chained call is one graph of all its iterations
+    key.append(reinterpret_cast<const char*>(&chain_iters), sizeof(chain_iters));
     key.append(reinterpret_cast<const char*>(&state), sizeof(state));
     key.append(reinterpret_cast<const char*>(&K), sizeof(K));
     key.append(reinterpret_cast<const char*>(&groups), sizeof(groups));
@@ -2397,13 +2443,37 @@ int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K,
     std::memset(&io0, 0, sizeof(io0));
     if (io) io0 = *io;
     key.append(reinterpret_cast<const char*>(&io0), sizeof(io0));
+    if (groups > 1) {
+        if (!h->roll_graph || key != h->roll_key) {
+            if (h->roll_graph) { cudaGraphExecDestroy(h->roll_graph); h->roll_graph = nullptr; h->roll_key.clear(); }
+            // first use of these arguments: plain launches (validates, sizes the scratch); second use: captured
+            if (key != h->roll_key_seen) {
+                h->roll_key_seen = key;
+                return rollout_chains(h, state, iterations, K, pa, tensor_cores, ra, io, groups, st);
+            }
+            CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            rc = rollout_chains(h, state, iterations, K, pa, tensor_cores, ra, io, groups, st);
+            cudaGraph_t graph = nullptr;
+            cudaError_t ce = cudaStreamEndCapture(st, &graph);
+            if (rc || ce != cudaSuccess) {
+                if (graph) cudaGraphDestroy(graph);
+                return rc ? rc : fail(SIT_E_CUDA, std::string("graph capture: ") + cudaGetErrorString(ce));
+            }
+            ce = cudaGraphInstantiate(&h->roll_graph, graph, 0);
+            cudaGraphDestroy(graph);
+            if (ce != cudaSuccess) { h->roll_graph = nullptr; return fail(SIT_E_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(ce)); }
+            h->roll_key = key;
+        }
+        CUDA_TRY(cudaGraphLaunch(h->roll_graph, st));
+        return SIT_OK;
+    }
     if (!h->roll_graph || key != h->roll_key) {
         if (h->roll_graph) { cudaGraphExecDestroy(h->roll_graph); h->roll_graph = nullptr; }
         // one eager iteration first: validates the arguments and sizes the scratch outside the capture
-        if ((rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, groups, st))) return rc;
+        if ((rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, st))) return rc;
         if (--iterations == 0) return SIT_OK;
         CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, groups, st);
+        rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, st);
         cudaGraph_t graph = nullptr;
         cudaError_t ce = cudaStreamEndCapture(st, &graph);
         if (rc || ce != cudaSuccess) {

@@ -183,7 +183,8 @@ class IntermediateWaypointSampler:
         _lib.check(e.L.sit_rollout_group_count(e.h, C.byref(groups)))
         tc = bool(getattr(self.policy, 'tensor_cores', False))
         per_group = 5 + (0 if isinstance(self.policy, UniformPolicy) else 1)   # count, gather, [mlp], sample, resample, step
-        self.launches += (per_group * groups.value + (1 if tc else 0)) * iterations
+        # (several groups: one pack per call, the weights do not change inside it)
+        self.launches += per_group * groups.value * iterations + (1 if tc else 0) * (iterations if groups.value == 1 else 1)
 
     # ---- results ----------------------------------------------------------------------------------------------
     def n_transitions(self) -> int:

@@ -245,6 +245,41 @@ def test_full_size_rollout_properties_and_shard_invariance():
         assert torch.equal(keyed(part, lo, lo + B // 2), keyed(whole, lo, lo + B // 2)), f"shard at {lo} differs from the whole batch"
 
 
+@pytest.mark.parametrize("groups", [2, 3])
+def test_chained_collect_graph_equals_plain_launches_and_fills_the_ring_in_one_order(monkeypatch, groups):
+    """Several env groups: sit_rollout_collect runs the whole call as independent per-group chains (policy -> K steps -> policy
+    ...), joined at the end of the call only, and replays it from ONE graph from the second call with the same arguments
+    on.  The groups reserve their replay rows in a fixed order (events between the count kernels), so the ring is identical
+    row for row between the graph replay, plain launches and a second run -- whatever the overlap on the GPU was."""
+    from sac_maritime_ast_b200 import _lib, rollout as ro
+    monkeypatch.setenv("SIT_ROLLOUT_GROUPS", str(groups))
+    pol = ro.GaussianPolicy(hidden_size=64, device="cuda:0", seed=3, obs_scale="space", tensor_cores=True)
+    B = 1500                                                  # ragged: groups of 768 + 732, or 512 + 512 + 476
+    rings = []
+    for graph in (True, False, True):
+        smp = _make(B, "fp32", pol, cap=200, auto_reset="hard")
+        smp.begin()
+        for j in range(4):                                    # plain launches, capture, replay, replay
+            smp.collect(12, 16, graph=graph)
+            if j == 0:                                        # before the 4096-row ring wraps
+                torch.cuda.synchronize()
+                assert B <= smp.n_opened() <= smp.capacity
+                ids = smp.replay[:B, 23].contiguous().view(torch.int32)
+                assert torch.equal(ids, torch.arange(B, dtype=torch.int32, device=ids.device)), \
+                    "first decisions: group after group, env order"
+        smp.collect(5, 16, graph=graph)                       # other arguments: a new graph on their second use
+        smp.collect(5, 16, graph=graph)
+        torch.cuda.synchronize()
+        c = smp.counters.cpu().numpy()
+        assert c[_lib.RC_CLOSED] == c[_lib.RC_TRANSITIONS] == c[_lib.RC_DECISIONS] > 2 * B
+        rings.append((smp.replay.clone(), c.copy(), smp.env.stats.clone(), {k: smp.env.f[k].clone() for k in ("north", "psi", "flags", "ep_steps")}))
+    for other in rings[1:]:
+        assert np.array_equal(rings[0][1], other[1]) and torch.equal(rings[0][2], other[2])
+        assert torch.equal(rings[0][0].view(torch.int32), other[0].view(torch.int32)), "ring contents differ"
+        for k, v in rings[0][3].items():
+            assert torch.equal(v, other[3][k]), k
+
+
 def test_replay_ring_order_is_deterministic_and_closed_rows_are_counted():
     """Two runs with one seed fill the replay ring IDENTICALLY (row for row, not only as a set): the compaction orders
     the pending envs by env index whatever the CTA scheduling.  SIT_RC_CLOSED trails SIT_RC_TRANSITIONS between a policy
