@@ -2364,6 +2364,17 @@ static int rollout_chains(SitHandle h, void* state, int iterations, int K, const
     CUDA_TRY(cudaEventRecord(h->pipe_in, st));
     for (int gi = 1; gi < groups; ++gi) CUDA_TRY(cudaStreamWaitEvent(h->pipe[gi - 1], h->pipe_in, 0));
     cudaEvent_t prev = nullptr;
+    // SIT_ROLLOUT_TRACE=1 (plain launches only): timed events around every policy chain and step kernel, printed as a
+    // per-group timeline [us since the start of the call] on stderr after a synchronise -- a debugging aid, not a product path
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(st, &cap);
+    const bool trace = cap == cudaStreamCaptureStatusNone && std::getenv("SIT_ROLLOUT_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    auto mark = [&](cudaStream_t s_) {
+        if (!trace) return;
+        cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, s_); tev.push_back(e);
+    };
+    mark(st);
     for (int it = 0; it < iterations; ++it) {
         for (int gi = 0; gi < groups; ++gi) {
             RollArgs ra = ra0;
@@ -2375,8 +2386,11 @@ static int rollout_chains(SitHandle h, void* state, int iterations, int K, const
                 rc = rollout_policy_t<double>(h, state, pa, tensor_cores, ra, gi, gs, prev, h->cnt_ev[gi]);
                 if (!rc) rc = rollout_step_t<double>(h, state, K, ra, io, gs);
             } else {
+                mark(gs);
                 rc = rollout_policy_t<float>(h, state, pa, tensor_cores, ra, gi, gs, prev, h->cnt_ev[gi]);
+                mark(gs);
                 if (!rc) rc = rollout_step_t<float>(h, state, K, ra, io, gs);
+                mark(gs);
             }
             if (rc) break;
             prev = h->cnt_ev[gi];
@@ -2387,6 +2401,23 @@ static int rollout_chains(SitHandle h, void* state, int iterations, int K, const
         cudaError_t e1 = cudaEventRecord(h->pipe_done[gi - 1], h->pipe[gi - 1]);
         cudaError_t e2 = e1 == cudaSuccess ? cudaStreamWaitEvent(st, h->pipe_done[gi - 1], 0) : e1;
         if (e2 != cudaSuccess && !rc) rc = fail(SIT_E_CUDA, std::string("rollout_chains join: ") + cudaGetErrorString(e2));
+    }
+    if (trace && !tev.empty()) {
+        mark(st);
+        cudaStreamSynchronize(st);
+        float total = 0.f;
+        cudaEventElapsedTime(&total, tev.front(), tev.back());
+        std::fprintf(stderr, "[sit trace] %d iterations x %d groups, K = %d: %.1f us\n", iterations, groups, K, total * 1e3f);
+        if (h->cfg.precision != SIT_F64 && tev.size() == (size_t)(2 + 3 * iterations * groups))
+            for (int it = 0; it < iterations; ++it)
+                for (int gi = 0; gi < groups; ++gi) {
+                    float a = 0.f, b = 0.f, c = 0.f;
+                    const size_t j = 1 + 3 * ((size_t)it * groups + gi);
+                    cudaEventElapsedTime(&a, tev.front(), tev[j]); cudaEventElapsedTime(&b, tev.front(), tev[j + 1]);
+                    cudaEventElapsedTime(&c, tev.front(), tev[j + 2]);
+                    std::fprintf(stderr, "[sit trace] it %2d group %d: policy %7.1f .. %7.1f  step .. %7.1f\n", it, gi, a * 1e3f, b * 1e3f, c * 1e3f);
+                }
+        for (cudaEvent_t e : tev) cudaEventDestroy(e);
     }
     return rc;
 }
