@@ -435,6 +435,167 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const GemmTC t) {
     (g.C + (long long)z * g.c_zs)[(long long)m * g.ldc + n] = acc;
 }
 
+// ---- fused forward of one 3-layer network on the tensor-core path ------------------------------------------------------
+// out = W2^T relu(W1^T relu(W0^T x)) for 128 batch rows per CTA and `Z` networks (grid.y), the hidden activations h1, h2
+// written to HBM on the way for the backward pass.  One kernel instead of three (thin-k, tcgen05 tile GEMM, skinny-n):
+//   layer 0 (k = 11 / 12 inputs) on the CUDA cores, fp32, ascending k like gemm_thin_k_kernel; the relu'd row goes to h1
+//     (fp32) and, as bf16, into the canonical K-major image of the A operand in shared memory;
+//   layer 1 (H x H) on tcgen05: the bf16 image of W1 (pack_w1_nets_kernel, canonical K-major, rows = output unit) lands with
+//     ONE bulk async copy while layer 0 is computed; 128 x H fp32 accumulator in TMEM; the bias row of the augmented layer
+//     is added in fp32 in the epilogue;
+//   layer 2 (1 or 2 outputs) folded into the epilogue: the thread that owns a row reads its accumulator columns, applies
+//     bias + relu, writes h2 and accumulates the outputs in fp32, ascending k inside each column half, the two halves added
+//     in a fixed order -- deterministic.
+struct FwdTC {
+    const float* X; int kin1;                 // [B][kin1] input rows, last column = 1 (the bias input)
+    const float* W; long long w_zs;           // network block (augmented layers at l0, l1, l2), stride between the Z networks
+    long long l0, l1, l2;
+    const unsigned char* w1p; long long w1p_zs;   // bf16 image of W1's H x H part, bytes
+    float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld], outputs [Z][B][nout]
+    int B, H, ld, nout, tmem_cols;
+};
+// bf16 K-major images of the H x H part of layer 1 of `n_nets` networks (net q at ws + net_off[q], image q at w1p + q H H 2)
+struct PackNets { long long w_off[5]; };
+__global__ void __launch_bounds__(256) pack_w1_nets_kernel(const float* ws, unsigned char* w1p, const PackNets pn, const int H) {
+    const float* w1 = ws + pn.w_off[blockIdx.y];
+    unsigned char* dst = w1p + (size_t)blockIdx.y * H * H * 2;
+    const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;
+    for (int item = blockIdx.x * 256 + threadIdx.x; item < H * (H >> 3); item += gridDim.x * 256) {
+        const int nn = item % H, kc = item / H;
+        const float* w = w1 + (size_t)(kc * 8) * H + nn;
+        uint4 v;
+        v.x = pack_bf16x2(w[0], w[H]); v.y = pack_bf16x2(w[2 * H], w[3 * H]);
+        v.z = pack_bf16x2(w[4 * H], w[5 * H]); v.w = pack_bf16x2(w[6 * H], w[7 * H]);
+        *reinterpret_cast<uint4*>(dst + (size_t)(nn >> 3) * sbo + (size_t)kc * lbo + (nn & 7) * 16) = v;
+    }
+}
+
+__global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
+    extern __shared__ __align__(128) unsigned char fw_smem[];
+    const int H = f.H, tid = threadIdx.x, warp = tid >> 5, z = blockIdx.y;
+    const int m0 = blockIdx.x * TCG_M;
+    const float* W = f.W + (long long)z * f.w_zs;
+    unsigned char* sA = fw_smem;                                      // [128/8][H/8][8][8] bf16
+    unsigned char* sB = sA + (size_t)TCG_M * H * 2;                   // [H/8][H/8][8][8] bf16, rows = output unit
+    float* s_w2 = reinterpret_cast<float*>(sB + (size_t)H * H * 2);   // [H + 1][2]
+    float* s_b1 = s_w2 + 2 * (H + 1);                                 // [H]
+    float* s_part = s_b1 + H;                                         // [128][2]
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + 2 * TCG_M + 2);   // [0]: MMAs done, [1]: W1 image landed (8-byte aligned)
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2);
+    float* s_w0 = reinterpret_cast<float*>(s_bar + 4);                // [kin1][H] (the network blocks are only 4-byte aligned in the workspace)
+    const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(f.tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    if (tid == 32) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar + 1)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::);
+        const uint32_t bytes = (uint32_t)H * (uint32_t)H * 2u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(s_bar + 1)), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(sB)), "l"(f.w1p + (long long)z * f.w1p_zs), "r"(bytes), "r"(smem_u32(s_bar + 1)) : "memory");
+    }
+    for (int i = tid; i < (H + 1) * f.nout; i += 256) {
+        const int k = i / f.nout, j = i % f.nout;
+        s_w2[2 * k + j] = W[f.l2 + i];
+        if (f.nout == 1) s_w2[2 * k + 1] = 0.f;
+    }
+    for (int i = tid; i < H; i += 256) s_b1[i] = W[f.l1 + (long long)H * H + i];
+    for (int i = tid; i < f.kin1 * H; i += 256) s_w0[i] = W[f.l0 + i];
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+    const uint32_t tmem_base = *s_tmem;
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(H >> 3) << 17) | ((uint32_t)(TCG_M >> 4) << 24);
+    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H >> 1;
+    const int m = m0 + row;
+    const bool live = m < f.B;
+
+    // layer 0: relu(x . W0) for this thread's row and column half
+    float x[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) x[c] = (live && c < f.kin1) ? f.X[(long long)m * f.kin1 + c] : 0.f;
+    const float* W0 = s_w0;
+    float* h1 = f.H1 + (long long)z * f.hz + (long long)m * f.ld;
+    for (int k0 = half * kh; k0 < (half + 1) * kh; k0 += 8) {
+        float a[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = 0.f;
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+            if (c < f.kin1) {
+                const float4 wa = *reinterpret_cast<const float4*>(W0 + c * H + k0);
+                const float4 wb = *reinterpret_cast<const float4*>(W0 + c * H + k0 + 4);
+                a[0] = fmaf(x[c], wa.x, a[0]); a[1] = fmaf(x[c], wa.y, a[1]); a[2] = fmaf(x[c], wa.z, a[2]); a[3] = fmaf(x[c], wa.w, a[3]);
+                a[4] = fmaf(x[c], wb.x, a[4]); a[5] = fmaf(x[c], wb.y, a[5]); a[6] = fmaf(x[c], wb.z, a[6]); a[7] = fmaf(x[c], wb.w, a[7]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = fmaxf(a[j], 0.f);
+        if (live) {
+            *reinterpret_cast<float4*>(h1 + k0) = make_float4(a[0], a[1], a[2], a[3]);
+            *reinterpret_cast<float4*>(h1 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
+        }
+        uint4 v;
+        v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
+        *reinterpret_cast<uint4*>(sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16) = v;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    // layer 1 on the tensor cores: D[128 x H] (TMEM, fp32) = A[128 x H] . B[H x H]
+    if (tid == 0) {
+        mbar_wait(smem_u32(s_bar + 1), 0u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::);
+        const uint64_t da = umma_desc_kmajor_noswizzle(smem_u32(sA), lbo, sbo), db = umma_desc_kmajor_noswizzle(smem_u32(sB), lbo, sbo);
+        for (int ks = 0; ks < (H >> 4); ++ks) {
+            const uint64_t adv = (uint64_t)((ks * 2 * lbo) >> 4);
+            const uint32_t acc = ks > 0 ? 1u : 0u;
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                         ::"r"(tmem_base), "l"(da + adv), "l"(db + adv), "r"(idesc), "r"(acc) : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(s_bar)) : "memory");
+    }
+    mbar_wait(smem_u32(s_bar), 0u);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+    // epilogue: h2 = relu(D + b1) -> HBM, output layer accumulated on the way
+    float o0 = 0.f, o1 = 0.f;
+    float* h2 = f.H2 + (long long)z * f.hz + (long long)m * f.ld;
+    const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    for (int c0 = half * kh; c0 < (half + 1) * kh; c0 += 16) {
+        uint32_t r[16];
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                       "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                     : "r"(taddr + (uint32_t)c0));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        float hv[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            hv[j] = fmaxf(__uint_as_float(r[j]) + s_b1[c0 + j], 0.0f);
+            const float2 w = reinterpret_cast<const float2*>(s_w2)[c0 + j];
+            o0 = fmaf(hv[j], w.x, o0);
+            o1 = fmaf(hv[j], w.y, o1);
+        }
+        if (live) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(h2 + c0 + j) = make_float4(hv[j], hv[j + 1], hv[j + 2], hv[j + 3]);
+        }
+    }
+    if (half == 1) { s_part[2 * row] = o0; s_part[2 * row + 1] = o1; }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+    if (half == 0 && live) {
+        float* out = f.Out + (long long)z * f.B * f.nout + (long long)m * f.nout;
+        out[0] = o0 + s_part[2 * row] + s_w2[2 * H];
+        if (f.nout == 2) out[1] = o1 + s_part[2 * row + 1] + s_w2[2 * H + 1];
+    }
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(f.tmem_cols));
+}
+
 // ---- workspace ------------------------------------------------------------------------------------------------------
 struct Net { long long l0, l1, l2; };   // float offsets of the three augmented layer blocks inside a network block
 struct Layout {
@@ -446,8 +607,9 @@ struct Layout {
     long long o_xs, o_xs2, o_xsa, o_xs2a, o_xspi, o_r, o_mask;
     long long o_hp1, o_hp2, o_op, o_hq1, o_hq2, o_oq, o_oqt, o_hqt1, o_hqt2;   // hqt*: scratch activations of the target critics
     long long o_doq, o_dhq2, o_dhq1, o_da, o_dop, o_dhp2, o_dhp1;
-    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, total;
+    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, o_w1p, total;
     int tc;                             // large-batch products on tcgen05 (gemm_tc_kernel)
+    int fused_fwd;                      // tc: a network's forward as ONE kernel (mlp_fwd_tc_kernel); SIT_SAC_FUSED_FWD=0 keeps the three products
     int ldh;                            // leading dimension of the hidden activations [B][ldh]: H weights' inputs + the ones
                                         // column (H + 1), padded to a multiple of 4 floats on the tensor-core path so that
                                         // every row starts 16-byte aligned (128-bit operand loads)
@@ -455,6 +617,8 @@ struct Layout {
 
 static void make_layout(Layout& L, int H, int B, int tc) {
     L.H = H; L.B = B; L.tc = tc; L.ldh = tc ? H + 4 : H + 1;
+    L.fused_fwd = tc && H % 16 == 0;
+    if (const char* e = std::getenv("SIT_SAC_FUSED_FWD")) if (std::atoi(e) == 0) L.fused_fwd = 0;
     L.pol.l0 = 0; L.pol.l1 = (long long)(S + 1) * H; L.pol.l2 = L.pol.l1 + (long long)(H + 1) * H;
     L.P_pol = L.pol.l2 + (long long)(H + 1) * 2;
     L.q.l0 = 0; L.q.l1 = (long long)(SA + 1) * H; L.q.l2 = L.q.l1 + (long long)(H + 1) * H;
@@ -480,6 +644,7 @@ static void make_layout(Layout& L, int H, int B, int tc) {
     L.o_idx = take(b); L.o_losses = take(SIT_SAC_N_LOSS); L.o_updates = take(2);   // updates: one unsigned long long
     L.o_obs_scale = take(S);
     L.o_part = take(tc ? 3 * 2LL * TCG_MAX_SPLITS * (H + 1) * H : 0);   // split-k partial tiles [z][split][M][N], one region per concurrent weight-gradient product
+    L.o_w1p = take(tc ? 5LL * H * H / 2 : 0);   // bf16 K-major images of W1 (H x H): policy, q1, q2, q1 target, q2 target
     L.total = o;
 }
 
@@ -709,6 +874,8 @@ struct SitSac_ {
 
 namespace sac {
 
+static size_t fwd_smem_bytes(int H, int kin1) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 1040 + 32 + (size_t)kin1 * H * 4; }
+
 struct Launcher {
     cudaStream_t st;
     float* ws;
@@ -764,14 +931,37 @@ struct Launcher {
         else gemm_kernel<false, false><<<grid, 256, 0, st>>>(g);
     }
     // forward of a 3-layer network: X [B][kin+1] -> h1, h2 [Z][B][H+1] (relu, ones column kept) -> out [Z][B][nout]
+    // net_id: index of the (first) network's bf16 W1 image in the workspace (0 policy, 1 q1, 2 q2, 3 / 4 their targets);
+    // -1 or the SIMT path: the three products as separate launches
     void forward(long long oX, int kin, long long oW, long long w_zs, const Net& n, int nout, long long oH1, long long oH2,
-                 long long oOut, int Z) const {
+                 long long oOut, int Z, int net_id = -1) const {
         const int B = L.B, H = L.H;
         const int ld = L.ldh;
         const long long hz = (long long)B * ld;
+        if (L.tc && L.fused_fwd && net_id >= 0) {
+            FwdTC f;
+            f.X = ws + oX; f.kin1 = kin + 1; f.W = ws + oW; f.w_zs = w_zs; f.l0 = n.l0; f.l1 = n.l1; f.l2 = n.l2;
+            f.w1p = reinterpret_cast<const unsigned char*>(ws + L.o_w1p) + (size_t)net_id * H * H * 2; f.w1p_zs = (long long)H * H * 2;
+            f.H1 = ws + oH1; f.H2 = ws + oH2; f.Out = ws + oOut; f.hz = hz;
+            f.B = B; f.H = H; f.ld = ld; f.nout = nout;
+            f.tmem_cols = 32;
+            while (f.tmem_cols < H) f.tmem_cols <<= 1;
+            mlp_fwd_tc_kernel<<<dim3((B + TCG_M - 1) / TCG_M, Z), 256, fwd_smem_bytes(H, kin + 1), st>>>(f);
+            return;
+        }
         gemm(oX, kin + 1, 1, 0, oW + n.l0, H, 1, w_zs, oH1, ld, hz, B, H, kin + 1, Z, EPI_RELU);
         gemm(oH1, ld, 1, hz, oW + n.l1, H, 1, w_zs, oH2, ld, hz, B, H, H + 1, Z, EPI_RELU);
         gemm(oH2, ld, 1, hz, oW + n.l2, nout, 1, w_zs, oOut, nout, (long long)B * nout, B, nout, H + 1, Z, EPI_STORE);
+    }
+    // bf16 images of W1 for the fused forward: networks [first, first + count) of (policy, q1, q2, q1 target, q2 target)
+    void pack_w1(int first, int count, cudaStream_t on) const {
+        if (!(L.tc && L.fused_fwd)) return;
+        const long long off[5] = {L.o_pol + L.pol.l1, L.o_q + L.q.l1, L.o_q + L.P_q + L.q.l1, L.o_qt + L.q.l1, L.o_qt + L.P_q + L.q.l1};
+        PackNets pn;
+        for (int q = 0; q < 5; ++q) pn.w_off[q] = off[std::min(4, first + q)];
+        const int H = L.H;
+        pack_w1_nets_kernel<<<dim3((H * (H >> 3) + 255) / 256, count), 256, 0, on>>>(
+            ws, reinterpret_cast<unsigned char*>(ws + L.o_w1p) + (size_t)first * H * H * 2, pn, H);
     }
     // backward: dOut [Z][B][nout] -> (optionally) weight gradients into the grad block, and d/dX of the first `dx_cols`
     // input columns starting at column dx_first (0 columns: stop at layer 0's weight gradient)
@@ -818,26 +1008,28 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     cudaStream_t s2 = X2.st;
     auto fork2 = [&](int e) { if (par) { cudaEventRecord(h->ev2[e], st); cudaStreamWaitEvent(s2, h->ev2[e], 0); } };
     auto join2 = [&](int e) { if (par) { cudaEventRecord(h->ev2[e], s2); cudaStreamWaitEvent(st, h->ev2[e], 0); } };
+    X.pack_w1(0, 5, st);       // weights as the caller left them (also after a load through sit_sac_field)
     batch_kernel<<<eb, 256, 0, st>>>(ws, L, hp, replay, capacity, n_rows);
     // critics on (s, a): needs the batch only -> beside the target computation
     fork2(0);
-    X2.forward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2);
+    X2.forward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
     // target: a' ~ pi(s'), Q targets on (s', a')
-    X.forward(L.o_xs2, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1);
+    X.forward(L.o_xs2, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0);
     head_kernel<<<eb, 256, 0, st>>>(ws, L, L.o_eps_next, L.o_xs2a, L.o_logp_next);
-    X.forward(L.o_xs2a, SA, L.o_qt, L.P_q, L.q, 1, L.o_hqt1, L.o_hqt2, L.o_oqt, 2);
+    X.forward(L.o_xs2a, SA, L.o_qt, L.P_q, L.q, 1, L.o_hqt1, L.o_hqt2, L.o_oqt, 2, 3);
     join2(1);
     // loss, backward, Adam (+ soft target update)
     critic_loss_kernel<<<1, 1024, 0, st>>>(ws, L, hp);
     // policy on s (its own buffers, the policy's weights): beside the critics' backward and Adam
     fork2(2);
-    X2.forward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1);
+    X2.forward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0);
     head_kernel<<<eb, 256, 0, s2>>>(ws, L, L.o_eps_cur, L.o_xspi, L.o_logp_cur);
     X.backward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, true, L.o_grad + L.P_pol, 0, 0, 0);
     adam_kernel<<<(unsigned)((2 * L.P_q + 255) / 256), 256, 0, st>>>(ws, L, hp, L.P_pol, 2 * L.P_q, L.o_qt - L.o_q, 1);
+    X.pack_w1(1, 2, st);       // the updated critics
     join2(3);
     // critics (updated) on (s, a~), d/da through the critics, policy backward, Adam
-    X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2);
+    X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
     policy_seed_kernel<<<1, 1024, 0, st>>>(ws, L);
     X.backward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, false, 0, L.o_da, S, 1);
     policy_grad_kernel<<<eb, 256, 0, st>>>(ws, L);
@@ -876,6 +1068,8 @@ int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out) {
     {
         cudaError_t ce = cudaSetDevice(device);
         if (ce == cudaSuccess && tc) ce = cudaFuncSetAttribute(sac::gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (ce == cudaSuccess && tc)
+            ce = cudaFuncSetAttribute(sac::mlp_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sac::fwd_smem_bytes(cfg->hidden, sac::SA + 1));
         // two internal streams: independent parts of an update run as parallel branches of its CUDA graph (at batch 64 the
         // update is a chain of few-microsecond launches, at batch 4096 every product leaves most of the GPU idle)
         if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
