@@ -454,19 +454,30 @@ struct FwdTC {
     float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld], outputs [Z][B][nout]
     int B, H, ld, nout, tmem_cols;
 };
-// bf16 K-major images of the H x H part of layer 1 of `n_nets` networks (net q at ws + net_off[q], image q at w1p + q H H 2)
-struct PackNets { long long w_off[5]; };
+// bf16 K-major images of the H x H part W1[k][n] of layer 1 (entry q: weights at ws + w_off[q], image number img[q] of H H 2
+// bytes each).  Forward image (by_k = 0): operand rows = output unit n, contraction along k.  Backward image (by_k = 1):
+// operand rows = input unit k, contraction along n (d h1 = d h2 . W1^T).
+#define SAC_W1_IMAGES 8   /* forward: policy, q1, q2, q1 target, q2 target; backward: policy, q1, q2 */
+struct PackNets { long long w_off[SAC_W1_IMAGES]; int img[SAC_W1_IMAGES], by_k[SAC_W1_IMAGES]; };
 __global__ void __launch_bounds__(256) pack_w1_nets_kernel(const float* ws, unsigned char* w1p, const PackNets pn, const int H) {
     const float* w1 = ws + pn.w_off[blockIdx.y];
-    unsigned char* dst = w1p + (size_t)blockIdx.y * H * H * 2;
+    unsigned char* dst = w1p + (size_t)pn.img[blockIdx.y] * H * H * 2;
     const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;
+    const bool by_k = pn.by_k[blockIdx.y] != 0;
     for (int item = blockIdx.x * 256 + threadIdx.x; item < H * (H >> 3); item += gridDim.x * 256) {
-        const int nn = item % H, kc = item / H;
-        const float* w = w1 + (size_t)(kc * 8) * H + nn;
         uint4 v;
-        v.x = pack_bf16x2(w[0], w[H]); v.y = pack_bf16x2(w[2 * H], w[3 * H]);
-        v.z = pack_bf16x2(w[4 * H], w[5 * H]); v.w = pack_bf16x2(w[6 * H], w[7 * H]);
-        *reinterpret_cast<uint4*>(dst + (size_t)(nn >> 3) * sbo + (size_t)kc * lbo + (nn & 7) * 16) = v;
+        int r, c;                                   // operand row, 8-wide chunk along the contraction
+        if (!by_k) {                                // row = n, chunk of 8 consecutive k (stride H in memory)
+            r = item % H; c = item / H;
+            const float* w = w1 + (size_t)(c * 8) * H + r;
+            v.x = pack_bf16x2(w[0], w[H]); v.y = pack_bf16x2(w[2 * H], w[3 * H]);
+            v.z = pack_bf16x2(w[4 * H], w[5 * H]); v.w = pack_bf16x2(w[6 * H], w[7 * H]);
+        } else {                                    // row = k, chunk of 8 consecutive n (contiguous in memory)
+            c = item % (H >> 3); r = item / (H >> 3);
+            const float* w = w1 + (size_t)r * H + c * 8;
+            v.x = pack_bf16x2(w[0], w[1]); v.y = pack_bf16x2(w[2], w[3]); v.z = pack_bf16x2(w[4], w[5]); v.w = pack_bf16x2(w[6], w[7]);
+        }
+        *reinterpret_cast<uint4*>(dst + (size_t)(r >> 3) * sbo + (size_t)c * lbo + (r & 7) * 16) = v;
     }
 }
 
@@ -596,6 +607,142 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(f.tmem_cols));
 }
 
+// ---- fused input-gradient chain of one 3-layer network on the tensor-core path ------------------------------------------
+// d h2 = (d out . W2^T) masked by h2 > 0 (CUDA cores, ascending output index like gemm_thin_k_kernel) -> HBM (for the
+// weight-gradient product of layer 1) and, as bf16, the A image;  d h1 = (d h2 . W1^T) masked by h1 > 0 on tcgen05 (W1's
+// by-k bf16 image, one bulk copy) -> HBM (for layer 0's weight gradient);  optionally d x of ONE input column (the action
+// of the critics: d Q / d a) accumulated in the epilogue, ascending k inside each column half, halves added in a fixed order.
+// One kernel instead of thin-k + tile GEMM (+ skinny-n); the weight-gradient products stay on gemm_tc_kernel.
+struct BwdTC {
+    const float* DOut; int nout;              // [Z][B][nout]
+    const float* W; long long w_zs; long long l0, l2;
+    const unsigned char* w1p; long long w1p_zs;   // by-k bf16 image of W1
+    const float *H1, *H2; long long hz; int ld;   // forward activations (masks) [Z][B][ld]
+    float *DH2, *DH1;                         // [Z][B][H], nullptr: not stored (no weight gradients wanted)
+    float* DX; int dx_row;                    // [Z][B] or nullptr; row of W0 (input column) the gradient is taken for
+    int B, H, tmem_cols;
+};
+__global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
+    extern __shared__ __align__(128) unsigned char bw_smem[];
+    const int H = f.H, tid = threadIdx.x, warp = tid >> 5, z = blockIdx.y;
+    const int m0 = blockIdx.x * TCG_M;
+    const float* W = f.W + (long long)z * f.w_zs;
+    unsigned char* sA = bw_smem;
+    unsigned char* sB = sA + (size_t)TCG_M * H * 2;
+    float* s_w2 = reinterpret_cast<float*>(sB + (size_t)H * H * 2);   // [H][2]
+    float* s_wx = s_w2 + 2 * H;                                       // [H]: row dx_row of W0
+    float* s_part = s_wx + H;                                         // [128]
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + TCG_M);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2);
+    const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(f.tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    if (tid == 32) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar + 1)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::);
+        const uint32_t bytes = (uint32_t)H * (uint32_t)H * 2u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(s_bar + 1)), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(sB)), "l"(f.w1p + (long long)z * f.w1p_zs), "r"(bytes), "r"(smem_u32(s_bar + 1)) : "memory");
+    }
+    for (int i = tid; i < H * f.nout; i += 256) {
+        const int k = i / f.nout, j = i % f.nout;
+        s_w2[2 * k + j] = W[f.l2 + i];
+        if (f.nout == 1) s_w2[2 * k + 1] = 0.f;
+    }
+    for (int i = tid; i < H; i += 256) s_wx[i] = f.DX ? W[f.l0 + (long long)f.dx_row * H + i] : 0.f;
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+    const uint32_t tmem_base = *s_tmem;
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(H >> 3) << 17) | ((uint32_t)(TCG_M >> 4) << 24);
+    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H >> 1;
+    const int m = m0 + row;
+    const bool live = m < f.B;
+
+    // layer 2: d h2 for this thread's row and column half
+    const float* dout = f.DOut + (long long)z * f.B * f.nout + (long long)m * f.nout;
+    const float d0 = live ? dout[0] : 0.f, d1 = (live && f.nout == 2) ? dout[1] : 0.f;
+    const float* h2 = f.H2 + (long long)z * f.hz + (long long)m * f.ld;
+    float* dh2 = f.DH2 ? f.DH2 + ((long long)z * f.B + m) * H : nullptr;
+    for (int k0 = half * kh; k0 < (half + 1) * kh; k0 += 8) {
+        float4 ma = make_float4(0.f, 0.f, 0.f, 0.f), mb = ma;
+        if (live) { ma = *reinterpret_cast<const float4*>(h2 + k0); mb = *reinterpret_cast<const float4*>(h2 + k0 + 4); }
+        const float hm[8] = {ma.x, ma.y, ma.z, ma.w, mb.x, mb.y, mb.z, mb.w};
+        float a[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float2 w = reinterpret_cast<const float2*>(s_w2)[k0 + j];
+            float acc = fmaf(d0, w.x, 0.f);
+            if (f.nout == 2) acc = fmaf(d1, w.y, acc);
+            a[j] = hm[j] > 0.f ? acc : 0.f;
+        }
+        if (live && dh2) {
+            *reinterpret_cast<float4*>(dh2 + k0) = make_float4(a[0], a[1], a[2], a[3]);
+            *reinterpret_cast<float4*>(dh2 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
+        }
+        uint4 v;
+        v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
+        *reinterpret_cast<uint4*>(sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16) = v;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    // layer 1 on the tensor cores: D[128 x H(k)] = d h2 [128 x H(n)] . W1^T [H(n) x H(k)]
+    if (tid == 0) {
+        mbar_wait(smem_u32(s_bar + 1), 0u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::);
+        const uint64_t da = umma_desc_kmajor_noswizzle(smem_u32(sA), lbo, sbo), db = umma_desc_kmajor_noswizzle(smem_u32(sB), lbo, sbo);
+        for (int ks = 0; ks < (H >> 4); ++ks) {
+            const uint64_t adv = (uint64_t)((ks * 2 * lbo) >> 4);
+            const uint32_t acc = ks > 0 ? 1u : 0u;
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                         ::"r"(tmem_base), "l"(da + adv), "l"(db + adv), "r"(idesc), "r"(acc) : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(s_bar)) : "memory");
+    }
+    mbar_wait(smem_u32(s_bar), 0u);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+    // epilogue: d h1 = D masked by h1 > 0 -> HBM; d x accumulated on the way
+    float dx = 0.f;
+    const float* h1 = f.H1 + (long long)z * f.hz + (long long)m * f.ld;
+    float* dh1 = f.DH1 ? f.DH1 + ((long long)z * f.B + m) * H : nullptr;
+    const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    for (int c0 = half * kh; c0 < (half + 1) * kh; c0 += 16) {
+        uint32_t r[16];
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                       "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                     : "r"(taddr + (uint32_t)c0));
+        float hm[16];
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) {
+            const float4 q = live ? *reinterpret_cast<const float4*>(h1 + c0 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+            hm[j] = q.x; hm[j + 1] = q.y; hm[j + 2] = q.z; hm[j + 3] = q.w;
+        }
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        float g[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            g[j] = hm[j] > 0.f ? __uint_as_float(r[j]) : 0.f;
+            dx = fmaf(g[j], s_wx[c0 + j], dx);
+        }
+        if (live && dh1) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(dh1 + c0 + j) = make_float4(g[j], g[j + 1], g[j + 2], g[j + 3]);
+        }
+    }
+    if (half == 1) s_part[row] = dx;
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+    if (half == 0 && live && f.DX) f.DX[(long long)z * f.B + m] = dx + s_part[row];
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(f.tmem_cols));
+}
+
 // ---- workspace ------------------------------------------------------------------------------------------------------
 struct Net { long long l0, l1, l2; };   // float offsets of the three augmented layer blocks inside a network block
 struct Layout {
@@ -644,7 +791,7 @@ static void make_layout(Layout& L, int H, int B, int tc) {
     L.o_idx = take(b); L.o_losses = take(SIT_SAC_N_LOSS); L.o_updates = take(2);   // updates: one unsigned long long
     L.o_obs_scale = take(S);
     L.o_part = take(tc ? 3 * 2LL * TCG_MAX_SPLITS * (H + 1) * H : 0);   // split-k partial tiles [z][split][M][N], one region per concurrent weight-gradient product
-    L.o_w1p = take(tc ? 5LL * H * H / 2 : 0);   // bf16 K-major images of W1 (H x H): policy, q1, q2, q1 target, q2 target
+    L.o_w1p = take(tc ? (long long)SAC_W1_IMAGES * H * H / 2 : 0);   // bf16 K-major images of W1 (pack_w1_nets_kernel)
     L.total = o;
 }
 
@@ -870,10 +1017,13 @@ struct SitSac_ {
     // third branch: the critics' forward on (s, a) beside the target computation, and the policy's forward on s beside the
     // critics' backward + Adam (independent until the joins below)
     cudaStream_t side2; cudaEvent_t ev2[4];
+    // fourth: layer 0's weight-gradient product beside layer 1's (fused backward)
+    cudaStream_t side3; cudaEvent_t ev3[2];
 };
 
 namespace sac {
 
+static size_t bwd_smem_bytes(int H) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 512 + 32; }
 static size_t fwd_smem_bytes(int H, int kin1) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 1040 + 32 + (size_t)kin1 * H * 4; }
 
 struct Launcher {
@@ -882,7 +1032,9 @@ struct Launcher {
     const Layout& L;
     cudaStream_t side;           // nullptr: everything on `st`
     cudaEvent_t* ev;
-    mutable int branch;          // 0: launch on st; 1 .. 3: launch on `side`, split-k partials in region branch - 1
+    mutable int branch;          // 0: launch on st; 1 .. 3: launch on `side` (3: on `side_b` when there is one), split-k partials in region branch - 1
+    cudaStream_t side_b = nullptr;   // second side stream of the fused backward: layer 0's weight gradient beside layer 1's
+    cudaEvent_t* ev_b = nullptr;
     // C[z] (M x N, ldc) = epi(A[z] . B[z]);  A(m,k) = A[m a_rs + k a_cs], B(k,n) = B[k b_rs + n b_cs]
     void gemm(long long oA, int a_rs, int a_cs, long long a_zs, long long oB, int b_rs, int b_cs, long long b_zs, long long oC,
               int ldc, long long c_zs, int M, int N, int K, int Z, int epi, long long oH = 0, int ldh = 0, long long h_zs = 0) const {
@@ -890,7 +1042,7 @@ struct Launcher {
         g.A = ws + oA; g.B = ws + oB; g.C = ws + oC; g.Hm = ws + oH;
         g.M = M; g.N = N; g.K = K; g.a_rs = a_rs; g.a_cs = a_cs; g.b_rs = b_rs; g.b_cs = b_cs; g.ldc = ldc; g.ldh = ldh;
         g.a_zs = a_zs; g.b_zs = b_zs; g.c_zs = c_zs; g.h_zs = h_zs; g.epi = epi;
-        cudaStream_t st = branch > 0 ? side : this->st;      // the branch this product belongs to
+        cudaStream_t st = branch > 0 ? ((branch == 3 && side_b) ? side_b : side) : this->st;      // the branch this product belongs to
         if (L.tc && K <= 16) {
             gemm_thin_k_kernel<<<dim3((M + THIN_ROWS - 1) / THIN_ROWS, 1, Z), 256, 0, st>>>(g);
             return;
@@ -953,24 +1105,54 @@ struct Launcher {
         gemm(oH1, ld, 1, hz, oW + n.l1, H, 1, w_zs, oH2, ld, hz, B, H, H + 1, Z, EPI_RELU);
         gemm(oH2, ld, 1, hz, oW + n.l2, nout, 1, w_zs, oOut, nout, (long long)B * nout, B, nout, H + 1, Z, EPI_STORE);
     }
-    // bf16 images of W1 for the fused forward: networks [first, first + count) of (policy, q1, q2, q1 target, q2 target)
-    void pack_w1(int first, int count, cudaStream_t on) const {
+    // bf16 images of W1 for the fused forward / backward kernels: all eight, or (critics_only) the four of q1, q2
+    void pack_w1(bool critics_only, cudaStream_t on) const {
         if (!(L.tc && L.fused_fwd)) return;
         const long long off[5] = {L.o_pol + L.pol.l1, L.o_q + L.q.l1, L.o_q + L.P_q + L.q.l1, L.o_qt + L.q.l1, L.o_qt + L.P_q + L.q.l1};
         PackNets pn;
-        for (int q = 0; q < 5; ++q) pn.w_off[q] = off[std::min(4, first + q)];
+        int n = 0;
+        auto add = [&](int net, int img, int by_k) { pn.w_off[n] = off[net]; pn.img[n] = img; pn.by_k[n] = by_k; ++n; };
+        if (!critics_only) { add(0, 0, 0); add(3, 3, 0); add(4, 4, 0); add(0, 5, 1); }
+        add(1, 1, 0); add(2, 2, 0); add(1, 6, 1); add(2, 7, 1);
+        for (int q = n; q < SAC_W1_IMAGES; ++q) { pn.w_off[q] = 0; pn.img[q] = 0; pn.by_k[q] = 0; }
         const int H = L.H;
-        pack_w1_nets_kernel<<<dim3((H * (H >> 3) + 255) / 256, count), 256, 0, on>>>(
-            ws, reinterpret_cast<unsigned char*>(ws + L.o_w1p) + (size_t)first * H * H * 2, pn, H);
+        pack_w1_nets_kernel<<<dim3((H * (H >> 3) + 255) / 256, n), 256, 0, on>>>(ws, reinterpret_cast<unsigned char*>(ws + L.o_w1p), pn, H);
     }
     // backward: dOut [Z][B][nout] -> (optionally) weight gradients into the grad block, and d/dX of the first `dx_cols`
     // input columns starting at column dx_first (0 columns: stop at layer 0's weight gradient)
     void backward(long long oX, int kin, long long oW, long long w_zs, const Net& n, int nout, long long oH1, long long oH2,
                   long long oDOut, long long oDH2, long long oDH1, int Z, bool want_dw, long long oG, long long oDX, int dx_first,
-                  int dx_cols) const {
+                  int dx_cols, int bw_img = -1) const {
         const int B = L.B, H = L.H;
         const int ld = L.ldh;
         const long long hz = (long long)B * ld, dz = (long long)B * H, oz = (long long)B * nout;
+        if (L.tc && L.fused_fwd && bw_img >= 0 && dx_cols <= 1) {
+            // input-gradient chain as ONE kernel; the three weight-gradient products beside / after it on the side streams
+            const bool par2 = want_dw && side != nullptr;
+            if (par2) { cudaEventRecord(ev[0], st); cudaStreamWaitEvent(side, ev[0], 0); }             // dOut is ready
+            if (want_dw) { branch = par2 ? 1 : 0; gemm(oH2, 1, ld, hz, oDOut, nout, 1, oz, oG + n.l2, nout, w_zs, H + 1, nout, B, Z, EPI_STORE); branch = 0; }
+            BwdTC f;
+            f.DOut = ws + oDOut; f.nout = nout; f.W = ws + oW; f.w_zs = w_zs; f.l0 = n.l0; f.l2 = n.l2;
+            f.w1p = reinterpret_cast<const unsigned char*>(ws + L.o_w1p) + (size_t)bw_img * H * H * 2; f.w1p_zs = (long long)H * H * 2;
+            f.H1 = ws + oH1; f.H2 = ws + oH2; f.hz = hz; f.ld = ld;
+            f.DH2 = want_dw ? ws + oDH2 : nullptr; f.DH1 = want_dw ? ws + oDH1 : nullptr;
+            f.DX = dx_cols > 0 ? ws + oDX : nullptr; f.dx_row = dx_first;
+            f.B = B; f.H = H; f.tmem_cols = 32;
+            while (f.tmem_cols < H) f.tmem_cols <<= 1;
+            mlp_bwd_tc_kernel<<<dim3((B + TCG_M - 1) / TCG_M, Z), 256, bwd_smem_bytes(H), st>>>(f);
+            if (want_dw) {
+                const bool two = par2 && side_b != nullptr;
+                if (par2) { cudaEventRecord(ev[1], st); cudaStreamWaitEvent(side, ev[1], 0); if (two) cudaStreamWaitEvent(side_b, ev[1], 0); }
+                branch = par2 ? 2 : 0;
+                gemm(oH1, 1, ld, hz, oDH2, H, 1, dz, oG + n.l1, H, w_zs, H + 1, H, B, Z, EPI_STORE);
+                branch = par2 ? 3 : 0;
+                gemm(oX, 1, kin + 1, 0, oDH1, H, 1, dz, oG + n.l0, H, w_zs, kin + 1, H, B, Z, EPI_STORE);
+                branch = 0;
+                if (two) { cudaEventRecord(ev_b[0], side_b); cudaStreamWaitEvent(st, ev_b[0], 0); }
+                if (par2) { cudaEventRecord(ev[3], side); cudaStreamWaitEvent(st, ev[3], 0); }
+            }
+            return;
+        }
         // The weight-gradient products (dW2, dW1, dW0) hang off the input-gradient chain dOut -> dH2 -> dH1 from the side: with a
         // side stream they run beside it (each waits for the one gradient it reads), which matters because every product of
         // the update leaves most of the GPU idle.  Without a side stream: in program order.
@@ -1003,12 +1185,12 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     const int B = L.B, H = L.H;
     const int eb = (B + 255) / 256;
     const bool par = st != nullptr && h->side != nullptr;   // branches on internal streams (all captured into the one graph)
-    const Launcher X{st, ws, L, par ? h->side : nullptr, h->ev, 0};
+    const Launcher X{st, ws, L, par ? h->side : nullptr, h->ev, 0, (par && L.tc && L.fused_fwd) ? h->side3 : nullptr, h->ev3};   // side_b only where the fused backward joins it
     const Launcher X2{par ? h->side2 : st, ws, L, nullptr, nullptr, 0};
     cudaStream_t s2 = X2.st;
     auto fork2 = [&](int e) { if (par) { cudaEventRecord(h->ev2[e], st); cudaStreamWaitEvent(s2, h->ev2[e], 0); } };
     auto join2 = [&](int e) { if (par) { cudaEventRecord(h->ev2[e], s2); cudaStreamWaitEvent(st, h->ev2[e], 0); } };
-    X.pack_w1(0, 5, st);       // weights as the caller left them (also after a load through sit_sac_field)
+    X.pack_w1(false, st);      // weights as the caller left them (also after a load through sit_sac_field)
     batch_kernel<<<eb, 256, 0, st>>>(ws, L, hp, replay, capacity, n_rows);
     // critics on (s, a): needs the batch only -> beside the target computation
     fork2(0);
@@ -1024,16 +1206,16 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     fork2(2);
     X2.forward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0);
     head_kernel<<<eb, 256, 0, s2>>>(ws, L, L.o_eps_cur, L.o_xspi, L.o_logp_cur);
-    X.backward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, true, L.o_grad + L.P_pol, 0, 0, 0);
+    X.backward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, true, L.o_grad + L.P_pol, 0, 0, 0, 6);
     adam_kernel<<<(unsigned)((2 * L.P_q + 255) / 256), 256, 0, st>>>(ws, L, hp, L.P_pol, 2 * L.P_q, L.o_qt - L.o_q, 1);
-    X.pack_w1(1, 2, st);       // the updated critics
+    X.pack_w1(true, st);       // the updated critics
     join2(3);
     // critics (updated) on (s, a~), d/da through the critics, policy backward, Adam
     X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
     policy_seed_kernel<<<1, 1024, 0, st>>>(ws, L);
-    X.backward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, false, 0, L.o_da, S, 1);
+    X.backward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, false, 0, L.o_da, S, 1, 6);
     policy_grad_kernel<<<eb, 256, 0, st>>>(ws, L);
-    X.backward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_dop, L.o_dhp2, L.o_dhp1, 1, true, L.o_grad, 0, 0, 0);
+    X.backward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_dop, L.o_dhp2, L.o_dhp1, 1, true, L.o_grad, 0, 0, 0, 5);
     adam_kernel<<<(unsigned)((L.P_pol + 255) / 256), 256, 0, st>>>(ws, L, hp, 0, L.P_pol, 0, 0);
     alpha_kernel<<<1, 32, 0, st>>>(ws, L, hp, losses);
     (void)H;
@@ -1055,9 +1237,10 @@ int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out) {
     if (device < 0 || device >= ndev) return fail(SIT_E_INVALID, "bad device index");
     SitSac_* h = new (std::nothrow) SitSac_();
     if (!h) return fail(SIT_E_INVALID, "out of memory");
-    h->cfg = *cfg; h->device = device; h->graph = nullptr; h->side = nullptr; h->side2 = nullptr;
+    h->cfg = *cfg; h->device = device; h->graph = nullptr; h->side = nullptr; h->side2 = nullptr; h->side3 = nullptr;
     for (auto& e : h->ev) e = nullptr;
     for (auto& e : h->ev2) e = nullptr;
+    for (auto& e : h->ev3) e = nullptr;
     // tensor cores from batch 1024 on: below that an update is 37 dependent few-microsecond launches and latency, not math,
     // is the cost (the SIMT products run at batch 64 in 220 us per update)
     const int tc = (cfg->tensor_cores && cfg->batch_size >= 1024 && cfg->hidden >= 128) ? 1 : 0;
@@ -1076,11 +1259,16 @@ int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out) {
         for (auto& e : h->ev) if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
         if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking);
         for (auto& e : h->ev2) if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&h->side3, cudaStreamNonBlocking);
+        for (auto& e : h->ev3) if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        if (ce == cudaSuccess && tc) ce = cudaFuncSetAttribute(sac::mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sac::bwd_smem_bytes(cfg->hidden));
         if (ce != cudaSuccess) {
             if (h->side) cudaStreamDestroy(h->side);
             if (h->side2) cudaStreamDestroy(h->side2);
+            if (h->side3) cudaStreamDestroy(h->side3);
             for (auto& e : h->ev) if (e) cudaEventDestroy(e);
             for (auto& e : h->ev2) if (e) cudaEventDestroy(e);
+            for (auto& e : h->ev3) if (e) cudaEventDestroy(e);
             delete h;
             return fail(SIT_E_CUDA, std::string("learner set-up: ") + cudaGetErrorString(ce));
         }
@@ -1094,8 +1282,10 @@ int sit_sac_destroy(SitSac h) {
     if (h->graph) cudaGraphExecDestroy(h->graph);
     if (h->side) cudaStreamDestroy(h->side);
     if (h->side2) cudaStreamDestroy(h->side2);
+    if (h->side3) cudaStreamDestroy(h->side3);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     for (auto& e : h->ev2) if (e) cudaEventDestroy(e);
+    for (auto& e : h->ev3) if (e) cudaEventDestroy(e);
     delete h;
     return SIT_OK;
 }
