@@ -452,6 +452,7 @@ struct FwdTC {
     long long l0, l1, l2;
     const unsigned char* w1p; long long w1p_zs;   // bf16 image of W1's H x H part, bytes
     float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld], outputs [Z][B][nout]
+    uint32_t *M1, *M2;                        // sign bits of h1, h2 for the fused backward: [Z][B][8 words] (4 per column half), or nullptr
     int B, H, ld, nout, tmem_cols;
 };
 // bf16 K-major images of the H x H part W1[k][n] of layer 1 (entry q: weights at ws + w_off[q], image number img[q] of H H 2
@@ -479,6 +480,16 @@ __global__ void __launch_bounds__(256) pack_w1_nets_kernel(const float* ws, unsi
         }
         *reinterpret_cast<uint4*>(dst + (size_t)(r >> 3) * sbo + (size_t)c * lbo + (r & 7) * 16) = v;
     }
+}
+
+// 128-bit row mask of one column half as four words: set / read `n` bits at bit offset `at` (n = 8 or 16, never across a word)
+__device__ __forceinline__ void mask_put(uint4& w, const int at, const uint32_t bits) {
+    const uint32_t v = bits << (at & 31);
+    if (at < 32) w.x |= v; else if (at < 64) w.y |= v; else if (at < 96) w.z |= v; else w.w |= v;
+}
+__device__ __forceinline__ uint32_t mask_get(const uint4& w, const int at) {
+    const uint32_t v = at < 32 ? w.x : (at < 64 ? w.y : (at < 96 ? w.z : w.w));
+    return v >> (at & 31);
 }
 
 __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
@@ -531,6 +542,7 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     for (int c = 0; c < 16; ++c) x[c] = (live && c < f.kin1) ? f.X[(long long)m * f.kin1 + c] : 0.f;
     const float* W0 = s_w0;
     float* h1 = f.H1 + (long long)z * f.hz + (long long)m * f.ld;
+    uint4 mk = make_uint4(0u, 0u, 0u, 0u);
     for (int k0 = half * kh; k0 < (half + 1) * kh; k0 += 8) {
         float a[8];
 #pragma unroll
@@ -544,8 +556,10 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
                 a[4] = fmaf(x[c], wb.x, a[4]); a[5] = fmaf(x[c], wb.y, a[5]); a[6] = fmaf(x[c], wb.z, a[6]); a[7] = fmaf(x[c], wb.w, a[7]);
             }
         }
+        uint32_t bits = 0u;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) a[j] = fmaxf(a[j], 0.f);
+        for (int j = 0; j < 8; ++j) { a[j] = fmaxf(a[j], 0.f); bits |= (a[j] > 0.f ? 1u : 0u) << j; }
+        mask_put(mk, k0 - half * kh, bits);
         if (live) {
             *reinterpret_cast<float4*>(h1 + k0) = make_float4(a[0], a[1], a[2], a[3]);
             *reinterpret_cast<float4*>(h1 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
@@ -554,6 +568,7 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
         v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
         *reinterpret_cast<uint4*>(sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16) = v;
     }
+    if (live && f.M1) *reinterpret_cast<uint4*>(f.M1 + ((long long)z * f.B + m) * 8 + half * 4) = mk;
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     // layer 1 on the tensor cores: D[128 x H] (TMEM, fp32) = A[128 x H] . B[H x H]
@@ -575,6 +590,7 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     // epilogue: h2 = relu(D + b1) -> HBM, output layer accumulated on the way
     float o0 = 0.f, o1 = 0.f;
     float* h2 = f.H2 + (long long)z * f.hz + (long long)m * f.ld;
+    mk = make_uint4(0u, 0u, 0u, 0u);
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     for (int c0 = half * kh; c0 < (half + 1) * kh; c0 += 16) {
         uint32_t r[16];
@@ -584,18 +600,22 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
                      : "r"(taddr + (uint32_t)c0));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         float hv[16];
+        uint32_t bits = 0u;
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             hv[j] = fmaxf(__uint_as_float(r[j]) + s_b1[c0 + j], 0.0f);
+            bits |= (hv[j] > 0.f ? 1u : 0u) << j;
             const float2 w = reinterpret_cast<const float2*>(s_w2)[c0 + j];
             o0 = fmaf(hv[j], w.x, o0);
             o1 = fmaf(hv[j], w.y, o1);
         }
+        mask_put(mk, c0 - half * kh, bits);
         if (live) {
 #pragma unroll
             for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(h2 + c0 + j) = make_float4(hv[j], hv[j + 1], hv[j + 2], hv[j + 3]);
         }
     }
+    if (live && f.M2) *reinterpret_cast<uint4*>(f.M2 + ((long long)z * f.B + m) * 8 + half * 4) = mk;
     if (half == 1) { s_part[2 * row] = o0; s_part[2 * row + 1] = o1; }
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
     __syncthreads();
@@ -617,7 +637,7 @@ struct BwdTC {
     const float* DOut; int nout;              // [Z][B][nout]
     const float* W; long long w_zs; long long l0, l2;
     const unsigned char* w1p; long long w1p_zs;   // by-k bf16 image of W1
-    const float *H1, *H2; long long hz; int ld;   // forward activations (masks) [Z][B][ld]
+    const uint32_t *M1, *M2;                  // sign bits of the forward activations h1, h2 (mlp_fwd_tc_kernel): [Z][B][8 words]
     float *DH2, *DH1;                         // [Z][B][H], nullptr: not stored (no weight gradients wanted)
     float* DX; int dx_row;                    // [Z][B] or nullptr; row of W0 (input column) the gradient is taken for
     int B, H, tmem_cols;
@@ -667,19 +687,18 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
     // layer 2: d h2 for this thread's row and column half
     const float* dout = f.DOut + (long long)z * f.B * f.nout + (long long)m * f.nout;
     const float d0 = live ? dout[0] : 0.f, d1 = (live && f.nout == 2) ? dout[1] : 0.f;
-    const float* h2 = f.H2 + (long long)z * f.hz + (long long)m * f.ld;
+    const uint4 mk2 = live ? *reinterpret_cast<const uint4*>(f.M2 + ((long long)z * f.B + m) * 8 + half * 4) : make_uint4(0u, 0u, 0u, 0u);
+    const uint4 mk1 = live ? *reinterpret_cast<const uint4*>(f.M1 + ((long long)z * f.B + m) * 8 + half * 4) : make_uint4(0u, 0u, 0u, 0u);
     float* dh2 = f.DH2 ? f.DH2 + ((long long)z * f.B + m) * H : nullptr;
     for (int k0 = half * kh; k0 < (half + 1) * kh; k0 += 8) {
-        float4 ma = make_float4(0.f, 0.f, 0.f, 0.f), mb = ma;
-        if (live) { ma = *reinterpret_cast<const float4*>(h2 + k0); mb = *reinterpret_cast<const float4*>(h2 + k0 + 4); }
-        const float hm[8] = {ma.x, ma.y, ma.z, ma.w, mb.x, mb.y, mb.z, mb.w};
+        const uint32_t bits = mask_get(mk2, k0 - half * kh);
         float a[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float2 w = reinterpret_cast<const float2*>(s_w2)[k0 + j];
             float acc = fmaf(d0, w.x, 0.f);
             if (f.nout == 2) acc = fmaf(d1, w.y, acc);
-            a[j] = hm[j] > 0.f ? acc : 0.f;
+            a[j] = (bits >> j & 1u) ? acc : 0.f;
         }
         if (live && dh2) {
             *reinterpret_cast<float4*>(dh2 + k0) = make_float4(a[0], a[1], a[2], a[3]);
@@ -709,7 +728,6 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::);
     // epilogue: d h1 = D masked by h1 > 0 -> HBM; d x accumulated on the way
     float dx = 0.f;
-    const float* h1 = f.H1 + (long long)z * f.hz + (long long)m * f.ld;
     float* dh1 = f.DH1 ? f.DH1 + ((long long)z * f.B + m) * H : nullptr;
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     for (int c0 = half * kh; c0 < (half + 1) * kh; c0 += 16) {
@@ -718,17 +736,12 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
                      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
                        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
                      : "r"(taddr + (uint32_t)c0));
-        float hm[16];
-#pragma unroll
-        for (int j = 0; j < 16; j += 4) {
-            const float4 q = live ? *reinterpret_cast<const float4*>(h1 + c0 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
-            hm[j] = q.x; hm[j + 1] = q.y; hm[j + 2] = q.z; hm[j + 3] = q.w;
-        }
+        const uint32_t bits = mask_get(mk1, c0 - half * kh);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         float g[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-            g[j] = hm[j] > 0.f ? __uint_as_float(r[j]) : 0.f;
+            g[j] = (bits >> j & 1u) ? __uint_as_float(r[j]) : 0.f;
             dx = fmaf(g[j], s_wx[c0 + j], dx);
         }
         if (live && dh1) {
@@ -754,7 +767,7 @@ struct Layout {
     long long o_xs, o_xs2, o_xsa, o_xs2a, o_xspi, o_r, o_mask;
     long long o_hp1, o_hp2, o_op, o_hq1, o_hq2, o_oq, o_oqt, o_hqt1, o_hqt2;   // hqt*: scratch activations of the target critics
     long long o_doq, o_dhq2, o_dhq1, o_da, o_dop, o_dhp2, o_dhp1;
-    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, o_w1p, total;
+    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, o_w1p, o_mhp, o_mhq, total;
     int tc;                             // large-batch products on tcgen05 (gemm_tc_kernel)
     int fused_fwd;                      // tc: a network's forward as ONE kernel (mlp_fwd_tc_kernel); SIT_SAC_FUSED_FWD=0 keeps the three products
     int ldh;                            // leading dimension of the hidden activations [B][ldh]: H weights' inputs + the ones
@@ -792,6 +805,8 @@ static void make_layout(Layout& L, int H, int B, int tc) {
     L.o_obs_scale = take(S);
     L.o_part = take(tc ? 3 * 2LL * TCG_MAX_SPLITS * (H + 1) * H : 0);   // split-k partial tiles [z][split][M][N], one region per concurrent weight-gradient product
     L.o_w1p = take(tc ? (long long)SAC_W1_IMAGES * H * H / 2 : 0);   // bf16 K-major images of W1 (pack_w1_nets_kernel)
+    L.o_mhp = take(tc ? 2LL * b * 8 : 0);        // sign bits of the policy's h1 | h2 (fused forward -> fused backward), 8 words per row
+    L.o_mhq = take(tc ? 2LL * 2 * b * 8 : 0);    // ... of the critics' h1 [2][B] | h2 [2][B]
     L.total = o;
 }
 
@@ -1095,6 +1110,9 @@ struct Launcher {
             f.X = ws + oX; f.kin1 = kin + 1; f.W = ws + oW; f.w_zs = w_zs; f.l0 = n.l0; f.l1 = n.l1; f.l2 = n.l2;
             f.w1p = reinterpret_cast<const unsigned char*>(ws + L.o_w1p) + (size_t)net_id * H * H * 2; f.w1p_zs = (long long)H * H * 2;
             f.H1 = ws + oH1; f.H2 = ws + oH2; f.Out = ws + oOut; f.hz = hz;
+            const long long om = oH1 == L.o_hp1 ? L.o_mhp : (oH1 == L.o_hq1 ? L.o_mhq : -1);      // the target critics have no backward
+            f.M1 = om >= 0 ? reinterpret_cast<uint32_t*>(ws + om) : nullptr;
+            f.M2 = om >= 0 ? f.M1 + (long long)Z * B * 8 : nullptr;
             f.B = B; f.H = H; f.ld = ld; f.nout = nout;
             f.tmem_cols = 32;
             while (f.tmem_cols < H) f.tmem_cols <<= 1;
@@ -1134,7 +1152,7 @@ struct Launcher {
             BwdTC f;
             f.DOut = ws + oDOut; f.nout = nout; f.W = ws + oW; f.w_zs = w_zs; f.l0 = n.l0; f.l2 = n.l2;
             f.w1p = reinterpret_cast<const unsigned char*>(ws + L.o_w1p) + (size_t)bw_img * H * H * 2; f.w1p_zs = (long long)H * H * 2;
-            f.H1 = ws + oH1; f.H2 = ws + oH2; f.hz = hz; f.ld = ld;
+            f.M1 = reinterpret_cast<const uint32_t*>(ws + (oH1 == L.o_hp1 ? L.o_mhp : L.o_mhq)); f.M2 = f.M1 + (long long)Z * B * 8;
             f.DH2 = want_dw ? ws + oDH2 : nullptr; f.DH1 = want_dw ? ws + oDH1 : nullptr;
             f.DX = dx_cols > 0 ? ws + oDX : nullptr; f.dx_row = dx_first;
             f.B = B; f.H = H; f.tmem_cols = 32;
