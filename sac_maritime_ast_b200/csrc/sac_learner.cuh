@@ -452,7 +452,7 @@ struct FwdTC {
     long long l0, l1, l2;
     const unsigned char* w1p; long long w1p_zs;   // bf16 image of W1's H x H part, bytes
     float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld], outputs [Z][B][nout]
-    uint32_t *M1, *M2;                        // sign bits of h1, h2 for the fused backward: [Z][B][8 words] (4 per column half), or nullptr
+    uint32_t *M1, *M2;                        // sign bits of h1, h2 for the fused backward: [Z][B][8 words], bit k of a row = word k >> 5, bit k & 31; or nullptr
     int B, H, ld, nout, tmem_cols;
 };
 // bf16 K-major images of the H x H part W1[k][n] of layer 1 (entry q: weights at ws + w_off[q], image number img[q] of H H 2
@@ -482,22 +482,35 @@ __global__ void __launch_bounds__(256) pack_w1_nets_kernel(const float* ws, unsi
     }
 }
 
-// 128-bit row mask of one column half as four words: set / read `n` bits at bit offset `at` (n = 8 or 16, never across a word)
-__device__ __forceinline__ void mask_put(uint4& w, const int at, const uint32_t bits) {
-    const uint32_t v = bits << (at & 31);
-    if (at < 32) w.x |= v; else if (at < 64) w.y |= v; else if (at < 96) w.z |= v; else w.w |= v;
+// Row masks: sign bits of a row's H activations as 8 words, bit k of the row = word k >> 5, bit k & 31.
+__device__ __forceinline__ uint32_t mask_word(const uint4& lo, const uint4& hi, const int word) {
+    return word < 4 ? (word < 2 ? (word == 0 ? lo.x : lo.y) : (word == 2 ? lo.z : lo.w))
+                    : (word < 6 ? (word == 4 ? hi.x : hi.y) : (word == 6 ? hi.z : hi.w));
 }
-__device__ __forceinline__ uint32_t mask_get(const uint4& w, const int at) {
-    const uint32_t v = at < 32 ? w.x : (at < 64 ? w.y : (at < 96 ? w.z : w.w));
-    return v >> (at & 31);
+// Epilogue stores: a thread owns one accumulator row (TMEM lane), so its 16 values of a chunk would go out as 16-byte pieces
+// of 32 different rows per instruction.  The warp transposes the chunk through a private [32][16] staging tile (row stride
+// 20 floats: conflict-free 128-bit accesses) and stores 8 rows x 64 contiguous bytes per instruction instead.
+#define FUSED_STG_STRIDE 20
+__device__ __forceinline__ void staged_store16(float* stg, const int lane, const float (&v)[16], float* gbase, const long long ld,
+                                               const int rows_left) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(stg + lane * FUSED_STG_STRIDE + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    __syncwarp();
+#pragma unroll
+    for (int pass = 0; pass < 4; ++pass) {
+        const int rr = pass * 8 + (lane >> 2), cc = (lane & 3) * 4;
+        const float4 q = *reinterpret_cast<const float4*>(stg + rr * FUSED_STG_STRIDE + cc);
+        if (rr < rows_left) *reinterpret_cast<float4*>(gbase + (long long)rr * ld + cc) = q;
+    }
+    __syncwarp();
 }
 
 __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     extern __shared__ __align__(128) unsigned char fw_smem[];
-    const int H = f.H, tid = threadIdx.x, warp = tid >> 5, z = blockIdx.y;
+    const int H = f.H, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, z = blockIdx.y;
     const int m0 = blockIdx.x * TCG_M;
     const float* W = f.W + (long long)z * f.w_zs;
-    unsigned char* sA = fw_smem;                                      // [128/8][H/8][8][8] bf16
+    unsigned char* sA = fw_smem;                                      // [128/8][H/8][8][8] bf16; after the MMAs: staging tiles
     unsigned char* sB = sA + (size_t)TCG_M * H * 2;                   // [H/8][H/8][8][8] bf16, rows = output unit
     float* s_w2 = reinterpret_cast<float*>(sB + (size_t)H * H * 2);   // [H + 1][2]
     float* s_b1 = s_w2 + 2 * (H + 1);                                 // [H]
@@ -520,6 +533,16 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"(smem_u32(sB)), "l"(f.w1p + (long long)z * f.w1p_zs), "r"(bytes), "r"(smem_u32(s_bar + 1)) : "memory");
     }
+    // layer 0 mapping: a warp owns 16 rows as two blocks of 8; lane = (row of the block, 8-column group of a 32-column
+    // step), so one instruction writes 8 rows x 128 contiguous bytes of h1 and 512 contiguous bytes of the A image
+    const int rsub = lane & 7, grp = lane >> 3;
+    float x[2][12];
+#pragma unroll
+    for (int rb = 0; rb < 2; ++rb) {
+        const int m = m0 + warp * 16 + rb * 8 + rsub;
+#pragma unroll
+        for (int c = 0; c < 12; ++c) x[rb][c] = (m < f.B && c < f.kin1) ? f.X[(long long)m * f.kin1 + c] : 0.f;
+    }
     for (int i = tid; i < (H + 1) * f.nout; i += 256) {
         const int k = i / f.nout, j = i % f.nout;
         s_w2[2 * k + j] = W[f.l2 + i];
@@ -532,43 +555,44 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::);
     const uint32_t tmem_base = *s_tmem;
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(H >> 3) << 17) | ((uint32_t)(TCG_M >> 4) << 24);
-    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H >> 1;
-    const int m = m0 + row;
-    const bool live = m < f.B;
 
-    // layer 0: relu(x . W0) for this thread's row and column half
-    float x[16];
+    // layer 0: relu(x . W0), fp32, ascending input index
 #pragma unroll
-    for (int c = 0; c < 16; ++c) x[c] = (live && c < f.kin1) ? f.X[(long long)m * f.kin1 + c] : 0.f;
-    const float* W0 = s_w0;
-    float* h1 = f.H1 + (long long)z * f.hz + (long long)m * f.ld;
-    uint4 mk = make_uint4(0u, 0u, 0u, 0u);
-    for (int k0 = half * kh; k0 < (half + 1) * kh; k0 += 8) {
-        float a[8];
+    for (int rb = 0; rb < 2; ++rb) {
+        const int row = warp * 16 + rb * 8 + rsub, m = m0 + row;
+        const bool live = m < f.B;
+        float* h1 = f.H1 + (long long)z * f.hz + (long long)m * f.ld;
+        for (int it = 0; it < (H >> 5); ++it) {
+            const int k0 = it * 32 + grp * 8;
+            float a[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) a[j] = 0.f;
+            for (int j = 0; j < 8; ++j) a[j] = 0.f;
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
-            if (c < f.kin1) {
-                const float4 wa = *reinterpret_cast<const float4*>(W0 + c * H + k0);
-                const float4 wb = *reinterpret_cast<const float4*>(W0 + c * H + k0 + 4);
-                a[0] = fmaf(x[c], wa.x, a[0]); a[1] = fmaf(x[c], wa.y, a[1]); a[2] = fmaf(x[c], wa.z, a[2]); a[3] = fmaf(x[c], wa.w, a[3]);
-                a[4] = fmaf(x[c], wb.x, a[4]); a[5] = fmaf(x[c], wb.y, a[5]); a[6] = fmaf(x[c], wb.z, a[6]); a[7] = fmaf(x[c], wb.w, a[7]);
+            for (int c = 0; c < 12; ++c) {
+                if (c < f.kin1) {
+                    const float4 wa = *reinterpret_cast<const float4*>(s_w0 + c * H + k0);
+                    const float4 wb = *reinterpret_cast<const float4*>(s_w0 + c * H + k0 + 4);
+                    const float xc = x[rb][c];
+                    a[0] = fmaf(xc, wa.x, a[0]); a[1] = fmaf(xc, wa.y, a[1]); a[2] = fmaf(xc, wa.z, a[2]); a[3] = fmaf(xc, wa.w, a[3]);
+                    a[4] = fmaf(xc, wb.x, a[4]); a[5] = fmaf(xc, wb.y, a[5]); a[6] = fmaf(xc, wb.z, a[6]); a[7] = fmaf(xc, wb.w, a[7]);
+                }
             }
-        }
-        uint32_t bits = 0u;
+            uint32_t bits = 0u;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { a[j] = fmaxf(a[j], 0.f); bits |= (a[j] > 0.f ? 1u : 0u) << j; }
-        mask_put(mk, k0 - half * kh, bits);
-        if (live) {
-            *reinterpret_cast<float4*>(h1 + k0) = make_float4(a[0], a[1], a[2], a[3]);
-            *reinterpret_cast<float4*>(h1 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
+            for (int j = 0; j < 8; ++j) { a[j] = fmaxf(a[j], 0.f); bits |= (a[j] > 0.f ? 1u : 0u) << j; }
+            bits <<= 8 * grp;                                          // the four column groups of a row make up mask word `it`
+            bits |= __shfl_xor_sync(0xffffffffu, bits, 8);
+            bits |= __shfl_xor_sync(0xffffffffu, bits, 16);
+            if (live) {
+                if (grp == 0 && f.M1) f.M1[((long long)z * f.B + m) * 8 + it] = bits;
+                *reinterpret_cast<float4*>(h1 + k0) = make_float4(a[0], a[1], a[2], a[3]);
+                *reinterpret_cast<float4*>(h1 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
+            }
+            uint4 v;
+            v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
+            *reinterpret_cast<uint4*>(sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16) = v;
         }
-        uint4 v;
-        v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
-        *reinterpret_cast<uint4*>(sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16) = v;
     }
-    if (live && f.M1) *reinterpret_cast<uint4*>(f.M1 + ((long long)z * f.B + m) * 8 + half * 4) = mk;
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     // layer 1 on the tensor cores: D[128 x H] (TMEM, fp32) = A[128 x H] . B[H x H]
@@ -587,10 +611,16 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     }
     mbar_wait(smem_u32(s_bar), 0u);
     asm volatile("tcgen05.fence::after_thread_sync;" ::);
-    // epilogue: h2 = relu(D + b1) -> HBM, output layer accumulated on the way
+    // epilogue: thread = accumulator row, the two thread halves take the two column halves; h2 = relu(D + b1) -> HBM through
+    // the warp's staging tile (the A image is dead), output layer accumulated on the way
+    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H >> 1;
+    const int m = m0 + row;
+    const bool live = m < f.B;
+    float* stg = reinterpret_cast<float*>(sA) + warp * 32 * FUSED_STG_STRIDE;
+    const int wrow0 = m0 + (warp & 3) * 32;                            // first row of this warp's 32
+    float* h2w = f.H2 + (long long)z * f.hz + (long long)wrow0 * f.ld;
     float o0 = 0.f, o1 = 0.f;
-    float* h2 = f.H2 + (long long)z * f.hz + (long long)m * f.ld;
-    mk = make_uint4(0u, 0u, 0u, 0u);
+    uint32_t mword = 0u;
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     for (int c0 = half * kh; c0 < (half + 1) * kh; c0 += 16) {
         uint32_t r[16];
@@ -609,13 +639,11 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
             o0 = fmaf(hv[j], w.x, o0);
             o1 = fmaf(hv[j], w.y, o1);
         }
-        mask_put(mk, c0 - half * kh, bits);
-        if (live) {
-#pragma unroll
-            for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(h2 + c0 + j) = make_float4(hv[j], hv[j + 1], hv[j + 2], hv[j + 3]);
-        }
+        mword |= bits << (c0 & 31);                                    // kh is a multiple of 32: a word belongs to one half
+        if ((c0 & 16) && live && f.M2) { f.M2[((long long)z * f.B + m) * 8 + (c0 >> 5)] = mword; }
+        if (c0 & 16) mword = 0u;
+        staged_store16(stg, lane, hv, h2w + c0, f.ld, f.B - wrow0);
     }
-    if (live && f.M2) *reinterpret_cast<uint4*>(f.M2 + ((long long)z * f.B + m) * 8 + half * 4) = mk;
     if (half == 1) { s_part[2 * row] = o0; s_part[2 * row + 1] = o1; }
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
     __syncthreads();
@@ -644,10 +672,10 @@ struct BwdTC {
 };
 __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
     extern __shared__ __align__(128) unsigned char bw_smem[];
-    const int H = f.H, tid = threadIdx.x, warp = tid >> 5, z = blockIdx.y;
+    const int H = f.H, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, z = blockIdx.y;
     const int m0 = blockIdx.x * TCG_M;
     const float* W = f.W + (long long)z * f.w_zs;
-    unsigned char* sA = bw_smem;
+    unsigned char* sA = bw_smem;                                      // A image; after the MMAs: staging tiles
     unsigned char* sB = sA + (size_t)TCG_M * H * 2;
     float* s_w2 = reinterpret_cast<float*>(sB + (size_t)H * H * 2);   // [H][2]
     float* s_wx = s_w2 + 2 * H;                                       // [H]: row dx_row of W0
@@ -669,6 +697,30 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"(smem_u32(sB)), "l"(f.w1p + (long long)z * f.w1p_zs), "r"(bytes), "r"(smem_u32(s_bar + 1)) : "memory");
     }
+    // layer 2 mapping as in the forward kernel: lane = (row of an 8-row block, 8-column group of a 32-column step)
+    const int rsub = lane & 7, grp = lane >> 3;
+    float d0[2], d1[2];
+    uint4 mlo[2], mhi[2];
+#pragma unroll
+    for (int rb = 0; rb < 2; ++rb) {
+        const int m = m0 + warp * 16 + rb * 8 + rsub;
+        const bool lv = m < f.B;
+        const float* dout = f.DOut + (long long)z * f.B * f.nout + (long long)m * f.nout;
+        d0[rb] = lv ? dout[0] : 0.f;
+        d1[rb] = (lv && f.nout == 2) ? dout[1] : 0.f;
+        const uint4* mp = reinterpret_cast<const uint4*>(f.M2 + ((long long)z * f.B + m) * 8);
+        mlo[rb] = lv ? mp[0] : make_uint4(0u, 0u, 0u, 0u);
+        mhi[rb] = lv ? mp[1] : make_uint4(0u, 0u, 0u, 0u);
+    }
+    // epilogue mask (h1 > 0) of this thread's accumulator row
+    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H >> 1;
+    const int m = m0 + row;
+    const bool live = m < f.B;
+    uint4 m1lo = make_uint4(0u, 0u, 0u, 0u), m1hi = m1lo;
+    if (live) {
+        const uint4* mp = reinterpret_cast<const uint4*>(f.M1 + ((long long)z * f.B + m) * 8);
+        m1lo = mp[0]; m1hi = mp[1];
+    }
     for (int i = tid; i < H * f.nout; i += 256) {
         const int k = i / f.nout, j = i % f.nout;
         s_w2[2 * k + j] = W[f.l2 + i];
@@ -680,33 +732,31 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::);
     const uint32_t tmem_base = *s_tmem;
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(H >> 3) << 17) | ((uint32_t)(TCG_M >> 4) << 24);
-    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H >> 1;
-    const int m = m0 + row;
-    const bool live = m < f.B;
 
-    // layer 2: d h2 for this thread's row and column half
-    const float* dout = f.DOut + (long long)z * f.B * f.nout + (long long)m * f.nout;
-    const float d0 = live ? dout[0] : 0.f, d1 = (live && f.nout == 2) ? dout[1] : 0.f;
-    const uint4 mk2 = live ? *reinterpret_cast<const uint4*>(f.M2 + ((long long)z * f.B + m) * 8 + half * 4) : make_uint4(0u, 0u, 0u, 0u);
-    const uint4 mk1 = live ? *reinterpret_cast<const uint4*>(f.M1 + ((long long)z * f.B + m) * 8 + half * 4) : make_uint4(0u, 0u, 0u, 0u);
-    float* dh2 = f.DH2 ? f.DH2 + ((long long)z * f.B + m) * H : nullptr;
-    for (int k0 = half * kh; k0 < (half + 1) * kh; k0 += 8) {
-        const uint32_t bits = mask_get(mk2, k0 - half * kh);
-        float a[8];
+    // layer 2: d h2 = (d out . W2^T) where h2 > 0
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float2 w = reinterpret_cast<const float2*>(s_w2)[k0 + j];
-            float acc = fmaf(d0, w.x, 0.f);
-            if (f.nout == 2) acc = fmaf(d1, w.y, acc);
-            a[j] = (bits >> j & 1u) ? acc : 0.f;
+    for (int rb = 0; rb < 2; ++rb) {
+        const int r2 = warp * 16 + rb * 8 + rsub, m2 = m0 + r2;
+        float* dh2 = f.DH2 ? f.DH2 + ((long long)z * f.B + m2) * H : nullptr;
+        for (int it = 0; it < (H >> 5); ++it) {
+            const int k0 = it * 32 + grp * 8;
+            const uint32_t bits = mask_word(mlo[rb], mhi[rb], it) >> (8 * grp);
+            float a[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float2 w = reinterpret_cast<const float2*>(s_w2)[k0 + j];
+                float acc = fmaf(d0[rb], w.x, 0.f);
+                if (f.nout == 2) acc = fmaf(d1[rb], w.y, acc);
+                a[j] = (bits >> j & 1u) ? acc : 0.f;
+            }
+            if (m2 < f.B && dh2) {
+                *reinterpret_cast<float4*>(dh2 + k0) = make_float4(a[0], a[1], a[2], a[3]);
+                *reinterpret_cast<float4*>(dh2 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
+            }
+            uint4 v;
+            v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
+            *reinterpret_cast<uint4*>(sA + (size_t)(r2 >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (r2 & 7) * 16) = v;
         }
-        if (live && dh2) {
-            *reinterpret_cast<float4*>(dh2 + k0) = make_float4(a[0], a[1], a[2], a[3]);
-            *reinterpret_cast<float4*>(dh2 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
-        }
-        uint4 v;
-        v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
-        *reinterpret_cast<uint4*>(sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16) = v;
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
@@ -726,9 +776,11 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
     }
     mbar_wait(smem_u32(s_bar), 0u);
     asm volatile("tcgen05.fence::after_thread_sync;" ::);
-    // epilogue: d h1 = D masked by h1 > 0 -> HBM; d x accumulated on the way
+    // epilogue: d h1 = D where h1 > 0 -> HBM through the warp's staging tile; d x accumulated on the way
     float dx = 0.f;
-    float* dh1 = f.DH1 ? f.DH1 + ((long long)z * f.B + m) * H : nullptr;
+    float* stg = reinterpret_cast<float*>(sA) + warp * 32 * FUSED_STG_STRIDE;
+    const int wrow0 = m0 + (warp & 3) * 32;
+    float* dh1w = f.DH1 ? f.DH1 + ((long long)z * f.B + wrow0) * H : nullptr;
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     for (int c0 = half * kh; c0 < (half + 1) * kh; c0 += 16) {
         uint32_t r[16];
@@ -736,7 +788,7 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
                      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
                        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
                      : "r"(taddr + (uint32_t)c0));
-        const uint32_t bits = mask_get(mk1, c0 - half * kh);
+        const uint32_t bits = mask_word(m1lo, m1hi, c0 >> 5) >> (c0 & 31);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         float g[16];
 #pragma unroll
@@ -744,10 +796,7 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
             g[j] = (bits >> j & 1u) ? __uint_as_float(r[j]) : 0.f;
             dx = fmaf(g[j], s_wx[c0 + j], dx);
         }
-        if (live && dh1) {
-#pragma unroll
-            for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(dh1 + c0 + j) = make_float4(g[j], g[j + 1], g[j + 2], g[j + 3]);
-        }
+        if (dh1w) staged_store16(stg, lane, g, dh1w + c0, H, f.B - wrow0);
     }
     if (half == 1) s_part[row] = dx;
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
@@ -777,7 +826,7 @@ struct Layout {
 
 static void make_layout(Layout& L, int H, int B, int tc) {
     L.H = H; L.B = B; L.tc = tc; L.ldh = tc ? H + 4 : H + 1;
-    L.fused_fwd = tc && H % 16 == 0;
+    L.fused_fwd = tc && H % 64 == 0;         // column halves of whole 32-bit mask words
     if (const char* e = std::getenv("SIT_SAC_FUSED_FWD")) if (std::atoi(e) == 0) L.fused_fwd = 0;
     L.pol.l0 = 0; L.pol.l1 = (long long)(S + 1) * H; L.pol.l2 = L.pol.l1 + (long long)(H + 1) * H;
     L.P_pol = L.pol.l2 + (long long)(H + 1) * 2;
