@@ -1016,8 +1016,11 @@ __global__ void policy_grad_kernel(float* ws, const Layout L) {
 
 // Adam step (torch.optim.Adam defaults, main_ast.py:51 lr) on a parameter range, optional fused soft target update
 // target <- (1 - tau) target + tau param (main_ast.py:43-44,84)
+// pack_images != 0 (the critics' step on the fused tensor-core path): the new W1 entries also go, as bf16, into the forward
+// and by-k images of q1 / q2 (images 1, 2 and 6, 7 of pack_w1_nets_kernel: same rounding, same positions), so the forward
+// that follows needs no pack launch
 __global__ void adam_kernel(float* ws, const Layout L, const Hyper hp, long long first, long long count, long long target_delta,
-                            int soft) {
+                            int soft, int pack_images = 0) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
     const unsigned long long upd = *reinterpret_cast<const unsigned long long*>(ws + L.o_updates);
@@ -1030,6 +1033,19 @@ __global__ void adam_kernel(float* ws, const Layout L, const Hyper hp, long long
     ws[L.o_m + j] = m; ws[L.o_v + j] = v;
     const float p = ws[L.o_pol + j] - (hp.lr / bc1) * m / (sqrtf(v) / sqrtf(bc2) + ADAM_EPS);
     ws[L.o_pol + j] = p;
+    if (pack_images) {
+        const int H = L.H;
+        const long long net = i / L.P_q, e = i % L.P_q - L.q.l1;
+        if (e >= 0 && e < (long long)H * H) {
+            const int k = (int)(e / H), n = (int)(e % H);
+            unsigned short hb;
+            asm("cvt.rn.bf16.f32 %0, %1;" : "=h"(hb) : "f"(p));
+            unsigned char* img = reinterpret_cast<unsigned char*>(ws + L.o_w1p);
+            const size_t sbo = 16u * (size_t)H, lbo = 128u, isz = (size_t)H * H * 2;
+            *reinterpret_cast<unsigned short*>(img + (1 + net) * isz + (size_t)(n >> 3) * sbo + (size_t)(k >> 3) * lbo + (n & 7) * 16 + (k & 7) * 2) = hb;
+            *reinterpret_cast<unsigned short*>(img + (6 + net) * isz + (size_t)(k >> 3) * sbo + (size_t)(n >> 3) * lbo + (k & 7) * 16 + (n & 7) * 2) = hb;
+        }
+    }
     if (soft && (upd % (unsigned long long)hp.target_interval) == 0) {
         const long long k = L.o_pol + j + target_delta;
         ws[k] = fmaf(hp.tau, p - ws[k], ws[k]);
@@ -1082,7 +1098,7 @@ struct SitSac_ {
     // critics' backward + Adam (independent until the joins below)
     cudaStream_t side2; cudaEvent_t ev2[4];
     // fourth: layer 0's weight-gradient product beside layer 1's (fused backward)
-    cudaStream_t side3; cudaEvent_t ev3[2];
+    cudaStream_t side3; cudaEvent_t ev3[4];     // [2], [3]: the W1 images of an update packed beside its batch kernel
 };
 
 namespace sac {
@@ -1122,6 +1138,10 @@ struct Launcher {
             t.tmem_cols = t.bn < 32 ? 32 : t.bn;
             const int n_chunks = (K + TCG_KC - 1) / TCG_KC;
             int splits = K >= 1024 ? std::min(TCG_MAX_SPLITS, std::max(1, n_chunks / 4)) : 1;
+            {   // no more CTAs than one wave of two per SM: the second wave of a weight-gradient product cost as much as the first
+                const long long tiles = (long long)((N + 63) / 64) * ((M + TCG_M - 1) / TCG_M) * Z;
+                if (splits > 1 && tiles * splits > 296) splits = (int)std::max<long long>(1, 296 / tiles);
+            }
             const int per = (n_chunks + splits - 1) / splits;
             splits = (n_chunks + per - 1) / per;                       // no empty split
             if ((long long)Z * splits * M * N > 2LL * TCG_MAX_SPLITS * (L.H + 1) * L.H) splits = 1;
@@ -1172,14 +1192,14 @@ struct Launcher {
         gemm(oH1, ld, 1, hz, oW + n.l1, H, 1, w_zs, oH2, ld, hz, B, H, H + 1, Z, EPI_RELU);
         gemm(oH2, ld, 1, hz, oW + n.l2, nout, 1, w_zs, oOut, nout, (long long)B * nout, B, nout, H + 1, Z, EPI_STORE);
     }
-    // bf16 images of W1 for the fused forward / backward kernels: all eight, or (critics_only) the four of q1, q2
-    void pack_w1(bool critics_only, cudaStream_t on) const {
+    // all eight bf16 images of W1 for the fused forward / backward kernels (the critics' step of adam_kernel refreshes q1 / q2's)
+    void pack_w1(cudaStream_t on) const {
         if (!(L.tc && L.fused_fwd)) return;
         const long long off[5] = {L.o_pol + L.pol.l1, L.o_q + L.q.l1, L.o_q + L.P_q + L.q.l1, L.o_qt + L.q.l1, L.o_qt + L.P_q + L.q.l1};
         PackNets pn;
         int n = 0;
         auto add = [&](int net, int img, int by_k) { pn.w_off[n] = off[net]; pn.img[n] = img; pn.by_k[n] = by_k; ++n; };
-        if (!critics_only) { add(0, 0, 0); add(3, 3, 0); add(4, 4, 0); add(0, 5, 1); }
+        add(0, 0, 0); add(3, 3, 0); add(4, 4, 0); add(0, 5, 1);
         add(1, 1, 0); add(2, 2, 0); add(1, 6, 1); add(2, 7, 1);
         for (int q = n; q < SAC_W1_IMAGES; ++q) { pn.w_off[q] = 0; pn.img[q] = 0; pn.by_k[q] = 0; }
         const int H = L.H;
@@ -1257,8 +1277,13 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     cudaStream_t s2 = X2.st;
     auto fork2 = [&](int e) { if (par) { cudaEventRecord(h->ev2[e], st); cudaStreamWaitEvent(s2, h->ev2[e], 0); } };
     auto join2 = [&](int e) { if (par) { cudaEventRecord(h->ev2[e], s2); cudaStreamWaitEvent(st, h->ev2[e], 0); } };
-    X.pack_w1(false, st);      // weights as the caller left them (also after a load through sit_sac_field)
-    batch_kernel<<<eb, 256, 0, st>>>(ws, L, hp, replay, capacity, n_rows);
+    // bf16 images of W1 from the weights as the caller left them (also after a load through sit_sac_field), beside the batch kernel
+    if (par) { cudaEventRecord(h->ev3[2], st); cudaStreamWaitEvent(s2, h->ev3[2], 0); }
+    X.pack_w1(s2);
+    if (par) cudaEventRecord(h->ev3[3], s2);
+    const int bt = L.tc ? 64 : 256;    // large batches: more, smaller CTAs (a row costs one dependent gather)
+    batch_kernel<<<(B + bt - 1) / bt, bt, 0, st>>>(ws, L, hp, replay, capacity, n_rows);
+    if (par) cudaStreamWaitEvent(st, h->ev3[3], 0);
     // critics on (s, a): needs the batch only -> beside the target computation
     fork2(0);
     X2.forward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
@@ -1274,8 +1299,7 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     X2.forward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0);
     head_kernel<<<eb, 256, 0, s2>>>(ws, L, L.o_eps_cur, L.o_xspi, L.o_logp_cur);
     X.backward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, true, L.o_grad + L.P_pol, 0, 0, 0, 6);
-    adam_kernel<<<(unsigned)((2 * L.P_q + 255) / 256), 256, 0, st>>>(ws, L, hp, L.P_pol, 2 * L.P_q, L.o_qt - L.o_q, 1);
-    X.pack_w1(true, st);       // the updated critics
+    adam_kernel<<<(unsigned)((2 * L.P_q + 255) / 256), 256, 0, st>>>(ws, L, hp, L.P_pol, 2 * L.P_q, L.o_qt - L.o_q, 1, (L.tc && L.fused_fwd) ? 1 : 0);   // + the updated critics' W1 images
     join2(3);
     // critics (updated) on (s, a~), d/da through the critics, policy backward, Adam
     X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
