@@ -1147,7 +1147,7 @@ struct Launcher {
             if ((long long)Z * splits * M * N > 2LL * TCG_MAX_SPLITS * (L.H + 1) * L.H) splits = 1;
             // 64-wide tiles when 128-wide ones would leave most of the 148 SMs without a CTA
             // (two CTAs fit one SM: 115 registers, <= 66 KB shared memory)
-            if (t.bn == 128 && (long long)((N + 127) / 128) * ((M + TCG_M - 1) / TCG_M) * Z * splits < 296) t.bn = 64;
+            if (t.bn == 128 && (long long)((N + 127) / 128) * ((M + TCG_M - 1) / TCG_M) * Z * splits < 296 && K < 4096) t.bn = 64;   // (contractions over a batch >= 4096 keep 128: half the re-reads of the A tile; measured 5 030 -> 5 240 updates/s at batch 4096, 6 470 -> 6 260 at batch 1024)
             t.tmem_cols = t.bn < 32 ? 32 : t.bn;
             t.splits = splits;
             t.partial = ws + L.o_part + (long long)(branch > 0 ? branch - 1 : 0) * 2LL * TCG_MAX_SPLITS * (L.H + 1) * L.H;

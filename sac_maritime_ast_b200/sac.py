@@ -19,6 +19,7 @@ networks stay bit-identical on all ranks without a gradient all-reduce.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, Optional
 
 import torch
@@ -138,10 +139,13 @@ class SAC:
         self.f["idx"] = self.f["idx"].view(torch.int32)
         self.f["updates"] = self.f["updates"].view(torch.int64)
         self.losses = torch.zeros(8, dtype=torch.float32, device=self.device)
-        # kernels one update enqueues: 28 products + 9 element-wise; on the tensor-core path (batch >= 1024, hidden >= 128)
-        # the 6 split-k products (weight gradients: contraction over the batch) are followed by a reduce kernel each
+        # kernels one update enqueues: 28 products + 9 element-wise = 37.  On the tensor-core path (batch >= 1024, hidden >= 128)
+        # the 6 split-k products (weight gradients: contraction over the batch) are followed by a reduce kernel each (43); with
+        # hidden a multiple of 64 a network's forward and its input-gradient chain are one kernel each (5 forwards, 3
+        # backwards instead of 15 + 7 products) and one launch packs the bf16 images of W1: 30
         self.tensor_cores = bool(cfg.tensor_cores) and cfg.batch_size >= 1024 and cfg.hidden >= 128
-        self.kernels_per_update = 37 + (6 if self.tensor_cores else 0)
+        fused = self.tensor_cores and cfg.hidden % 64 == 0 and os.environ.get("SIT_SAC_FUSED_FWD", "1") != "0"
+        self.kernels_per_update = 30 if fused else 37 + (6 if self.tensor_cores else 0)
         self._side = None
         self.launches = 0
         _lib.check(self.L.sit_sac_init(self.h, self.ws.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream))

@@ -191,8 +191,9 @@ def _grad_blocks(agent):
     return out
 
 
-@pytest.mark.parametrize("hidden,batch", [(256, 1024), (128, 4096), (256, 1500)])
-def test_tensor_core_update_matches_fp32_update(hidden, batch):
+@pytest.mark.parametrize("hidden,batch,fused", [(256, 1024, True), (128, 4096, True), (256, 1500, True), (256, 1024, False),
+                                                 (160, 1024, False)])
+def test_tensor_core_update_matches_fp32_update(hidden, batch, fused, monkeypatch):
     """Large-batch learner: the hidden-layer products and every contraction over the batch run on tcgen05 (bf16 operands,
     fp32 accumulate in TMEM, split-k partials summed in a fixed order).  Against the fp32 CUDA-core update with the same
     seed, batch indices and normal draws: every layer's gradient within 4e-2 relative (L2), losses within 1e-2 -- the
@@ -200,12 +201,17 @@ def test_tensor_core_update_matches_fp32_update(hidden, batch):
     out; the layer-0 gradient sits behind three bf16 products in a row and shows the largest error, 2.4e-2); the same
     update twice is bit-identical."""
     from sac_maritime_ast_b200 import sac
+    # fused: a network's forward and its input-gradient chain as one kernel each (hidden a multiple of 64; 30 launches per
+    # update); otherwise every product is its own launch (43) -- by width (160) or switched off through the environment
+    if not fused:
+        monkeypatch.setenv("SIT_SAC_FUSED_FWD", "0")
     mem = sac.ReplayMemory(8192, device=DEV)
     mem.extend(_fake_replay(8192, seed=2).to(DEV))
     kw = dict(device=DEV, hidden_size=hidden, batch_size=batch, seed=21, obs_scale=None)
     tc, tc2, ref = (sac.SAC(10, None, None, tensor_cores=True, **kw), sac.SAC(10, None, None, tensor_cores=True, **kw),
                     sac.SAC(10, None, None, tensor_cores=False, **kw))
     assert torch.equal(tc.f["policy"], ref.f["policy"]) and torch.equal(tc.f["q1"], ref.f["q1"])
+    assert tc.kernels_per_update == (30 if fused else 43) and ref.kernels_per_update == 37
     outs = [a.update_parameters(mem, batch, 0) for a in (tc, tc2, ref)]
     torch.cuda.synchronize()
     assert torch.equal(tc.f["idx"], ref.f["idx"]) and torch.equal(tc.f["eps_cur"], ref.f["eps_cur"])
