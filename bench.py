@@ -792,11 +792,12 @@ def learner_leg(sit, dev, sampler, batch=64, hidden=256, n=400, warm=50):
         res = {"updates_per_s": n / (ms * 1e-3), "us_per_update": ms * 1e3 / n, "samples_per_s": n * b / (ms * 1e-3),
                "approx_tflops": flop * n / (ms * 1e-3) / 1e12, "kernels_per_update": agent.kernels_per_update,
                "products": "tcgen05 bf16 x bf16 -> fp32 (TMEM): fused forward / input-gradient kernels per network, split-k weight gradients"
-                           if (tc and b >= 1024) else "fp32 CUDA cores",
+                           if ((tc and b >= 1024) or tc == 2) else "fp32 CUDA cores",
                "losses_finite": bool(torch.isfinite(ls).all()), "alpha": float(ls[4])}
         agent.close()
         return res
     out[f"batch_{batch}"] = run(batch, True)
+    out[f"batch_{batch}_tc"] = run(batch, 2)          # opt-in: the tensor-core path at the reference's batch size
     out["batch_1024"] = run(1024, True)
     out["batch_4096"] = run(4096, True)
     out["batch_4096_fp32_only"] = run(4096, False)

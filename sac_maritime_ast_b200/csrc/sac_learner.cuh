@@ -1334,7 +1334,7 @@ int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out) {
     for (auto& e : h->ev3) e = nullptr;
     // tensor cores from batch 1024 on: below that an update is 37 dependent few-microsecond launches and latency, not math,
     // is the cost (the SIMT products run at batch 64 in 220 us per update)
-    const int tc = (cfg->tensor_cores && cfg->batch_size >= 1024 && cfg->hidden >= 128) ? 1 : 0;
+    const int tc = (cfg->tensor_cores && (cfg->batch_size >= 1024 || cfg->tensor_cores >= 2) && cfg->hidden >= 128) ? 1 : 0;
     sac::make_layout(h->L, cfg->hidden, cfg->batch_size, tc);
     h->hp.gamma = cfg->gamma; h->hp.tau = cfg->tau; h->hp.lr = cfg->lr; h->hp.alpha0 = cfg->alpha;
     h->hp.auto_alpha = cfg->automatic_entropy_tuning ? 1 : 0; h->hp.target_interval = cfg->target_update_interval;

@@ -123,7 +123,8 @@ class SAC:
             obs_scale = default_obs_scale()
         for c in range(_lib.N_OBS):
             cfg.obs_scale[c] = 1.0 if obs_scale is None else float(obs_scale[c])
-        cfg.tensor_cores = int(bool(arg("tensor_cores", True)))
+        tcv = arg("tensor_cores", True)
+        cfg.tensor_cores = 2 if (tcv == 2 and tcv is not True) else int(bool(tcv))   # 2: also below batch 1024
         self.cfg, self.hidden, self.batch_size, self.use_graph = cfg, cfg.hidden, cfg.batch_size, bool(use_graph)
         self.h = C.c_void_p()
         idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
@@ -143,9 +144,10 @@ class SAC:
         # the 6 split-k products (weight gradients: contraction over the batch) are followed by a reduce kernel each (43); with
         # hidden a multiple of 64 a network's forward and its input-gradient chain are one kernel each (5 forwards, 3
         # backwards instead of 15 + 7 products) and one launch packs the bf16 images of W1: 30
-        self.tensor_cores = bool(cfg.tensor_cores) and cfg.batch_size >= 1024 and cfg.hidden >= 128
+        self.tensor_cores = bool(cfg.tensor_cores) and (cfg.batch_size >= 1024 or cfg.tensor_cores >= 2) and cfg.hidden >= 128
         fused = self.tensor_cores and cfg.hidden % 64 == 0 and os.environ.get("SIT_SAC_FUSED_FWD", "1") != "0"
-        self.kernels_per_update = 30 if fused else 37 + (6 if self.tensor_cores else 0)
+        splitk = 6 if (self.tensor_cores and cfg.batch_size >= 1024) else 0          # reduce kernels of the split-k weight gradients
+        self.kernels_per_update = (24 if fused else 37) + splitk
         self._side = None
         self.launches = 0
         _lib.check(self.L.sit_sac_init(self.h, self.ws.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream))

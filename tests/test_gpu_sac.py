@@ -192,7 +192,7 @@ def _grad_blocks(agent):
 
 
 @pytest.mark.parametrize("hidden,batch,fused", [(256, 1024, True), (128, 4096, True), (256, 1500, True), (256, 1024, False),
-                                                 (160, 1024, False)])
+                                                 (160, 1024, False), (256, 64, True), (128, 300, True), (256, 200, False)])
 def test_tensor_core_update_matches_fp32_update(hidden, batch, fused, monkeypatch):
     """Large-batch learner: the hidden-layer products and every contraction over the batch run on tcgen05 (bf16 operands,
     fp32 accumulate in TMEM, split-k partials summed in a fixed order).  Against the fp32 CUDA-core update with the same
@@ -208,10 +208,11 @@ def test_tensor_core_update_matches_fp32_update(hidden, batch, fused, monkeypatc
     mem = sac.ReplayMemory(8192, device=DEV)
     mem.extend(_fake_replay(8192, seed=2).to(DEV))
     kw = dict(device=DEV, hidden_size=hidden, batch_size=batch, seed=21, obs_scale=None)
-    tc, tc2, ref = (sac.SAC(10, None, None, tensor_cores=True, **kw), sac.SAC(10, None, None, tensor_cores=True, **kw),
+    want = True if batch >= 1024 else 2          # 2: the tensor-core path below batch 1024 too (opt-in)
+    tc, tc2, ref = (sac.SAC(10, None, None, tensor_cores=want, **kw), sac.SAC(10, None, None, tensor_cores=want, **kw),
                     sac.SAC(10, None, None, tensor_cores=False, **kw))
     assert torch.equal(tc.f["policy"], ref.f["policy"]) and torch.equal(tc.f["q1"], ref.f["q1"])
-    assert tc.kernels_per_update == (30 if fused else 43) and ref.kernels_per_update == 37
+    assert tc.kernels_per_update == (24 if fused else 37) + (6 if batch >= 1024 else 0) and ref.kernels_per_update == 37
     outs = [a.update_parameters(mem, batch, 0) for a in (tc, tc2, ref)]
     torch.cuda.synchronize()
     assert torch.equal(tc.f["idx"], ref.f["idx"]) and torch.equal(tc.f["eps_cur"], ref.f["eps_cur"])
@@ -220,7 +221,8 @@ def test_tensor_core_update_matches_fp32_update(hidden, batch, fused, monkeypatc
     gt, gr = _grad_blocks(tc), _grad_blocks(ref)
     for name in gr:
         rel = float((gt[name] - gr[name]).norm() / (gr[name].norm() + 1e-12))
-        assert rel <= 4e-2, (name, rel)
+        # (below batch 1024 the opt-in path sums the bf16 rounding over fewer rows: 5.3e-2 measured for q1.l0 at batch 300)
+        assert rel <= (4e-2 if batch >= 1024 else 8e-2), (name, rel)
         assert float(gr[name].norm()) > 0
     for a in (tc, tc2, ref):
         a.update(mem, 6)
