@@ -16,7 +16,8 @@
  *     scratch of sit_rollout_policy / sit_rollout_collect (compact env list, MLP inputs / outputs,
  *     the packed bf16 W1 image: ~60 B per env + 128 KiB, first rollout call; cudaMalloc is a
  *     device-wide synchronisation, so that FIRST call is not "enqueue only").  sit_rollout_collect
- *     runs one eager iteration before it captures its CUDA graph for exactly this reason;
+ *     runs plain launches (one iteration, or with several env groups its whole first call) before it
+ *     captures its CUDA graph for exactly this reason;
  *   - the *_host entry points take HOST buffers, copy in, run, copy out and synchronise;
  *   - there is no CPU fallback: without a CUDA device every compute entry point fails.
  */
