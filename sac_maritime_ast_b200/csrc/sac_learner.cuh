@@ -454,6 +454,9 @@ struct FwdTC {
     float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld], outputs [Z][B][nout]
     uint32_t *M1, *M2;                        // sign bits of h1, h2 for the fused backward: [Z][B][8 words], bit k of a row = word k >> 5, bit k & 31; or nullptr
     int B, H, ld, nout, tmem_cols;
+    // policy only (nullptr otherwise): the tanh-Gaussian head of head_kernel in the epilogue -- a = tanh(mu + sigma eps) into the
+    // action column of a critic input buffer [B][SA + 1], log pi into logp [B]
+    const float* eps; float* xa; float* logp;
 };
 // bf16 K-major images of the H x H part W1[k][n] of layer 1 (entry q: weights at ws + w_off[q], image number img[q] of H H 2
 // bytes each).  Forward image (by_k = 0): operand rows = output unit n, contraction along k.  Backward image (by_k = 1):
@@ -649,8 +652,19 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     __syncthreads();
     if (half == 0 && live) {
         float* out = f.Out + (long long)z * f.B * f.nout + (long long)m * f.nout;
-        out[0] = o0 + s_part[2 * row] + s_w2[2 * H];
-        if (f.nout == 2) out[1] = o1 + s_part[2 * row + 1] + s_w2[2 * H + 1];
+        const float mu = o0 + s_part[2 * row] + s_w2[2 * H];
+        out[0] = mu;
+        if (f.nout == 2) {
+            const float lsr = o1 + s_part[2 * row + 1] + s_w2[2 * H + 1];
+            out[1] = lsr;
+            if (f.eps) {                                               // same arithmetic as head_kernel
+                const float ls = fminf(fmaxf(lsr, LOG_SIG_MIN), LOG_SIG_MAX);
+                const float eps = f.eps[m];
+                const float a = tanhf(fmaf(expf(ls), eps, mu));
+                f.xa[(long long)m * (SA + 1) + S] = a;
+                f.logp[m] = -0.5f * eps * eps - ls - 0.91893853320467274f - logf(1.0f - a * a + SQUASH_EPS);
+            }
+        }
     }
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(f.tmem_cols));
 }
@@ -1170,7 +1184,7 @@ struct Launcher {
     // net_id: index of the (first) network's bf16 W1 image in the workspace (0 policy, 1 q1, 2 q2, 3 / 4 their targets);
     // -1 or the SIMT path: the three products as separate launches
     void forward(long long oX, int kin, long long oW, long long w_zs, const Net& n, int nout, long long oH1, long long oH2,
-                 long long oOut, int Z, int net_id = -1) const {
+                 long long oOut, int Z, int net_id = -1, long long oEps = -1, long long oXa = 0, long long oLogp = 0) const {
         const int B = L.B, H = L.H;
         const int ld = L.ldh;
         const long long hz = (long long)B * ld;
@@ -1183,6 +1197,7 @@ struct Launcher {
             f.M1 = om >= 0 ? reinterpret_cast<uint32_t*>(ws + om) : nullptr;
             f.M2 = om >= 0 ? f.M1 + (long long)Z * B * 8 : nullptr;
             f.B = B; f.H = H; f.ld = ld; f.nout = nout;
+            f.eps = oEps >= 0 ? ws + oEps : nullptr; f.xa = ws + oXa; f.logp = ws + oLogp;
             f.tmem_cols = 32;
             while (f.tmem_cols < H) f.tmem_cols <<= 1;
             mlp_fwd_tc_kernel<<<dim3((B + TCG_M - 1) / TCG_M, Z), 256, fwd_smem_bytes(H, kin + 1), st>>>(f);
@@ -1288,16 +1303,17 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     fork2(0);
     X2.forward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
     // target: a' ~ pi(s'), Q targets on (s', a')
-    X.forward(L.o_xs2, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0);
-    head_kernel<<<eb, 256, 0, st>>>(ws, L, L.o_eps_next, L.o_xs2a, L.o_logp_next);
+    const bool fused = L.tc && L.fused_fwd;      // the policy's forward kernel then also applies the tanh-Gaussian head
+    X.forward(L.o_xs2, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0, L.o_eps_next, L.o_xs2a, L.o_logp_next);
+    if (!fused) head_kernel<<<eb, 256, 0, st>>>(ws, L, L.o_eps_next, L.o_xs2a, L.o_logp_next);
     X.forward(L.o_xs2a, SA, L.o_qt, L.P_q, L.q, 1, L.o_hqt1, L.o_hqt2, L.o_oqt, 2, 3);
     join2(1);
     // loss, backward, Adam (+ soft target update)
     critic_loss_kernel<<<1, 1024, 0, st>>>(ws, L, hp);
     // policy on s (its own buffers, the policy's weights): beside the critics' backward and Adam
     fork2(2);
-    X2.forward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0);
-    head_kernel<<<eb, 256, 0, s2>>>(ws, L, L.o_eps_cur, L.o_xspi, L.o_logp_cur);
+    X2.forward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0, L.o_eps_cur, L.o_xspi, L.o_logp_cur);
+    if (!fused) head_kernel<<<eb, 256, 0, s2>>>(ws, L, L.o_eps_cur, L.o_xspi, L.o_logp_cur);
     X.backward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, true, L.o_grad + L.P_pol, 0, 0, 0, 6);
     adam_kernel<<<(unsigned)((2 * L.P_q + 255) / 256), 256, 0, st>>>(ws, L, hp, L.P_pol, 2 * L.P_q, L.o_qt - L.o_q, 1, (L.tc && L.fused_fwd) ? 1 : 0);   // + the updated critics' W1 images
     join2(3);
