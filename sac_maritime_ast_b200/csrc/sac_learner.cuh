@@ -546,13 +546,28 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
 #pragma unroll
         for (int c = 0; c < 12; ++c) x[rb][c] = (m < f.B && c < f.kin1) ? f.X[(long long)m * f.kin1 + c] : 0.f;
     }
-    for (int i = tid; i < (H + 1) * f.nout; i += 256) {
-        const int k = i / f.nout, j = i % f.nout;
-        s_w2[2 * k + j] = W[f.l2 + i];
-        if (f.nout == 1) s_w2[2 * k + 1] = 0.f;
+    {   // small operands -> shared memory with ALL loads of a thread in flight together (a loop of dependent
+        // load -> store trips cost one L2 round trip each: 15 of them were 9 of this kernel's 19 us)
+        float t0[12], t2[3], t1 = 0.f;
+        const int n0 = f.kin1 * H, n2 = (H + 1) * f.nout;              // <= 12 x 256 | <= 257 x 2
+#pragma unroll
+        for (int q = 0; q < 12; ++q) { const int i = tid + q * 256; t0[q] = i < n0 ? W[f.l0 + i] : 0.f; }
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { const int i = tid + q * 256; t2[q] = i < n2 ? W[f.l2 + i] : 0.f; }
+        if (tid < H) t1 = W[f.l1 + (long long)H * H + tid];
+#pragma unroll
+        for (int q = 0; q < 12; ++q) { const int i = tid + q * 256; if (i < n0) s_w0[i] = t0[q]; }
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const int i = tid + q * 256;
+            if (i < n2) {
+                const int k = i / f.nout, j = i % f.nout;
+                s_w2[2 * k + j] = t2[q];
+                if (f.nout == 1) s_w2[2 * k + 1] = 0.f;
+            }
+        }
+        if (tid < H) s_b1[tid] = t1;
     }
-    for (int i = tid; i < H; i += 256) s_b1[i] = W[f.l1 + (long long)H * H + i];
-    for (int i = tid; i < f.kin1 * H; i += 256) s_w0[i] = W[f.l0 + i];
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::);
@@ -735,12 +750,23 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
         const uint4* mp = reinterpret_cast<const uint4*>(f.M1 + ((long long)z * f.B + m) * 8);
         m1lo = mp[0]; m1hi = mp[1];
     }
-    for (int i = tid; i < H * f.nout; i += 256) {
-        const int k = i / f.nout, j = i % f.nout;
-        s_w2[2 * k + j] = W[f.l2 + i];
-        if (f.nout == 1) s_w2[2 * k + 1] = 0.f;
+    {   // small operands: all loads of a thread in flight together (see the forward kernel)
+        float t2[2], tx = 0.f;
+        const int n2 = H * f.nout;                                       // <= 512
+#pragma unroll
+        for (int q = 0; q < 2; ++q) { const int i = tid + q * 256; t2[q] = i < n2 ? W[f.l2 + i] : 0.f; }
+        if (tid < H && f.DX) tx = W[f.l0 + (long long)f.dx_row * H + tid];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int i = tid + q * 256;
+            if (i < n2) {
+                const int k = i / f.nout, j = i % f.nout;
+                s_w2[2 * k + j] = t2[q];
+                if (f.nout == 1) s_w2[2 * k + 1] = 0.f;
+            }
+        }
+        if (tid < H) s_wx[tid] = tx;
     }
-    for (int i = tid; i < H; i += 256) s_wx[i] = f.DX ? W[f.l0 + (long long)f.dx_row * H + i] : 0.f;
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::);
