@@ -494,6 +494,10 @@ __device__ __forceinline__ uint32_t mask_word(const uint4& lo, const uint4& hi, 
 // of 32 different rows per instruction.  The warp transposes the chunk through a private [32][16] staging tile (row stride
 // 20 floats: conflict-free 128-bit accesses) and stores 8 rows x 64 contiguous bytes per instruction instead.
 #define FUSED_STG_STRIDE 20
+// CTA shape of the fused kernels: 16 warps (the 8-warp version issued 32 % of the time: two warps per scheduler cannot hide
+// the dependent-issue latency of the layer-0 FMA chains and the epilogue); a warp owns 8 rows in the layer-0 / layer-2 phase,
+// the four thread quarters take the four column quarters of the accumulator in the epilogue
+constexpr int FUSED_NT = 512, FUSED_NW = FUSED_NT / 32, FUSED_RB = TCG_M / (8 * FUSED_NW), FUSED_NQ = FUSED_NT / TCG_M;
 __device__ __forceinline__ void staged_store16(float* stg, const int lane, const float (&v)[16], float* gbase, const long long ld,
                                                const int rows_left) {
 #pragma unroll
@@ -508,7 +512,7 @@ __device__ __forceinline__ void staged_store16(float* stg, const int lane, const
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
+__global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     extern __shared__ __align__(128) unsigned char fw_smem[];
     const int H = f.H, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, z = blockIdx.y;
     const int m0 = blockIdx.x * TCG_M;
@@ -517,8 +521,8 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     unsigned char* sB = sA + (size_t)TCG_M * H * 2;                   // [H/8][H/8][8][8] bf16, rows = output unit
     float* s_w2 = reinterpret_cast<float*>(sB + (size_t)H * H * 2);   // [H + 1][2]
     float* s_b1 = s_w2 + 2 * (H + 1);                                 // [H]
-    float* s_part = s_b1 + H;                                         // [128][2]
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + 2 * TCG_M + 2);   // [0]: MMAs done, [1]: W1 image landed (8-byte aligned)
+    float* s_part = s_b1 + H;                                         // [FUSED_NQ - 1][128][2]
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + 2 * TCG_M * (FUSED_NQ - 1) + 2);   // [0]: MMAs done, [1]: W1 image landed (8-byte aligned)
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2);
     float* s_w0 = reinterpret_cast<float*>(s_bar + 4);                // [kin1][H] (the network blocks are only 4-byte aligned in the workspace)
     const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;
@@ -536,30 +540,31 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"(smem_u32(sB)), "l"(f.w1p + (long long)z * f.w1p_zs), "r"(bytes), "r"(smem_u32(s_bar + 1)) : "memory");
     }
-    // layer 0 mapping: a warp owns 16 rows as two blocks of 8; lane = (row of the block, 8-column group of a 32-column
+    // layer 0 mapping: a warp owns FUSED_RB blocks of 8 rows; lane = (row of the block, 8-column group of a 32-column
     // step), so one instruction writes 8 rows x 128 contiguous bytes of h1 and 512 contiguous bytes of the A image
     const int rsub = lane & 7, grp = lane >> 3;
-    float x[2][12];
+    float x[FUSED_RB][12];
 #pragma unroll
-    for (int rb = 0; rb < 2; ++rb) {
-        const int m = m0 + warp * 16 + rb * 8 + rsub;
+    for (int rb = 0; rb < FUSED_RB; ++rb) {
+        const int m = m0 + warp * (8 * FUSED_RB) + rb * 8 + rsub;
 #pragma unroll
         for (int c = 0; c < 12; ++c) x[rb][c] = (m < f.B && c < f.kin1) ? f.X[(long long)m * f.kin1 + c] : 0.f;
     }
     {   // small operands -> shared memory with ALL loads of a thread in flight together (a loop of dependent
         // load -> store trips cost one L2 round trip each: 15 of them were 9 of this kernel's 19 us)
-        float t0[12], t2[3], t1 = 0.f;
+        constexpr int Q0 = 12 * 256 / FUSED_NT, Q2 = (2 * 257 + FUSED_NT - 1) / FUSED_NT;
+        float t0[Q0], t2[Q2], t1 = 0.f;
         const int n0 = f.kin1 * H, n2 = (H + 1) * f.nout;              // <= 12 x 256 | <= 257 x 2
 #pragma unroll
-        for (int q = 0; q < 12; ++q) { const int i = tid + q * 256; t0[q] = i < n0 ? W[f.l0 + i] : 0.f; }
+        for (int q = 0; q < Q0; ++q) { const int i = tid + q * FUSED_NT; t0[q] = i < n0 ? W[f.l0 + i] : 0.f; }
 #pragma unroll
-        for (int q = 0; q < 3; ++q) { const int i = tid + q * 256; t2[q] = i < n2 ? W[f.l2 + i] : 0.f; }
+        for (int q = 0; q < Q2; ++q) { const int i = tid + q * FUSED_NT; t2[q] = i < n2 ? W[f.l2 + i] : 0.f; }
         if (tid < H) t1 = W[f.l1 + (long long)H * H + tid];
 #pragma unroll
-        for (int q = 0; q < 12; ++q) { const int i = tid + q * 256; if (i < n0) s_w0[i] = t0[q]; }
+        for (int q = 0; q < Q0; ++q) { const int i = tid + q * FUSED_NT; if (i < n0) s_w0[i] = t0[q]; }
 #pragma unroll
-        for (int q = 0; q < 3; ++q) {
-            const int i = tid + q * 256;
+        for (int q = 0; q < Q2; ++q) {
+            const int i = tid + q * FUSED_NT;
             if (i < n2) {
                 const int k = i / f.nout, j = i % f.nout;
                 s_w2[2 * k + j] = t2[q];
@@ -576,8 +581,8 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
 
     // layer 0: relu(x . W0), fp32, ascending input index
 #pragma unroll
-    for (int rb = 0; rb < 2; ++rb) {
-        const int row = warp * 16 + rb * 8 + rsub, m = m0 + row;
+    for (int rb = 0; rb < FUSED_RB; ++rb) {
+        const int row = warp * (8 * FUSED_RB) + rb * 8 + rsub, m = m0 + row;
         const bool live = m < f.B;
         float* h1 = f.H1 + (long long)z * f.hz + (long long)m * f.ld;
         for (int it = 0; it < (H >> 5); ++it) {
@@ -629,9 +634,9 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
     }
     mbar_wait(smem_u32(s_bar), 0u);
     asm volatile("tcgen05.fence::after_thread_sync;" ::);
-    // epilogue: thread = accumulator row, the two thread halves take the two column halves; h2 = relu(D + b1) -> HBM through
+    // epilogue: thread = accumulator row, the FUSED_NQ thread quarters take the column quarters; h2 = relu(D + b1) -> HBM through
     // the warp's staging tile (the A image is dead), output layer accumulated on the way
-    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H >> 1;
+    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H / FUSED_NQ;      // (`half`: this thread's column part)
     const int m = m0 + row;
     const bool live = m < f.B;
     float* stg = reinterpret_cast<float*>(sA) + warp * 32 * FUSED_STG_STRIDE;
@@ -657,20 +662,22 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_tc_kernel(const FwdTC f) {
             o0 = fmaf(hv[j], w.x, o0);
             o1 = fmaf(hv[j], w.y, o1);
         }
-        mword |= bits << (c0 & 31);                                    // kh is a multiple of 32: a word belongs to one half
+        mword |= bits << (c0 & 31);                                    // kh is a multiple of 32: a word belongs to one column part
         if ((c0 & 16) && live && f.M2) { f.M2[((long long)z * f.B + m) * 8 + (c0 >> 5)] = mword; }
         if (c0 & 16) mword = 0u;
         staged_store16(stg, lane, hv, h2w + c0, f.ld, f.B - wrow0);
     }
-    if (half == 1) { s_part[2 * row] = o0; s_part[2 * row + 1] = o1; }
+    if (half > 0) { s_part[2 * ((half - 1) * TCG_M + row)] = o0; s_part[2 * ((half - 1) * TCG_M + row) + 1] = o1; }
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
     __syncthreads();
     if (half == 0 && live) {
         float* out = f.Out + (long long)z * f.B * f.nout + (long long)m * f.nout;
-        const float mu = o0 + s_part[2 * row] + s_w2[2 * H];
+#pragma unroll
+        for (int q = 0; q < FUSED_NQ - 1; ++q) { o0 += s_part[2 * (q * TCG_M + row)]; o1 += s_part[2 * (q * TCG_M + row) + 1]; }   // fixed order
+        const float mu = o0 + s_w2[2 * H];
         out[0] = mu;
         if (f.nout == 2) {
-            const float lsr = o1 + s_part[2 * row + 1] + s_w2[2 * H + 1];
+            const float lsr = o1 + s_w2[2 * H + 1];
             out[1] = lsr;
             if (f.eps) {                                               // same arithmetic as head_kernel
                 const float ls = fminf(fmaxf(lsr, LOG_SIG_MIN), LOG_SIG_MAX);
@@ -699,7 +706,7 @@ struct BwdTC {
     float* DX; int dx_row;                    // [Z][B] or nullptr; row of W0 (input column) the gradient is taken for
     int B, H, tmem_cols;
 };
-__global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
+__global__ void __launch_bounds__(FUSED_NT, 1) mlp_bwd_tc_kernel(const BwdTC f) {
     extern __shared__ __align__(128) unsigned char bw_smem[];
     const int H = f.H, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, z = blockIdx.y;
     const int m0 = blockIdx.x * TCG_M;
@@ -708,8 +715,8 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
     unsigned char* sB = sA + (size_t)TCG_M * H * 2;
     float* s_w2 = reinterpret_cast<float*>(sB + (size_t)H * H * 2);   // [H][2]
     float* s_wx = s_w2 + 2 * H;                                       // [H]: row dx_row of W0
-    float* s_part = s_wx + H;                                         // [128]
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + TCG_M);
+    float* s_part = s_wx + H;                                         // [FUSED_NQ - 1][128]
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + TCG_M * (FUSED_NQ - 1));
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2);
     const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;
 
@@ -728,11 +735,11 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
     }
     // layer 2 mapping as in the forward kernel: lane = (row of an 8-row block, 8-column group of a 32-column step)
     const int rsub = lane & 7, grp = lane >> 3;
-    float d0[2], d1[2];
-    uint4 mlo[2], mhi[2];
+    float d0[FUSED_RB], d1[FUSED_RB];
+    uint4 mlo[FUSED_RB], mhi[FUSED_RB];
 #pragma unroll
-    for (int rb = 0; rb < 2; ++rb) {
-        const int m = m0 + warp * 16 + rb * 8 + rsub;
+    for (int rb = 0; rb < FUSED_RB; ++rb) {
+        const int m = m0 + warp * (8 * FUSED_RB) + rb * 8 + rsub;
         const bool lv = m < f.B;
         const float* dout = f.DOut + (long long)z * f.B * f.nout + (long long)m * f.nout;
         d0[rb] = lv ? dout[0] : 0.f;
@@ -742,7 +749,7 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
         mhi[rb] = lv ? mp[1] : make_uint4(0u, 0u, 0u, 0u);
     }
     // epilogue mask (h1 > 0) of this thread's accumulator row
-    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H >> 1;
+    const int row = tid & (TCG_M - 1), half = tid >> 7, kh = H / FUSED_NQ;      // (`half`: this thread's column part)
     const int m = m0 + row;
     const bool live = m < f.B;
     uint4 m1lo = make_uint4(0u, 0u, 0u, 0u), m1hi = m1lo;
@@ -751,14 +758,15 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
         m1lo = mp[0]; m1hi = mp[1];
     }
     {   // small operands: all loads of a thread in flight together (see the forward kernel)
-        float t2[2], tx = 0.f;
+        constexpr int Q2 = (2 * 256 + FUSED_NT - 1) / FUSED_NT;
+        float t2[Q2], tx = 0.f;
         const int n2 = H * f.nout;                                       // <= 512
 #pragma unroll
-        for (int q = 0; q < 2; ++q) { const int i = tid + q * 256; t2[q] = i < n2 ? W[f.l2 + i] : 0.f; }
+        for (int q = 0; q < Q2; ++q) { const int i = tid + q * FUSED_NT; t2[q] = i < n2 ? W[f.l2 + i] : 0.f; }
         if (tid < H && f.DX) tx = W[f.l0 + (long long)f.dx_row * H + tid];
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            const int i = tid + q * 256;
+        for (int q = 0; q < Q2; ++q) {
+            const int i = tid + q * FUSED_NT;
             if (i < n2) {
                 const int k = i / f.nout, j = i % f.nout;
                 s_w2[2 * k + j] = t2[q];
@@ -775,8 +783,8 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
 
     // layer 2: d h2 = (d out . W2^T) where h2 > 0
 #pragma unroll
-    for (int rb = 0; rb < 2; ++rb) {
-        const int r2 = warp * 16 + rb * 8 + rsub, m2 = m0 + r2;
+    for (int rb = 0; rb < FUSED_RB; ++rb) {
+        const int r2 = warp * (8 * FUSED_RB) + rb * 8 + rsub, m2 = m0 + r2;
         float* dh2 = f.DH2 ? f.DH2 + ((long long)z * f.B + m2) * H : nullptr;
         for (int it = 0; it < (H >> 5); ++it) {
             const int k0 = it * 32 + grp * 8;
@@ -838,10 +846,14 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_tc_kernel(const BwdTC f) {
         }
         if (dh1w) staged_store16(stg, lane, g, dh1w + c0, H, f.B - wrow0);
     }
-    if (half == 1) s_part[row] = dx;
+    if (half > 0) s_part[(half - 1) * TCG_M + row] = dx;
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
     __syncthreads();
-    if (half == 0 && live && f.DX) f.DX[(long long)z * f.B + m] = dx + s_part[row];
+    if (half == 0 && live && f.DX) {
+#pragma unroll
+        for (int q = 0; q < FUSED_NQ - 1; ++q) dx += s_part[q * TCG_M + row];       // fixed order
+        f.DX[(long long)z * f.B + m] = dx;
+    }
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(f.tmem_cols));
 }
 
@@ -866,7 +878,7 @@ struct Layout {
 
 static void make_layout(Layout& L, int H, int B, int tc) {
     L.H = H; L.B = B; L.tc = tc; L.ldh = tc ? H + 4 : H + 1;
-    L.fused_fwd = tc && H % 64 == 0;         // column halves of whole 32-bit mask words
+    L.fused_fwd = tc && H % (32 * FUSED_NQ) == 0;   // column quarters of whole 32-bit mask words: H = 128 or 256
     if (const char* e = std::getenv("SIT_SAC_FUSED_FWD")) if (std::atoi(e) == 0) L.fused_fwd = 0;
     L.pol.l0 = 0; L.pol.l1 = (long long)(S + 1) * H; L.pol.l2 = L.pol.l1 + (long long)(H + 1) * H;
     L.P_pol = L.pol.l2 + (long long)(H + 1) * 2;
@@ -1143,8 +1155,8 @@ struct SitSac_ {
 
 namespace sac {
 
-static size_t bwd_smem_bytes(int H) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 512 + 32; }
-static size_t fwd_smem_bytes(int H, int kin1) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 1040 + 32 + (size_t)kin1 * H * 4; }
+static size_t bwd_smem_bytes(int H) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 512 * (FUSED_NQ - 1) + 32; }
+static size_t fwd_smem_bytes(int H, int kin1) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 16 + 1024 * (FUSED_NQ - 1) + 32 + (size_t)kin1 * H * 4; }
 
 struct Launcher {
     cudaStream_t st;
@@ -1226,7 +1238,7 @@ struct Launcher {
             f.eps = oEps >= 0 ? ws + oEps : nullptr; f.xa = ws + oXa; f.logp = ws + oLogp;
             f.tmem_cols = 32;
             while (f.tmem_cols < H) f.tmem_cols <<= 1;
-            mlp_fwd_tc_kernel<<<dim3((B + TCG_M - 1) / TCG_M, Z), 256, fwd_smem_bytes(H, kin + 1), st>>>(f);
+            mlp_fwd_tc_kernel<<<dim3((B + TCG_M - 1) / TCG_M, Z), FUSED_NT, fwd_smem_bytes(H, kin + 1), st>>>(f);
             return;
         }
         gemm(oX, kin + 1, 1, 0, oW + n.l0, H, 1, w_zs, oH1, ld, hz, B, H, kin + 1, Z, EPI_RELU);
@@ -1267,7 +1279,7 @@ struct Launcher {
             f.DX = dx_cols > 0 ? ws + oDX : nullptr; f.dx_row = dx_first;
             f.B = B; f.H = H; f.tmem_cols = 32;
             while (f.tmem_cols < H) f.tmem_cols <<= 1;
-            mlp_bwd_tc_kernel<<<dim3((B + TCG_M - 1) / TCG_M, Z), 256, bwd_smem_bytes(H), st>>>(f);
+            mlp_bwd_tc_kernel<<<dim3((B + TCG_M - 1) / TCG_M, Z), FUSED_NT, bwd_smem_bytes(H), st>>>(f);
             if (want_dw) {
                 const bool two = par2 && side_b != nullptr;
                 if (par2) { cudaEventRecord(ev[1], st); cudaStreamWaitEvent(side, ev[1], 0); if (two) cudaStreamWaitEvent(side_b, ev[1], 0); }

@@ -142,11 +142,11 @@ class SAC:
         self.losses = torch.zeros(8, dtype=torch.float32, device=self.device)
         # kernels one update enqueues: 28 products + 9 element-wise = 37.  On the tensor-core path (batch >= 1024, hidden >= 128)
         # the 6 split-k products (weight gradients: contraction over the batch) are followed by a reduce kernel each (43); with
-        # hidden a multiple of 64 a network's forward and its input-gradient chain are one kernel each (5 forwards, 3
+        # hidden a multiple of 128 a network's forward and its input-gradient chain are one kernel each (5 forwards, 3
         # backwards instead of 15 + 7 products, the policy's tanh-Gaussian head in its forward kernel) and one launch packs the
         # bf16 images of W1: 28 (22 below batch 1024, where no product is split)
         self.tensor_cores = bool(cfg.tensor_cores) and (cfg.batch_size >= 1024 or cfg.tensor_cores >= 2) and cfg.hidden >= 128
-        fused = self.tensor_cores and cfg.hidden % 64 == 0 and os.environ.get("SIT_SAC_FUSED_FWD", "1") != "0"
+        fused = self.tensor_cores and cfg.hidden % 128 == 0 and os.environ.get("SIT_SAC_FUSED_FWD", "1") != "0"
         splitk = 6 if (self.tensor_cores and cfg.batch_size >= 1024) else 0          # reduce kernels of the split-k weight gradients
         self.kernels_per_update = (22 if fused else 37) + splitk
         self._side = None
