@@ -451,7 +451,7 @@ struct FwdTC {
     const float* W; long long w_zs;           // network block (augmented layers at l0, l1, l2), stride between the Z networks
     long long l0, l1, l2;
     const unsigned char* w1p; long long w1p_zs;   // bf16 image of W1's H x H part, bytes
-    float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld], outputs [Z][B][nout]
+    float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld] (nullptr: not kept -- a pass no backward goes through), outputs [Z][B][nout]
     uint32_t *M1, *M2;                        // sign bits of h1, h2 for the fused backward: [Z][B][8 words], bit k of a row = word k >> 5, bit k & 31; or nullptr
     int B, H, ld, nout, tmem_cols;
     // policy only (nullptr otherwise): the tanh-Gaussian head of head_kernel in the epilogue -- a = tanh(mu + sigma eps) into the
@@ -606,7 +606,7 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) 
             bits <<= 8 * grp;                                          // the four column groups of a row make up mask word `it`
             bits |= __shfl_xor_sync(0xffffffffu, bits, 8);
             bits |= __shfl_xor_sync(0xffffffffu, bits, 16);
-            if (live) {
+            if (live && f.H1) {                                        // (no backward through this pass: nothing is kept)
                 if (grp == 0 && f.M1) f.M1[((long long)z * f.B + m) * 8 + it] = bits;
                 *reinterpret_cast<float4*>(h1 + k0) = make_float4(a[0], a[1], a[2], a[3]);
                 *reinterpret_cast<float4*>(h1 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
@@ -665,7 +665,7 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) 
         mword |= bits << (c0 & 31);                                    // kh is a multiple of 32: a word belongs to one column part
         if ((c0 & 16) && live && f.M2) { f.M2[((long long)z * f.B + m) * 8 + (c0 >> 5)] = mword; }
         if (c0 & 16) mword = 0u;
-        staged_store16(stg, lane, hv, h2w + c0, f.ld, f.B - wrow0);
+        if (f.H2) staged_store16(stg, lane, hv, h2w + c0, f.ld, f.B - wrow0);
     }
     if (half > 0) { s_part[2 * ((half - 1) * TCG_M + row)] = o0; s_part[2 * ((half - 1) * TCG_M + row) + 1] = o1; }
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
@@ -1222,7 +1222,7 @@ struct Launcher {
     // net_id: index of the (first) network's bf16 W1 image in the workspace (0 policy, 1 q1, 2 q2, 3 / 4 their targets);
     // -1 or the SIMT path: the three products as separate launches
     void forward(long long oX, int kin, long long oW, long long w_zs, const Net& n, int nout, long long oH1, long long oH2,
-                 long long oOut, int Z, int net_id = -1, long long oEps = -1, long long oXa = 0, long long oLogp = 0) const {
+                 long long oOut, int Z, int net_id = -1, long long oEps = -1, long long oXa = 0, long long oLogp = 0, bool keep = true) const {
         const int B = L.B, H = L.H;
         const int ld = L.ldh;
         const long long hz = (long long)B * ld;
@@ -1230,8 +1230,8 @@ struct Launcher {
             FwdTC f;
             f.X = ws + oX; f.kin1 = kin + 1; f.W = ws + oW; f.w_zs = w_zs; f.l0 = n.l0; f.l1 = n.l1; f.l2 = n.l2;
             f.w1p = reinterpret_cast<const unsigned char*>(ws + L.o_w1p) + (size_t)net_id * H * H * 2; f.w1p_zs = (long long)H * H * 2;
-            f.H1 = ws + oH1; f.H2 = ws + oH2; f.Out = ws + oOut; f.hz = hz;
-            const long long om = oH1 == L.o_hp1 ? L.o_mhp : (oH1 == L.o_hq1 ? L.o_mhq : -1);      // the target critics have no backward
+            f.H1 = keep ? ws + oH1 : nullptr; f.H2 = keep ? ws + oH2 : nullptr; f.Out = ws + oOut; f.hz = hz;
+            const long long om = !keep ? -1 : (oH1 == L.o_hp1 ? L.o_mhp : (oH1 == L.o_hq1 ? L.o_mhq : -1));
             f.M1 = om >= 0 ? reinterpret_cast<uint32_t*>(ws + om) : nullptr;
             f.M2 = om >= 0 ? f.M1 + (long long)Z * B * 8 : nullptr;
             f.B = B; f.H = H; f.ld = ld; f.nout = nout;
@@ -1342,9 +1342,9 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     X2.forward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
     // target: a' ~ pi(s'), Q targets on (s', a')
     const bool fused = L.tc && L.fused_fwd;      // the policy's forward kernel then also applies the tanh-Gaussian head
-    X.forward(L.o_xs2, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0, L.o_eps_next, L.o_xs2a, L.o_logp_next);
+    X.forward(L.o_xs2, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0, L.o_eps_next, L.o_xs2a, L.o_logp_next, false);   // a' ~ pi(s'): no backward, activations not kept
     if (!fused) head_kernel<<<eb, 256, 0, st>>>(ws, L, L.o_eps_next, L.o_xs2a, L.o_logp_next);
-    X.forward(L.o_xs2a, SA, L.o_qt, L.P_q, L.q, 1, L.o_hqt1, L.o_hqt2, L.o_oqt, 2, 3);
+    X.forward(L.o_xs2a, SA, L.o_qt, L.P_q, L.q, 1, L.o_hqt1, L.o_hqt2, L.o_oqt, 2, 3, -1, 0, 0, false);   // targets: no backward
     join2(1);
     // loss, backward, Adam (+ soft target update)
     critic_loss_kernel<<<1, 1024, 0, st>>>(ws, L, hp);
