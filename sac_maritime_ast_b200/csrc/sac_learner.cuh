@@ -1191,7 +1191,8 @@ struct Launcher {
             const int n_chunks = (K + TCG_KC - 1) / TCG_KC;
             int splits = K >= 1024 ? std::min(TCG_MAX_SPLITS, std::max(1, n_chunks / 4)) : 1;
             {   // no more CTAs than one wave of two per SM: the second wave of a weight-gradient product cost as much as the first
-                const long long tiles = (long long)((N + 63) / 64) * ((M + TCG_M - 1) / TCG_M) * Z;
+                const bool wide = t.bn == 128 && K >= 4096;            // (these keep their 128-wide tiles, below)
+                const long long tiles = (long long)((N + (wide ? 127 : 63)) / (wide ? 128 : 64)) * ((M + TCG_M - 1) / TCG_M) * Z;
                 if (splits > 1 && tiles * splits > 296) splits = (int)std::max<long long>(1, 296 / tiles);
             }
             const int per = (n_chunks + splits - 1) / splits;
