@@ -381,8 +381,8 @@ typedef struct SitSacConfig {
     int32_t tensor_cores;              /* 1: H x H products of the update on tcgen05 (bf16 operands, fp32 accumulate) when
                                           batch_size >= 1024 (below that the update stays in fp32, within fp32 rounding of a
                                           torch autograd restatement); 2: at every batch size (the reference's batch 64 runs
-                                          as 24 launches instead of 37); 0: fp32 CUDA cores everywhere.  With hidden a multiple
-                                          of 64 a network's forward and its input-gradient chain are one kernel each */
+                                          as 22 launches instead of 37); 0: fp32 CUDA cores everywhere.  With hidden a multiple
+                                          of 128 a network's forward and its input-gradient chain are one kernel each */
     int32_t _pad;
 } SitSacConfig;
 typedef struct SitSac_* SitSac;
