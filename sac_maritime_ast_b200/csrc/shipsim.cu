@@ -392,10 +392,10 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     const EnvP<R>& EP = A.EP;
     const int lane = threadIdx.x & 31;
     const unsigned PAIR = 3u << (lane & 30);
-    // Exchanges between the two ships of an env.  Rollout: envs waiting for an action skip the step, so only the lane pair is
-    // converged at the exchange points.  Otherwise every lane of the warp reaches them: the full mask lets the warp exchange
-    // without a per-pair WARPSYNC on a computed mask and reconverges it every step (env leg 1.34e10 -> 1.43e10 env-steps/s).
-    const unsigned XM = ROLL ? PAIR : FULL;
+    // The exchanges between the two ships of an env sit where EVERY lane of the warp arrives (in the rollout too: an env that
+    // waits for an action skips the phases around them, not the exchanges), so they use the full mask: no per-pair WARPSYNC
+    // on a computed mask, and the warp reconverges every step (env leg 1.34e10 -> 1.43e10 env-steps/s).  PAIR is left for
+    // the one exchange inside a pair-uniform branch (the rollout's decision event).
 
     Ship<R> s;
     load_ship(s, g, i);
@@ -489,12 +489,15 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             }
         }
 
-        // ---- exchange post-step positions inside the lane pair ---------------------------------------
-        const double oth_n = __shfl_xor_sync(XM, s.N, 1), oth_e = __shfl_xor_sync(XM, s.E, 1);
-        const double n_t = is_obs ? oth_n : s.N, e_t = is_obs ? oth_e : s.E;
-        const double n_o = is_obs ? s.N : oth_n, e_o = is_obs ? s.E : oth_e;
-        const double ddn = n_t - n_o, dde = e_t - e_o;
-        ship_d2 = __dadd_rn(__dmul_rn(ddn, ddn), __dmul_rn(dde, dde));
+        }
+        // ---- exchange post-step positions inside the lane pair (whole warp: an env that waits for an action exchanges its
+        // held positions, nothing reads the result) ----------------------------------------------------------------
+        {
+            const double oth_n = __shfl_xor_sync(FULL, s.N, 1), oth_e = __shfl_xor_sync(FULL, s.E, 1);
+            const double n_t = is_obs ? oth_n : s.N, e_t = is_obs ? oth_e : s.E;
+            const double n_o = is_obs ? s.N : oth_n, e_o = is_obs ? s.E : oth_e;
+            const double ddn = n_t - n_o, dde = e_t - e_o;
+            ship_d2 = __dadd_rn(__dmul_rn(ddn, ddn), __dmul_rn(dde, dde));
         }
 
         // ---- phase B (whole warp): distance to the nearest ring + hull containment, nearest-ring cache -------
@@ -522,16 +525,16 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             }
         }
 
-        if (live) {   // ---- phase C: rewards, terminal checks, outputs, episode restart ------------------------------
-        const R dmap = sqrt_(d2map);
+        int st = 0; bool dn_ = false; R part = (R)0; bool collide = false; R ect = (R)0, dmap = (R)0; bool stop_in = false;
+        if (live) {   // ---- phase C: rewards, terminal checks ------------------------------------------------------------
+        dmap = sqrt_(d2map);
         const bool outside = pn < EP.lo_n[role] || pn > EP.hi_n[role] || pe < EP.lo_e[role] || pe > EP.hi_e[role];
         const double dnE = s.N - (double)endN, deE = s.E - (double)endE;
         const bool arrived = __dadd_rn(__dmul_rn(dnE, dnE), __dmul_rn(deE, deE)) <= EP.arrive2;   // decided in double in both precisions
-        const R ect = s.e_ct;
+        ect = s.e_ct;
 
         // ---- per-ship reward terms and terminal checks (sequential stop_flag gating) -------------------
-        int st = 0; bool dn_ = false; R part;
-        const bool stop_in = PARTS && stop;      // the obstacle ship's non-terminal terms see the flag from before this step
+        stop_in = PARTS && stop;      // the obstacle ship's non-terminal terms see the flag from before this step
         if (!is_obs) {
             // test_ship_non_terminal_state_reward :628-664
             const R ntt = abs_(ect) * EP.inv_e_tol + ((R)1 - dmap * EP.inv_max_north) * (R)0.01;
@@ -566,12 +569,14 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             o.rud = ro_; o.thr = snt;
         }
         // shared_terminal_state_reward :883-904, is_ship_collision :584-603
-        const bool collide = ship_d2 < EP.collide2;
+        collide = ship_d2 < EP.collide2;
         if (collide) { stop = true; dn_ = true; st |= SIT_ST_COLLISION; }
-
-        const R part_t = __shfl_xor_sync(XM, part, 1);
-        const int st_o = __shfl_xor_sync(XM, st, 1);
-        const bool dn_o = __shfl_xor_sync(XM, (int)dn_, 1) != 0;
+        }
+        // partial reward, status bits and done flag of the other ship of the env (whole warp, see above)
+        const R part_t = __shfl_xor_sync(FULL, part, 1);
+        const int st_o = __shfl_xor_sync(FULL, st, 1);
+        const bool dn_o = __shfl_xor_sync(FULL, (int)dn_, 1) != 0;
+        if (live) {   // ---- phase C, continued: outputs, replay rows, episode restart ----------------------------------------
         done = dn_ || dn_o;
         status = st | st_o;
         R reward = (R)0;
