@@ -391,11 +391,9 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
     const ShipP<R>& P = SAME ? A.P[0] : A.P[role];
     const EnvP<R>& EP = A.EP;
     const int lane = threadIdx.x & 31;
-    const unsigned PAIR = 3u << (lane & 30);
     // The exchanges between the two ships of an env sit where EVERY lane of the warp arrives (in the rollout too: an env that
     // waits for an action skips the phases around them, not the exchanges), so they use the full mask: no per-pair WARPSYNC
-    // on a computed mask, and the warp reconverges every step (env leg 1.34e10 -> 1.43e10 env-steps/s).  PAIR is left for
-    // the one exchange inside a pair-uniform branch (the rollout's decision event).
+    // on a computed mask, and the warp reconverges every step (env leg 1.34e10 -> 1.43e10 env-steps/s, rollout 3.13e7 -> 3.26e7).
 
     Ship<R> s;
     load_ship(s, g, i);
@@ -525,7 +523,7 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
             }
         }
 
-        int st = 0; bool dn_ = false; R part = (R)0; bool collide = false; R ect = (R)0, dmap = (R)0; bool stop_in = false;
+        int st = 0; bool dn_ = false; R part = (R)0; bool collide = false; R ect = (R)0, dmap = (R)0; bool stop_in = false, dec = false;
         if (live) {   // ---- phase C: rewards, terminal checks ------------------------------------------------------------
         dmap = sqrt_(d2map);
         const bool outside = pn < EP.lo_n[role] || pn > EP.hi_n[role] || pe < EP.lo_e[role] || pe > EP.hi_e[role];
@@ -671,12 +669,14 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
         } else if (ROLL) {
             // decision event: the obstacle ship is inside the radius of acceptance of its current intermediate
             // waypoint (controllers.py:317-325; the same squared test as the waypoint switch, LOS_guidance.py:96)
-            bool dec = false;
             if (is_obs && !stop && n_dec < ro.sampling_frequency && s.k < s.n_wp - 1) {
                 const double dn = s.cN - s.N, de = s.cE - s.E;
                 dec = __dadd_rn(__dmul_rn(dn, dn), __dmul_rn(de, de)) <= P.ra2;
             }
-            dec = __shfl_sync(PAIR, (int)dec, lane | 1) != 0;   // (pair-uniform branch: only the pair is converged here)
+        }
+        }   // live
+        if (ROLL) {   // the obstacle lane's decision flag reaches the test lane (whole warp; false for envs that did not step)
+            dec = __shfl_sync(FULL, (int)dec, lane | 1) != 0;
             if (dec) {
                 pending = true;
                 if (active) {
@@ -689,7 +689,6 @@ env_step_kernel(const __grid_constant__ EnvKArgs<R> A, const ShipPtrs<R> g, cons
                 }
             }
         }
-        }   // live
         // ---- warp-level reduction of termination / collision flags --------------------------------------
         if (io.stats) {
             const bool cnt_lane = active && is_obs && live;
