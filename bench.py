@@ -687,7 +687,7 @@ def long_horizon_leg(sit, dev, rank, B=65536, K=64, total_steps=10000, mode_ever
             "finite": bool(torch.isfinite(env.f["north"]).all() and torch.isfinite(env.f["omega"]).all())}
 
 
-def rollout_leg(sit, dev, B=65536, K=48, iters=40, warm_iters=20, hidden=256, precision="fp32", mode="gaussian",
+def rollout_leg(sit, dev, B=65536, K=80, iters=40, warm_iters=20, hidden=256, precision="fp32", mode="gaussian",
                 env_id_offset=0, tc=1, world=1, barrier=None, segments=4):
     """BASELINE config 4: SAC-AST rollout, policy MLP 10 -> 256 -> 256 -> 2 with fixed seeded weights evaluated on the
     decision-event subset between step launches, transitions compacted into a device replay ring; after every segment of

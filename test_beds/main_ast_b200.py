@@ -57,7 +57,7 @@ def parse_args(argv=None):
     p.add_argument("--target_update_interval", type=int, default=1)
     # batching
     p.add_argument("--n_envs", type=int, default=4096, help="two-ship environments over all ranks")
-    p.add_argument("--k_steps", type=int, default=48, help="env steps per launch")
+    p.add_argument("--k_steps", type=int, default=80, help="env steps per launch")
     p.add_argument("--collect_iterations", type=int, default=8, help="(policy, k_steps) iterations per segment")
     p.add_argument("--precision", default="fp32", choices=["fp32", "fp64"])
     p.add_argument("--tensor_cores", type=int, default=1, help="policy hidden layer on tcgen05 (bf16 operands)")

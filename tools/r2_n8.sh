@@ -6,7 +6,7 @@ O=gpurun_out
 T="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517"
 timeout 900 $T bench.py --gpus $N > $O/r2n${N}_bench.json 2> $O/r2n${N}_bench.err; echo "bench rc=$?"; tail -c 400 $O/r2n${N}_bench.err
 timeout 300 $T tools/h2d_probe.py > $O/r2n${N}_h2d.log 2>&1; tail -1 $O/r2n${N}_h2d.log
-timeout 400 $T test_beds/main_ast_b200.py --n_envs 65536 --num_steps 1024 --start_steps 512 --k_steps 48 --collect_iterations 8 --max_updates_per_segment 16 > $O/r2n${N}_train.log 2>&1; tail -3 $O/r2n${N}_train.log
+timeout 400 $T test_beds/main_ast_b200.py --n_envs 65536 --num_steps 1024 --start_steps 512 --k_steps 80 --collect_iterations 8 --max_updates_per_segment 16 > $O/r2n${N}_train.log 2>&1; tail -3 $O/r2n${N}_train.log
 timeout 400 $T bench.py --impl reference --gpus $N --steps 20 --warmup 3 > $O/r2n${N}_ref.json 2> $O/r2n${N}_ref.err; echo "ref rc=$?"
 python - <<PY
 import json
