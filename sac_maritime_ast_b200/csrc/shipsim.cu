@@ -2430,6 +2430,7 @@ static int rollout_chains(SitHandle h, void* state, int iterations, int K, const
     return rc;
 }
 
+#define SIT_CHAIN_MAX_ITERS 64   /* iterations per graph of a chained sit_rollout_collect call */
 extern "C" {
 
 int sit_rollout_group_count(SitHandle h, int32_t* groups) {
@@ -2468,6 +2469,18 @@ int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K,
         if (groups > 1) return rollout_chains(h, state, iterations, K, pa, tensor_cores, ra, io, groups, st);
         for (int it = 0; it < iterations; ++it)
             if ((rc = rollout_iteration(h, state, K, pa, tensor_cores, ra, io, st))) return rc;
+        return SIT_OK;
+    }
+    if (groups > 1 && iterations > SIT_CHAIN_MAX_ITERS) {
+        // a long chained call: whole chunks of SIT_CHAIN_MAX_ITERS iterations (one graph, reused), the rest as plain launches --
+        // the graph of a call holds ~7 nodes per group and iteration
+        for (int left = iterations; left > 0;) {
+            const int n = std::min<int>(left, SIT_CHAIN_MAX_ITERS);
+            rc = n == SIT_CHAIN_MAX_ITERS ? sit_rollout_collect(h, state, n, K, pol, ro, io, use_graph, stream)
+                                          : rollout_chains(h, state, n, K, pa, tensor_cores, ra, io, groups, st);
+            if (rc) return rc;
+            left -= n;
+        }
         return SIT_OK;
     }
     std::string key;

@@ -269,6 +269,8 @@ def test_chained_collect_graph_equals_plain_launches_and_fills_the_ring_in_one_o
                     "first decisions: group after group, env order"
         smp.collect(5, 16, graph=graph)                       # other arguments: a new graph on their second use
         smp.collect(5, 16, graph=graph)
+        smp.collect(70, 4, graph=graph)                       # a long call: 64 iterations per graph, the rest as plain launches
+        smp.collect(70, 4, graph=graph)
         torch.cuda.synchronize()
         c = smp.counters.cpu().numpy()
         assert c[_lib.RC_CLOSED] == c[_lib.RC_TRANSITIONS] == c[_lib.RC_DECISIONS] > 2 * B
