@@ -309,7 +309,8 @@ int sit_rollout_step_k(SitHandle h, void* state, int32_t K, const SitRollout* ro
  * updates.  use_graph != 0 (and a non-default stream): replayed from a CUDA graph -- with one env group a graph of one
  * iteration, launched `iterations` times; with several groups (sit_rollout_group_count) ONE graph of the whole call, the
  * groups as independent chains that are joined at the end of the call only (captured on the second call with the same
- * arguments; the first runs as plain launches).  The graph is re-captured when any argument changes.  Enqueues only. */
+ * arguments; the first runs as plain launches; a call of more than 64 iterations runs as 64-iteration graphs plus a
+ * plain-launch remainder).  The graph is re-captured when any argument changes.  Enqueues only. */
 int sit_rollout_collect(SitHandle h, void* state, int32_t iterations, int32_t K, const SitPolicy* pol, const SitRollout* ro,
                         const SitEnvIO* io, int32_t use_graph, void* stream);
 /* mark every env pending at the start of a rollout (after sit_reset + sit_env_init_step) */
