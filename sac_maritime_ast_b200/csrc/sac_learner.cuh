@@ -452,6 +452,7 @@ struct FwdTC {
     long long l0, l1, l2;
     const unsigned char* w1p; long long w1p_zs;   // bf16 image of W1's H x H part, bytes
     float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld] (nullptr: not kept -- a pass no backward goes through), outputs [Z][B][nout]
+    unsigned char* IMG1; long long img_zs;    // bf16 tile image of h1 for d W1 (nullptr: none), bytes between the Z networks
     uint32_t *M1, *M2;                        // sign bits of h1, h2 for the fused backward: [Z][B][8 words], bit k of a row = word k >> 5, bit k & 31; or nullptr
     int B, H, ld, nout, tmem_cols;
     // policy only (nullptr otherwise): the tanh-Gaussian head of head_kernel in the epilogue -- a = tanh(mu + sigma eps) into the
@@ -510,6 +511,29 @@ __device__ __forceinline__ void staged_store16(float* stg, const int lane, const
         if (rr < rows_left) *reinterpret_cast<float4*>(gbase + (long long)rr * ld + cc) = q;
     }
     __syncwarp();
+}
+
+// d W1 operand images: element (feature f, batch row m) of a network's [rows][H] matrix lives in block (f / 128, m / 64) of
+// 16 KB at (f % 128 / 8) 1024 + (m % 64 / 8) 128 + (f % 8) 16 + (m % 8) 2 -- the canonical K-major core-matrix order with the
+// batch as K (LBO 128, SBO 1024).  In the layer-0 / layer-2 phase a warp has just written four 8 x 8 core matrices
+// (8 rows x 8 features, features contiguous) of the A image in shared memory; ldmatrix.trans hands every lane two batch rows
+// of one feature per matrix, i.e. 4 contiguous bytes of the transposed order: four 32-bit stores per lane.
+// `core` = shared address of the lane's own 16-byte row of its core matrix (lane = (row of the block, matrix)).
+__device__ __forceinline__ void image_store_warp(unsigned char* img, const int n_chunks, const int k0_warp, const int m_blk, const uint32_t core,
+                                                 const int lane) {
+    uint32_t q0, q1, q2, q3;
+    __syncwarp();
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3) : "r"(core));
+    // matrix j = features k0_warp + 8 j .. + 7; this lane: feature lane / 4 of each, batch rows m_blk + 2 (lane % 4), + 1
+    const int fr = lane >> 2, mr = m_blk + 2 * (lane & 3);
+    const uint32_t q[4] = {q0, q1, q2, q3};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int f = k0_warp + 8 * j + fr;
+        unsigned char* p = img + ((size_t)(f >> 7) * n_chunks + (mr >> 6)) * 16384 + (size_t)((f & 127) >> 3) * 1024 + (size_t)((mr & 63) >> 3) * 128 +
+                           (f & 7) * 16 + (mr & 7) * 2;
+        *reinterpret_cast<uint32_t*>(p) = q[j];
+    }
 }
 
 __global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) {
@@ -613,7 +637,10 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) 
             }
             uint4 v;
             v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
-            *reinterpret_cast<uint4*>(sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16) = v;
+            unsigned char* core = sA + (size_t)(row >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (row & 7) * 16;
+            *reinterpret_cast<uint4*>(core) = v;
+            // (rows past the batch are zero rows of the image: x = 0 there)
+            if (f.IMG1) image_store_warp(f.IMG1 + (long long)z * f.img_zs, (int)gridDim.x * 2, it * 32, m - rsub, smem_u32(core), lane);
         }
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -702,6 +729,8 @@ struct BwdTC {
     const float* W; long long w_zs; long long l0, l2;
     const unsigned char* w1p; long long w1p_zs;   // by-k bf16 image of W1
     const uint32_t *M1, *M2;                  // sign bits of the forward activations h1, h2 (mlp_fwd_tc_kernel): [Z][B][8 words]
+    unsigned char* IMG2; long long img_zs;    // bf16 tile image of d h2 for d W1 (nullptr: none)
+    float* colsum;                            // [Z][row tiles][H] column sums of this CTA's d h2 rows (with IMG2)
     float *DH2, *DH1;                         // [Z][B][H], nullptr: not stored (no weight gradients wanted)
     float* DX; int dx_row;                    // [Z][B] or nullptr; row of W0 (input column) the gradient is taken for
     int B, H, tmem_cols;
@@ -718,6 +747,7 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_bwd_tc_kernel(const BwdTC f) 
     float* s_part = s_wx + H;                                         // [FUSED_NQ - 1][128]
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_part + TCG_M * (FUSED_NQ - 1));
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 2);
+    float* s_cs = reinterpret_cast<float*>(s_bar + 4);                // [FUSED_NW x FUSED_RB][H] column sums of 8-row blocks (IMG2 only)
     const uint32_t sbo = 16u * (uint32_t)H, lbo = 128u;
 
     if (warp == 0) {
@@ -803,7 +833,26 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_bwd_tc_kernel(const BwdTC f) 
             }
             uint4 v;
             v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
-            *reinterpret_cast<uint4*>(sA + (size_t)(r2 >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (r2 & 7) * 16) = v;
+            unsigned char* core = sA + (size_t)(r2 >> 3) * sbo + (size_t)(k0 >> 3) * lbo + (r2 & 7) * 16;
+            *reinterpret_cast<uint4*>(core) = v;
+            if (f.IMG2) {
+                image_store_warp(f.IMG2 + (long long)z * f.img_zs, (int)gridDim.x * 2, it * 32, m2 - rsub, smem_u32(core), lane);
+                // column sums of this warp's 8 rows (fp32, fixed tree), for the bias row of d W1
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float c = a[j];
+                    c += __shfl_xor_sync(0xffffffffu, c, 1); c += __shfl_xor_sync(0xffffffffu, c, 2); c += __shfl_xor_sync(0xffffffffu, c, 4);
+                    if (rsub == 0) s_cs[(warp * FUSED_RB + rb) * H + k0 + j] = c;
+                }
+            }
+        }
+    }
+    if (f.IMG2) {                                                       // 8-row sums -> the CTA's 128-row sums, ascending row order
+        __syncthreads();
+        for (int n = tid; n < H; n += FUSED_NT) {
+            float c = 0.f;
+            for (int q = 0; q < FUSED_NW * FUSED_RB; ++q) c += s_cs[q * H + n];
+            f.colsum[((long long)z * gridDim.x + blockIdx.x) * H + n] = c;
         }
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -857,6 +906,117 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_bwd_tc_kernel(const BwdTC f) 
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(f.tmem_cols));
 }
 
+// ---- layer 1's weight gradient from the operand images ----------------------------------------------------------------------
+// d W1[k][n] = sum over the batch of h1[b][k] d h2[b][n]: both operands are bf16 tile images with the batch as K (written by
+// the fused kernels, above), so a CTA's whole k range is fetched with two bulk copies per 64-row chunk -- all of them in
+// flight at once -- instead of being converted through registers chunk after chunk.  Grid (n tiles, m tiles, Z x splits),
+// 128 x 128 output tile, fp32 partial tiles [z][split][H][H] summed in split order by dw1_reduce_kernel.
+constexpr int DWI_STAGES = 4;
+struct DwImg {
+    const unsigned char *A, *Bm; long long a_zs, b_zs;   // images of h1 and d h2, bytes between networks
+    int n_chunks, splits, H;                              // 64-row chunks per network
+    float* partial;                                       // [Z][splits][H][H]
+};
+__global__ void __launch_bounds__(256, 1) dw_img_tc_kernel(const DwImg t) {
+    extern __shared__ __align__(128) unsigned char dwi_smem[];   // DWI_STAGES x (A 16 KB | B 16 KB); after the MMAs: staging tiles
+    __shared__ uint64_t s_full[DWI_STAGES], s_done;
+    __shared__ uint32_t s_tmem;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int z = blockIdx.z / t.splits, sp = blockIdx.z % t.splits;
+    const int per = (t.n_chunks + t.splits - 1) / t.splits;
+    const int c_lo = sp * per, c_hi = min(t.n_chunks, c_lo + per), n_my = max(0, c_hi - c_lo);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(128));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    if (tid == 32) {
+        for (int i = 0; i < DWI_STAGES; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_full[i])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_done)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::);
+        // a CTA's k range is at most DWI_STAGES chunks (the host picks the splits so): every block is requested at once
+        const unsigned char* a = t.A + (long long)z * t.a_zs + ((size_t)blockIdx.y * t.n_chunks + c_lo) * 16384;
+        const unsigned char* b = t.Bm + (long long)z * t.b_zs + ((size_t)blockIdx.x * t.n_chunks + c_lo) * 16384;
+        for (int i = 0; i < n_my; ++i) {
+            const uint32_t bar = smem_u32(&s_full[i]), dstA = smem_u32(dwi_smem + (size_t)i * 32768), dstB = dstA + 16384;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(32768u) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dstA), "l"(a + (size_t)i * 16384), "r"(16384u), "r"(bar) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dstB), "l"(b + (size_t)i * 16384), "r"(16384u), "r"(bar) : "memory");
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+    const uint32_t tmem_base = s_tmem;
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(TCG_M >> 4) << 24);
+    if (tid == 0) {
+        for (int i = 0; i < n_my; ++i) {
+            mbar_wait(smem_u32(&s_full[i]), 0u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::);
+            const uint32_t sa = smem_u32(dwi_smem + (size_t)i * 32768);
+            const uint64_t da = umma_desc_kmajor_noswizzle(sa, 128u, 1024u), db = umma_desc_kmajor_noswizzle(sa + 16384u, 128u, 1024u);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const uint64_t adv = (uint64_t)((ks * 256) >> 4);
+                const uint32_t acc = (i > 0 || ks > 0) ? 1u : 0u;
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                             "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                             ::"r"(tmem_base), "l"(da + adv), "l"(db + adv), "r"(idesc), "r"(acc) : "memory");
+            }
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_done)) : "memory");
+    }
+    mbar_wait(smem_u32(&s_done), 0u);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::);
+    // accumulator rows (thread = TMEM lane, the two thread halves take the two column halves) -> the partial tile, through the
+    // warp's staging tile (8 rows x 64 contiguous bytes per store)
+    const int half = tid >> 7;
+    float* stg = reinterpret_cast<float*>(dwi_smem) + warp * 32 * FUSED_STG_STRIDE;
+    const int H = t.H, m0 = blockIdx.y * TCG_M + (warp & 3) * 32, n0 = blockIdx.x * 128;
+    float* P = t.partial + (((long long)z * t.splits + sp) * H + m0) * H + n0;
+    const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    for (int c0 = half * 64; c0 < (half + 1) * 64; c0 += 16) {
+        uint32_t r[16];
+        float v[16];
+        if (n_my > 0) {
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                         : "r"(taddr + (uint32_t)c0));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = n_my > 0 ? __uint_as_float(r[j]) : 0.f;
+        if (n0 + c0 < H) staged_store16(stg, lane, v, P + c0, H, H - m0);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::);
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128));
+}
+// grad[z][m][n] (augmented layer [H + 1][H]) = sum over the splits, in split order, of the partial tiles (m < H), or over the
+// row tiles, in ascending order, of the fused backward kernel's column sums (m = H, the bias row)
+__global__ void __launch_bounds__(256) dw1_reduce_kernel(const DwImg t, float* grad, const long long g_zs, const float* colsum, const int row_tiles) {
+    const int H = t.H, z = blockIdx.y;
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= (long long)(H + 1) * H) return;
+    float acc = 0.f;
+    if (i < (long long)H * H) {
+        const float* pp = t.partial + (long long)z * t.splits * H * H + i;
+        for (int q0 = 0; q0 < t.splits; q0 += 8) {
+            float x[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) x[q] = q0 + q < t.splits ? pp[(long long)(q0 + q) * H * H] : 0.f;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) acc += x[q];
+        }
+    } else {
+        const int n = (int)(i - (long long)H * H);
+        for (int q = 0; q < row_tiles; ++q) acc += colsum[((long long)z * row_tiles + q) * H + n];
+    }
+    grad[(long long)z * g_zs + i] = acc;
+}
+
 // ---- workspace ------------------------------------------------------------------------------------------------------
 struct Net { long long l0, l1, l2; };   // float offsets of the three augmented layer blocks inside a network block
 struct Layout {
@@ -868,8 +1028,9 @@ struct Layout {
     long long o_xs, o_xs2, o_xsa, o_xs2a, o_xspi, o_r, o_mask;
     long long o_hp1, o_hp2, o_op, o_hq1, o_hq2, o_oq, o_oqt, o_hqt1, o_hqt2;   // hqt*: scratch activations of the target critics
     long long o_doq, o_dhq2, o_dhq1, o_da, o_dop, o_dhp2, o_dhp1;
-    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, o_w1p, o_mhp, o_mhq, total;
+    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, o_w1p, o_mhp, o_mhq, o_img_hp1, o_img_hq1, o_img_dhp2, o_img_dhq2, o_colsum, total;
     int tc;                             // large-batch products on tcgen05 (gemm_tc_kernel)
+    int dw_img;                         // fused path: layer 1's weight gradient from bf16 tile images (dw_img_tc_kernel); SIT_SAC_DW_IMG=0: gemm_tc_kernel
     int fused_fwd;                      // tc: a network's forward as ONE kernel (mlp_fwd_tc_kernel); SIT_SAC_FUSED_FWD=0 keeps the three products
     int ldh;                            // leading dimension of the hidden activations [B][ldh]: H weights' inputs + the ones
                                         // column (H + 1), padded to a multiple of 4 floats on the tensor-core path so that
@@ -908,6 +1069,16 @@ static void make_layout(Layout& L, int H, int B, int tc) {
     L.o_w1p = take(tc ? (long long)SAC_W1_IMAGES * H * H / 2 : 0);   // bf16 K-major images of W1 (pack_w1_nets_kernel)
     L.o_mhp = take(tc ? 2LL * b * 8 : 0);        // sign bits of the policy's h1 | h2 (fused forward -> fused backward), 8 words per row
     L.o_mhq = take(tc ? 2LL * 2 * b * 8 : 0);    // ... of the critics' h1 [2][B] | h2 [2][B]
+    // operand images of layer 1's weight gradient d W1 = h1^T . d h2 (contraction over the batch): bf16, [z][128-feature
+    // tile][64-row chunk] blocks of 16 KB in the UMMA canonical K-major layout (K = batch), written by the fused forward
+    // (h1) and backward (d h2) kernels, fetched by dw_img_tc_kernel with one bulk copy per block
+    L.dw_img = L.fused_fwd && B >= 2048;      // (below: the image stores and the reduce launch cost more than the product saves -- batch 1024 7 400 -> 7 280, batch 64 10 600 -> 9 390 updates/s)
+    if (const char* e = std::getenv("SIT_SAC_DW_IMG")) if (std::atoi(e) == 0) L.dw_img = 0;
+    {
+        const long long rows = (b + TCG_M - 1) / TCG_M * TCG_M, img = L.dw_img ? rows * H * 2 / 4 : 0;   // floats per network
+        L.o_img_hp1 = take(img); L.o_img_hq1 = take(2 * img); L.o_img_dhp2 = take(img); L.o_img_dhq2 = take(2 * img);
+        L.o_colsum = take(L.dw_img ? 2 * (rows / TCG_M) * H : 0);   // per-CTA column sums of d h2 (the bias row of d W1)
+    }
     L.total = o;
 }
 
@@ -1155,7 +1326,7 @@ struct SitSac_ {
 
 namespace sac {
 
-static size_t bwd_smem_bytes(int H) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 512 * (FUSED_NQ - 1) + 32; }
+static size_t bwd_smem_bytes(int H) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 512 * (FUSED_NQ - 1) + 32 + (size_t)FUSED_NW * FUSED_RB * H * 4; }
 static size_t fwd_smem_bytes(int H, int kin1) { return (size_t)TCG_M * H * 2 + (size_t)H * H * 2 + (size_t)12 * H + 16 + 1024 * (FUSED_NQ - 1) + 32 + (size_t)kin1 * H * 4; }
 
 struct Launcher {
@@ -1223,7 +1394,7 @@ struct Launcher {
     // net_id: index of the (first) network's bf16 W1 image in the workspace (0 policy, 1 q1, 2 q2, 3 / 4 their targets);
     // -1 or the SIMT path: the three products as separate launches
     void forward(long long oX, int kin, long long oW, long long w_zs, const Net& n, int nout, long long oH1, long long oH2,
-                 long long oOut, int Z, int net_id = -1, long long oEps = -1, long long oXa = 0, long long oLogp = 0, bool keep = true) const {
+                 long long oOut, int Z, int net_id = -1, long long oEps = -1, long long oXa = 0, long long oLogp = 0, bool keep = true, bool img = true) const {
         const int B = L.B, H = L.H;
         const int ld = L.ldh;
         const long long hz = (long long)B * ld;
@@ -1235,6 +1406,9 @@ struct Launcher {
             const long long om = !keep ? -1 : (oH1 == L.o_hp1 ? L.o_mhp : (oH1 == L.o_hq1 ? L.o_mhq : -1));
             f.M1 = om >= 0 ? reinterpret_cast<uint32_t*>(ws + om) : nullptr;
             f.M2 = om >= 0 ? f.M1 + (long long)Z * B * 8 : nullptr;
+            const long long rows = (long long)(B + TCG_M - 1) / TCG_M * TCG_M;
+            const long long oi = (keep && img && L.dw_img) ? (oH1 == L.o_hp1 ? L.o_img_hp1 : (oH1 == L.o_hq1 ? L.o_img_hq1 : -1)) : -1;
+            f.IMG1 = oi >= 0 ? reinterpret_cast<unsigned char*>(ws + oi) : nullptr; f.img_zs = rows * H * 2;
             f.B = B; f.H = H; f.ld = ld; f.nout = nout;
             f.eps = oEps >= 0 ? ws + oEps : nullptr; f.xa = ws + oXa; f.logp = ws + oLogp;
             f.tmem_cols = 32;
@@ -1278,14 +1452,31 @@ struct Launcher {
             f.M1 = reinterpret_cast<const uint32_t*>(ws + (oH1 == L.o_hp1 ? L.o_mhp : L.o_mhq)); f.M2 = f.M1 + (long long)Z * B * 8;
             f.DH2 = want_dw ? ws + oDH2 : nullptr; f.DH1 = want_dw ? ws + oDH1 : nullptr;
             f.DX = dx_cols > 0 ? ws + oDX : nullptr; f.dx_row = dx_first;
+            const long long rows = (long long)(B + TCG_M - 1) / TCG_M * TCG_M;
+            const int n_chunks = (int)(rows / 64);
+            const bool dwi = want_dw && L.dw_img && n_chunks <= DWI_STAGES * TCG_MAX_SPLITS;      // a CTA's k range fits its stages
+            const bool is_pol = oH1 == L.o_hp1;
+            f.IMG2 = dwi ? reinterpret_cast<unsigned char*>(ws + (is_pol ? L.o_img_dhp2 : L.o_img_dhq2)) : nullptr; f.img_zs = rows * H * 2;
+            f.colsum = ws + L.o_colsum;
             f.B = B; f.H = H; f.tmem_cols = 32;
             while (f.tmem_cols < H) f.tmem_cols <<= 1;
             mlp_bwd_tc_kernel<<<dim3((B + TCG_M - 1) / TCG_M, Z), FUSED_NT, bwd_smem_bytes(H), st>>>(f);
             if (want_dw) {
                 const bool two = par2 && side_b != nullptr;
                 if (par2) { cudaEventRecord(ev[1], st); cudaStreamWaitEvent(side, ev[1], 0); if (two) cudaStreamWaitEvent(side_b, ev[1], 0); }
-                branch = par2 ? 2 : 0;
-                gemm(oH1, 1, ld, hz, oDH2, H, 1, dz, oG + n.l1, H, w_zs, H + 1, H, B, Z, EPI_STORE);
+                if (dwi) {      // layer 1's weight gradient from the operand images the fused kernels wrote
+                    DwImg t;
+                    t.A = reinterpret_cast<const unsigned char*>(ws + (is_pol ? L.o_img_hp1 : L.o_img_hq1)); t.Bm = f.IMG2;
+                    t.a_zs = t.b_zs = rows * H * 2; t.n_chunks = n_chunks; t.splits = (n_chunks + DWI_STAGES - 1) / DWI_STAGES; t.H = H;
+                    t.partial = ws + L.o_part + 1LL * 2LL * TCG_MAX_SPLITS * (L.H + 1) * L.H;          // region of branch 2
+                    cudaStream_t ss = par2 ? side : st;
+                    dw_img_tc_kernel<<<dim3(H / 128, H / 128, Z * t.splits), 256, DWI_STAGES * 32768, ss>>>(t);
+                    dw1_reduce_kernel<<<dim3((unsigned)(((long long)(H + 1) * H + 255) / 256), Z), 256, 0, ss>>>(
+                        t, ws + oG + n.l1, w_zs, ws + L.o_colsum, (int)(rows / TCG_M));
+                } else {
+                    branch = par2 ? 2 : 0;
+                    gemm(oH1, 1, ld, hz, oDH2, H, 1, dz, oG + n.l1, H, w_zs, H + 1, H, B, Z, EPI_STORE);
+                }
                 branch = par2 ? 3 : 0;
                 gemm(oX, 1, kin + 1, 0, oDH1, H, 1, dz, oG + n.l0, H, w_zs, kin + 1, H, B, Z, EPI_STORE);
                 branch = 0;
@@ -1357,7 +1548,7 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     adam_kernel<<<(unsigned)((2 * L.P_q + 255) / 256), 256, 0, st>>>(ws, L, hp, L.P_pol, 2 * L.P_q, L.o_qt - L.o_q, 1, (L.tc && L.fused_fwd) ? 1 : 0);   // + the updated critics' W1 images
     join2(3);
     // critics (updated) on (s, a~), d/da through the critics, policy backward, Adam
-    X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
+    X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1, -1, 0, 0, true, false);   // (only d Q / d a goes back through this pass: no d W1 image)
     policy_seed_kernel<<<1, 1024, 0, st>>>(ws, L);
     X.backward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, false, 0, L.o_da, S, 1, 6);
     policy_grad_kernel<<<eb, 256, 0, st>>>(ws, L);
@@ -1407,6 +1598,7 @@ int sit_sac_create(const SitSacConfig* cfg, int device, SitSac* out) {
         for (auto& e : h->ev2) if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
         if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&h->side3, cudaStreamNonBlocking);
         for (auto& e : h->ev3) if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        if (ce == cudaSuccess && tc) ce = cudaFuncSetAttribute(sac::dw_img_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sac::DWI_STAGES * 32768);
         if (ce == cudaSuccess && tc) ce = cudaFuncSetAttribute(sac::mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sac::bwd_smem_bytes(cfg->hidden));
         if (ce != cudaSuccess) {
             if (h->side) cudaStreamDestroy(h->side);

@@ -148,7 +148,7 @@ class SAC:
         self.tensor_cores = bool(cfg.tensor_cores) and (cfg.batch_size >= 1024 or cfg.tensor_cores >= 2) and cfg.hidden >= 128
         fused = self.tensor_cores and cfg.hidden % 128 == 0 and os.environ.get("SIT_SAC_FUSED_FWD", "1") != "0"
         splitk = 6 if (self.tensor_cores and cfg.batch_size >= 1024) else 0          # reduce kernels of the split-k weight gradients
-        self.kernels_per_update = (22 if fused else 37) + splitk
+        self.kernels_per_update = (22 if fused else 37) + splitk      # (from batch 2048 on layer 1's weight gradient comes from operand images: product + reduce as well)
         self._side = None
         self.launches = 0
         _lib.check(self.L.sit_sac_init(self.h, self.ws.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream))
