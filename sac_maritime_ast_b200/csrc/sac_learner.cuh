@@ -453,6 +453,7 @@ struct FwdTC {
     const unsigned char* w1p; long long w1p_zs;   // bf16 image of W1's H x H part, bytes
     float *H1, *H2, *Out; long long hz;       // activations [Z][B][ld] (nullptr: not kept -- a pass no backward goes through), outputs [Z][B][nout]
     unsigned char* IMG1; long long img_zs;    // bf16 tile image of h1 for d W1 (nullptr: none), bytes between the Z networks
+    unsigned char* IMG0;                      // ... of the input rows for d W0 (one 128-feature tile, shared by the Z networks)
     uint32_t *M1, *M2;                        // sign bits of h1, h2 for the fused backward: [Z][B][8 words], bit k of a row = word k >> 5, bit k & 31; or nullptr
     int B, H, ld, nout, tmem_cols;
     // policy only (nullptr otherwise): the tanh-Gaussian head of head_kernel in the epilogue -- a = tanh(mu + sigma eps) into the
@@ -499,16 +500,30 @@ __device__ __forceinline__ uint32_t mask_word(const uint4& lo, const uint4& hi, 
 // the dependent-issue latency of the layer-0 FMA chains and the epilogue); a warp owns 8 rows in the layer-0 / layer-2 phase,
 // the four thread quarters take the four column quarters of the accumulator in the epilogue
 constexpr int FUSED_NT = 512, FUSED_NW = FUSED_NT / 32, FUSED_RB = TCG_M / (8 * FUSED_NW), FUSED_NQ = FUSED_NT / TCG_M;
+// img != nullptr: the 32 x 16 tile also goes, as bf16, into an operand image (see image_store_warp): block base of feature tile
+// f0 / 128 and of the tile's 64-row chunk already applied by the caller, f0 = first feature, r0 = first row inside the chunk
 __device__ __forceinline__ void staged_store16(float* stg, const int lane, const float (&v)[16], float* gbase, const long long ld,
-                                               const int rows_left) {
+                                               const int rows_left, unsigned char* img = nullptr, const int f0 = 0, const int r0 = 0) {
 #pragma unroll
     for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(stg + lane * FUSED_STG_STRIDE + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
     __syncwarp();
+    if (img) {      // lane = (feature of the 16, one of two 8-row groups per pass): 8 rows of one feature = one 16-byte piece
+        const int c = lane & 15, g = lane >> 4, f = (f0 & 127) + c;
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const int rg = 2 * p + g;
+            const float* col = stg + (rg * 8) * FUSED_STG_STRIDE + c;
+            uint4 w;
+            w.x = pack_bf16x2(col[0], col[FUSED_STG_STRIDE]); w.y = pack_bf16x2(col[2 * FUSED_STG_STRIDE], col[3 * FUSED_STG_STRIDE]);
+            w.z = pack_bf16x2(col[4 * FUSED_STG_STRIDE], col[5 * FUSED_STG_STRIDE]); w.w = pack_bf16x2(col[6 * FUSED_STG_STRIDE], col[7 * FUSED_STG_STRIDE]);
+            *reinterpret_cast<uint4*>(img + (size_t)(f >> 3) * 1024 + (size_t)((r0 >> 3) + rg) * 128 + (f & 7) * 16) = w;
+        }
+    }
 #pragma unroll
     for (int pass = 0; pass < 4; ++pass) {
         const int rr = pass * 8 + (lane >> 2), cc = (lane & 3) * 4;
         const float4 q = *reinterpret_cast<const float4*>(stg + rr * FUSED_STG_STRIDE + cc);
-        if (rr < rows_left) *reinterpret_cast<float4*>(gbase + (long long)rr * ld + cc) = q;
+        if (gbase && rr < rows_left) *reinterpret_cast<float4*>(gbase + (long long)rr * ld + cc) = q;
     }
     __syncwarp();
 }
@@ -573,6 +588,17 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) 
         const int m = m0 + warp * (8 * FUSED_RB) + rb * 8 + rsub;
 #pragma unroll
         for (int c = 0; c < 12; ++c) x[rb][c] = (m < f.B && c < f.kin1) ? f.X[(long long)m * f.kin1 + c] : 0.f;
+        if (f.IMG0 && grp == 0 && z == 0) {      // the input rows as the A operand of d W0 (rows past the batch: zeros)
+            unsigned char* p = f.IMG0 + (size_t)(m >> 6) * 16384 + (size_t)((m & 63) >> 3) * 128 + (m & 7) * 2;
+#pragma unroll
+            for (int c = 0; c < 12; ++c) {
+                if (c < f.kin1) {
+                    unsigned short hb;
+                    asm("cvt.rn.bf16.f32 %0, %1;" : "=h"(hb) : "f"(x[rb][c]));
+                    *reinterpret_cast<unsigned short*>(p + (size_t)(c >> 3) * 1024 + (c & 7) * 16) = hb;
+                }
+            }
+        }
     }
     {   // small operands -> shared memory with ALL loads of a thread in flight together (a loop of dependent
         // load -> store trips cost one L2 round trip each: 15 of them were 9 of this kernel's 19 us)
@@ -632,8 +658,10 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) 
             bits |= __shfl_xor_sync(0xffffffffu, bits, 16);
             if (live && f.H1) {                                        // (no backward through this pass: nothing is kept)
                 if (grp == 0 && f.M1) f.M1[((long long)z * f.B + m) * 8 + it] = bits;
-                *reinterpret_cast<float4*>(h1 + k0) = make_float4(a[0], a[1], a[2], a[3]);
-                *reinterpret_cast<float4*>(h1 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
+                if (!f.IMG1) {                                         // (with the operand image nobody reads the fp32 h1)
+                    *reinterpret_cast<float4*>(h1 + k0) = make_float4(a[0], a[1], a[2], a[3]);
+                    *reinterpret_cast<float4*>(h1 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
+                }
             }
             uint4 v;
             v.x = pack_bf16x2(a[0], a[1]); v.y = pack_bf16x2(a[2], a[3]); v.z = pack_bf16x2(a[4], a[5]); v.w = pack_bf16x2(a[6], a[7]);
@@ -730,6 +758,7 @@ struct BwdTC {
     const unsigned char* w1p; long long w1p_zs;   // by-k bf16 image of W1
     const uint32_t *M1, *M2;                  // sign bits of the forward activations h1, h2 (mlp_fwd_tc_kernel): [Z][B][8 words]
     unsigned char* IMG2; long long img_zs;    // bf16 tile image of d h2 for d W1 (nullptr: none)
+    unsigned char* IMG1;                      // ... of d h1 for d W0 (with IMG2)
     float* colsum;                            // [Z][row tiles][H] column sums of this CTA's d h2 rows (with IMG2)
     float *DH2, *DH1;                         // [Z][B][H], nullptr: not stored (no weight gradients wanted)
     float* DX; int dx_row;                    // [Z][B] or nullptr; row of W0 (input column) the gradient is taken for
@@ -893,7 +922,8 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_bwd_tc_kernel(const BwdTC f) 
             g[j] = (bits >> j & 1u) ? __uint_as_float(r[j]) : 0.f;
             dx = fmaf(g[j], s_wx[c0 + j], dx);
         }
-        if (dh1w) staged_store16(stg, lane, g, dh1w + c0, H, f.B - wrow0);
+        if (dh1w || f.IMG1) staged_store16(stg, lane, g, dh1w ? dh1w + c0 : nullptr, H, f.B - wrow0,
+                                 f.IMG1 ? f.IMG1 + (long long)z * f.img_zs + ((size_t)(c0 >> 7) * (gridDim.x * 2) + (wrow0 >> 6)) * 16384 : nullptr, c0, wrow0 & 63);
     }
     if (half > 0) s_part[(half - 1) * TCG_M + row] = dx;
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
@@ -914,8 +944,8 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_bwd_tc_kernel(const BwdTC f) 
 constexpr int DWI_STAGES = 4;
 struct DwImg {
     const unsigned char *A, *Bm; long long a_zs, b_zs;   // images of h1 and d h2, bytes between networks
-    int n_chunks, splits, H;                              // 64-row chunks per network
-    float* partial;                                       // [Z][splits][H][H]
+    int n_chunks, splits, H, M;                           // 64-row chunks per network; M = rows of the product (features of A)
+    float* partial;                                       // [Z][splits][M][H]
 };
 __global__ void __launch_bounds__(256, 1) dw_img_tc_kernel(const DwImg t) {
     extern __shared__ __align__(128) unsigned char dwi_smem[];   // DWI_STAGES x (A 16 KB | B 16 KB); after the MMAs: staging tiles
@@ -974,7 +1004,7 @@ __global__ void __launch_bounds__(256, 1) dw_img_tc_kernel(const DwImg t) {
     const int half = tid >> 7;
     float* stg = reinterpret_cast<float*>(dwi_smem) + warp * 32 * FUSED_STG_STRIDE;
     const int H = t.H, m0 = blockIdx.y * TCG_M + (warp & 3) * 32, n0 = blockIdx.x * 128;
-    float* P = t.partial + (((long long)z * t.splits + sp) * H + m0) * H + n0;
+    float* P = t.partial + (((long long)z * t.splits + sp) * t.M + m0) * H + n0;
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     for (int c0 = half * 64; c0 < (half + 1) * 64; c0 += 16) {
         uint32_t r[16];
@@ -988,30 +1018,32 @@ __global__ void __launch_bounds__(256, 1) dw_img_tc_kernel(const DwImg t) {
         }
 #pragma unroll
         for (int j = 0; j < 16; ++j) v[j] = n_my > 0 ? __uint_as_float(r[j]) : 0.f;
-        if (n0 + c0 < H) staged_store16(stg, lane, v, P + c0, H, H - m0);
+        if (n0 + c0 < H) staged_store16(stg, lane, v, P + c0, H, t.M - m0);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::);
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128));
 }
-// grad[z][m][n] (augmented layer [H + 1][H]) = sum over the splits, in split order, of the partial tiles (m < H), or over the
-// row tiles, in ascending order, of the fused backward kernel's column sums (m = H, the bias row)
+// grad[z][m][n] (augmented layer [M (+ 1)][H]) = sum over the splits, in split order, of the partial tiles (m < M); with
+// `colsum`: one more row, the bias row of layer 1 = sum over the row tiles, in ascending order, of the fused backward
+// kernel's column sums
 __global__ void __launch_bounds__(256) dw1_reduce_kernel(const DwImg t, float* grad, const long long g_zs, const float* colsum, const int row_tiles) {
     const int H = t.H, z = blockIdx.y;
+    const long long mh = (long long)t.M * H;
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (i >= (long long)(H + 1) * H) return;
+    if (i >= mh + (colsum ? H : 0)) return;
     float acc = 0.f;
-    if (i < (long long)H * H) {
-        const float* pp = t.partial + (long long)z * t.splits * H * H + i;
+    if (i < mh) {
+        const float* pp = t.partial + (long long)z * t.splits * mh + i;
         for (int q0 = 0; q0 < t.splits; q0 += 8) {
             float x[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) x[q] = q0 + q < t.splits ? pp[(long long)(q0 + q) * H * H] : 0.f;
+            for (int q = 0; q < 8; ++q) x[q] = q0 + q < t.splits ? pp[(long long)(q0 + q) * mh] : 0.f;
 #pragma unroll
             for (int q = 0; q < 8; ++q) acc += x[q];
         }
     } else {
-        const int n = (int)(i - (long long)H * H);
+        const int n = (int)(i - mh);
         for (int q = 0; q < row_tiles; ++q) acc += colsum[((long long)z * row_tiles + q) * H + n];
     }
     grad[(long long)z * g_zs + i] = acc;
@@ -1028,7 +1060,7 @@ struct Layout {
     long long o_xs, o_xs2, o_xsa, o_xs2a, o_xspi, o_r, o_mask;
     long long o_hp1, o_hp2, o_op, o_hq1, o_hq2, o_oq, o_oqt, o_hqt1, o_hqt2;   // hqt*: scratch activations of the target critics
     long long o_doq, o_dhq2, o_dhq1, o_da, o_dop, o_dhp2, o_dhp1;
-    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, o_w1p, o_mhp, o_mhq, o_img_hp1, o_img_hq1, o_img_dhp2, o_img_dhq2, o_colsum, total;
+    long long o_eps_next, o_eps_cur, o_logp_next, o_logp_cur, o_idx, o_losses, o_updates, o_obs_scale, o_part, o_w1p, o_mhp, o_mhq, o_img_hp1, o_img_hq1, o_img_dhp2, o_img_dhq2, o_img_xp, o_img_xq, o_img_dhp1, o_img_dhq1, o_colsum, total;
     int tc;                             // large-batch products on tcgen05 (gemm_tc_kernel)
     int dw_img;                         // fused path: layer 1's weight gradient from bf16 tile images (dw_img_tc_kernel); SIT_SAC_DW_IMG=0: gemm_tc_kernel
     int fused_fwd;                      // tc: a network's forward as ONE kernel (mlp_fwd_tc_kernel); SIT_SAC_FUSED_FWD=0 keeps the three products
@@ -1077,6 +1109,10 @@ static void make_layout(Layout& L, int H, int B, int tc) {
     {
         const long long rows = (b + TCG_M - 1) / TCG_M * TCG_M, img = L.dw_img ? rows * H * 2 / 4 : 0;   // floats per network
         L.o_img_hp1 = take(img); L.o_img_hq1 = take(2 * img); L.o_img_dhp2 = take(img); L.o_img_dhq2 = take(2 * img);
+        // layer 0's weight gradient d W0 = x^T . d h1: the inputs as one 128-feature tile (11 / 12 of them used, the rest stays
+        // zero from sit_sac_init), d h1 like d h2
+        const long long ximg = L.dw_img ? rows * 128 * 2 / 4 : 0;
+        L.o_img_xp = take(ximg); L.o_img_xq = take(ximg); L.o_img_dhp1 = take(img); L.o_img_dhq1 = take(2 * img);
         L.o_colsum = take(L.dw_img ? 2 * (rows / TCG_M) * H : 0);   // per-CTA column sums of d h2 (the bias row of d W1)
     }
     L.total = o;
@@ -1409,6 +1445,7 @@ struct Launcher {
             const long long rows = (long long)(B + TCG_M - 1) / TCG_M * TCG_M;
             const long long oi = (keep && img && L.dw_img) ? (oH1 == L.o_hp1 ? L.o_img_hp1 : (oH1 == L.o_hq1 ? L.o_img_hq1 : -1)) : -1;
             f.IMG1 = oi >= 0 ? reinterpret_cast<unsigned char*>(ws + oi) : nullptr; f.img_zs = rows * H * 2;
+            f.IMG0 = oi >= 0 ? reinterpret_cast<unsigned char*>(ws + (oH1 == L.o_hp1 ? L.o_img_xp : L.o_img_xq)) : nullptr;
             f.B = B; f.H = H; f.ld = ld; f.nout = nout;
             f.eps = oEps >= 0 ? ws + oEps : nullptr; f.xa = ws + oXa; f.logp = ws + oLogp;
             f.tmem_cols = 32;
@@ -1450,13 +1487,15 @@ struct Launcher {
             f.DOut = ws + oDOut; f.nout = nout; f.W = ws + oW; f.w_zs = w_zs; f.l0 = n.l0; f.l2 = n.l2;
             f.w1p = reinterpret_cast<const unsigned char*>(ws + L.o_w1p) + (size_t)bw_img * H * H * 2; f.w1p_zs = (long long)H * H * 2;
             f.M1 = reinterpret_cast<const uint32_t*>(ws + (oH1 == L.o_hp1 ? L.o_mhp : L.o_mhq)); f.M2 = f.M1 + (long long)Z * B * 8;
-            f.DH2 = want_dw ? ws + oDH2 : nullptr; f.DH1 = want_dw ? ws + oDH1 : nullptr;
             f.DX = dx_cols > 0 ? ws + oDX : nullptr; f.dx_row = dx_first;
             const long long rows = (long long)(B + TCG_M - 1) / TCG_M * TCG_M;
             const int n_chunks = (int)(rows / 64);
             const bool dwi = want_dw && L.dw_img && n_chunks <= DWI_STAGES * TCG_MAX_SPLITS;      // a CTA's k range fits its stages
             const bool is_pol = oH1 == L.o_hp1;
             f.IMG2 = dwi ? reinterpret_cast<unsigned char*>(ws + (is_pol ? L.o_img_dhp2 : L.o_img_dhq2)) : nullptr; f.img_zs = rows * H * 2;
+            f.IMG1 = dwi ? reinterpret_cast<unsigned char*>(ws + (is_pol ? L.o_img_dhp1 : L.o_img_dhq1)) : nullptr;
+            // (with the images nobody reads the fp32 gradients: they are not stored)
+            f.DH2 = (want_dw && !dwi) ? ws + oDH2 : nullptr; f.DH1 = (want_dw && !dwi) ? ws + oDH1 : nullptr;
             f.colsum = ws + L.o_colsum;
             f.B = B; f.H = H; f.tmem_cols = 32;
             while (f.tmem_cols < H) f.tmem_cols <<= 1;
@@ -1467,7 +1506,7 @@ struct Launcher {
                 if (dwi) {      // layer 1's weight gradient from the operand images the fused kernels wrote
                     DwImg t;
                     t.A = reinterpret_cast<const unsigned char*>(ws + (is_pol ? L.o_img_hp1 : L.o_img_hq1)); t.Bm = f.IMG2;
-                    t.a_zs = t.b_zs = rows * H * 2; t.n_chunks = n_chunks; t.splits = (n_chunks + DWI_STAGES - 1) / DWI_STAGES; t.H = H;
+                    t.a_zs = t.b_zs = rows * H * 2; t.n_chunks = n_chunks; t.splits = (n_chunks + DWI_STAGES - 1) / DWI_STAGES; t.H = H; t.M = H;
                     t.partial = ws + L.o_part + 1LL * 2LL * TCG_MAX_SPLITS * (L.H + 1) * L.H;          // region of branch 2
                     cudaStream_t ss = par2 ? side : st;
                     dw_img_tc_kernel<<<dim3(H / 128, H / 128, Z * t.splits), 256, DWI_STAGES * 32768, ss>>>(t);
@@ -1477,8 +1516,18 @@ struct Launcher {
                     branch = par2 ? 2 : 0;
                     gemm(oH1, 1, ld, hz, oDH2, H, 1, dz, oG + n.l1, H, w_zs, H + 1, H, B, Z, EPI_STORE);
                 }
-                branch = par2 ? 3 : 0;
-                gemm(oX, 1, kin + 1, 0, oDH1, H, 1, dz, oG + n.l0, H, w_zs, kin + 1, H, B, Z, EPI_STORE);
+                if (dwi) {      // layer 0's: the input image as the one row tile
+                    DwImg t;
+                    t.A = reinterpret_cast<const unsigned char*>(ws + (is_pol ? L.o_img_xp : L.o_img_xq)); t.Bm = f.IMG1;
+                    t.a_zs = 0; t.b_zs = rows * H * 2; t.n_chunks = n_chunks; t.splits = (n_chunks + DWI_STAGES - 1) / DWI_STAGES; t.H = H; t.M = kin + 1;
+                    t.partial = ws + L.o_part + 2LL * 2LL * TCG_MAX_SPLITS * (L.H + 1) * L.H;          // region of branch 3
+                    cudaStream_t ss = two ? side_b : (par2 ? side : st);
+                    dw_img_tc_kernel<<<dim3(H / 128, 1, Z * t.splits), 256, DWI_STAGES * 32768, ss>>>(t);
+                    dw1_reduce_kernel<<<dim3((unsigned)(((long long)(kin + 1) * H + 255) / 256), Z), 256, 0, ss>>>(t, ws + oG + n.l0, w_zs, nullptr, 0);
+                } else {
+                    branch = par2 ? 3 : 0;
+                    gemm(oX, 1, kin + 1, 0, oDH1, H, 1, dz, oG + n.l0, H, w_zs, kin + 1, H, B, Z, EPI_STORE);
+                }
                 branch = 0;
                 if (two) { cudaEventRecord(ev_b[0], side_b); cudaStreamWaitEvent(st, ev_b[0], 0); }
                 if (par2) { cudaEventRecord(ev[3], side); cudaStreamWaitEvent(st, ev[3], 0); }

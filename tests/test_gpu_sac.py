@@ -192,7 +192,7 @@ def _grad_blocks(agent):
 
 
 @pytest.mark.parametrize("hidden,batch,fused", [(256, 1024, True), (128, 4096, True), (256, 1500, True), (256, 1024, False),
-                                                 (160, 1024, False), (256, 64, True), (128, 300, True), (256, 200, False)])
+                                                 (160, 1024, False), (256, 64, True), (128, 300, True), (256, 200, False), (256, 2048, True), (256, 2100, True)])
 def test_tensor_core_update_matches_fp32_update(hidden, batch, fused, monkeypatch):
     """Large-batch learner: the hidden-layer products and every contraction over the batch run on tcgen05 (bf16 operands,
     fp32 accumulate in TMEM, split-k partials summed in a fixed order).  Against the fp32 CUDA-core update with the same
