@@ -1104,7 +1104,9 @@ static void make_layout(Layout& L, int H, int B, int tc) {
     // operand images of layer 1's weight gradient d W1 = h1^T . d h2 (contraction over the batch): bf16, [z][128-feature
     // tile][64-row chunk] blocks of 16 KB in the UMMA canonical K-major layout (K = batch), written by the fused forward
     // (h1) and backward (d h2) kernels, fetched by dw_img_tc_kernel with one bulk copy per block
-    L.dw_img = L.fused_fwd && B >= 2048;      // (below: the image stores and the reduce launch cost more than the product saves -- batch 1024 7 400 -> 7 280, batch 64 10 600 -> 9 390 updates/s)
+    // from batch 256 (below, the image stores and the two reduce launches cost more than the products save: batch 64 10 600 ->
+    // 9 550 updates/s) up to the batch whose k range fits the stages of a CTA at the largest split count (8192)
+    L.dw_img = L.fused_fwd && B >= 256 && (B + TCG_M - 1) / TCG_M * 2 <= DWI_STAGES * TCG_MAX_SPLITS;
     if (const char* e = std::getenv("SIT_SAC_DW_IMG")) if (std::atoi(e) == 0) L.dw_img = 0;
     {
         const long long rows = (b + TCG_M - 1) / TCG_M * TCG_M, img = L.dw_img ? rows * H * 2 / 4 : 0;   // floats per network
@@ -1490,7 +1492,7 @@ struct Launcher {
             f.DX = dx_cols > 0 ? ws + oDX : nullptr; f.dx_row = dx_first;
             const long long rows = (long long)(B + TCG_M - 1) / TCG_M * TCG_M;
             const int n_chunks = (int)(rows / 64);
-            const bool dwi = want_dw && L.dw_img && n_chunks <= DWI_STAGES * TCG_MAX_SPLITS;      // a CTA's k range fits its stages
+            const bool dwi = want_dw && L.dw_img;
             const bool is_pol = oH1 == L.o_hp1;
             f.IMG2 = dwi ? reinterpret_cast<unsigned char*>(ws + (is_pol ? L.o_img_dhp2 : L.o_img_dhq2)) : nullptr; f.img_zs = rows * H * 2;
             f.IMG1 = dwi ? reinterpret_cast<unsigned char*>(ws + (is_pol ? L.o_img_dhp1 : L.o_img_dhq1)) : nullptr;

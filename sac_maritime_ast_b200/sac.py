@@ -148,7 +148,10 @@ class SAC:
         self.tensor_cores = bool(cfg.tensor_cores) and (cfg.batch_size >= 1024 or cfg.tensor_cores >= 2) and cfg.hidden >= 128
         fused = self.tensor_cores and cfg.hidden % 128 == 0 and os.environ.get("SIT_SAC_FUSED_FWD", "1") != "0"
         splitk = 6 if (self.tensor_cores and cfg.batch_size >= 1024) else 0          # reduce kernels of the split-k weight gradients
-        self.kernels_per_update = (22 if fused else 37) + splitk      # (from batch 2048 on layer 1's weight gradient comes from operand images: product + reduce as well)
+        # batch 256 .. 8192: the weight gradients of layers 0 and 1 come from bf16 operand images (product + reduce each, also
+        # below batch 1024 where the fp32 products have no reduce)
+        dw_img = fused and 256 <= cfg.batch_size <= 8192 and os.environ.get("SIT_SAC_DW_IMG", "1") != "0"
+        self.kernels_per_update = (22 if fused else 37) + splitk + (4 if (dw_img and cfg.batch_size < 1024) else 0)
         self._side = None
         self.launches = 0
         _lib.check(self.L.sit_sac_init(self.h, self.ws.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream))
