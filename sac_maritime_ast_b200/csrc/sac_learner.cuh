@@ -656,9 +656,9 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) 
             bits <<= 8 * grp;                                          // the four column groups of a row make up mask word `it`
             bits |= __shfl_xor_sync(0xffffffffu, bits, 8);
             bits |= __shfl_xor_sync(0xffffffffu, bits, 16);
-            if (live && f.H1) {                                        // (no backward through this pass: nothing is kept)
+            if (live) {                                                // (no backward through this pass: nothing is kept)
                 if (grp == 0 && f.M1) f.M1[((long long)z * f.B + m) * 8 + it] = bits;
-                if (!f.IMG1) {                                         // (with the operand image nobody reads the fp32 h1)
+                if (f.H1 && !f.IMG1) {                                 // (with the operand image nobody reads the fp32 h1)
                     *reinterpret_cast<float4*>(h1 + k0) = make_float4(a[0], a[1], a[2], a[3]);
                     *reinterpret_cast<float4*>(h1 + k0 + 4) = make_float4(a[4], a[5], a[6], a[7]);
                 }
@@ -1432,7 +1432,7 @@ struct Launcher {
     // net_id: index of the (first) network's bf16 W1 image in the workspace (0 policy, 1 q1, 2 q2, 3 / 4 their targets);
     // -1 or the SIMT path: the three products as separate launches
     void forward(long long oX, int kin, long long oW, long long w_zs, const Net& n, int nout, long long oH1, long long oH2,
-                 long long oOut, int Z, int net_id = -1, long long oEps = -1, long long oXa = 0, long long oLogp = 0, bool keep = true, bool img = true) const {
+                 long long oOut, int Z, int net_id = -1, long long oEps = -1, long long oXa = 0, long long oLogp = 0, int keep = 1, bool img = true) const {
         const int B = L.B, H = L.H;
         const int ld = L.ldh;
         const long long hz = (long long)B * ld;
@@ -1440,12 +1440,14 @@ struct Launcher {
             FwdTC f;
             f.X = ws + oX; f.kin1 = kin + 1; f.W = ws + oW; f.w_zs = w_zs; f.l0 = n.l0; f.l1 = n.l1; f.l2 = n.l2;
             f.w1p = reinterpret_cast<const unsigned char*>(ws + L.o_w1p) + (size_t)net_id * H * H * 2; f.w1p_zs = (long long)H * H * 2;
-            f.H1 = keep ? ws + oH1 : nullptr; f.H2 = keep ? ws + oH2 : nullptr; f.Out = ws + oOut; f.hz = hz;
+            // keep: 0 nothing (no backward through this pass), 1 activations + sign bits, 2 sign bits only (only an input gradient
+            // goes back through it)
+            f.H1 = keep == 1 ? ws + oH1 : nullptr; f.H2 = keep == 1 ? ws + oH2 : nullptr; f.Out = ws + oOut; f.hz = hz;
             const long long om = !keep ? -1 : (oH1 == L.o_hp1 ? L.o_mhp : (oH1 == L.o_hq1 ? L.o_mhq : -1));
             f.M1 = om >= 0 ? reinterpret_cast<uint32_t*>(ws + om) : nullptr;
             f.M2 = om >= 0 ? f.M1 + (long long)Z * B * 8 : nullptr;
             const long long rows = (long long)(B + TCG_M - 1) / TCG_M * TCG_M;
-            const long long oi = (keep && img && L.dw_img) ? (oH1 == L.o_hp1 ? L.o_img_hp1 : (oH1 == L.o_hq1 ? L.o_img_hq1 : -1)) : -1;
+            const long long oi = (keep == 1 && img && L.dw_img) ? (oH1 == L.o_hp1 ? L.o_img_hp1 : (oH1 == L.o_hq1 ? L.o_img_hq1 : -1)) : -1;
             f.IMG1 = oi >= 0 ? reinterpret_cast<unsigned char*>(ws + oi) : nullptr; f.img_zs = rows * H * 2;
             f.IMG0 = oi >= 0 ? reinterpret_cast<unsigned char*>(ws + (oH1 == L.o_hp1 ? L.o_img_xp : L.o_img_xq)) : nullptr;
             f.B = B; f.H = H; f.ld = ld; f.nout = nout;
@@ -1585,9 +1587,9 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     X2.forward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1);
     // target: a' ~ pi(s'), Q targets on (s', a')
     const bool fused = L.tc && L.fused_fwd;      // the policy's forward kernel then also applies the tanh-Gaussian head
-    X.forward(L.o_xs2, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0, L.o_eps_next, L.o_xs2a, L.o_logp_next, false);   // a' ~ pi(s'): no backward, activations not kept
+    X.forward(L.o_xs2, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0, L.o_eps_next, L.o_xs2a, L.o_logp_next, 0);   // a' ~ pi(s'): no backward, activations not kept
     if (!fused) head_kernel<<<eb, 256, 0, st>>>(ws, L, L.o_eps_next, L.o_xs2a, L.o_logp_next);
-    X.forward(L.o_xs2a, SA, L.o_qt, L.P_q, L.q, 1, L.o_hqt1, L.o_hqt2, L.o_oqt, 2, 3, -1, 0, 0, false);   // targets: no backward
+    X.forward(L.o_xs2a, SA, L.o_qt, L.P_q, L.q, 1, L.o_hqt1, L.o_hqt2, L.o_oqt, 2, 3, -1, 0, 0, 0);   // targets: no backward
     join2(1);
     // loss, backward, Adam (+ soft target update)
     critic_loss_kernel<<<1, 1024, 0, st>>>(ws, L, hp);
@@ -1599,7 +1601,7 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     adam_kernel<<<(unsigned)((2 * L.P_q + 255) / 256), 256, 0, st>>>(ws, L, hp, L.P_pol, 2 * L.P_q, L.o_qt - L.o_q, 1, (L.tc && L.fused_fwd) ? 1 : 0);   // + the updated critics' W1 images
     join2(3);
     // critics (updated) on (s, a~), d/da through the critics, policy backward, Adam
-    X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1, -1, 0, 0, true, false);   // (only d Q / d a goes back through this pass: no d W1 image)
+    X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1, -1, 0, 0, 2, false);   // only d Q / d a goes back through this pass: sign bits, no activations, no images
     policy_seed_kernel<<<1, 1024, 0, st>>>(ws, L);
     X.backward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, false, 0, L.o_da, S, 1, 6);
     policy_grad_kernel<<<eb, 256, 0, st>>>(ws, L);
