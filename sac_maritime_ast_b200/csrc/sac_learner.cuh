@@ -754,6 +754,10 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_fwd_tc_kernel(const FwdTC f) 
 // One kernel instead of thin-k + tile GEMM (+ skinny-n); the weight-gradient products stay on gemm_tc_kernel.
 struct BwdTC {
     const float* DOut; int nout;              // [Z][B][nout]
+    // seed != 0 (critics, nout = 1): d out computed here with the arithmetic of critic_loss_kernel (1) / policy_seed_kernel (2)
+    // instead of read, so those kernels -- still run for the losses they report and for layer 2's weight gradient -- leave
+    // the critical path
+    int seed; const float *oq, *oqt, *logp_next, *msk, *rew, *alpha; float gamma;
     const float* W; long long w_zs; long long l0, l2;
     const unsigned char* w1p; long long w1p_zs;   // by-k bf16 image of W1
     const uint32_t *M1, *M2;                  // sign bits of the forward activations h1, h2 (mlp_fwd_tc_kernel): [Z][B][8 words]
@@ -801,8 +805,19 @@ __global__ void __launch_bounds__(FUSED_NT, 1) mlp_bwd_tc_kernel(const BwdTC f) 
         const int m = m0 + warp * (8 * FUSED_RB) + rb * 8 + rsub;
         const bool lv = m < f.B;
         const float* dout = f.DOut + (long long)z * f.B * f.nout + (long long)m * f.nout;
-        d0[rb] = lv ? dout[0] : 0.f;
         d1[rb] = (lv && f.nout == 2) ? dout[1] : 0.f;
+        if (f.seed == 0 || !lv) {
+            d0[rb] = lv ? dout[0] : 0.f;
+        } else if (f.seed == 1) {
+            const float invB = 1.0f / (float)f.B;
+            const float qt = fminf(f.oqt[m], f.oqt[f.B + m]) - f.alpha[0] * f.logp_next[m];
+            const float y = fmaf(f.msk[m] * f.gamma, qt, f.rew[m]);
+            d0[rb] = 2.0f * (f.oq[(long long)z * f.B + m] - y) * invB;
+        } else {
+            const float invB = 1.0f / (float)f.B;
+            const float qa = f.oq[(long long)z * f.B + m], qb = f.oq[(long long)(1 - z) * f.B + m];
+            d0[rb] = qa < qb ? -invB : (qa == qb ? -0.5f * invB : 0.f);
+        }
         const uint4* mp = reinterpret_cast<const uint4*>(f.M2 + ((long long)z * f.B + m) * 8);
         mlo[rb] = lv ? mp[0] : make_uint4(0u, 0u, 0u, 0u);
         mhi[rb] = lv ? mp[1] : make_uint4(0u, 0u, 0u, 0u);
@@ -1374,6 +1389,7 @@ struct Launcher {
     cudaStream_t side;           // nullptr: everything on `st`
     cudaEvent_t* ev;
     mutable int branch;          // 0: launch on st; 1 .. 3: launch on `side` (3: on `side_b` when there is one), split-k partials in region branch - 1
+    const Hyper* hp = nullptr;       // for the loss kernels the fused backward moves to the side stream
     cudaStream_t side_b = nullptr;   // second side stream of the fused backward: layer 0's weight gradient beside layer 1's
     cudaEvent_t* ev_b = nullptr;
     // C[z] (M x N, ldc) = epi(A[z] . B[z]);  A(m,k) = A[m a_rs + k a_cs], B(k,n) = B[k b_rs + n b_cs]
@@ -1478,16 +1494,21 @@ struct Launcher {
     // input columns starting at column dx_first (0 columns: stop at layer 0's weight gradient)
     void backward(long long oX, int kin, long long oW, long long w_zs, const Net& n, int nout, long long oH1, long long oH2,
                   long long oDOut, long long oDH2, long long oDH1, int Z, bool want_dw, long long oG, long long oDX, int dx_first,
-                  int dx_cols, int bw_img = -1) const {
+                  int dx_cols, int bw_img = -1, int seed = 0) const {
         const int B = L.B, H = L.H;
         const int ld = L.ldh;
         const long long hz = (long long)B * ld, dz = (long long)B * H, oz = (long long)B * nout;
         if (L.tc && L.fused_fwd && bw_img >= 0 && dx_cols <= 1) {
             // input-gradient chain as ONE kernel; the three weight-gradient products beside / after it on the side streams
             const bool par2 = want_dw && side != nullptr;
-            if (par2) { cudaEventRecord(ev[0], st); cudaStreamWaitEvent(side, ev[0], 0); }             // dOut is ready
+            const bool seed_side = seed != 0 && side != nullptr;      // the loss kernel beside the backward kernel, which seeds itself
+            if (par2 || seed_side) { cudaEventRecord(ev[0], st); cudaStreamWaitEvent(side, ev[0], 0); }             // dOut (or its inputs) ready
+            if (seed == 1) critic_loss_kernel<<<1, 1024, 0, seed_side ? side : st>>>(ws, L, *hp);
+            if (seed == 2) policy_seed_kernel<<<1, 1024, 0, seed_side ? side : st>>>(ws, L);
             if (want_dw) { branch = par2 ? 1 : 0; gemm(oH2, 1, ld, hz, oDOut, nout, 1, oz, oG + n.l2, nout, w_zs, H + 1, nout, B, Z, EPI_STORE); branch = 0; }
             BwdTC f;
+            f.seed = seed_side ? seed : 0; f.oq = ws + L.o_oq; f.oqt = ws + L.o_oqt; f.logp_next = ws + L.o_logp_next; f.msk = ws + L.o_mask;
+            f.rew = ws + L.o_r; f.alpha = ws + L.o_alpha; f.gamma = hp ? hp->gamma : 0.f;
             f.DOut = ws + oDOut; f.nout = nout; f.W = ws + oW; f.w_zs = w_zs; f.l0 = n.l0; f.l2 = n.l2;
             f.w1p = reinterpret_cast<const unsigned char*>(ws + L.o_w1p) + (size_t)bw_img * H * H * 2; f.w1p_zs = (long long)H * H * 2;
             f.M1 = reinterpret_cast<const uint32_t*>(ws + (oH1 == L.o_hp1 ? L.o_mhp : L.o_mhq)); f.M2 = f.M1 + (long long)Z * B * 8;
@@ -1570,7 +1591,7 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     const int B = L.B, H = L.H;
     const int eb = (B + 255) / 256;
     const bool par = st != nullptr && h->side != nullptr;   // branches on internal streams (all captured into the one graph)
-    const Launcher X{st, ws, L, par ? h->side : nullptr, h->ev, 0, (par && L.tc && L.fused_fwd) ? h->side3 : nullptr, h->ev3};   // side_b only where the fused backward joins it
+    const Launcher X{st, ws, L, par ? h->side : nullptr, h->ev, 0, &hp, (par && L.tc && L.fused_fwd) ? h->side3 : nullptr, h->ev3};   // side_b only where the fused backward joins it
     const Launcher X2{par ? h->side2 : st, ws, L, nullptr, nullptr, 0};
     cudaStream_t s2 = X2.st;
     auto fork2 = [&](int e) { if (par) { cudaEventRecord(h->ev2[e], st); cudaStreamWaitEvent(s2, h->ev2[e], 0); } };
@@ -1592,18 +1613,18 @@ static void enqueue_update(SitSac_* h, float* ws, const float* replay, long long
     X.forward(L.o_xs2a, SA, L.o_qt, L.P_q, L.q, 1, L.o_hqt1, L.o_hqt2, L.o_oqt, 2, 3, -1, 0, 0, 0);   // targets: no backward
     join2(1);
     // loss, backward, Adam (+ soft target update)
-    critic_loss_kernel<<<1, 1024, 0, st>>>(ws, L, hp);
+    if (!fused) critic_loss_kernel<<<1, 1024, 0, st>>>(ws, L, hp);      // (fused: beside the backward kernel, which seeds itself)
     // policy on s (its own buffers, the policy's weights): beside the critics' backward and Adam
     fork2(2);
     X2.forward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_op, 1, 0, L.o_eps_cur, L.o_xspi, L.o_logp_cur);
     if (!fused) head_kernel<<<eb, 256, 0, s2>>>(ws, L, L.o_eps_cur, L.o_xspi, L.o_logp_cur);
-    X.backward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, true, L.o_grad + L.P_pol, 0, 0, 0, 6);
+    X.backward(L.o_xsa, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, true, L.o_grad + L.P_pol, 0, 0, 0, 6, fused ? 1 : 0);
     adam_kernel<<<(unsigned)((2 * L.P_q + 255) / 256), 256, 0, st>>>(ws, L, hp, L.P_pol, 2 * L.P_q, L.o_qt - L.o_q, 1, (L.tc && L.fused_fwd) ? 1 : 0);   // + the updated critics' W1 images
     join2(3);
     // critics (updated) on (s, a~), d/da through the critics, policy backward, Adam
     X.forward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_oq, 2, 1, -1, 0, 0, 2, false);   // only d Q / d a goes back through this pass: sign bits, no activations, no images
-    policy_seed_kernel<<<1, 1024, 0, st>>>(ws, L);
-    X.backward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, false, 0, L.o_da, S, 1, 6);
+    if (!fused) policy_seed_kernel<<<1, 1024, 0, st>>>(ws, L);
+    X.backward(L.o_xspi, SA, L.o_q, L.P_q, L.q, 1, L.o_hq1, L.o_hq2, L.o_doq, L.o_dhq2, L.o_dhq1, 2, false, 0, L.o_da, S, 1, 6, fused ? 2 : 0);
     policy_grad_kernel<<<eb, 256, 0, st>>>(ws, L);
     X.backward(L.o_xs, S, L.o_pol, 0, L.pol, 2, L.o_hp1, L.o_hp2, L.o_dop, L.o_dhp2, L.o_dhp1, 1, true, L.o_grad, 0, 0, 0, 5);
     adam_kernel<<<(unsigned)((L.P_pol + 255) / 256), 256, 0, st>>>(ws, L, hp, 0, L.P_pol, 0, 0);
