@@ -60,7 +60,7 @@ def parse_args(argv=None):
     p.add_argument("--k_steps", type=int, default=80, help="env steps per launch")
     p.add_argument("--collect_iterations", type=int, default=8, help="(policy, k_steps) iterations per segment")
     p.add_argument("--precision", default="fp32", choices=["fp32", "fp64"])
-    p.add_argument("--tensor_cores", type=int, default=1, help="policy hidden layer on tcgen05 (bf16 operands)")
+    p.add_argument("--tensor_cores", type=int, default=1, help="1: rollout policy hidden layer and the learner from batch 1024 on tcgen05 (bf16 operands); 2: the learner at every batch size; 0: fp32 CUDA cores")
     p.add_argument("--max_updates_per_segment", type=int, default=0, help="0 = update_per_step x steps per env")
     p.add_argument("--truncate_episodes", type=int, default=0,
                    help="0 (reference, main_ast.py:322,387): num_steps_episode only sets mask = 1 at that step and the episode "
